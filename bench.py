@@ -1,0 +1,336 @@
+#!/usr/bin/env python
+"""bench.py -- KMeans point-iterations/sec on B200 (BASELINE.json's metric).
+
+A step is one pass of the hot path over one batch of synthetic input: one KMeans.fit of
+maxIter rounds over the rows resident in HBM (DenseVectorGenerator data, seed 2; initial
+centroids from the reference sampler with the KMeans default seed).
+
+  python bench.py --gpus 1 --steps K --warmup W            # our arm (one rank per GPU under torchrun)
+  python bench.py --impl reference --steps K --warmup W    # the reference's CPU path (oracle port)
+
+Workloads (--workload; default c2 = BASELINE.json configs[1], the config the metric is quoted on
+that fits one GPU).  With N > 1 every rank holds the same number of rows (weak scaling) and the
+per-round k*d sums + k counts go through one ncclAllReduce.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (rows per GPU, d, k, rounds, description)
+    "c1": (10_000, 10, 2, 20, "benchmark-demo.json KMeans-1: 10k x 10, k=2, maxIter=20"),
+    "c1b": (1_000_000, 100, 10, 10, "kmeans-benchmark.json: 1M x 100, k=10, maxIter=10"),
+    "c2": (10_000_000, 64, 100, 20, "KMeans.fit 10M x 64 FP64, k=100, maxIter=20"),
+    "c4": (125_000_000, 64, 1000, 20, "KMeans.fit 125M x 64 per GPU (1B over 8), k=1000, maxIter=20"),
+    "c4s": (10_000_000, 64, 1000, 20, "KMeans.fit 10M x 64 per GPU, k=1000, maxIter=20 (config-4 shape, short)"),
+}
+DATA_SEED = 2
+METRIC = "KMeans point-iterations/sec"
+UNIT = "point-iterations/s"
+
+
+def read_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return json.load(f), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return {"hbm_gbs": 6650.0}, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled while the timed region runs."""
+
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baseline(d, k, seconds_target=12.0, threads=None):
+    """The oracle (a C port of the reference's CPU arithmetic; no JVM exists on this box) timed on
+    the host cores over a bounded sample of the same workload: one training round over `rows`
+    DenseVectorGenerator rows, rows split over the threads like Flink subtasks."""
+    import numpy as np
+    from oracle import oracle as O
+    threads = threads or O.max_threads()
+    probe = 20_000 * threads
+    x = O.generate_dense(DATA_SEED, 0, 1, probe, d)
+    cent = O.select_random_centroids([x], k, O.KMEANS_DEFAULT_SEED)
+    O.train_round_mt(x[:2000], cent, threads)
+    t0 = time.perf_counter()
+    O.train_round_mt(x, cent, threads)
+    rate = probe / (time.perf_counter() - t0)
+    rows = int(min(max(rate * seconds_target, probe), 4_000_000))
+    if rows > probe:
+        x = O.generate_dense(DATA_SEED, 0, 1, rows, d)
+    t0 = time.perf_counter()
+    O.train_round_mt(x[:rows], cent, threads)
+    dt = time.perf_counter() - t0
+    return {"value": rows / dt, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "oracle (C restatement of the reference's Java loop, not the JVM): 1 round over %d rows x %d,"
+                      " k=%d, %d threads, %.1f s" % (rows, d, k, threads, dt)}, x[:rows], cent
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path.  The JVM reference
+    cannot run here (no JDK on the box), so this is the oracle port on all host cores; each step is
+    a bounded sample (one round over `rows` rows of the workload)."""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    import numpy as np
+    from oracle import oracle as O
+    n, d, k, rounds, desc = WORKLOADS[args.workload]
+    threads = O.max_threads()
+    base, x, cent = cpu_baseline(d, k, seconds_target=3.0, threads=threads)
+    rows = x.shape[0]
+    for _ in range(args.warmup):
+        O.train_round_mt(x, cent, threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        O.train_round_mt(x, cent, threads)
+    dt = time.perf_counter() - t0
+    value = rows * args.steps / dt
+    base = dict(base, value=value,
+                sample="oracle port, %d threads: each step = 1 round over %d rows x %d, k=%d" % (threads, rows, d, k))
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": desc, "sample_rows_per_step": rows, "rounds_per_step": 1, "k": k, "d": d},
+        "cpu_baseline": base,
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import flink_ml_b200 as F
+    from flink_ml_b200 import kmeans as K
+    from flink_ml_b200 import native
+
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus %d needs torchrun with --nproc-per-node %d" % (args.gpus, args.gpus))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    host_group = None
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+        host_group = dist.new_group(backend="gloo")
+
+    n, d, k, rounds, desc = WORKLOADS[args.workload]
+    if args.rows:
+        n = args.rows
+    cluster = K.Cluster(rank, world, local, flags=native.FLAG_PROFILE, host_group=host_group)
+    ctx = cluster.context()
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)
+
+    # ---- synthetic data: DenseVectorGenerator shard `rank` of `world`, generated in HBM
+    total_rows = n * world
+    assert native.rows_on_task(total_rows, rank, world) == n
+    x = torch.empty((n, d), dtype=torch.float64, device=dev)
+    native.generate_dense_dev(local, stream.cuda_stream, DATA_SEED, rank, world, total_rows, d, x.data_ptr())
+    torch.cuda.synchronize()
+    ctx.adopt_points_dev(x.data_ptr(), n, d, keep=x)
+    est = F.KMeans(cluster).set_k(k).set_max_iter(rounds)
+    init = K.select_random_centroids(ctx, cluster, k, est.get_seed())
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_step():
+        ctx.set_centroids(init)
+        ctx.fit(rounds, want_model=False)
+
+    # ---- value: rows resident in HBM, K fits timed on the device
+    for _ in range(args.warmup):
+        one_step()
+    ctx.reset_profile()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    t0 = time.perf_counter()
+    e0.record(stream)
+    for _ in range(args.steps):
+        one_step()
+    e1.record(stream)
+    barrier()
+    wall = time.perf_counter() - t0
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    total_ms = float(ms.item())
+    clocks = sampler.stop() if rank == 0 else None
+    prof = ctx.profile()
+    value = float(total_rows) * rounds * args.steps / (total_ms * 1e-3)
+    model_c, model_w = ctx.get_model()
+
+    # ---- roofline of the dominant kernel (assign + accumulate), live CUDA-event durations
+    peaks, peak_src = read_peaks()
+    launches = max(prof["assign_launches"], 1)
+    assign_ms = prof["assign_ms"] / launches
+    flop_per_launch = 2.0 * k * d * n          # 2*k*d flop per point-iteration
+    bytes_per_launch = 8.0 * d * n             # 8*d bytes per point-iteration
+    dmma_peak, dfma_peak = native.measure_fp64_peaks(local, 300.0)
+    tf = flop_per_launch / (assign_ms * 1e-3) * 1e-12
+    gbs = bytes_per_launch / (assign_ms * 1e-3) * 1e-9
+    hbm_frac = gbs / peaks["hbm_gbs"]
+    tensor_frac = tf / dmma_peak if dmma_peak > 0 else 0.0
+    if tensor_frac >= hbm_frac:
+        roofline = {"bound": "tensor", "achieved": tf, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tensor_frac,
+                    "peak_source": "FP64 DMMA m8n8k4 microbenchmark run live by this bench "
+                                   "(MEASURED_PEAKS.json has no FP64 entry; datasheet 37-40 TFLOP/s)"}
+    else:
+        roofline = {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_frac,
+                    "peak_source": peak_src}
+    roofline.update({
+        "traffic": None, "kernel": "fmlk::assign_kernel<true>", "ms_per_launch": assign_ms,
+        "launches_timed": prof["assign_launches"], "share_of_step": prof["assign_ms"] / total_ms,
+        "hbm": {"achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_frac, "peak_source": peak_src},
+        "fp64_tensor": {"achieved": tf, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tensor_frac},
+        "fp64_fma_peak_tflops": dfma_peak, "launch": ctx.describe_launch(k, d, True),
+    })
+    ncu_traffic = os.path.join(ROOT, "profiles", "traffic_%s.json" % args.workload)
+    if os.path.exists(ncu_traffic):
+        try:
+            roofline["traffic"] = json.load(open(ncu_traffic)).get("dram_bytes_per_launch")
+        except Exception:
+            pass
+
+    # ---- e2e: the public API with HOST buffers: KMeans.fit(Table) -> model, H2D and D2H inside
+    e2e = None
+    if not args.no_e2e:
+        ctx.clear_points()
+        host = torch.empty((n, d), dtype=torch.float64, pin_memory=True)
+        host.copy_(x)
+        torch.cuda.synchronize()
+        del x
+        torch.cuda.empty_cache()
+        table = F.Table({"features": host.numpy()})
+        e2e_steps = max(1, min(args.steps, args.e2e_steps))
+        est.fit(table)  # warm-up (allocations, page tables)
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            model = est.fit(table)
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        md = F.KMeansModelData.from_table(model.get_model_data()[0])
+        ok = bool(np.allclose(md.centroids, model_c, rtol=1e-9, atol=0, equal_nan=True))
+        e2e = {"value": float(total_rows) * rounds * e2e_steps / float(dt.item()), "unit": UNIT,
+               "h2d_bytes_per_step": int(n * d * 8 + k * d * 8), "d2h_bytes_per_step": int(k * d * 8 + (k * d + k) * 8),
+               "steps": e2e_steps, "ms_per_step": float(dt.item()) / e2e_steps * 1e3,
+               "api": "flink_ml_b200.KMeans.fit(Table) from pinned host rows; timed on the host clock "
+                      "around the calls (max over ranks)", "model_matches_device_run": ok}
+
+    base = None
+    if rank == 0 and world == 1 and not args.no_cpu:
+        base, _, _ = cpu_baseline(d, k)
+
+    if rank == 0:
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": desc, "rows_per_gpu": n, "rows_total": total_rows, "d": d, "k": k,
+                       "rounds_per_step": rounds, "sharding": "rows by subtask as RowGenerator (rank = subtask)",
+                       "collective": "ncclAllReduce of k*d+k FP64 per round" if world > 1 else "none (1 GPU)",
+                       "l2": "inputs (%.2f GB per GPU) are larger than L2, no flush needed" % (n * d * 8 / 1e9)
+                       if n * d * 8 > 200e6 else "inputs fit in L2 (reference's own small config)",
+                       "data_seed": DATA_SEED, "init": "reference sampler, KMeans default seed"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": prof["total_launches"],
+            "roofline": roofline, "cpu_baseline": base,
+            "wall_ms_per_step": wall / args.steps * 1e3, "rechecked_rows": prof["rechecked_rows"],
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        cluster.close()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    ap.add_argument("--rows", type=int, default=0, help="override rows per GPU")
+    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "ours":
+        args.warmup = max(args.warmup, 3)  # timing rule: at least 3 warm-up steps
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

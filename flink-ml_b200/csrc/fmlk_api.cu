@@ -1,0 +1,1027 @@
+// fmlk_api.cu -- C ABI of libflinkml_kmeans_cuda.so (see include/fmlk.h).
+//
+// Host side of the B200 KMeans hot path: one context per Flink subtask / GPU, rows resident
+// in HBM across rounds, one stream, no host synchronisation inside fmlk_fit, NCCL (loaded
+// at run time, only when world > 1) for the per-round sum over subtasks.
+#include "../../include/fmlk.h"
+#include "fmlk_kernels.cuh"
+
+#include <dlfcn.h>
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+using namespace fmlk;
+
+// ------------------------------------------------------------------------------------------
+// NCCL, bound at run time so the library loads (and runs on one GPU) without it.  In a process
+// that already holds libnccl.so.2 (PyTorch, a JVM with NCCL bindings) dlopen returns that copy.
+namespace {
+
+typedef struct ncclComm *ncclComm_t;
+typedef struct {
+    char internal[FMLK_NCCL_ID_BYTES];
+} ncclUniqueId;
+enum { ncclSuccess = 0 };
+enum { ncclSum = 0 };
+enum { ncclFloat64 = 8 };
+
+struct NcclApi {
+    void *handle = nullptr;
+    int (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    int (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    int (*CommDestroy)(ncclComm_t) = nullptr;
+    int (*AllReduce)(const void *, void *, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    int (*AllGather)(const void *, void *, size_t, int, ncclComm_t, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(int) = nullptr;
+    std::string load_error;
+    bool ok = false;
+};
+
+NcclApi &nccl() {
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return api;
+    tried = true;
+    const char *names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char *nm : names) {
+        api.handle = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (api.handle) break;
+    }
+    if (!api.handle) {
+        const char *why = dlerror();
+        api.load_error = std::string("cannot load libnccl.so.2: ") + (why ? why : "?");
+        return api;
+    }
+    bool all = true;
+#define FMLK_SYM(field, name)                                              \
+    do {                                                                   \
+        *(void **)(&api.field) = dlsym(api.handle, name);                  \
+        if (!api.field) {                                                  \
+            all = false;                                                   \
+            api.load_error = std::string("libnccl lacks symbol ") + name;  \
+        }                                                                  \
+    } while (0)
+    FMLK_SYM(GetUniqueId, "ncclGetUniqueId");
+    FMLK_SYM(CommInitRank, "ncclCommInitRank");
+    FMLK_SYM(CommDestroy, "ncclCommDestroy");
+    FMLK_SYM(AllReduce, "ncclAllReduce");
+    FMLK_SYM(AllGather, "ncclAllGather");
+    FMLK_SYM(GetErrorString, "ncclGetErrorString");
+#undef FMLK_SYM
+    api.ok = all;
+    return api;
+}
+
+struct Chunk {
+    double *ptr;
+    int64_t rows;
+    int64_t cap;
+    bool owned;
+};
+
+struct LaunchCfg {
+    int warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid;
+    size_t smem;
+};
+
+thread_local std::string g_static_error;
+
+} // namespace
+
+struct fmlk_ctx {
+    int device = 0, rank = 0, world = 1, flags = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int sm_count = 0;
+    size_t smem_optin = 0;
+
+    int32_t d = 0; // row dimension (0: not fixed yet)
+    int32_t k = 0;
+    std::vector<Chunk> chunks;
+    int64_t n_total = 0;
+
+    // model-sized device buffers, (re)allocated in ensure_model()
+    int32_t k_cap = 0;
+    size_t kd_cap = 0;
+    double *centroids = nullptr; // k*d
+    double *weights = nullptr;   // k
+    double *cn = nullptr;        // k
+    double *h = nullptr;         // k_pad
+    double *cmax2 = nullptr;     // 1
+    double *red = nullptr;       // k*d + k : [sums | counts]
+    double *local_model = nullptr; // k*d + k (online)
+    double *gathered = nullptr;    // world * (k*d + k) (online, world > 1)
+    double *partials = nullptr;    // n_partials_cap * (k*d + k)
+    size_t partials_cap = 0;       // in doubles
+    unsigned long long *recheck = nullptr;
+
+    // staging for predict / online batches
+    double *stage_rows = nullptr;
+    size_t stage_rows_cap = 0; // doubles
+    int32_t *stage_labels = nullptr;
+    size_t stage_labels_cap = 0;
+
+    ncclComm_t comm = nullptr;
+
+    // profile
+    std::vector<cudaEvent_t> ev_pool;
+    size_t ev_used = 0;
+    double assign_ms = 0.0;
+    int64_t assign_launches = 0, total_launches = 0;
+
+    std::string err;
+};
+
+namespace {
+
+int fail(fmlk_ctx *ctx, int code, const std::string &msg) {
+    if (ctx) ctx->err = msg;
+    else g_static_error = msg;
+    return code;
+}
+
+#define CK(ctx, call)                                                                              \
+    do {                                                                                           \
+        cudaError_t e__ = (call);                                                                  \
+        if (e__ != cudaSuccess) {                                                                  \
+            int code__ = (e__ == cudaErrorMemoryAllocation) ? FMLK_ERR_NOMEM : FMLK_ERR_CUDA;      \
+            return fail(ctx, code__, std::string(#call) + ": " + cudaGetErrorString(e__));         \
+        }                                                                                          \
+    } while (0)
+
+#define CKN(ctx, call)                                                                             \
+    do {                                                                                           \
+        int r__ = (call);                                                                          \
+        if (r__ != ncclSuccess)                                                                    \
+            return fail(ctx, FMLK_ERR_NCCL, std::string(#call) + ": " + nccl().GetErrorString(r__)); \
+    } while (0)
+
+int use_device(fmlk_ctx *ctx) {
+    CK(ctx, cudaSetDevice(ctx->device));
+    return FMLK_OK;
+}
+
+int stride_for(int d) {
+    int d4 = (d + 3) & ~3;
+    return (d4 % 8 == 4) ? d4 : d4 + 4;
+}
+
+// Shared memory the assign kernel needs for a geometry (must mirror the carve-up in assign_kernel).
+size_t smem_bytes(int warps, int xs, int S, int k, int d, int k_pad, int nc_tile, int n_ctiles, bool sums) {
+    size_t dbl = (size_t)(n_ctiles > 1 ? 2 : 1) * nc_tile * S + k_pad + (size_t)warps * xs * kWarpRows * S +
+                 (sums ? (size_t)k * d : 0);
+    size_t ints = (sums ? (size_t)k : 0) + (size_t)warps * kWarpRows;
+    return dbl * 8 + ints * 4;
+}
+
+// Picks the launch geometry for (k, d).  Preference order: centroids resident in shared memory with
+// block-private sums; resident centroids with global-atomic sums; centroid tiles streamed from L2.
+int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
+    LaunchCfg c{};
+    c.S = stride_for(d);
+    c.ksteps = (d + 3) / 4;
+    c.k_pad = (k + 7) & ~7;
+    c.grid = ctx->sm_count;
+    const size_t budget = ctx->smem_optin;
+    // few centroids: HBM-bound, favour many warps with a prefetched second row tile;
+    // many centroids: FP64-bound, two warps per scheduler are enough and leave room for the model
+    static const int small_k[][2] = {{16, 2}, {16, 1}, {12, 1}, {8, 1}, {4, 1}};
+    static const int large_k[][2] = {{12, 1}, {8, 2}, {8, 1}, {4, 1}};
+    const int(*cand)[2] = (c.k_pad <= 32) ? small_k : large_k;
+    const int ncand = (c.k_pad <= 32) ? 5 : 4;
+    for (int pass = 0; pass < 2; pass++) {
+        const bool sums = accum && pass == 0;
+        if (!accum && pass == 1) break;
+        for (int i = 0; i < ncand; i++) {
+            size_t need = smem_bytes(cand[i][0], cand[i][1], c.S, k, d, c.k_pad, c.k_pad, 1, sums);
+            if (need <= budget) {
+                c.warps = cand[i][0];
+                c.xs = cand[i][1];
+                c.nc_tile = c.k_pad;
+                c.n_ctiles = 1;
+                c.sums_in_smem = sums ? 1 : 0;
+                c.n_partials = sums ? c.grid : 1;
+                c.smem = need;
+                *out = c;
+                return FMLK_OK;
+            }
+        }
+    }
+    // streaming: 8 warps, one row stage, the rest of shared memory split into two centroid tiles
+    c.warps = 8;
+    c.xs = 1;
+    c.sums_in_smem = 0;
+    c.n_partials = 1;
+    size_t fixed = smem_bytes(c.warps, c.xs, c.S, k, d, c.k_pad, 0, 2, false);
+    if (fixed + 2 * 8 * (size_t)c.S * 8 > budget)
+        return fail(ctx, FMLK_ERR_INVALID_ARG, "vector dimension too large for the shared-memory tiling");
+    int nc = (int)((budget - fixed) / (2 * (size_t)c.S * 8));
+    nc &= ~7;
+    nc = std::min(nc, c.k_pad);
+    c.nc_tile = nc;
+    c.n_ctiles = (c.k_pad + nc - 1) / nc;
+    c.smem = smem_bytes(c.warps, c.xs, c.S, k, d, c.k_pad, c.nc_tile, c.n_ctiles, false);
+    *out = c;
+    return FMLK_OK;
+}
+
+template <typename T>
+int dev_alloc(fmlk_ctx *ctx, T **p, size_t count) {
+    CK(ctx, cudaMalloc((void **)p, std::max<size_t>(count, 1) * sizeof(T)));
+    return FMLK_OK;
+}
+
+void dev_free(void *p) {
+    if (p) cudaFree(p);
+}
+
+int ensure_model(fmlk_ctx *ctx, int k, int d) {
+    // buffers are sized by element count: a model with no more centroids and no more elements fits
+    if (k <= ctx->k_cap && (size_t)k * d <= ctx->kd_cap) return FMLK_OK;
+    dev_free(ctx->centroids);
+    dev_free(ctx->weights);
+    dev_free(ctx->cn);
+    dev_free(ctx->h);
+    dev_free(ctx->cmax2);
+    dev_free(ctx->red);
+    dev_free(ctx->local_model);
+    dev_free(ctx->gathered);
+    ctx->centroids = ctx->weights = ctx->cn = ctx->h = ctx->cmax2 = ctx->red = ctx->local_model = ctx->gathered =
+        nullptr;
+    ctx->k_cap = 0;
+    ctx->kd_cap = 0;
+    const size_t kd = (size_t)k * d, len = kd + k;
+    int rc;
+    if ((rc = dev_alloc(ctx, &ctx->centroids, kd))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->weights, (size_t)k))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->cn, (size_t)k))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->h, (size_t)k + 8))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->cmax2, (size_t)1))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->red, len))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->local_model, len))) return rc;
+    if (ctx->world > 1 && (rc = dev_alloc(ctx, &ctx->gathered, len * ctx->world))) return rc;
+    if (!ctx->recheck) {
+        if ((rc = dev_alloc(ctx, &ctx->recheck, (size_t)1))) return rc;
+        CK(ctx, cudaMemsetAsync(ctx->recheck, 0, sizeof(unsigned long long), ctx->stream));
+    }
+    ctx->k_cap = k;
+    ctx->kd_cap = kd;
+    return FMLK_OK;
+}
+
+int ensure_partials(fmlk_ctx *ctx, size_t doubles) {
+    if (doubles <= ctx->partials_cap) return FMLK_OK;
+    dev_free(ctx->partials);
+    ctx->partials = nullptr;
+    ctx->partials_cap = 0;
+    int rc = dev_alloc(ctx, &ctx->partials, doubles);
+    if (rc) return rc;
+    ctx->partials_cap = doubles;
+    return FMLK_OK;
+}
+
+int ensure_stage(fmlk_ctx *ctx, size_t row_doubles, size_t labels) {
+    int rc;
+    if (row_doubles > ctx->stage_rows_cap) {
+        dev_free(ctx->stage_rows);
+        ctx->stage_rows = nullptr;
+        ctx->stage_rows_cap = 0;
+        if ((rc = dev_alloc(ctx, &ctx->stage_rows, row_doubles))) return rc;
+        ctx->stage_rows_cap = row_doubles;
+    }
+    if (labels > ctx->stage_labels_cap) {
+        dev_free(ctx->stage_labels);
+        ctx->stage_labels = nullptr;
+        ctx->stage_labels_cap = 0;
+        if ((rc = dev_alloc(ctx, &ctx->stage_labels, labels))) return rc;
+        ctx->stage_labels_cap = labels;
+    }
+    return FMLK_OK;
+}
+
+cudaEvent_t next_event(fmlk_ctx *ctx) {
+    if (ctx->ev_used == ctx->ev_pool.size()) {
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return nullptr;
+        ctx->ev_pool.push_back(e);
+    }
+    return ctx->ev_pool[ctx->ev_used++];
+}
+
+// Folds the recorded (start, stop) event pairs into the running totals.  Caller has synchronised.
+void drain_events(fmlk_ctx *ctx) {
+    for (size_t i = 0; i + 1 < ctx->ev_used; i += 2) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, ctx->ev_pool[i], ctx->ev_pool[i + 1]) == cudaSuccess) ctx->assign_ms += ms;
+    }
+    ctx->ev_used = 0;
+}
+
+int prep_centroids(fmlk_ctx *ctx) {
+    const int k_pad = (ctx->k + 7) & ~7;
+    prep_centroids_kernel<<<1, 256, 0, ctx->stream>>>(ctx->centroids, ctx->k, k_pad, ctx->d,
+                                                     (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0, ctx->cn, ctx->h,
+                                                     ctx->cmax2);
+    ctx->total_launches++;
+    CK(ctx, cudaGetLastError());
+    return FMLK_OK;
+}
+
+// Launches the assign kernel over one block of rows.  partials != null: accumulate.
+int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t n, int32_t *labels, bool accum) {
+    if (n <= 0) return FMLK_OK;
+    AssignParams p{};
+    p.x = x;
+    p.n = n;
+    p.d = ctx->d;
+    p.S = cfg.S;
+    p.ksteps = cfg.ksteps;
+    p.c = ctx->centroids;
+    p.cn = ctx->cn;
+    p.h = ctx->h;
+    p.cmax2 = ctx->cmax2;
+    p.k = ctx->k;
+    p.k_pad = cfg.k_pad;
+    p.nc_tile = cfg.nc_tile;
+    p.n_ctiles = cfg.n_ctiles;
+    p.thr_coef = 8.0 * (2.0 * ctx->d + 16.0) * 0x1.0p-53;
+    p.labels = labels;
+    p.partials = accum ? ctx->partials : nullptr;
+    p.n_partials = cfg.n_partials;
+    p.sums_in_smem = cfg.sums_in_smem;
+    p.xs = cfg.xs;
+    p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
+    p.recheck_count = ctx->recheck;
+    const int64_t tiles = (n + kWarpRows - 1) / kWarpRows;
+    const int grid = (int)std::min<int64_t>(cfg.grid, (tiles + cfg.warps - 1) / cfg.warps);
+    // a smaller grid still uses slot blockIdx % n_partials, all within the zeroed partials buffer
+    const bool prof = (ctx->flags & FMLK_FLAG_PROFILE) != 0;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (prof) {
+        e0 = next_event(ctx);
+        e1 = next_event(ctx);
+        if (e0 && e1) cudaEventRecord(e0, ctx->stream);
+    }
+    if (accum) assign_kernel<true><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
+    else assign_kernel<false><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
+    if (prof && e0 && e1) cudaEventRecord(e1, ctx->stream);
+    ctx->assign_launches++;
+    ctx->total_launches++;
+    CK(ctx, cudaGetLastError());
+    return FMLK_OK;
+}
+
+// [sums | counts] of this subtask's cached points for the current centroids -> ctx->red.
+int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
+    LaunchCfg cfg;
+    int rc = choose_cfg(ctx, ctx->k, ctx->d, true, &cfg);
+    if (rc) return rc;
+    const size_t len = (size_t)ctx->k * ctx->d + ctx->k;
+    if ((rc = ensure_partials(ctx, len * cfg.n_partials))) return rc;
+    if ((rc = prep_centroids(ctx))) return rc;
+    CK(ctx, cudaMemsetAsync(ctx->partials, 0, len * cfg.n_partials * sizeof(double), ctx->stream));
+    if (extra_rows) {
+        if ((rc = launch_assign(ctx, cfg, extra_rows, extra_n, nullptr, true))) return rc;
+    } else {
+        for (const Chunk &ch : ctx->chunks)
+            if ((rc = launch_assign(ctx, cfg, ch.ptr, ch.rows, nullptr, true))) return rc;
+    }
+    const int threads = 256;
+    reduce_partials_kernel<<<(unsigned)((len + threads - 1) / threads), threads, 0, ctx->stream>>>(
+        ctx->partials, cfg.n_partials, (int)len, ctx->red);
+    ctx->total_launches++;
+    CK(ctx, cudaGetLastError());
+    return FMLK_OK;
+}
+
+int one_train_round(fmlk_ctx *ctx) {
+    int rc = local_round(ctx, nullptr, 0);
+    if (rc) return rc;
+    const size_t len = (size_t)ctx->k * ctx->d + ctx->k;
+    if (ctx->world > 1)
+        CKN(ctx, nccl().AllReduce(ctx->red, ctx->red, len, ncclFloat64, ncclSum, ctx->comm, ctx->stream));
+    const int threads = 256;
+    finalize_centroids_kernel<<<(unsigned)(((size_t)ctx->k * ctx->d + threads - 1) / threads), threads, 0,
+                                ctx->stream>>>(ctx->red, ctx->k, ctx->d, ctx->centroids, ctx->weights);
+    ctx->total_launches++;
+    CK(ctx, cudaGetLastError());
+    return FMLK_OK;
+}
+
+int copy_model_out(fmlk_ctx *ctx, double *out_centroids, double *out_weights) {
+    if (out_centroids)
+        CK(ctx, cudaMemcpyAsync(out_centroids, ctx->centroids, (size_t)ctx->k * ctx->d * sizeof(double),
+                                cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_weights)
+        CK(ctx, cudaMemcpyAsync(out_weights, ctx->weights, (size_t)ctx->k * sizeof(double), cudaMemcpyDeviceToHost,
+                                ctx->stream));
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    drain_events(ctx);
+    return FMLK_OK;
+}
+
+int check_dim(fmlk_ctx *ctx, int32_t d) {
+    if (d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "vector dimension must be positive");
+    if (ctx->d != 0 && ctx->d != d) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
+    return FMLK_OK;
+}
+
+// Destination for n more rows: the tail of the last owned chunk, or a new chunk.
+int grow_points(fmlk_ctx *ctx, int64_t n, double **dst) {
+    if (!ctx->chunks.empty()) {
+        Chunk &last = ctx->chunks.back();
+        if (last.owned && last.cap - last.rows >= n) {
+            *dst = last.ptr + last.rows * ctx->d;
+            last.rows += n;
+            ctx->n_total += n;
+            return FMLK_OK;
+        }
+    }
+    // geometric growth keeps the chunk count (one kernel launch each per round) logarithmic
+    int64_t cap = std::max<int64_t>(n, std::min<int64_t>(std::max<int64_t>(ctx->n_total, 1 << 16), (int64_t)1 << 26));
+    double *p = nullptr;
+    cudaError_t e = cudaMalloc((void **)&p, (size_t)cap * ctx->d * sizeof(double));
+    if (e != cudaSuccess && cap > n) {
+        cudaGetLastError();
+        cap = n;
+        e = cudaMalloc((void **)&p, (size_t)cap * ctx->d * sizeof(double));
+    }
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(ctx, FMLK_ERR_NOMEM, std::string("cudaMalloc for the point cache: ") + cudaGetErrorString(e));
+    }
+    ctx->chunks.push_back(Chunk{p, n, cap, true});
+    ctx->n_total += n;
+    *dst = p;
+    return FMLK_OK;
+}
+
+} // namespace
+
+// ------------------------------------------------------------------------------------------
+extern "C" {
+
+const char *fmlk_version(void) { return "fmlk 0.1 sm_100a"; }
+
+int32_t fmlk_device_count(void) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        g_static_error = cudaGetErrorString(e);
+        return FMLK_ERR_CUDA;
+    }
+    return n;
+}
+
+int32_t fmlk_nccl_unique_id(uint8_t out[FMLK_NCCL_ID_BYTES]) {
+    if (!out) return fail(nullptr, FMLK_ERR_INVALID_ARG, "out is null");
+    NcclApi &api = nccl();
+    if (!api.ok) return fail(nullptr, FMLK_ERR_NCCL, api.load_error);
+    ncclUniqueId id;
+    int r = api.GetUniqueId(&id);
+    if (r != ncclSuccess) return fail(nullptr, FMLK_ERR_NCCL, api.GetErrorString(r));
+    memcpy(out, id.internal, FMLK_NCCL_ID_BYTES);
+    return FMLK_OK;
+}
+
+int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *nccl_id, int32_t flags,
+                    fmlk_ctx **out) {
+    if (!out) return fail(nullptr, FMLK_ERR_INVALID_ARG, "out is null");
+    *out = nullptr;
+    if (world < 1 || rank < 0 || rank >= world) return fail(nullptr, FMLK_ERR_INVALID_ARG, "bad rank / world");
+    int ndev = fmlk_device_count();
+    if (ndev <= 0) return fail(nullptr, FMLK_ERR_CUDA, "no CUDA device: this library has no CPU path");
+    if (device < 0 || device >= ndev) return fail(nullptr, FMLK_ERR_INVALID_ARG, "device index out of range");
+    fmlk_ctx *ctx = new (std::nothrow) fmlk_ctx();
+    if (!ctx) return fail(nullptr, FMLK_ERR_NOMEM, "out of host memory");
+    ctx->device = device;
+    ctx->rank = rank;
+    ctx->world = world;
+    ctx->flags = flags;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    int smem = 0, sms = 0, major = 0;
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+    if (e == cudaSuccess && major == 10) {
+        // the assign kernel sizes its shared memory per launch, up to the opt-in maximum
+        e = cudaFuncSetAttribute(assign_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    }
+    if (e != cudaSuccess) {
+        std::string m = std::string("device set-up: ") + cudaGetErrorString(e);
+        delete ctx;
+        return fail(nullptr, FMLK_ERR_CUDA, m);
+    }
+    if (major != 10) {
+        delete ctx;
+        return fail(nullptr, FMLK_ERR_CUDA, "this build targets sm_100a (B200) only");
+    }
+    ctx->own_stream = true;
+    ctx->smem_optin = (size_t)smem;
+    ctx->sm_count = sms;
+    if (world > 1) {
+        NcclApi &api = nccl();
+        if (!api.ok || !nccl_id) {
+            std::string m = api.ok ? "world > 1 needs an NCCL unique id" : api.load_error;
+            fmlk_destroy(ctx);
+            return fail(nullptr, api.ok ? FMLK_ERR_INVALID_ARG : FMLK_ERR_NCCL, m);
+        }
+        ncclUniqueId id;
+        memcpy(id.internal, nccl_id, FMLK_NCCL_ID_BYTES);
+        int r = api.CommInitRank(&ctx->comm, world, id, rank);
+        if (r != ncclSuccess) {
+            std::string m = std::string("ncclCommInitRank: ") + api.GetErrorString(r);
+            ctx->comm = nullptr;
+            fmlk_destroy(ctx);
+            return fail(nullptr, FMLK_ERR_NCCL, m);
+        }
+    }
+    *out = ctx;
+    return FMLK_OK;
+}
+
+void fmlk_destroy(fmlk_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->comm) nccl().CommDestroy(ctx->comm);
+    for (Chunk &c : ctx->chunks)
+        if (c.owned) dev_free(c.ptr);
+    dev_free(ctx->centroids);
+    dev_free(ctx->weights);
+    dev_free(ctx->cn);
+    dev_free(ctx->h);
+    dev_free(ctx->cmax2);
+    dev_free(ctx->red);
+    dev_free(ctx->local_model);
+    dev_free(ctx->gathered);
+    dev_free(ctx->partials);
+    dev_free(ctx->recheck);
+    dev_free(ctx->stage_rows);
+    dev_free(ctx->stage_labels);
+    for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    cudaGetLastError();
+    delete ctx;
+}
+
+const char *fmlk_last_error(const fmlk_ctx *ctx) { return ctx ? ctx->err.c_str() : g_static_error.c_str(); }
+
+int32_t fmlk_set_stream(fmlk_ctx *ctx, void *cuda_stream) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
+    ctx->stream = (cudaStream_t)cuda_stream;
+    ctx->own_stream = false;
+    return FMLK_OK;
+}
+
+int32_t fmlk_reserve_points(fmlk_ctx *ctx, int64_t n_rows, int32_t d) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = check_dim(ctx, d))) return rc;
+    if (n_rows <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "n_rows must be positive");
+    double *p = nullptr;
+    cudaError_t e = cudaMalloc((void **)&p, (size_t)n_rows * d * sizeof(double));
+    if (e != cudaSuccess) {
+        cudaGetLastError();
+        return fail(ctx, FMLK_ERR_NOMEM, std::string("cudaMalloc for the point cache: ") + cudaGetErrorString(e));
+    }
+    ctx->d = d;
+    ctx->chunks.push_back(Chunk{p, 0, n_rows, true});
+    return FMLK_OK;
+}
+
+static int32_t append_impl(fmlk_ctx *ctx, const double *rows, int64_t n, int32_t d, cudaMemcpyKind kind) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if (n < 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "n must be >= 0");
+    if ((rc = check_dim(ctx, d))) return rc;
+    if (n == 0) return FMLK_OK;
+    if (!rows) return fail(ctx, FMLK_ERR_INVALID_ARG, "rows is null");
+    ctx->d = d;
+    double *dst = nullptr;
+    if ((rc = grow_points(ctx, n, &dst))) return rc;
+    CK(ctx, cudaMemcpyAsync(dst, rows, (size_t)n * d * sizeof(double), kind, ctx->stream));
+    // the caller may reuse its buffer as soon as we return (Flink object reuse)
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    return FMLK_OK;
+}
+
+int32_t fmlk_append_points(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t d) {
+    return append_impl(ctx, rows_host, n, d, cudaMemcpyHostToDevice);
+}
+
+int32_t fmlk_append_points_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d) {
+    return append_impl(ctx, rows_dev, n, d, cudaMemcpyDeviceToDevice);
+}
+
+int32_t fmlk_adopt_points_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = check_dim(ctx, d);
+    if (rc) return rc;
+    if (n < 0 || (n > 0 && !rows_dev)) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad rows / n");
+    if (n == 0) return FMLK_OK;
+    ctx->d = d;
+    ctx->chunks.push_back(Chunk{const_cast<double *>(rows_dev), n, n, false});
+    ctx->n_total += n;
+    return FMLK_OK;
+}
+
+int32_t fmlk_clear_points(fmlk_ctx *ctx) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    for (Chunk &c : ctx->chunks)
+        if (c.owned) dev_free(c.ptr);
+    ctx->chunks.clear();
+    ctx->n_total = 0;
+    if (ctx->k == 0) ctx->d = 0;
+    return FMLK_OK;
+}
+
+int64_t fmlk_num_points(const fmlk_ctx *ctx) { return ctx ? ctx->n_total : 0; }
+
+int32_t fmlk_set_centroids(fmlk_ctx *ctx, const double *centroids_host, int32_t k, int32_t d) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if (k < 1) return fail(ctx, FMLK_ERR_INVALID_ARG, "k must be >= 1");
+    if (!centroids_host) return fail(ctx, FMLK_ERR_INVALID_ARG, "centroids is null");
+    if (d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "vector dimension must be positive");
+    if (ctx->n_total > 0 && ctx->d != d) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
+    if ((rc = ensure_model(ctx, k, d))) return rc;
+    ctx->k = k;
+    ctx->d = d;
+    CK(ctx, cudaMemcpyAsync(ctx->centroids, centroids_host, (size_t)k * d * sizeof(double), cudaMemcpyHostToDevice,
+                            ctx->stream));
+    CK(ctx, cudaMemsetAsync(ctx->weights, 0, (size_t)k * sizeof(double), ctx->stream));
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    return FMLK_OK;
+}
+
+static int need_model(fmlk_ctx *ctx) {
+    if (ctx->k == 0) return fail(ctx, FMLK_ERR_STATE, "no centroids set");
+    return FMLK_OK;
+}
+
+int32_t fmlk_train_round(fmlk_ctx *ctx, double *out_centroids, double *out_weights) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = need_model(ctx))) return rc;
+    if ((rc = one_train_round(ctx))) return rc;
+    return copy_model_out(ctx, out_centroids, out_weights);
+}
+
+int32_t fmlk_fit(fmlk_ctx *ctx, int32_t max_iter, double *out_centroids, double *out_weights) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = need_model(ctx))) return rc;
+    if (max_iter <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "maxIter must be > 0");
+    for (int it = 0; it < max_iter; it++)
+        if ((rc = one_train_round(ctx))) return rc;
+    return copy_model_out(ctx, out_centroids, out_weights);
+}
+
+int32_t fmlk_local_partials(fmlk_ctx *ctx, double *out_sums, int64_t *out_counts) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = need_model(ctx))) return rc;
+    if ((rc = local_round(ctx, nullptr, 0))) return rc;
+    const size_t kd = (size_t)ctx->k * ctx->d;
+    std::vector<double> cnt((size_t)ctx->k);
+    if (out_sums) CK(ctx, cudaMemcpyAsync(out_sums, ctx->red, kd * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(ctx, cudaMemcpyAsync(cnt.data(), ctx->red + kd, (size_t)ctx->k * sizeof(double), cudaMemcpyDeviceToHost,
+                            ctx->stream));
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    drain_events(ctx);
+    if (out_counts)
+        for (int i = 0; i < ctx->k; i++) out_counts[i] = (int64_t)cnt[(size_t)i];
+    return FMLK_OK;
+}
+
+int32_t fmlk_get_model(fmlk_ctx *ctx, double *out_centroids, double *out_weights) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = need_model(ctx))) return rc;
+    return copy_model_out(ctx, out_centroids, out_weights);
+}
+
+static int32_t predict_impl(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t *labels_dev) {
+    LaunchCfg cfg;
+    int rc = choose_cfg(ctx, ctx->k, ctx->d, false, &cfg);
+    if (rc) return rc;
+    if ((rc = prep_centroids(ctx))) return rc;
+    return launch_assign(ctx, cfg, rows_dev, n, labels_dev, false);
+}
+
+int32_t fmlk_predict_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d, int32_t *out_labels_dev) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = need_model(ctx))) return rc;
+    if (d != ctx->d) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
+    if (n < 0 || (n > 0 && (!rows_dev || !out_labels_dev))) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad rows / labels");
+    return predict_impl(ctx, rows_dev, n, out_labels_dev);
+}
+
+int32_t fmlk_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t d, int32_t *out_labels_host) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = need_model(ctx))) return rc;
+    if (d != ctx->d) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
+    if (n < 0 || (n > 0 && (!rows_host || !out_labels_host))) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad rows / labels");
+    if (n == 0) return FMLK_OK;
+    // micro-batches through a reusable staging buffer: copy in, label, copy out
+    const int64_t max_rows = std::max<int64_t>(1, ((int64_t)256 << 20) / ((int64_t)d * 8));
+    const int64_t step = std::min(n, max_rows);
+    if ((rc = ensure_stage(ctx, (size_t)step * d, (size_t)step))) return rc;
+    LaunchCfg cfg;
+    if ((rc = choose_cfg(ctx, ctx->k, ctx->d, false, &cfg))) return rc;
+    if ((rc = prep_centroids(ctx))) return rc;
+    for (int64_t off = 0; off < n; off += step) {
+        const int64_t m = std::min(step, n - off);
+        CK(ctx, cudaMemcpyAsync(ctx->stage_rows, rows_host + off * d, (size_t)m * d * sizeof(double),
+                                cudaMemcpyHostToDevice, ctx->stream));
+        if ((rc = launch_assign(ctx, cfg, ctx->stage_rows, m, ctx->stage_labels, false))) return rc;
+        CK(ctx, cudaMemcpyAsync(out_labels_host + off, ctx->stage_labels, (size_t)m * sizeof(int32_t),
+                                cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    drain_events(ctx);
+    return FMLK_OK;
+}
+
+int32_t fmlk_predict_cached(fmlk_ctx *ctx, int32_t *out_labels_host) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = need_model(ctx))) return rc;
+    if (ctx->n_total == 0) return FMLK_OK;
+    if (!out_labels_host) return fail(ctx, FMLK_ERR_INVALID_ARG, "labels is null");
+    if ((rc = ensure_stage(ctx, 0, (size_t)ctx->n_total))) return rc;
+    LaunchCfg cfg;
+    if ((rc = choose_cfg(ctx, ctx->k, ctx->d, false, &cfg))) return rc;
+    if ((rc = prep_centroids(ctx))) return rc;
+    int64_t off = 0;
+    for (const Chunk &ch : ctx->chunks) {
+        if ((rc = launch_assign(ctx, cfg, ch.ptr, ch.rows, ctx->stage_labels + off, false))) return rc;
+        off += ch.rows;
+    }
+    CK(ctx, cudaMemcpyAsync(out_labels_host, ctx->stage_labels, (size_t)ctx->n_total * sizeof(int32_t),
+                            cudaMemcpyDeviceToHost, ctx->stream));
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    drain_events(ctx);
+    return FMLK_OK;
+}
+
+int32_t fmlk_online_round(fmlk_ctx *ctx, const double *local_batch_host, int64_t n_local, int32_t d, int32_t k,
+                          double decay, double *centroids_inout, double *weights_inout) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if (k < 1 || d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad k / d");
+    if (!centroids_inout || !weights_inout) return fail(ctx, FMLK_ERR_INVALID_ARG, "model is null");
+    if (n_local < 0 || (n_local > 0 && !local_batch_host)) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad batch");
+    if (ctx->n_total > 0 && ctx->d != d) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
+    if ((rc = ensure_model(ctx, k, d))) return rc;
+    ctx->k = k;
+    ctx->d = d;
+    const size_t kd = (size_t)k * d, len = kd + k;
+    if ((rc = ensure_stage(ctx, (size_t)std::max<int64_t>(n_local, 1) * d, 0))) return rc;
+    CK(ctx, cudaMemcpyAsync(ctx->centroids, centroids_inout, kd * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    CK(ctx, cudaMemcpyAsync(ctx->weights, weights_inout, (size_t)k * sizeof(double), cudaMemcpyHostToDevice,
+                            ctx->stream));
+    if (n_local > 0)
+        CK(ctx, cudaMemcpyAsync(ctx->stage_rows, local_batch_host, (size_t)n_local * d * sizeof(double),
+                                cudaMemcpyHostToDevice, ctx->stream));
+    if (n_local > 0) {
+        if ((rc = local_round(ctx, ctx->stage_rows, n_local))) return rc;
+    } else {
+        CK(ctx, cudaMemsetAsync(ctx->red, 0, len * sizeof(double), ctx->stream));
+    }
+    const int threads = 256;
+    const unsigned blocks = (unsigned)((len + threads - 1) / threads);
+    online_update_kernel<<<blocks, threads, 0, ctx->stream>>>(ctx->red, k, d, decay / (double)ctx->world,
+                                                              (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0,
+                                                              ctx->centroids, ctx->weights, ctx->local_model);
+    ctx->total_launches++;
+    CK(ctx, cudaGetLastError());
+    if (ctx->world > 1) {
+        CKN(ctx, nccl().AllGather(ctx->local_model, ctx->gathered, len, ncclFloat64, ctx->comm, ctx->stream));
+        online_merge_kernel<<<blocks, threads, 0, ctx->stream>>>(ctx->gathered, ctx->world, k, d, ctx->centroids,
+                                                                 ctx->weights);
+        ctx->total_launches++;
+        CK(ctx, cudaGetLastError());
+    } else {
+        // a one-element window is emitted as it is: no merge arithmetic at parallelism 1
+        CK(ctx, cudaMemcpyAsync(ctx->centroids, ctx->local_model, kd * sizeof(double), cudaMemcpyDeviceToDevice,
+                                ctx->stream));
+        CK(ctx, cudaMemcpyAsync(ctx->weights, ctx->local_model + kd, (size_t)k * sizeof(double),
+                                cudaMemcpyDeviceToDevice, ctx->stream));
+    }
+    return copy_model_out(ctx, centroids_inout, weights_inout);
+}
+
+// java.util.Random as the JDK specifies it: 48-bit LCG; nextInt(bound) with the power-of-two
+// shortcut and the rejection loop whose overflow test wraps in 32 bits.
+namespace {
+struct JRandom {
+    uint64_t s;
+    explicit JRandom(int64_t seed) : s(((uint64_t)seed ^ kJrMult) & kJrMask) {}
+    inline int32_t next(int bits) {
+        s = (s * kJrMult + kJrAdd) & kJrMask;
+        return (int32_t)(uint32_t)(s >> (48 - bits));
+    }
+    inline int32_t next_int(int32_t bound) {
+        int32_t r = next(31);
+        const int32_t m = bound - 1;
+        if ((bound & m) == 0) return (int32_t)(((int64_t)bound * (int64_t)r) >> 31);
+        for (int32_t u = r;; u = next(31)) {
+            r = u % bound;
+            if ((int32_t)((uint32_t)u - (uint32_t)r + (uint32_t)m) >= 0) break;
+        }
+        return r;
+    }
+};
+} // namespace
+
+int32_t fmlk_reservoir(int64_t n, int32_t k, int64_t seed, int64_t *out_ids) {
+    if (n < 0 || k < 0 || (k > 0 && !out_ids)) return fail(nullptr, FMLK_ERR_INVALID_ARG, "bad reservoir arguments");
+    if (n > 0x7fffffffLL) return fail(nullptr, FMLK_ERR_INVALID_ARG, "a subtask samples at most 2^31-1 elements (Java int count)");
+    JRandom rnd(seed);
+    int32_t held = 0;
+    for (int64_t i = 0; i < n; i++) {
+        if (held < k) {
+            out_ids[held++] = i;
+        } else {
+            const int32_t idx = rnd.next_int((int32_t)(i + 1));
+            if (idx < k) out_ids[idx] = i;
+        }
+    }
+    return held;
+}
+
+int32_t fmlk_get_points(fmlk_ctx *ctx, const int64_t *row_ids, int32_t m, double *out_rows_host) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if (m < 0 || (m > 0 && (!row_ids || !out_rows_host))) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad row ids");
+    for (int32_t i = 0; i < m; i++) {
+        int64_t r = row_ids[i];
+        if (r < 0 || r >= ctx->n_total) return fail(ctx, FMLK_ERR_INVALID_ARG, "row id out of range");
+        const Chunk *src = nullptr;
+        for (const Chunk &ch : ctx->chunks) {
+            if (r < ch.rows) {
+                src = &ch;
+                break;
+            }
+            r -= ch.rows;
+        }
+        CK(ctx, cudaMemcpyAsync(out_rows_host + (size_t)i * ctx->d, src->ptr + r * ctx->d, (size_t)ctx->d * sizeof(double),
+                                cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    return FMLK_OK;
+}
+
+int32_t fmlk_generate_dense_dev(int32_t device, void *cuda_stream, int64_t seed, int32_t task, int32_t num_tasks,
+                                int64_t num_values, int32_t d, double *out_dev) {
+    if (num_tasks < 1 || task < 0 || task >= num_tasks || d <= 0 || num_values < 0 || !out_dev)
+        return fail(nullptr, FMLK_ERR_INVALID_ARG, "bad generator arguments");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, cudaGetErrorString(e));
+    const int64_t dv = num_values / num_tasks, md = num_values % num_tasks;
+    const int64_t rows = md > task ? dv + 1 : dv;
+    const int64_t count = rows * d;
+    if (count == 0) return FMLK_OK;
+    // Tuple2.of(seed, task).hashCode(), then Random's seed scrambling
+    const uint32_t hsh = (uint32_t)((uint64_t)seed ^ ((uint64_t)seed >> 32));
+    const int64_t rseed = (int64_t)(int32_t)(31u * hsh + (uint32_t)task);
+    const unsigned long long state = ((unsigned long long)rseed ^ kJrMult) & kJrMask;
+    const int threads = 256;
+    int64_t blocks64 = std::min<int64_t>((count + threads - 1) / threads, 148 * 16);
+    const unsigned long long T = (unsigned long long)blocks64 * threads;
+    // affine map of 2T LCG steps
+    unsigned long long a = kJrMult, c = kJrAdd, ra = 1ULL, rc = 0ULL, steps = 2ULL * T;
+    while (steps) {
+        if (steps & 1ULL) {
+            ra = (ra * a) & kJrMask;
+            rc = (rc * a + c) & kJrMask;
+        }
+        c = (c * a + c) & kJrMask;
+        a = (a * a) & kJrMask;
+        steps >>= 1;
+    }
+    generate_dense_kernel<<<(unsigned)blocks64, threads, 0, (cudaStream_t)cuda_stream>>>(state, count, ra, rc, out_dev);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, cudaGetErrorString(e));
+    return FMLK_OK;
+}
+
+int32_t fmlk_get_profile(fmlk_ctx *ctx, double *assign_ms, int64_t *assign_launches, int64_t *total_launches,
+                         int64_t *rechecked_rows) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    drain_events(ctx);
+    if (assign_ms) *assign_ms = ctx->assign_ms;
+    if (assign_launches) *assign_launches = ctx->assign_launches;
+    if (total_launches) *total_launches = ctx->total_launches;
+    if (rechecked_rows) {
+        unsigned long long v = 0;
+        if (ctx->recheck) CK(ctx, cudaMemcpy(&v, ctx->recheck, sizeof(v), cudaMemcpyDeviceToHost));
+        *rechecked_rows = (int64_t)v;
+    }
+    return FMLK_OK;
+}
+
+int32_t fmlk_reset_profile(fmlk_ctx *ctx) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    drain_events(ctx);
+    ctx->assign_ms = 0.0;
+    ctx->assign_launches = ctx->total_launches = 0;
+    if (ctx->recheck) CK(ctx, cudaMemset(ctx->recheck, 0, sizeof(unsigned long long)));
+    return FMLK_OK;
+}
+
+int32_t fmlk_measure_fp64_peaks(int32_t device, double ms, double *dmma_tflops, double *dfma_tflops) {
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, cudaGetErrorString(e));
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    double *out = nullptr;
+    if (cudaMalloc((void **)&out, 8) != cudaSuccess) return fail(nullptr, FMLK_ERR_NOMEM, "cudaMalloc");
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int grid = sms * 4, threads = 256;
+    double result[2] = {0.0, 0.0};
+    for (int which = 0; which < 2; which++) {
+        int iters = 2000;
+        double best = 0.0, spent = 0.0;
+        for (int rep = 0; rep < 64 && spent < ms; rep++) {
+            cudaEventRecord(e0);
+            if (which == 0) dmma_peak_kernel<<<grid, threads>>>(out, iters);
+            else dfma_peak_kernel<<<grid, threads>>>(out, iters);
+            cudaEventRecord(e1);
+            if (cudaEventSynchronize(e1) != cudaSuccess) break;
+            float t = 0.f;
+            cudaEventElapsedTime(&t, e0, e1);
+            // per iteration and thread: 16 DMMA (8*8*4*2 flop per warp each) or 16 FMA (2 flop)
+            const double flop = which == 0 ? (double)grid * (threads / 32) * iters * 16.0 * 512.0
+                                           : (double)grid * threads * iters * 16.0 * 2.0;
+            if (rep > 0) {
+                best = std::max(best, flop / (t * 1e-3) * 1e-12);
+                spent += t;
+            }
+            if (t < 5.f) iters *= 2;
+        }
+        result[which] = best;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, cudaGetErrorString(e));
+    if (dmma_tflops) *dmma_tflops = result[0];
+    if (dfma_tflops) *dfma_tflops = result[1];
+    return FMLK_OK;
+}
+
+int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumulate, char *out, int32_t out_len) {
+    if (!ctx || !out || out_len <= 0) return FMLK_ERR_INVALID_ARG;
+    LaunchCfg c;
+    int rc = choose_cfg(ctx, k, d, accumulate != 0, &c);
+    if (rc) return rc;
+    snprintf(out, (size_t)out_len,
+             "grid=%d block=%d smem=%zu warps=%d xs=%d S=%d ksteps=%d k_pad=%d nc_tile=%d n_ctiles=%d sums_in_smem=%d "
+             "n_partials=%d",
+             c.grid, c.warps * 32, c.smem, c.warps, c.xs, c.S, c.ksteps, c.k_pad, c.nc_tile, c.n_ctiles,
+             c.sums_in_smem, c.n_partials);
+    return FMLK_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,696 @@
+// fmlk_kernels.cuh -- sm_100a kernels of the KMeans hot path.
+//
+// Reference loops replaced (LIB/ = flink-ml-lib/src/main/java/org/apache/flink/ml/,
+// CORE/ = flink-ml-core/src/main/java/org/apache/flink/ml/):
+//   assign_kernel      findClosest + axpy + counts++ over the cached points,
+//                      LIB/clustering/kmeans/KMeans.java:291-295 with
+//                      CORE/common/distance/EuclideanDistanceMeasure.java:41-73;
+//                      also PredictLabelFunction.map, LIB/clustering/kmeans/KMeansModel.java:129-144
+//   prep_centroids     new VectorWithNorm(centroid), KMeans.java:279-282
+//   reduce_partials    CentroidsUpdateReducer, KMeans.java:185-198 (within one GPU)
+//   finalize_centroids ModelDataGenerator, KMeans.java:200-212
+//   online_update      ModelDataLocalUpdater, LIB/clustering/kmeans/OnlineKMeans.java:309-322
+//   online_merge       ModelDataGlobalReducer, OnlineKMeans.java:188-211
+//   generate_dense     DenseVectorGenerator / java.util.Random (benchmark data)
+//
+// How the assignment stays bit-identical to the Java scan while running on the FP64
+// tensor cores: the DMMA pass computes v_j = x.c_j - |c_j|^2/2 for every centroid and keeps
+// the best and second-best per row.  Both this value and the reference's own
+// max(0, pn*pn + cn*cn - 2*ddot) are within E = 2(2d+12)u(|x|^2+|c|^2) of the exact squared
+// distance, so when the two best differ by more than 4E (doubled once more for safety) the
+// Java scan -- whatever its summation order and whatever its lower-bound pruning skipped --
+// must pick the same centroid.  Rows that fail the test (exact ties, duplicates, NaN/Inf)
+// are replayed by exact_find_closest(), which executes the reference arithmetic operation
+// by operation (netlib's 4-way interleaved ddot/dnrm2, no FMA, the pruning branch, strict <).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+
+namespace fmlk {
+
+constexpr int kWarpRows = 16;  // rows per warp tile: two m8 tiles
+constexpr int kChunkTiles = 8; // n8 tiles per accumulator chunk (64 centroids)
+
+struct AssignParams {
+    const double *x; // n x d row-major, device
+    int64_t n;
+    int32_t d;
+    int32_t S;      // shared-memory row stride in doubles; S % 8 == 4 keeps 64-bit fragment loads conflict-free
+    int32_t ksteps; // ceil(d/4)
+    const double *c;     // k x d centroids
+    const double *cn;    // k norms, reference arithmetic
+    const double *h;     // k_pad: |c|^2/2 ; +inf beyond k
+    const double *cmax2; // max finite |c|^2
+    int32_t k;
+    int32_t k_pad;    // k rounded up to 8
+    int32_t nc_tile;  // centroids per shared-memory tile (multiple of 8)
+    int32_t n_ctiles; // 1: all centroids stay resident in shared memory
+    double thr_coef;  // 8 (2d+16) 2^-53
+    int32_t *labels;  // n, or null
+    double *partials; // [n_partials][k*d + k], or null: no accumulation (predict)
+    int32_t n_partials;
+    int32_t sums_in_smem;
+    int32_t xs;       // row-tile stages per warp (1 or 2; 2 only when n_ctiles == 1)
+    int32_t fma_mode; // exact path follows the JDK>=11 netlib variant
+    unsigned long long *recheck_count;
+};
+
+// ------------------------------------------------------------------------------------------
+// small PTX helpers
+
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async8(void *smem_dst, const void *gmem_src) {
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(s), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+// D(8x8) += A(8x4, row) * B(4x8, col), FP64 tensor core (SASS: DMMA.8x8x4).
+__device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1)
+                 : "d"(a), "d"(b));
+}
+
+// ------------------------------------------------------------------------------------------
+// reference arithmetic, operation by operation (never contracted: _rn intrinsics)
+
+__device__ __forceinline__ double ref_mul_add(double a, double b, double acc, int fma_mode) {
+    return fma_mode ? fma(a, b, acc) : __dadd_rn(acc, __dmul_rn(a, b));
+}
+
+// netlib JavaBLAS ddot, unit strides (CORE/linalg/BLAS.java:86-88): four interleaved partial
+// sums, ((s0+s1)+s2)+s3, sequential tail.
+__device__ __forceinline__ double ref_ddot(const double *x, const double *y, int d, int fma_mode) {
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int i = 0, n4 = d & ~3;
+    for (; i < n4; i += 4) {
+        s0 = ref_mul_add(x[i + 0], y[i + 0], s0, fma_mode);
+        s1 = ref_mul_add(x[i + 1], y[i + 1], s1, fma_mode);
+        s2 = ref_mul_add(x[i + 2], y[i + 2], s2, fma_mode);
+        s3 = ref_mul_add(x[i + 3], y[i + 3], s3, fma_mode);
+    }
+    double sum = __dadd_rn(0.0, __dadd_rn(__dadd_rn(__dadd_rn(s0, s1), s2), s3));
+    for (; i < d; i++) sum = ref_mul_add(x[i], y[i], sum, fma_mode);
+    return sum;
+}
+
+// netlib JavaBLAS dnrm2 before the square root (CORE/linalg/BLAS.java:124-126).
+__device__ __forceinline__ double ref_sumsq(const double *x, int d, int fma_mode) {
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int i = 0, n4 = d & ~3;
+    for (; i < n4; i += 4) {
+        s0 = ref_mul_add(x[i + 0], x[i + 0], s0, fma_mode);
+        s1 = ref_mul_add(x[i + 1], x[i + 1], s1, fma_mode);
+        s2 = ref_mul_add(x[i + 2], x[i + 2], s2, fma_mode);
+        s3 = ref_mul_add(x[i + 3], x[i + 3], s3, fma_mode);
+    }
+    double sum = __dadd_rn(__dadd_rn(__dadd_rn(s0, s1), s2), s3);
+    for (; i < d; i++) sum = ref_mul_add(x[i], x[i], sum, fma_mode);
+    return sum;
+}
+
+// Math.max(0.0, v): NaN stays NaN.
+__device__ __forceinline__ double java_max0(double v) { return (v != v) ? v : (v > 0.0 ? v : 0.0); }
+
+// EuclideanDistanceMeasure.distanceSquare (EuclideanDistanceMeasure.java:41-50).
+__device__ __forceinline__ double ref_dist2(double pn, double cn, double dot) {
+    double s = __dadd_rn(__dmul_rn(pn, pn), __dmul_rn(cn, cn));
+    return java_max0(__dadd_rn(s, -__dmul_rn(2.0, dot)));
+}
+
+// EuclideanDistanceMeasure.findClosest (EuclideanDistanceMeasure.java:53-73) for one row, by one
+// warp.  Lane l evaluates centroids l, l+32, ... exactly; the sequential scan (pruning branch,
+// strict <, first index wins) is then replayed in index order over each group of 32.  A group
+// in which no distance is below the running best cannot change it and is skipped.
+// x: the row (shared or global memory), c/cn: global.  All lanes return the label.
+__device__ int exact_find_closest(const double *x, const double *c, const double *cn, int k, int d,
+                                  int fma_mode) {
+    const int lane = threadIdx.x & 31;
+    const double pn = sqrt(ref_sumsq(x, d, fma_mode)); // correctly rounded, as Math.sqrt
+    double best = INFINITY;
+    int best_idx = 0;
+    for (int base = 0; base < k; base += 32) {
+        const int j = base + lane;
+        double dist = INFINITY, lb = INFINITY;
+        if (j < k) {
+            const double cnj = cn[j];
+            const double lbs = __dadd_rn(pn, -cnj);
+            lb = __dmul_rn(lbs, lbs);
+            dist = ref_dist2(pn, cnj, ref_ddot(x, c + (size_t)j * d, d, fma_mode));
+        }
+        if (__ballot_sync(0xffffffffu, dist < best) == 0u) continue;
+        const int cnt = min(32, k - base);
+        for (int t = 0; t < cnt; t++) {
+            const double dt = __shfl_sync(0xffffffffu, dist, t);
+            const double lt = __shfl_sync(0xffffffffu, lb, t);
+            if (lt >= best) continue;
+            if (dt < best) {
+                best = dt;
+                best_idx = base + t;
+            }
+        }
+    }
+    return best_idx;
+}
+
+// ------------------------------------------------------------------------------------------
+// assign (+ accumulate) kernel
+
+struct Top2 {
+    double best, second;
+    int idx;
+};
+
+__device__ __forceinline__ void top2_push(Top2 &t, double v, int col) {
+    // explicit compares: a NaN score (NaN centroid, NaN row) never wins, as in the Java scan
+    if (v > t.best) {
+        t.second = t.best;
+        t.best = v;
+        t.idx = col;
+    } else if (v > t.second) {
+        t.second = v;
+    }
+}
+
+__device__ __forceinline__ void top2_merge_xor(Top2 &t, int off) {
+    const double ob = __shfl_xor_sync(0xffffffffu, t.best, off);
+    const double os = __shfl_xor_sync(0xffffffffu, t.second, off);
+    const int oi = __shfl_xor_sync(0xffffffffu, t.idx, off);
+    const double loser = ob > t.best ? t.best : ob; // neither is NaN
+    if (ob > t.best || (ob == t.best && oi < t.idx)) {
+        t.best = ob;
+        t.idx = oi;
+    }
+    t.second = fmax(fmax(t.second, os), loser);
+}
+
+// Copies `rows` rows of d doubles (contiguous in global memory) into shared rows of stride S.
+// All 32 lanes take part.  vec16: d even and the source 16-byte aligned.
+__device__ __forceinline__ void warp_load_rows(double *dst, const double *src, int rows, int d, int S,
+                                               int lane, bool vec16) {
+    if (vec16) {
+        const int cpr = d >> 1; // 16-byte chunks per row
+        const int total = rows * cpr;
+        for (int i = lane; i < total; i += 32) {
+            const int r = i / cpr, q = i - r * cpr;
+            cp_async16(dst + (size_t)r * S + 2 * q, src + (size_t)r * d + 2 * q);
+        }
+    } else {
+        const int total = rows * d;
+        for (int i = lane; i < total; i += 32) {
+            const int r = i / d, q = i - r * d;
+            cp_async8(dst + (size_t)r * S + q, src + (size_t)r * d + q);
+        }
+    }
+}
+
+// One accumulator chunk of a warp tile: 16 rows x (cnt <= 8) n8 tiles over the whole d.
+// xa0/xa1: this lane's A-fragment addresses for rows frow and frow+8; cb: its B-fragment
+// address in the first n8 tile; hcol: &h[first column this lane owns]; col0: that column.
+template <bool FULL>
+__device__ __forceinline__ void mma_chunk(const double *xa0, const double *xa1, const double *cb, int S,
+                                          int ksteps, int cnt, const double *hcol, int col0, Top2 &t0,
+                                          Top2 &t1) {
+    double acc0[kChunkTiles][2], acc1[kChunkTiles][2];
+#pragma unroll
+    for (int j = 0; j < kChunkTiles; j++) {
+        // accumulators start at -|c|^2/2, so the tile comes out as x.c - |c|^2/2
+        const bool on = FULL || j < cnt;
+        const double h0 = on ? -hcol[j * 8] : 0.0;
+        const double h1 = on ? -hcol[j * 8 + 1] : 0.0;
+        acc0[j][0] = h0;
+        acc0[j][1] = h1;
+        acc1[j][0] = h0;
+        acc1[j][1] = h1;
+    }
+    const size_t tstride = (size_t)8 * S;
+#pragma unroll 2
+    for (int ks = 0; ks < ksteps; ks++) {
+        const double a0 = xa0[ks * 4], a1 = xa1[ks * 4];
+#pragma unroll
+        for (int j = 0; j < kChunkTiles; j++) {
+            if (FULL || j < cnt) {
+                const double b = cb[j * tstride + ks * 4];
+                dmma884(acc0[j][0], acc0[j][1], a0, b);
+                dmma884(acc1[j][0], acc1[j][1], a1, b);
+            }
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < kChunkTiles; j++) {
+        if (FULL || j < cnt) {
+            const int col = col0 + j * 8;
+            top2_push(t0, acc0[j][0], col);
+            top2_push(t0, acc0[j][1], col + 1);
+            top2_push(t1, acc1[j][0], col);
+            top2_push(t1, acc1[j][1], col + 1);
+        }
+    }
+}
+
+template <bool ACCUM>
+__global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31;
+    const int warp = threadIdx.x >> 5;
+    const int nwarps = blockDim.x >> 5;
+    const int S = p.S;
+    const int c_bufs = p.n_ctiles > 1 ? 2 : 1;
+    const size_t ctile_elems = (size_t)p.nc_tile * S;
+    const size_t xtile_elems = (size_t)kWarpRows * S;
+
+    double *Cs = reinterpret_cast<double *>(smem_raw);
+    double *hs = Cs + c_bufs * ctile_elems;
+    double *Xall = hs + p.k_pad;
+    double *Xw = Xall + (size_t)warp * p.xs * xtile_elems;
+    double *sums_s = Xall + (size_t)nwarps * p.xs * xtile_elems;
+    const size_t sums_elems = (ACCUM && p.sums_in_smem) ? (size_t)p.k * p.d : 0;
+    int *counts_s = reinterpret_cast<int *>(sums_s + sums_elems);
+    int *lab_s = counts_s + ((ACCUM && p.sums_in_smem) ? p.k : 0) + warp * kWarpRows;
+
+    const bool vec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.x) & 15) == 0);
+    const bool cvec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15) == 0);
+
+    // ---- one-time set-up: zero everything (pad columns and pad rows must read as 0) ----
+    {
+        const size_t zero_elems = c_bufs * ctile_elems + p.k_pad + (size_t)nwarps * p.xs * xtile_elems + sums_elems;
+        for (size_t i = threadIdx.x; i < zero_elems; i += blockDim.x) Cs[i] = 0.0;
+        if (ACCUM && p.sums_in_smem)
+            for (int i = threadIdx.x; i < p.k; i += blockDim.x) counts_s[i] = 0;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < p.k_pad; i += blockDim.x) hs[i] = p.h[i];
+    if (p.n_ctiles == 1) {
+        // resident centroids: k rows of d doubles, rows k..nc_tile-1 stay zero (their h is +inf)
+        if (cvec16) {
+            const int cpr = p.d >> 1, total = p.k * cpr;
+            for (int i = threadIdx.x; i < total; i += blockDim.x) {
+                const int r = i / cpr, q = i - r * cpr;
+                cp_async16(Cs + (size_t)r * S + 2 * q, p.c + (size_t)r * p.d + 2 * q);
+            }
+        } else {
+            const int total = p.k * p.d;
+            for (int i = threadIdx.x; i < total; i += blockDim.x) {
+                const int r = i / p.d, q = i - r * p.d;
+                cp_async8(Cs + (size_t)r * S + q, p.c + (size_t)r * p.d + q);
+            }
+        }
+        cp_async_commit();
+        cp_async_wait<0>();
+    }
+    __syncthreads();
+
+    const double cmax2 = *p.cmax2;
+    const int64_t total_tiles = (p.n + kWarpRows - 1) / kWarpRows;
+    const int64_t gw = (int64_t)blockIdx.x * nwarps + warp;
+    const int64_t GW = (int64_t)gridDim.x * nwarps;
+    const int64_t rounds = (total_tiles + GW - 1) / GW;
+    const int frow = lane >> 2; // fragment row / B-fragment column within an 8-tile
+    const int fk = lane & 3;    // fragment k index
+    unsigned long long local_rechecks = 0;
+
+    // streaming mode bookkeeping: which buffer holds the C tile of the current step
+    int cbuf = 0;
+    if (p.n_ctiles > 1) {
+        // prefetch C tile 0 into buffer 0
+        const int rows0 = min(p.nc_tile, p.k);
+        const int cpr = cvec16 ? (p.d >> 1) : p.d;
+        const int total = rows0 * cpr;
+        for (int i = threadIdx.x; i < total; i += blockDim.x) {
+            const int r = i / cpr, q = i - r * cpr;
+            if (cvec16) cp_async16(Cs + (size_t)r * S + 2 * q, p.c + (size_t)r * p.d + 2 * q);
+            else cp_async8(Cs + (size_t)r * S + q, p.c + (size_t)r * p.d + q);
+        }
+        cp_async_commit();
+    }
+
+    // resident mode with two stages: start the first tile's load
+    if (p.xs == 2 && gw < total_tiles) {
+        const int64_t row0 = gw * kWarpRows;
+        const int rows = (int)min((int64_t)kWarpRows, p.n - row0);
+        warp_load_rows(Xw, p.x + row0 * p.d, rows, p.d, S, lane, vec16);
+    }
+    if (p.xs == 2) cp_async_commit();
+
+    for (int64_t it = 0; it < rounds; it++) {
+        const int64_t tile = it * GW + gw;
+        const bool active = tile < total_tiles;
+        const int64_t row0 = tile * kWarpRows;
+        const int rows_valid = active ? (int)min((int64_t)kWarpRows, p.n - row0) : 0;
+        double *Xt = Xw + (p.xs == 2 ? (size_t)(it & 1) * xtile_elems : 0);
+
+        if (p.xs == 2) {
+            // prefetch the next round's tile into the other stage, then wait for this one
+            const int64_t ntile = tile + GW;
+            if (ntile < total_tiles) {
+                const int64_t nrow0 = ntile * kWarpRows;
+                const int nrows = (int)min((int64_t)kWarpRows, p.n - nrow0);
+                warp_load_rows(Xw + (size_t)((it + 1) & 1) * xtile_elems, p.x + nrow0 * p.d, nrows, p.d, S, lane,
+                               vec16);
+            }
+            cp_async_commit();
+            cp_async_wait<1>();
+            __syncwarp();
+        } else {
+            if (active) warp_load_rows(Xt, p.x + row0 * p.d, rows_valid, p.d, S, lane, vec16);
+            cp_async_commit();
+            if (p.n_ctiles == 1) {
+                cp_async_wait<0>();
+                __syncwarp();
+            }
+        }
+
+        Top2 t0 = {-INFINITY, -INFINITY, 0}, t1 = {-INFINITY, -INFINITY, 0};
+        double nsq0 = 0.0, nsq1 = 0.0;
+
+        for (int ct = 0; ct < p.n_ctiles; ct++) {
+            const double *Ct = Cs + (size_t)cbuf * ctile_elems;
+            const int ct_base = ct * p.nc_tile; // first centroid of this tile
+            if (p.n_ctiles > 1) {
+                // my copies of this step's tile (and my row tile) have landed; after the barrier so
+                // have everyone's, and everyone is done reading the other buffer.
+                cp_async_wait<0>();
+                __syncthreads();
+                // prefetch the next step's C tile into the other buffer
+                int nct = ct + 1;
+                bool more = true;
+                if (nct == p.n_ctiles) {
+                    nct = 0;
+                    more = (it + 1 < rounds);
+                }
+                if (more) {
+                    const int nbase = nct * p.nc_tile;
+                    const int nrows = min(p.nc_tile, p.k - nbase);
+                    double *dstb = Cs + (size_t)(cbuf ^ 1) * ctile_elems;
+                    const int cpr = cvec16 ? (p.d >> 1) : p.d;
+                    const int total = p.nc_tile * cpr;
+                    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+                        const int r = i / cpr, q = i - r * cpr;
+                        if (r < nrows) {
+                            if (cvec16)
+                                cp_async16(dstb + (size_t)r * S + 2 * q, p.c + (size_t)(nbase + r) * p.d + 2 * q);
+                            else
+                                cp_async8(dstb + (size_t)r * S + q, p.c + (size_t)(nbase + r) * p.d + q);
+                        } else {
+                            // rows past k in the last tile: zero (their h is +inf)
+                            if (cvec16) {
+                                dstb[(size_t)r * S + 2 * q] = 0.0;
+                                dstb[(size_t)r * S + 2 * q + 1] = 0.0;
+                            } else {
+                                dstb[(size_t)r * S + q] = 0.0;
+                            }
+                        }
+                    }
+                }
+                cp_async_commit();
+            }
+
+            if (active) {
+                const double *xa0 = Xt + (size_t)frow * S + fk;
+                const double *xa1 = xa0 + (size_t)8 * S;
+                if (ct == 0) {
+                    // |x|^2 of the two rows this quad owns (any order: only feeds the threshold)
+                    for (int ks = 0; ks < p.ksteps; ks++) {
+                        const double a0 = xa0[ks * 4], a1 = xa1[ks * 4];
+                        nsq0 = fma(a0, a0, nsq0);
+                        nsq1 = fma(a1, a1, nsq1);
+                    }
+                }
+                const int tiles_here = (min(p.nc_tile, p.k_pad - ct_base)) >> 3; // n8 tiles in this C tile
+                for (int ch = 0; ch < tiles_here; ch += kChunkTiles) {
+                    const int cnt = min(kChunkTiles, tiles_here - ch);
+                    const double *cb = Ct + (size_t)(ch * 8 + frow) * S + fk;
+                    const int col0 = ct_base + ch * 8 + fk * 2;
+                    if (cnt == kChunkTiles) mma_chunk<true>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1);
+                    else mma_chunk<false>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1);
+                }
+            }
+            if (p.n_ctiles > 1) cbuf ^= 1;
+        }
+
+        if (active) {
+            // combine the four lanes of each quad (same rows, different columns)
+            top2_merge_xor(t0, 1);
+            top2_merge_xor(t0, 2);
+            top2_merge_xor(t1, 1);
+            top2_merge_xor(t1, 2);
+            nsq0 += __shfl_xor_sync(0xffffffffu, nsq0, 1);
+            nsq0 += __shfl_xor_sync(0xffffffffu, nsq0, 2);
+            nsq1 += __shfl_xor_sync(0xffffffffu, nsq1, 1);
+            nsq1 += __shfl_xor_sync(0xffffffffu, nsq1, 2);
+
+            // decision margin in squared-distance units: D = |x|^2 - 2 v
+            const bool ok0 = 2.0 * (t0.best - t0.second) > p.thr_coef * (nsq0 + cmax2);
+            const bool ok1 = 2.0 * (t1.best - t1.second) > p.thr_coef * (nsq1 + cmax2);
+            const bool flag0 = !ok0 && (frow < rows_valid);
+            const bool flag1 = !ok1 && (frow + 8 < rows_valid);
+            if (fk == 0) {
+                lab_s[frow] = t0.idx;
+                lab_s[frow + 8] = t1.idx;
+            }
+            // bit r of `flagged`: row r of the tile needs the exact replay
+            unsigned f0 = __ballot_sync(0xffffffffu, flag0 && fk == 0);
+            unsigned f1 = __ballot_sync(0xffffffffu, flag1 && fk == 0);
+            unsigned flagged = 0;
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                flagged |= ((f0 >> (4 * r)) & 1u) << r;
+                flagged |= ((f1 >> (4 * r)) & 1u) << (r + 8);
+            }
+            __syncwarp();
+            while (flagged) {
+                const int r = __ffs(flagged) - 1;
+                flagged &= flagged - 1;
+                const int lab = exact_find_closest(Xt + (size_t)r * S, p.c, p.cn, p.k, p.d, p.fma_mode);
+                if (lane == 0) {
+                    lab_s[r] = lab;
+                    local_rechecks++;
+                }
+            }
+            __syncwarp();
+
+            if (p.labels != nullptr && lane < rows_valid) p.labels[row0 + lane] = lab_s[lane];
+
+            if (ACCUM) {
+                // sums[label] += row, counts[label]++ (KMeans.java:293-294), rows of one label first
+                // added together in registers so each (label, column) costs one atomic per tile
+                const int my_lab = (lane < rows_valid) ? lab_s[lane] : -1;
+                unsigned pending = (rows_valid >= 32) ? 0xffffffffu : ((1u << rows_valid) - 1u);
+                while (pending) {
+                    const int r0 = __ffs(pending) - 1;
+                    const int L = __shfl_sync(0xffffffffu, my_lab, r0);
+                    const unsigned grp = __ballot_sync(0xffffffffu, my_lab == L) & pending;
+                    pending &= ~grp;
+                    for (int c = lane; c < p.d; c += 32) {
+                        double a = 0.0;
+                        unsigned g = grp;
+                        while (g) {
+                            const int r = __ffs(g) - 1;
+                            g &= g - 1;
+                            a += Xt[(size_t)r * S + c];
+                        }
+                        if (p.sums_in_smem) atomicAdd(&sums_s[(size_t)L * p.d + c], a);
+                        else atomicAdd(&p.partials[(size_t)L * p.d + c], a);
+                    }
+                    if (lane == 0) {
+                        if (p.sums_in_smem) atomicAdd(&counts_s[L], __popc(grp));
+                        else atomicAdd(&p.partials[(size_t)p.k * p.d + L], (double)__popc(grp));
+                    }
+                }
+            }
+            __syncwarp(); // the tile buffer and lab_s are reused next round
+        }
+    }
+    cp_async_wait<0>();
+
+    if (ACCUM && p.sums_in_smem) {
+        // this CTA's partial, added to its own slot (plain read-modify-write: slot b belongs to CTA b)
+        __syncthreads();
+        double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
+        for (int i = threadIdx.x; i < p.k * p.d; i += blockDim.x) slot[i] += sums_s[i];
+        for (int i = threadIdx.x; i < p.k; i += blockDim.x) slot[(size_t)p.k * p.d + i] += (double)counts_s[i];
+    }
+    if (lane == 0 && local_rechecks && p.recheck_count) atomicAdd(p.recheck_count, local_rechecks);
+}
+
+// ------------------------------------------------------------------------------------------
+// per-round small kernels
+
+// VectorWithNorm of every centroid (KMeans.java:279-282) in reference arithmetic, plus the
+// values the assign kernel needs: h = |c|^2/2 (+inf for padding) and the largest finite |c|^2.
+__global__ void prep_centroids_kernel(const double *c, int k, int k_pad, int d, int fma_mode, double *cn,
+                                      double *h, double *cmax2) {
+    __shared__ double red[256];
+    double mx = 0.0;
+    for (int j = threadIdx.x; j < k_pad; j += blockDim.x) {
+        if (j < k) {
+            const double ss = ref_sumsq(c + (size_t)j * d, d, fma_mode);
+            cn[j] = sqrt(ss);
+            h[j] = 0.5 * ss;
+            if (isfinite(ss) && ss > mx) mx = ss;
+        } else {
+            h[j] = INFINITY;
+        }
+    }
+    red[threadIdx.x] = mx;
+    __syncthreads();
+    for (int s = blockDim.x >> 1; s > 0; s >>= 1) {
+        if (threadIdx.x < s) red[threadIdx.x] = fmax(red[threadIdx.x], red[threadIdx.x + s]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) *cmax2 = red[0];
+}
+
+// out[i] = sum over CTA slots b = 0..n_partials-1 of partials[b][i], in slot order.
+__global__ void reduce_partials_kernel(const double *partials, int n_partials, int len, double *out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= len) return;
+    double s = partials[i];
+    for (int b = 1; b < n_partials; b++) s = __dadd_rn(s, partials[(size_t)b * len + i]);
+    out[i] = s;
+}
+
+// ModelDataGenerator.map (KMeans.java:200-212): scal(1.0 / count), weights = counts.
+// red = [k*d sums | k counts as doubles].  count == 0 -> 1/0 = +Inf, 0 * Inf = NaN, as the reference.
+__global__ void finalize_centroids_kernel(const double *red, int k, int d, double *centroids, double *weights) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < k * d) {
+        const double cnt = red[(size_t)k * d + i / d];
+        centroids[i] = __dmul_rn(red[i], __ddiv_rn(1.0, cnt));
+    }
+    if (i < k) weights[i] = red[(size_t)k * d + i];
+}
+
+// ModelDataLocalUpdater (OnlineKMeans.java:309-322) on [k*d sums | k counts]:
+//   weights *= decay / parallelism; for counts > 0: w += n; lambda = n / w;
+//   c = c * (1 - lambda); c += (lambda / n) * sums.
+// out = [k*d centroids | k weights] (the layout the cross-rank merge gathers).
+__global__ void online_update_kernel(const double *red, int k, int d, double decay_over_p, int fma_mode,
+                                     const double *centroids, const double *weights, double *out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= k * d + k) return;
+    const int j = i < k * d ? i / d : i - k * d;
+    const double cnt = red[(size_t)k * d + j];
+    double w = __dmul_rn(weights[j], decay_over_p);
+    if (i >= k * d) {
+        out[i] = cnt > 0.0 ? __dadd_rn(w, cnt) : w;
+        return;
+    }
+    double c = centroids[i];
+    if (cnt > 0.0) {
+        w = __dadd_rn(w, cnt);
+        const double lambda = __ddiv_rn(cnt, w);
+        c = __dmul_rn(c, __dadd_rn(1.0, -lambda));
+        c = ref_mul_add(__ddiv_rn(lambda, cnt), red[i], c, fma_mode);
+    }
+    out[i] = c;
+}
+
+// ModelDataGlobalReducer (OnlineKMeans.java:188-211) over `world` gathered local models
+// [world][k*d + k], applied pairwise in rank order: c = (c*w + c'*w') / max(w + w', 1e-16); w += w'.
+__global__ void online_merge_kernel(const double *gathered, int world, int k, int d, double *centroids,
+                                    double *weights) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int len = k * d + k;
+    if (i >= len) return;
+    const int j = i < k * d ? i / d : i - k * d;
+    double w = gathered[(size_t)k * d + j];
+    double c = i < k * d ? gathered[i] : 0.0;
+    for (int t = 1; t < world; t++) {
+        const double *g = gathered + (size_t)t * len;
+        const double w2 = g[(size_t)k * d + j];
+        if (i < k * d) {
+            double den = __dadd_rn(w, w2);
+            if (den == den && !(den > 1e-16)) den = 1e-16; // Math.max(den, 1e-16)
+            c = __ddiv_rn(__dadd_rn(__dmul_rn(c, w), __dmul_rn(g[i], w2)), den);
+        }
+        w = __dadd_rn(w, w2);
+    }
+    if (i < k * d) centroids[i] = c;
+    else weights[j] = w;
+}
+
+// ------------------------------------------------------------------------------------------
+// java.util.Random on the device (benchmark data; bit-identical to the JDK's LCG)
+
+constexpr unsigned long long kJrMult = 0x5DEECE66DULL;
+constexpr unsigned long long kJrAdd = 0xBULL;
+constexpr unsigned long long kJrMask = (1ULL << 48) - 1;
+
+// state after `steps` LCG steps from s: binary powering of the affine map.
+__device__ __forceinline__ unsigned long long jr_jump(unsigned long long s, unsigned long long steps) {
+    unsigned long long a = kJrMult, c = kJrAdd;     // current power of the map
+    unsigned long long ra = 1ULL, rc = 0ULL;        // accumulated map
+    while (steps) {
+        if (steps & 1ULL) {
+            ra = (ra * a) & kJrMask;
+            rc = (rc * a + c) & kJrMask;
+        }
+        c = (c * a + c) & kJrMask;
+        a = (a * a) & kJrMask;
+        steps >>= 1;
+    }
+    return (ra * s + rc) & kJrMask;
+}
+
+// out[e] = the e-th nextDouble() of Random(seed) for e in [0, count).  Thread t produces
+// e = t, t + T, ...; (stride_a, stride_c) is the affine map of 2T LCG steps (host-computed).
+__global__ void generate_dense_kernel(unsigned long long seed_state, int64_t count, unsigned long long stride_a,
+                                      unsigned long long stride_c, double *out) {
+    const int64_t T = (int64_t)gridDim.x * blockDim.x;
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= count) return;
+    unsigned long long s = jr_jump(seed_state, 2ULL * (unsigned long long)t);
+    for (int64_t e = t; e < count; e += T) {
+        const unsigned long long s1 = (s * kJrMult + kJrAdd) & kJrMask;
+        const unsigned long long s2 = (s1 * kJrMult + kJrAdd) & kJrMask;
+        const long long hi = (long long)(s1 >> 22); // next(26)
+        const long long lo = (long long)(s2 >> 21); // next(27)
+        out[e] = (double)((hi << 27) + lo) * 0x1.0p-53;
+        s = (stride_a * s + stride_c) & kJrMask;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// FP64 peak microbenchmarks (register-resident; the roofline denominators for the assign kernel)
+
+__global__ void __launch_bounds__(256) dmma_peak_kernel(double *out, int iters) {
+    double a = 1.0 + threadIdx.x * 1e-9, b = 1.0 - threadIdx.x * 1e-9;
+    double c[16][2];
+#pragma unroll
+    for (int j = 0; j < 16; j++) c[j][0] = c[j][1] = 0.0;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int j = 0; j < 16; j++) dmma884(c[j][0], c[j][1], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int j = 0; j < 16; j++) s += c[j][0] + c[j][1];
+    if (s == 123.456) out[0] = s;
+}
+
+__global__ void __launch_bounds__(256) dfma_peak_kernel(double *out, int iters) {
+    double a = 1.0 + threadIdx.x * 1e-9, b = 1e-9;
+    double c[16];
+#pragma unroll
+    for (int j = 0; j < 16; j++) c[j] = j;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int j = 0; j < 16; j++) c[j] = fma(c[j], a, b);
+    }
+    double s = 0.0;
+#pragma unroll
+    for (int j = 0; j < 16; j++) s += c[j];
+    if (s == 123.456) out[0] = s;
+}
+
+} // namespace fmlk

@@ -1,0 +1,306 @@
+"""ctypes binding of libflinkml_kmeans_cuda.so (include/fmlk.h).
+
+The binding a JVM caller would use instead is the JNI shim described in INTEGRATION.md; both
+sit on the same C ABI.  Loading fails loudly if the library has not been built
+(``python -c "import __graft_entry__ as g; g.build()"``): there is no CPU fallback.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libflinkml_kmeans_cuda.so")
+
+OK = 0
+ERR_INVALID_ARG, ERR_STATE, ERR_DIM, ERR_CUDA, ERR_NCCL, ERR_NOMEM = -1, -2, -3, -4, -5, -6
+FLAG_PROFILE = 0x1
+FLAG_BLAS_FMA = 0x2
+NCCL_ID_BYTES = 128
+
+
+class IllegalArgumentError(ValueError):
+    """FMLK_ERR_INVALID_ARG / FMLK_ERR_DIM: Java's IllegalArgumentException."""
+
+
+class IllegalStateError(RuntimeError):
+    """FMLK_ERR_STATE: Java's IllegalStateException."""
+
+
+class NativeError(RuntimeError):
+    """CUDA / NCCL / allocation failure inside the library."""
+
+
+_EXC = {ERR_INVALID_ARG: IllegalArgumentError, ERR_DIM: IllegalArgumentError, ERR_STATE: IllegalStateError,
+        ERR_CUDA: NativeError, ERR_NCCL: NativeError, ERR_NOMEM: NativeError}
+
+# every symbol include/fmlk.h declares: name -> (restype, argtypes)
+_vp, _i32, _i64, _f64 = C.c_void_p, C.c_int32, C.c_int64, C.c_double
+SIGNATURES = {
+    "fmlk_version": (C.c_char_p, []),
+    "fmlk_device_count": (_i32, []),
+    "fmlk_nccl_unique_id": (_i32, [_vp]),
+    "fmlk_create": (_i32, [_i32, _i32, _i32, _vp, _i32, C.POINTER(_vp)]),
+    "fmlk_destroy": (None, [_vp]),
+    "fmlk_last_error": (C.c_char_p, [_vp]),
+    "fmlk_set_stream": (_i32, [_vp, _vp]),
+    "fmlk_reserve_points": (_i32, [_vp, _i64, _i32]),
+    "fmlk_append_points": (_i32, [_vp, _vp, _i64, _i32]),
+    "fmlk_append_points_dev": (_i32, [_vp, _vp, _i64, _i32]),
+    "fmlk_adopt_points_dev": (_i32, [_vp, _vp, _i64, _i32]),
+    "fmlk_clear_points": (_i32, [_vp]),
+    "fmlk_num_points": (_i64, [_vp]),
+    "fmlk_set_centroids": (_i32, [_vp, _vp, _i32, _i32]),
+    "fmlk_train_round": (_i32, [_vp, _vp, _vp]),
+    "fmlk_fit": (_i32, [_vp, _i32, _vp, _vp]),
+    "fmlk_local_partials": (_i32, [_vp, _vp, _vp]),
+    "fmlk_get_model": (_i32, [_vp, _vp, _vp]),
+    "fmlk_predict": (_i32, [_vp, _vp, _i64, _i32, _vp]),
+    "fmlk_predict_dev": (_i32, [_vp, _vp, _i64, _i32, _vp]),
+    "fmlk_predict_cached": (_i32, [_vp, _vp]),
+    "fmlk_online_round": (_i32, [_vp, _vp, _i64, _i32, _i32, _f64, _vp, _vp]),
+    "fmlk_reservoir": (_i32, [_i64, _i32, _i64, _vp]),
+    "fmlk_get_points": (_i32, [_vp, _vp, _i32, _vp]),
+    "fmlk_generate_dense_dev": (_i32, [_i32, _vp, _i64, _i32, _i32, _i64, _i32, _vp]),
+    "fmlk_get_profile": (_i32, [_vp, C.POINTER(_f64), C.POINTER(_i64), C.POINTER(_i64), C.POINTER(_i64)]),
+    "fmlk_reset_profile": (_i32, [_vp]),
+    "fmlk_measure_fp64_peaks": (_i32, [_i32, _f64, C.POINTER(_f64), C.POINTER(_f64)]),
+    "fmlk_describe_launch": (_i32, [_vp, _i32, _i32, _i32, C.c_char_p, _i32]),
+}
+
+_lib = None
+
+
+def lib():
+    """The loaded library; raises if it is missing (no fallback of any kind)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise NativeError("%s is not built; run __graft_entry__.build() (nvcc, sm_100a)" % LIB_PATH)
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def _check(rc, handle=None):
+    if rc >= 0:
+        return rc
+    msg = lib().fmlk_last_error(handle)
+    msg = msg.decode() if msg else "error %d" % rc
+    raise _EXC.get(rc, NativeError)(msg)
+
+
+def version():
+    return lib().fmlk_version().decode()
+
+
+def device_count():
+    return _check(lib().fmlk_device_count())
+
+
+def nccl_unique_id():
+    buf = (C.c_uint8 * NCCL_ID_BYTES)()
+    _check(lib().fmlk_nccl_unique_id(buf))
+    return bytes(buf)
+
+
+def reservoir(n, k, seed):
+    """SamplingOperator (DataStreamUtils.java:633-704): ids held after n elements."""
+    ids = np.empty(max(int(k), 1), dtype=np.int64)
+    m = _check(lib().fmlk_reservoir(int(n), int(k), int(seed), ids.ctypes.data))
+    return ids[:m].copy()
+
+
+def generate_dense_dev(device, stream, seed, task, num_tasks, num_values, d, out_ptr):
+    _check(lib().fmlk_generate_dense_dev(int(device), stream, int(seed), int(task), int(num_tasks), int(num_values),
+                                         int(d), out_ptr))
+
+
+def measure_fp64_peaks(device=0, ms=200.0):
+    a, b = _f64(), _f64()
+    _check(lib().fmlk_measure_fp64_peaks(int(device), float(ms), C.byref(a), C.byref(b)))
+    return a.value, b.value
+
+
+def rows_on_task(num_values, task, num_tasks):
+    """RowGenerator.java:51-53."""
+    dv, md = divmod(int(num_values), int(num_tasks))
+    return dv + 1 if md > task else dv
+
+
+def _f64_matrix(a):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    if a.ndim == 1:
+        a = a.reshape(1, -1)
+    if a.ndim != 2:
+        raise IllegalArgumentError("expected an n x d matrix")
+    return a
+
+
+class Context:
+    """One subtask's GPU state (fmlk_ctx): the HBM-resident point cache and the model."""
+
+    def __init__(self, device=0, rank=0, world=1, nccl_id=None, flags=0):
+        self._h = _vp()
+        idbuf = None
+        if nccl_id is not None:
+            idbuf = (C.c_uint8 * NCCL_ID_BYTES).from_buffer_copy(nccl_id)
+        _check(lib().fmlk_create(int(device), int(rank), int(world), idbuf, int(flags), C.byref(self._h)))
+        self.device, self.rank, self.world = int(device), int(rank), int(world)
+        self.k = 0
+        self.d = 0
+        self._keep = []  # adopted device tensors kept alive
+
+    # -- lifetime
+    def close(self):
+        if self._h:
+            lib().fmlk_destroy(self._h)
+            self._h = _vp()
+            self._keep = []
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _ck(self, rc):
+        return _check(rc, self._h)
+
+    def set_stream(self, stream_ptr):
+        self._ck(lib().fmlk_set_stream(self._h, stream_ptr))
+
+    # -- point cache
+    def reserve_points(self, n, d):
+        self._ck(lib().fmlk_reserve_points(self._h, int(n), int(d)))
+        self.d = int(d)
+
+    def append_points(self, rows):
+        rows = _f64_matrix(rows)
+        n, d = rows.shape
+        self._ck(lib().fmlk_append_points(self._h, rows.ctypes.data, n, d))
+        if n:
+            self.d = d
+
+    def append_points_ptr(self, host_ptr, n, d):
+        """Host rows given as a raw address (e.g. a pinned torch tensor's data_ptr())."""
+        self._ck(lib().fmlk_append_points(self._h, host_ptr, int(n), int(d)))
+        self.d = int(d)
+
+    def append_points_dev(self, dev_ptr, n, d):
+        self._ck(lib().fmlk_append_points_dev(self._h, dev_ptr, int(n), int(d)))
+        self.d = int(d)
+
+    def adopt_points_dev(self, dev_ptr, n, d, keep=None):
+        self._ck(lib().fmlk_adopt_points_dev(self._h, dev_ptr, int(n), int(d)))
+        self.d = int(d)
+        if keep is not None:
+            self._keep.append(keep)
+
+    def clear_points(self):
+        self._ck(lib().fmlk_clear_points(self._h))
+        self._keep = []
+
+    def num_points(self):
+        return int(lib().fmlk_num_points(self._h))
+
+    def get_points(self, ids):
+        ids = np.ascontiguousarray(ids, dtype=np.int64)
+        out = np.empty((ids.size, self.d), dtype=np.float64)
+        self._ck(lib().fmlk_get_points(self._h, ids.ctypes.data, ids.size, out.ctypes.data))
+        return out
+
+    # -- training
+    def set_centroids(self, centroids):
+        c = _f64_matrix(centroids)
+        self._ck(lib().fmlk_set_centroids(self._h, c.ctypes.data, c.shape[0], c.shape[1]))
+        self.k, self.d = c.shape
+
+    def _model_out(self):
+        return np.empty((self.k, self.d), dtype=np.float64), np.empty(self.k, dtype=np.float64)
+
+    def train_round(self):
+        c, w = self._model_out()
+        self._ck(lib().fmlk_train_round(self._h, c.ctypes.data, w.ctypes.data))
+        return c, w
+
+    def fit(self, max_iter, want_model=True):
+        if not want_model:
+            self._ck(lib().fmlk_fit(self._h, int(max_iter), None, None))
+            return None
+        c, w = self._model_out()
+        self._ck(lib().fmlk_fit(self._h, int(max_iter), c.ctypes.data, w.ctypes.data))
+        return c, w
+
+    def local_partials(self):
+        sums = np.empty((self.k, self.d), dtype=np.float64)
+        counts = np.empty(self.k, dtype=np.int64)
+        self._ck(lib().fmlk_local_partials(self._h, sums.ctypes.data, counts.ctypes.data))
+        return sums, counts
+
+    def get_model(self):
+        c, w = self._model_out()
+        self._ck(lib().fmlk_get_model(self._h, c.ctypes.data, w.ctypes.data))
+        return c, w
+
+    # -- inference
+    def predict(self, rows):
+        rows = _f64_matrix(rows)
+        n, d = rows.shape
+        out = np.empty(n, dtype=np.int32)
+        self._ck(lib().fmlk_predict(self._h, rows.ctypes.data, n, d, out.ctypes.data))
+        return out
+
+    def predict_ptr(self, host_ptr, n, d, out_ptr):
+        self._ck(lib().fmlk_predict(self._h, host_ptr, int(n), int(d), out_ptr))
+
+    def predict_dev(self, dev_ptr, n, d, out_dev_ptr):
+        self._ck(lib().fmlk_predict_dev(self._h, dev_ptr, int(n), int(d), out_dev_ptr))
+
+    def predict_cached(self):
+        out = np.empty(self.num_points(), dtype=np.int32)
+        self._ck(lib().fmlk_predict_cached(self._h, out.ctypes.data))
+        return out
+
+    # -- online
+    def online_round(self, local_batch, centroids, weights, decay):
+        c = np.array(_f64_matrix(centroids), copy=True, order="C")
+        w = np.array(weights, dtype=np.float64, copy=True).reshape(-1)
+        k, d = c.shape
+        if w.size != k:
+            raise IllegalArgumentError("weights size must equal the number of centroids")
+        b = np.ascontiguousarray(local_batch, dtype=np.float64)
+        if b.size == 0:
+            b = b.reshape(0, d)
+        b = _f64_matrix(b) if b.shape[0] else b
+        if b.shape[0] and b.shape[1] != d:
+            raise IllegalArgumentError("Vector size mismatched.")
+        self._ck(lib().fmlk_online_round(self._h, b.ctypes.data if b.shape[0] else None, b.shape[0], d, k,
+                                         float(decay), c.ctypes.data, w.ctypes.data))
+        self.k, self.d = k, d
+        return c, w
+
+    # -- measurement
+    def profile(self):
+        ms, al, tl, rr = _f64(), _i64(), _i64(), _i64()
+        self._ck(lib().fmlk_get_profile(self._h, C.byref(ms), C.byref(al), C.byref(tl), C.byref(rr)))
+        return {"assign_ms": ms.value, "assign_launches": al.value, "total_launches": tl.value,
+                "rechecked_rows": rr.value}
+
+    def reset_profile(self):
+        self._ck(lib().fmlk_reset_profile(self._h))
+
+    def describe_launch(self, k, d, accumulate=True):
+        buf = C.create_string_buffer(512)
+        self._ck(lib().fmlk_describe_launch(self._h, int(k), int(d), 1 if accumulate else 0, buf, 512))
+        return buf.value.decode()

@@ -1,0 +1,179 @@
+/*
+ * fmlk.h -- C ABI of libflinkml_kmeans_cuda.so: the B200 (sm_100a) KMeans hot path
+ * of Flink ML behind the reference's three operator bodies.
+ *
+ * The reference (weibozhao/flink-ml @ 169aca44) has no FFI for this path; the seams
+ * are the per-subtask operator bodies, and each entry point below replaces one of
+ * them.  Citations are reference file:line with
+ *   LIB/  = flink-ml-lib/src/main/java/org/apache/flink/ml/
+ *   CORE/ = flink-ml-core/src/main/java/org/apache/flink/ml/
+ *
+ * Conventions
+ *   - every function returns 0 (FMLK_OK) or a negative fmlk_status; the message of
+ *     the last failure on a context is available from fmlk_last_error();
+ *   - host buffers are caller-owned, native-endian FP64 / int32, row-major; the
+ *     library copies what it needs and never keeps a host pointer past the call;
+ *   - one context == one Flink subtask == one GPU; a context is driven by one
+ *     thread at a time (Flink's mailbox thread) and is not re-entrant;
+ *   - there is NO CPU fallback: without a usable CUDA device every compute entry
+ *     point fails with FMLK_ERR_CUDA.
+ */
+#ifndef FMLK_H_
+#define FMLK_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fmlk_ctx fmlk_ctx;
+
+typedef enum fmlk_status {
+    FMLK_OK = 0,
+    FMLK_ERR_INVALID_ARG = -1, /* Java side: IllegalArgumentException (Preconditions.checkArgument) */
+    FMLK_ERR_STATE = -2,       /* Java side: IllegalStateException (Preconditions.checkState)       */
+    FMLK_ERR_DIM = -3,         /* IllegalArgumentException("Vector size mismatched.") CORE/linalg/BLAS.java:36,70 */
+    FMLK_ERR_CUDA = -4,        /* RuntimeException: CUDA runtime failure or no device */
+    FMLK_ERR_NCCL = -5,        /* RuntimeException: NCCL missing or failed */
+    FMLK_ERR_NOMEM = -6        /* RuntimeException: device or host allocation failed */
+} fmlk_status;
+
+/* fmlk_create flags */
+#define FMLK_FLAG_PROFILE 0x1  /* time every assign-kernel launch with CUDA events (fmlk_get_profile) */
+#define FMLK_FLAG_BLAS_FMA 0x2 /* exact paths follow netlib's JDK>=11 (Math.fma) variant instead of JDK 8 */
+
+#define FMLK_NCCL_ID_BYTES 128
+
+/* Library / build identification ("fmlk <version> sm_100a"). */
+const char *fmlk_version(void);
+
+/* Number of CUDA devices visible, or a negative status. */
+int32_t fmlk_device_count(void);
+
+/* ncclGetUniqueId, for the caller to distribute to the other subtasks (in Flink it
+ * rides the broadcast of the initial centroids, LIB/clustering/kmeans/KMeans.java:153-161). */
+int32_t fmlk_nccl_unique_id(uint8_t out[FMLK_NCCL_ID_BYTES]);
+
+/* Binds a context to `device` (subtaskIndex % deviceCount at operator open()).  world > 1
+ * joins the NCCL communicator identified by nccl_id (ncclCommInitRank); world == 1 ignores it.
+ * Replaces operator construction + initializeState, KMeans.java:226-249. */
+int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *nccl_id_or_null,
+                    int32_t flags, fmlk_ctx **out);
+
+/* Releases device memory, streams and the communicator (operator close() /
+ * onIterationTerminated, KMeans.java:302-307).  NULL is accepted. */
+void fmlk_destroy(fmlk_ctx *ctx);
+
+const char *fmlk_last_error(const fmlk_ctx *ctx);
+
+/* Runs the library's work on the given cudaStream_t (default: a stream the context owns). */
+int32_t fmlk_set_stream(fmlk_ctx *ctx, void *cuda_stream);
+
+/* ---- point cache: replaces ListStateWithCache<VectorWithNorm> (KMeans.java:222,240-246) ---- */
+
+/* Optional: size the HBM-resident cache for n_rows x d up front (one allocation). */
+int32_t fmlk_reserve_points(fmlk_ctx *ctx, int64_t n_rows, int32_t d);
+
+/* processElement1 (KMeans.java:257-260) for a micro-batch of n rows: copies host rows
+ * into HBM, where they stay for every round.  d must match earlier appends (FMLK_ERR_DIM). */
+int32_t fmlk_append_points(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t d);
+
+/* Same with the rows already on this context's device (device-to-device copy). */
+int32_t fmlk_append_points_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d);
+
+/* Zero-copy variant: the context reads caller-owned device memory in place; the caller
+ * keeps it alive and unchanged until fmlk_clear_points / fmlk_destroy. */
+int32_t fmlk_adopt_points_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d);
+
+/* points.clear() (KMeans.java:305). */
+int32_t fmlk_clear_points(fmlk_ctx *ctx);
+
+int64_t fmlk_num_points(const fmlk_ctx *ctx);
+
+/* ---- training: CentroidsUpdateAccumulator + reducer + model generator ---- */
+
+/* processElement2 (KMeans.java:262-266): the centroids of the coming round, k x d.  1 <= k. */
+int32_t fmlk_set_centroids(fmlk_ctx *ctx, const double *centroids_host, int32_t k, int32_t d);
+
+/* One round = onEpochWatermarkIncremented (KMeans.java:269-300) on this subtask's points,
+ * the sum over subtasks (CentroidsUpdateReducer, KMeans.java:185-198; an NCCL all-reduce
+ * of the k*d sums and k counts when world > 1) and ModelDataGenerator (KMeans.java:200-212).
+ * The new centroids become the next round's; every rank gets the identical result.
+ * out_* may be NULL to skip the device-to-host copy. */
+int32_t fmlk_train_round(fmlk_ctx *ctx, double *out_centroids, double *out_weights);
+
+/* max_iter rounds back to back with no host synchronisation in between
+ * (TerminateOnMaxIter, CORE/common/iteration/TerminateOnMaxIter.java:47-52: exactly
+ * max_iter rounds; ForwardInputsOfLastRound: the last round's model is returned). */
+int32_t fmlk_fit(fmlk_ctx *ctx, int32_t max_iter, double *out_centroids, double *out_weights);
+
+/* This subtask's (sums, counts) for the current centroids, before any cross-subtask
+ * reduction: the record emitted at KMeans.java:297.  Does not change the centroids. */
+int32_t fmlk_local_partials(fmlk_ctx *ctx, double *out_sums, int64_t *out_counts);
+
+/* Current centroids (k x d) and weights (k) as held on the device. */
+int32_t fmlk_get_model(fmlk_ctx *ctx, double *out_centroids, double *out_weights);
+
+/* ---- inference: PredictLabelFunction.map (LIB/clustering/kmeans/KMeansModel.java:129-144)
+ *      and PredictLabelOperator (LIB/clustering/kmeans/OnlineKMeansModel.java:170-180) ---- */
+
+/* Labels n host rows against the context's current centroids (fmlk_set_centroids). */
+int32_t fmlk_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t d,
+                     int32_t *out_labels_host);
+
+/* Device-resident rows and labels (no host copies). */
+int32_t fmlk_predict_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d,
+                         int32_t *out_labels_dev);
+
+/* Labels the rows in the point cache, in append order, into a host buffer of fmlk_num_points(). */
+int32_t fmlk_predict_cached(fmlk_ctx *ctx, int32_t *out_labels_host);
+
+/* ---- OnlineKMeans: ModelDataLocalUpdater.alignAndComputeModelData
+ *      (LIB/clustering/kmeans/OnlineKMeans.java:271-325) followed by ModelDataGlobalReducer
+ *      (OnlineKMeans.java:188-211) over the `world` subtasks in rank order ---- */
+
+/* local_batch_host: this subtask's slice of the global batch (DataStreamUtils.java:609-626),
+ * n_local x d.  centroids_inout (k x d) / weights_inout (k): the broadcast model in, the merged
+ * model out (identical on every rank).  The call (re)establishes the context's k and d. */
+int32_t fmlk_online_round(fmlk_ctx *ctx, const double *local_batch_host, int64_t n_local, int32_t d,
+                          int32_t k, double decay, double *centroids_inout, double *weights_inout);
+
+/* ---- initial centroids: KMeans.selectRandomCentroids (KMeans.java:310-327) ---- */
+
+/* One SamplingOperator (CORE/common/datastream/DataStreamUtils.java:633-704) over a stream of
+ * n elements numbered 0..n-1: reservoir of k with java.util.Random(seed).  Writes the ids held
+ * at end of input, in list order, to out_ids[k] and returns how many (min(n, k)), or a negative
+ * status.  Host-only integer work; the two-stage composition across subtasks
+ * (DataStreamUtils.java:212-227) is the caller's, with the rows fetched by fmlk_get_points. */
+int32_t fmlk_reservoir(int64_t n, int32_t k, int64_t seed, int64_t *out_ids);
+
+/* Copies m cached rows, by position in append order, to out_rows_host (m x d). */
+int32_t fmlk_get_points(fmlk_ctx *ctx, const int64_t *row_ids, int32_t m, double *out_rows_host);
+
+/* ---- measurement helpers (used by tests/ and bench.py; not needed by a Flink operator) ---- */
+
+/* DenseVectorGenerator rows (flink-ml-benchmark .../common/RowGenerator.java:47-56,
+ * DenseVectorGenerator.java:44-50) of subtask `task` of `num_tasks`, written straight into
+ * device memory: rows_on_task x d doubles, bit-identical to java.util.Random.nextDouble(). */
+int32_t fmlk_generate_dense_dev(int32_t device, void *cuda_stream, int64_t seed, int32_t task,
+                                int32_t num_tasks, int64_t num_values, int32_t d, double *out_dev);
+
+/* With FMLK_FLAG_PROFILE: device time and launch count of the assign kernel, and the count
+ * of all kernel launches, accumulated since the last fmlk_reset_profile. */
+int32_t fmlk_get_profile(fmlk_ctx *ctx, double *assign_ms, int64_t *assign_launches,
+                         int64_t *total_launches, int64_t *rechecked_rows);
+int32_t fmlk_reset_profile(fmlk_ctx *ctx);
+
+/* Sustained FP64 tensor-core (DMMA m8n8k4) and FP64 FMA throughput of `device` in TFLOP/s,
+ * from a register-resident microbenchmark run for about `ms` milliseconds each. */
+int32_t fmlk_measure_fp64_peaks(int32_t device, double ms, double *dmma_tflops, double *dfma_tflops);
+
+/* Launch geometry the assign kernel would use for (k, d): for DESIGN.md / bench reporting. */
+int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumulate,
+                             char *out, int32_t out_len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FMLK_H_ */

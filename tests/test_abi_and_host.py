@@ -1,0 +1,208 @@
+"""CPU-side checks (no GPU): the C-ABI library loads and exports every symbol include/fmlk.h
+declares; host logic (params, model bytes, sampler composition, batch split) matches the oracle
+and the reference's own test expectations."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+import flink_ml_b200 as F
+from flink_ml_b200 import kmeans as K
+from flink_ml_b200 import native
+from oracle import oracle as O
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared_symbols():
+    text = open(os.path.join(ROOT, "include", "fmlk.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(fmlk_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    declared = _declared_symbols()
+    assert len(declared) >= 25
+    out = subprocess.check_output(["nm", "-D", "--defined-only", native.LIB_PATH]).decode()
+    exported = set(re.findall(r" T (fmlk_[a-z0-9_]+)", out))
+    assert set(declared) <= exported, sorted(set(declared) - exported)
+    # and the ctypes binding covers exactly the header
+    assert sorted(native.SIGNATURES) == declared
+    L = native.lib()
+    for name in declared:
+        assert getattr(L, name) is not None
+    assert native.version().endswith("sm_100a")
+
+
+def test_library_has_no_oracle_or_torch_dependency():
+    out = subprocess.check_output(["ldd", native.LIB_PATH]).decode()
+    assert "oracle" not in out and "torch" not in out and "nccl" not in out  # NCCL is dlopen'ed when world > 1
+
+
+def test_no_cpu_fallback_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(native.NativeError, match="no CPU path|CUDA"):
+        native.Context(0)
+
+
+def test_product_never_imports_oracle():
+    pkg = os.path.join(ROOT, "flink-ml_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".h")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in text.lower().replace("test oracle", ""), os.path.join(dirpath, f)
+
+
+# ---------------------------------------------------------------- params (G8)
+def test_kmeans_param_defaults():
+    """KMeansTest.java:125-148."""
+    km = F.KMeans()
+    assert km.get_features_col() == "features" and km.get_prediction_col() == "prediction"
+    assert km.get_distance_measure() == "euclidean" and km.get_init_mode() == "random"
+    assert km.get_k() == 2 and km.get_max_iter() == 20
+    assert km.get_seed() == K.java_string_hash("org.apache.flink.ml.clustering.kmeans.KMeans") == -235125357
+    km.set_k(9).set_features_col("test_feature").set_prediction_col("test_prediction").set_k(3) \
+        .set_max_iter(30).set_seed(100)
+    assert (km.get_features_col(), km.get_prediction_col(), km.get_k(), km.get_max_iter(), km.get_seed()) == \
+        ("test_feature", "test_prediction", 3, 30, 100)
+    with pytest.raises(ValueError):
+        km.set_k(1)           # ParamValidators.gt(1)
+    with pytest.raises(ValueError):
+        km.set_max_iter(0)    # gt(0)
+    with pytest.raises(ValueError):
+        km.set_distance_measure("chebyshev")
+    with pytest.raises(ValueError):
+        km.set_init_mode("k-means++")
+
+
+def test_online_kmeans_param_defaults():
+    """OnlineKMeansTest.java:273-298."""
+    ok = F.OnlineKMeans()
+    assert ok.get_features_col() == "features" and ok.get_prediction_col() == "prediction"
+    assert ok.get_batch_strategy() == "count" and ok.get_distance_measure() == "euclidean"
+    assert ok.get_global_batch_size() == 32 and ok.get_decay_factor() == 0.0
+    assert ok.get_seed() == 861956550
+    ok.set_features_col("test_feature").set_prediction_col("test_prediction").set_global_batch_size(5) \
+        .set_decay_factor(0.25).set_seed(100)
+    assert (ok.get_global_batch_size(), ok.get_decay_factor(), ok.get_seed()) == (5, 0.25, 100)
+    with pytest.raises(ValueError):
+        ok.set_decay_factor(1.5)
+    with pytest.raises(ValueError):
+        ok.set_global_batch_size(0)
+
+
+def test_non_euclidean_is_rejected_not_emulated():
+    km = F.KMeans().set_distance_measure("cosine")
+    with pytest.raises(ValueError, match="not available on the CUDA path"):
+        km.fit(F.Table({"features": np.zeros((4, 2))}))
+    with pytest.raises(ValueError):
+        F.KMeans().fit()  # exactly one input table (KMeans.java:88)
+
+
+def test_online_batch_smaller_than_parallelism_message():
+    """OnlineKMeansTest.java:431-451: exact IllegalStateException message."""
+    est = F.OnlineKMeans(K.Cluster(rank=0, world=4)).set_global_batch_size(2).set_initial_model_data(
+        F.KMeansModelData.generate_random_model_data(2, 2, 0.0, 0).to_table())
+    with pytest.raises(K.IllegalStateError) as e:
+        est.fit(F.Table({"features": np.zeros((6, 2))}))
+    assert str(e.value) == ("There are more subtasks in the training process than the number "
+                            "of elements in each batch. Some subtasks might be idling forever.")
+
+
+# ---------------------------------------------------------------- model data (G7)
+def test_model_data_bytes_match_oracle_and_round_trip(tmp_path):
+    md = F.KMeansModelData.generate_random_model_data(3, 5, 0.0, 1)
+    oc, ow = O.random_model_data(3, 5, 0.0, 1)
+    assert np.array_equal(md.centroids, oc) and np.array_equal(md.weights, ow)
+    assert md.encode() == O.model_encode(oc, ow)
+    back, used = F.KMeansModelData.decode(md.encode())
+    assert used == len(md.encode()) and np.array_equal(back.centroids, md.centroids)
+    with pytest.raises(EOFError):
+        F.KMeansModelData.decode(md.encode()[:-3])
+    # save / load keeps the table schema (KMeansTest.java:229-231)
+    model = F.KMeansModel().set_model_data(md.to_table()).set_k(3).set_prediction_col("p")
+    model.save(str(tmp_path / "m"))
+    loaded = F.KMeansModel.load(str(tmp_path / "m"))
+    assert loaded.get_model_data()[0].get_column_names() == ["centroids", "weights"]
+    assert loaded.get_k() == 3 and loaded.get_prediction_col() == "p"
+    got = F.KMeansModelData.from_table(loaded.get_model_data()[0])
+    assert np.array_equal(got.centroids, md.centroids) and np.array_equal(got.weights, md.weights)
+    with pytest.raises(IOError):
+        model.save(str(tmp_path / "m"))  # metadata must not exist (ReadWriteUtils.java:95)
+    est = F.KMeans().set_k(7).set_seed(5)
+    est.save(str(tmp_path / "e"))
+    assert F.KMeans.load(str(tmp_path / "e")).get_param_map() == est.get_param_map()
+
+
+# ---------------------------------------------------------------- sampler / split
+def test_reservoir_matches_oracle():
+    for n, k, seed in [(0, 3, 1), (3, 5, 1), (10, 10, -7), (1000, 10, 123), (100000, 100, -235125357),
+                       (5000, 1, 2 ** 40 + 3)]:
+        assert native.reservoir(n, k, seed).tolist() == O.reservoir(n, k, seed).tolist()
+
+
+def test_split_global_batch_matches_oracle():
+    for length, p in [(6, 4), (32, 8), (100000, 8), (7, 7), (5, 1)]:
+        sizes = [s for _, s in K.split_global_batch(length, p)]
+        assert sizes == O.split_batch(length, p).tolist()
+        offs = [o for o, _ in K.split_global_batch(length, p)]
+        assert offs == np.concatenate([[0], np.cumsum(sizes)[:-1]]).tolist()
+
+
+class _FakeCtx:
+    """Stands in for a native context's point cache (host arrays), to test host composition."""
+
+    def __init__(self, rows):
+        self.rows, self.d = rows, rows.shape[1]
+
+    def num_points(self):
+        return self.rows.shape[0]
+
+    def get_points(self, ids):
+        return self.rows[ids]
+
+
+def test_select_random_centroids_single_subtask():
+    x = O.generate_dense(2, 0, 1, 500, 4)
+    got = K.select_random_centroids(_FakeCtx(x), K.Cluster(), 7, -235125357)
+    assert np.array_equal(got, O.select_random_centroids([x], 7, -235125357))
+
+
+def _worker(rank, world, port, q):
+    import torch.distributed as dist
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, rank=rank, world_size=world)
+    shard = O.generate_dense(2, rank, world, 501, 3)
+    got = K.select_random_centroids(_FakeCtx(shard), K.Cluster(rank, world), 5, 99)
+    q.put((rank, got))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_stage_sampler_world2_gloo():
+    """world_size-2 gloo run of the N>1 host path: both ranks derive the identical initial
+    centroids, equal to the oracle's two-stage sampler at p=2 (subtask order 0,1)."""
+    import torch.multiprocessing as mp
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = dict(q.get(timeout=120) for _ in range(2))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    shards = [O.generate_dense(2, r, 2, 501, 3) for r in range(2)]
+    want = O.select_random_centroids(shards, 5, 99)
+    assert np.array_equal(res[0], want) and np.array_equal(res[1], want)
+
+
+def test_rows_on_task_matches_row_generator():
+    for n, p in [(10, 4), (10 ** 9, 8), (7, 7), (3, 5)]:
+        assert [native.rows_on_task(n, t, p) for t in range(p)] == [O.rows_on_task(n, t, p) for t in range(p)]
