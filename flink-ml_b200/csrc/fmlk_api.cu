@@ -99,7 +99,8 @@ struct fmlk_ctx {
     int sm_count = 0;
     size_t smem_optin = 0;
 
-    int32_t d = 0; // row dimension (0: not fixed yet)
+    int32_t d = 0;  // dimension of the cached rows (0: cache empty and nothing reserved)
+    int32_t md = 0; // dimension of the model (centroids)
     int32_t k = 0;
     std::vector<Chunk> chunks;
     int64_t n_total = 0;
@@ -323,7 +324,7 @@ void drain_events(fmlk_ctx *ctx) {
 
 int prep_centroids(fmlk_ctx *ctx) {
     const int k_pad = (ctx->k + 7) & ~7;
-    prep_centroids_kernel<<<1, 256, 0, ctx->stream>>>(ctx->centroids, ctx->k, k_pad, ctx->d,
+    prep_centroids_kernel<<<1, 256, 0, ctx->stream>>>(ctx->centroids, ctx->k, k_pad, ctx->md,
                                                      (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0, ctx->cn, ctx->h,
                                                      ctx->cmax2);
     ctx->total_launches++;
@@ -337,7 +338,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     AssignParams p{};
     p.x = x;
     p.n = n;
-    p.d = ctx->d;
+    p.d = ctx->md;
     p.S = cfg.S;
     p.ksteps = cfg.ksteps;
     p.c = ctx->centroids;
@@ -348,7 +349,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.k_pad = cfg.k_pad;
     p.nc_tile = cfg.nc_tile;
     p.n_ctiles = cfg.n_ctiles;
-    p.thr_coef = 8.0 * (2.0 * ctx->d + 16.0) * 0x1.0p-53;
+    p.thr_coef = 8.0 * (2.0 * ctx->md + 16.0) * 0x1.0p-53;
     p.labels = labels;
     p.partials = accum ? ctx->partials : nullptr;
     p.n_partials = cfg.n_partials;
@@ -377,10 +378,11 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
 
 // [sums | counts] of this subtask's cached points for the current centroids -> ctx->red.
 int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
+    if (!extra_rows && ctx->n_total > 0 && ctx->d != ctx->md) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
     LaunchCfg cfg;
-    int rc = choose_cfg(ctx, ctx->k, ctx->d, true, &cfg);
+    int rc = choose_cfg(ctx, ctx->k, ctx->md, true, &cfg);
     if (rc) return rc;
-    const size_t len = (size_t)ctx->k * ctx->d + ctx->k;
+    const size_t len = (size_t)ctx->k * ctx->md + ctx->k;
     if ((rc = ensure_partials(ctx, len * cfg.n_partials))) return rc;
     if ((rc = prep_centroids(ctx))) return rc;
     CK(ctx, cudaMemsetAsync(ctx->partials, 0, len * cfg.n_partials * sizeof(double), ctx->stream));
@@ -401,12 +403,12 @@ int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
 int one_train_round(fmlk_ctx *ctx) {
     int rc = local_round(ctx, nullptr, 0);
     if (rc) return rc;
-    const size_t len = (size_t)ctx->k * ctx->d + ctx->k;
+    const size_t len = (size_t)ctx->k * ctx->md + ctx->k;
     if (ctx->world > 1)
         CKN(ctx, nccl().AllReduce(ctx->red, ctx->red, len, ncclFloat64, ncclSum, ctx->comm, ctx->stream));
     const int threads = 256;
-    finalize_centroids_kernel<<<(unsigned)(((size_t)ctx->k * ctx->d + threads - 1) / threads), threads, 0,
-                                ctx->stream>>>(ctx->red, ctx->k, ctx->d, ctx->centroids, ctx->weights);
+    finalize_centroids_kernel<<<(unsigned)(((size_t)ctx->k * ctx->md + threads - 1) / threads), threads, 0,
+                                ctx->stream>>>(ctx->red, ctx->k, ctx->md, ctx->centroids, ctx->weights);
     ctx->total_launches++;
     CK(ctx, cudaGetLastError());
     return FMLK_OK;
@@ -414,7 +416,7 @@ int one_train_round(fmlk_ctx *ctx) {
 
 int copy_model_out(fmlk_ctx *ctx, double *out_centroids, double *out_weights) {
     if (out_centroids)
-        CK(ctx, cudaMemcpyAsync(out_centroids, ctx->centroids, (size_t)ctx->k * ctx->d * sizeof(double),
+        CK(ctx, cudaMemcpyAsync(out_centroids, ctx->centroids, (size_t)ctx->k * ctx->md * sizeof(double),
                                 cudaMemcpyDeviceToHost, ctx->stream));
     if (out_weights)
         CK(ctx, cudaMemcpyAsync(out_weights, ctx->weights, (size_t)ctx->k * sizeof(double), cudaMemcpyDeviceToHost,
@@ -424,6 +426,7 @@ int copy_model_out(fmlk_ctx *ctx, double *out_centroids, double *out_weights) {
     return FMLK_OK;
 }
 
+// d against the rows already cached (or reserved); the model's dimension is checked when used.
 int check_dim(fmlk_ctx *ctx, int32_t d) {
     if (d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "vector dimension must be positive");
     if (ctx->d != 0 && ctx->d != d) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
@@ -649,7 +652,7 @@ int32_t fmlk_clear_points(fmlk_ctx *ctx) {
         if (c.owned) dev_free(c.ptr);
     ctx->chunks.clear();
     ctx->n_total = 0;
-    if (ctx->k == 0) ctx->d = 0;
+    ctx->d = 0;
     return FMLK_OK;
 }
 
@@ -665,7 +668,7 @@ int32_t fmlk_set_centroids(fmlk_ctx *ctx, const double *centroids_host, int32_t 
     if (ctx->n_total > 0 && ctx->d != d) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
     if ((rc = ensure_model(ctx, k, d))) return rc;
     ctx->k = k;
-    ctx->d = d;
+    ctx->md = d;
     CK(ctx, cudaMemcpyAsync(ctx->centroids, centroids_host, (size_t)k * d * sizeof(double), cudaMemcpyHostToDevice,
                             ctx->stream));
     CK(ctx, cudaMemsetAsync(ctx->weights, 0, (size_t)k * sizeof(double), ctx->stream));
@@ -704,7 +707,7 @@ int32_t fmlk_local_partials(fmlk_ctx *ctx, double *out_sums, int64_t *out_counts
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
     if ((rc = local_round(ctx, nullptr, 0))) return rc;
-    const size_t kd = (size_t)ctx->k * ctx->d;
+    const size_t kd = (size_t)ctx->k * ctx->md;
     std::vector<double> cnt((size_t)ctx->k);
     if (out_sums) CK(ctx, cudaMemcpyAsync(out_sums, ctx->red, kd * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
     CK(ctx, cudaMemcpyAsync(cnt.data(), ctx->red + kd, (size_t)ctx->k * sizeof(double), cudaMemcpyDeviceToHost,
@@ -726,7 +729,7 @@ int32_t fmlk_get_model(fmlk_ctx *ctx, double *out_centroids, double *out_weights
 
 static int32_t predict_impl(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t *labels_dev) {
     LaunchCfg cfg;
-    int rc = choose_cfg(ctx, ctx->k, ctx->d, false, &cfg);
+    int rc = choose_cfg(ctx, ctx->k, ctx->md, false, &cfg);
     if (rc) return rc;
     if ((rc = prep_centroids(ctx))) return rc;
     return launch_assign(ctx, cfg, rows_dev, n, labels_dev, false);
@@ -737,7 +740,7 @@ int32_t fmlk_predict_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
-    if (d != ctx->d) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
+    if (d != ctx->md) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
     if (n < 0 || (n > 0 && (!rows_dev || !out_labels_dev))) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad rows / labels");
     return predict_impl(ctx, rows_dev, n, out_labels_dev);
 }
@@ -747,7 +750,7 @@ int32_t fmlk_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t 
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
-    if (d != ctx->d) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
+    if (d != ctx->md) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
     if (n < 0 || (n > 0 && (!rows_host || !out_labels_host))) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad rows / labels");
     if (n == 0) return FMLK_OK;
     // micro-batches through a reusable staging buffer: copy in, label, copy out
@@ -755,7 +758,7 @@ int32_t fmlk_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t 
     const int64_t step = std::min(n, max_rows);
     if ((rc = ensure_stage(ctx, (size_t)step * d, (size_t)step))) return rc;
     LaunchCfg cfg;
-    if ((rc = choose_cfg(ctx, ctx->k, ctx->d, false, &cfg))) return rc;
+    if ((rc = choose_cfg(ctx, ctx->k, ctx->md, false, &cfg))) return rc;
     if ((rc = prep_centroids(ctx))) return rc;
     for (int64_t off = 0; off < n; off += step) {
         const int64_t m = std::min(step, n - off);
@@ -776,10 +779,11 @@ int32_t fmlk_predict_cached(fmlk_ctx *ctx, int32_t *out_labels_host) {
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
     if (ctx->n_total == 0) return FMLK_OK;
+    if (ctx->d != ctx->md) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
     if (!out_labels_host) return fail(ctx, FMLK_ERR_INVALID_ARG, "labels is null");
     if ((rc = ensure_stage(ctx, 0, (size_t)ctx->n_total))) return rc;
     LaunchCfg cfg;
-    if ((rc = choose_cfg(ctx, ctx->k, ctx->d, false, &cfg))) return rc;
+    if ((rc = choose_cfg(ctx, ctx->k, ctx->md, false, &cfg))) return rc;
     if ((rc = prep_centroids(ctx))) return rc;
     int64_t off = 0;
     for (const Chunk &ch : ctx->chunks) {
@@ -801,10 +805,9 @@ int32_t fmlk_online_round(fmlk_ctx *ctx, const double *local_batch_host, int64_t
     if (k < 1 || d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad k / d");
     if (!centroids_inout || !weights_inout) return fail(ctx, FMLK_ERR_INVALID_ARG, "model is null");
     if (n_local < 0 || (n_local > 0 && !local_batch_host)) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad batch");
-    if (ctx->n_total > 0 && ctx->d != d) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
     if ((rc = ensure_model(ctx, k, d))) return rc;
     ctx->k = k;
-    ctx->d = d;
+    ctx->md = d;
     const size_t kd = (size_t)k * d, len = kd + k;
     if ((rc = ensure_stage(ctx, (size_t)std::max<int64_t>(n_local, 1) * d, 0))) return rc;
     CK(ctx, cudaMemcpyAsync(ctx->centroids, centroids_inout, kd * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));

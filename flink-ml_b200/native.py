@@ -152,7 +152,8 @@ class Context:
         _check(lib().fmlk_create(int(device), int(rank), int(world), idbuf, int(flags), C.byref(self._h)))
         self.device, self.rank, self.world = int(device), int(rank), int(world)
         self.k = 0
-        self.d = 0
+        self.d = 0   # dimension of the cached rows
+        self.md = 0  # dimension of the model
         self._keep = []  # adopted device tensors kept alive
 
     # -- lifetime
@@ -210,6 +211,7 @@ class Context:
     def clear_points(self):
         self._ck(lib().fmlk_clear_points(self._h))
         self._keep = []
+        self.d = 0
 
     def num_points(self):
         return int(lib().fmlk_num_points(self._h))
@@ -224,10 +226,10 @@ class Context:
     def set_centroids(self, centroids):
         c = _f64_matrix(centroids)
         self._ck(lib().fmlk_set_centroids(self._h, c.ctypes.data, c.shape[0], c.shape[1]))
-        self.k, self.d = c.shape
+        self.k, self.md = c.shape
 
     def _model_out(self):
-        return np.empty((self.k, self.d), dtype=np.float64), np.empty(self.k, dtype=np.float64)
+        return np.empty((self.k, self.md), dtype=np.float64), np.empty(self.k, dtype=np.float64)
 
     def train_round(self):
         c, w = self._model_out()
@@ -243,7 +245,7 @@ class Context:
         return c, w
 
     def local_partials(self):
-        sums = np.empty((self.k, self.d), dtype=np.float64)
+        sums = np.empty((self.k, self.md), dtype=np.float64)
         counts = np.empty(self.k, dtype=np.int64)
         self._ck(lib().fmlk_local_partials(self._h, sums.ctypes.data, counts.ctypes.data))
         return sums, counts
@@ -287,7 +289,7 @@ class Context:
             raise IllegalArgumentError("Vector size mismatched.")
         self._ck(lib().fmlk_online_round(self._h, b.ctypes.data if b.shape[0] else None, b.shape[0], d, k,
                                          float(decay), c.ctypes.data, w.ctypes.data))
-        self.k, self.d = k, d
+        self.k, self.md = k, d
         return c, w
 
     # -- measurement
