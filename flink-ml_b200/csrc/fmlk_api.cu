@@ -84,7 +84,7 @@ struct Chunk {
 };
 
 struct LaunchCfg {
-    int warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid;
+    int warps, acc_warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid;
     size_t smem;
 };
 
@@ -172,12 +172,16 @@ int stride_for(int d) {
 }
 
 // Shared memory the assign kernel needs for a geometry (must mirror the carve-up in assign_kernel).
-size_t smem_bytes(int warps, int xs, int S, int k, int d, int k_pad, int nc_tile, int n_ctiles, bool sums) {
+size_t smem_bytes(int warps, int acc, int xs, int S, int k, int d, int k_pad, int nc_tile, int n_ctiles, bool sums) {
     size_t dbl = (size_t)(n_ctiles > 1 ? 2 : 1) * nc_tile * S + k_pad + (size_t)warps * xs * kWarpRows * S +
                  (sums ? (size_t)k * d : 0);
-    size_t ints = (sums ? (size_t)k : 0) + (size_t)warps * kWarpRows;
+    size_t ints = (sums ? (size_t)k : 0) + (size_t)warps * xs * kWarpRows + (size_t)warps * xs + warps +
+                  (size_t)warps * acc;
     return dbl * 8 + ints * 4;
 }
+
+// accumulator warps: one per 32 columns, at most 4 (lanes then take several columns each)
+int acc_warps_for(int d) { return std::min(4, (d + 31) / 32); }
 
 // Picks the launch geometry for (k, d).  Preference order: centroids resident in shared memory with
 // block-private sums; resident centroids with global-atomic sums; centroid tiles streamed from L2.
@@ -187,18 +191,19 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     c.ksteps = (d + 3) / 4;
     c.k_pad = (k + 7) & ~7;
     c.grid = ctx->sm_count;
+    c.acc_warps = accum ? acc_warps_for(d) : 0;
     const size_t budget = ctx->smem_optin;
-    // few centroids: HBM-bound, favour many warps with a prefetched second row tile;
-    // many centroids: FP64-bound, two warps per scheduler are enough and leave room for the model
-    static const int small_k[][2] = {{16, 2}, {16, 1}, {12, 1}, {8, 1}, {4, 1}};
-    static const int large_k[][2] = {{12, 1}, {8, 2}, {8, 1}, {4, 1}};
+    // few centroids: HBM-bound, favour a prefetched second row tile per warp;
+    // many centroids: FP64-bound, three MMA warps per scheduler with one tile each
+    static const int small_k[][2] = {{12, 2}, {12, 1}, {8, 1}, {4, 1}};
+    static const int large_k[][2] = {{12, 1}, {8, 1}, {4, 1}, {4, 1}};
     const int(*cand)[2] = (c.k_pad <= 32) ? small_k : large_k;
-    const int ncand = (c.k_pad <= 32) ? 5 : 4;
+    const int ncand = 4;
     for (int pass = 0; pass < 2; pass++) {
         const bool sums = accum && pass == 0;
         if (!accum && pass == 1) break;
         for (int i = 0; i < ncand; i++) {
-            size_t need = smem_bytes(cand[i][0], cand[i][1], c.S, k, d, c.k_pad, c.k_pad, 1, sums);
+            size_t need = smem_bytes(cand[i][0], c.acc_warps, cand[i][1], c.S, k, d, c.k_pad, c.k_pad, 1, sums);
             if (need <= budget) {
                 c.warps = cand[i][0];
                 c.xs = cand[i][1];
@@ -212,12 +217,12 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
             }
         }
     }
-    // streaming: 8 warps, one row stage, the rest of shared memory split into two centroid tiles
+    // streaming: 8 MMA warps, one row stage, the rest of shared memory split into two centroid tiles
     c.warps = 8;
     c.xs = 1;
     c.sums_in_smem = 0;
     c.n_partials = 1;
-    size_t fixed = smem_bytes(c.warps, c.xs, c.S, k, d, c.k_pad, 0, 2, false);
+    size_t fixed = smem_bytes(c.warps, c.acc_warps, c.xs, c.S, k, d, c.k_pad, 0, 2, false);
     if (fixed + 2 * 8 * (size_t)c.S * 8 > budget)
         return fail(ctx, FMLK_ERR_INVALID_ARG, "vector dimension too large for the shared-memory tiling");
     int nc = (int)((budget - fixed) / (2 * (size_t)c.S * 8));
@@ -225,7 +230,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     nc = std::min(nc, c.k_pad);
     c.nc_tile = nc;
     c.n_ctiles = (c.k_pad + nc - 1) / nc;
-    c.smem = smem_bytes(c.warps, c.xs, c.S, k, d, c.k_pad, c.nc_tile, c.n_ctiles, false);
+    c.smem = smem_bytes(c.warps, c.acc_warps, c.xs, c.S, k, d, c.k_pad, c.nc_tile, c.n_ctiles, false);
     *out = c;
     return FMLK_OK;
 }
@@ -355,6 +360,8 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.n_partials = cfg.n_partials;
     p.sums_in_smem = cfg.sums_in_smem;
     p.xs = cfg.xs;
+    p.mma_warps = cfg.warps;
+    p.acc_warps = cfg.acc_warps;
     p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
     p.recheck_count = ctx->recheck;
     const int64_t tiles = (n + kWarpRows - 1) / kWarpRows;
@@ -367,7 +374,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
         e1 = next_event(ctx);
         if (e0 && e1) cudaEventRecord(e0, ctx->stream);
     }
-    if (accum) assign_kernel<true><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
+    if (accum) assign_kernel<true><<<grid, (cfg.warps + cfg.acc_warps) * 32, cfg.smem, ctx->stream>>>(p);
     else assign_kernel<false><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
     if (prof && e0 && e1) cudaEventRecord(e1, ctx->stream);
     ctx->assign_launches++;
@@ -1020,9 +1027,10 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
     int rc = choose_cfg(ctx, k, d, accumulate != 0, &c);
     if (rc) return rc;
     snprintf(out, (size_t)out_len,
-             "grid=%d block=%d smem=%zu warps=%d xs=%d S=%d ksteps=%d k_pad=%d nc_tile=%d n_ctiles=%d sums_in_smem=%d "
-             "n_partials=%d",
-             c.grid, c.warps * 32, c.smem, c.warps, c.xs, c.S, c.ksteps, c.k_pad, c.nc_tile, c.n_ctiles,
+             "grid=%d block=%d smem=%zu mma_warps=%d acc_warps=%d xs=%d S=%d ksteps=%d k_pad=%d nc_tile=%d n_ctiles=%d "
+             "sums_in_smem=%d n_partials=%d",
+             c.grid, (c.warps + c.acc_warps) * 32, c.smem, c.warps, c.acc_warps, c.xs, c.S, c.ksteps, c.k_pad,
+             c.nc_tile, c.n_ctiles,
              c.sums_in_smem, c.n_partials);
     return FMLK_OK;
 }

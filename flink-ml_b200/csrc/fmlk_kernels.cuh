@@ -51,7 +51,9 @@ struct AssignParams {
     double *partials; // [n_partials][k*d + k], or null: no accumulation (predict)
     int32_t n_partials;
     int32_t sums_in_smem;
-    int32_t xs;       // row-tile stages per warp (1 or 2; 2 only when n_ctiles == 1)
+    int32_t xs;       // row-tile stages per MMA warp (1 or 2; 2 only when n_ctiles == 1)
+    int32_t mma_warps; // warps that load + multiply + label
+    int32_t acc_warps; // warps that own columns of the sums (accumulate launches only)
     int32_t fma_mode; // exact path follows the JDK>=11 netlib variant
     unsigned long long *recheck_count;
 };
@@ -170,15 +172,14 @@ struct Top2 {
     int idx;
 };
 
+// Branch-free update with explicit compares: a NaN score (NaN centroid, NaN row) never wins and
+// never becomes the runner-up, as in the Java scan.
 __device__ __forceinline__ void top2_push(Top2 &t, double v, int col) {
-    // explicit compares: a NaN score (NaN centroid, NaN row) never wins, as in the Java scan
-    if (v > t.best) {
-        t.second = t.best;
-        t.best = v;
-        t.idx = col;
-    } else if (v > t.second) {
-        t.second = v;
-    }
+    const bool gt = v > t.best;
+    const bool gs = v > t.second;
+    t.second = gt ? t.best : (gs ? v : t.second);
+    t.idx = gt ? col : t.idx;
+    t.best = gt ? v : t.best;
 }
 
 __device__ __forceinline__ void top2_merge_xor(Top2 &t, int off) {
@@ -193,33 +194,58 @@ __device__ __forceinline__ void top2_merge_xor(Top2 &t, int off) {
     t.second = fmax(fmax(t.second, os), loser);
 }
 
-// Copies `rows` rows of d doubles (contiguous in global memory) into shared rows of stride S.
-// All 32 lanes take part.  vec16: d even and the source 16-byte aligned.
-__device__ __forceinline__ void warp_load_rows(double *dst, const double *src, int rows, int d, int S,
-                                               int lane, bool vec16) {
+// Copies `rows` rows of d doubles (contiguous in global memory) into shared rows of stride S, by
+// `nthreads` cooperating threads of which this is number `tid`.  vec16: d even, source 16-byte aligned.
+__device__ __forceinline__ void load_rows_async(double *dst, const double *src, int rows, int d, int S, int tid,
+                                                int nthreads, bool vec16) {
     if (vec16) {
         const int cpr = d >> 1; // 16-byte chunks per row
-        const int total = rows * cpr;
-        for (int i = lane; i < total; i += 32) {
-            const int r = i / cpr, q = i - r * cpr;
-            cp_async16(dst + (size_t)r * S + 2 * q, src + (size_t)r * d + 2 * q);
+        if (cpr >= nthreads / 2) {
+            for (int r = 0; r < rows; r++)
+                for (int q = tid; q < cpr; q += nthreads) cp_async16(dst + (size_t)r * S + 2 * q, src + (size_t)r * d + 2 * q);
+        } else {
+            const int total = rows * cpr;
+            for (int i = tid; i < total; i += nthreads) {
+                const int r = i / cpr, q = i - r * cpr;
+                cp_async16(dst + (size_t)r * S + 2 * q, src + (size_t)r * d + 2 * q);
+            }
         }
     } else {
         const int total = rows * d;
-        for (int i = lane; i < total; i += 32) {
+        for (int i = tid; i < total; i += nthreads) {
             const int r = i / d, q = i - r * d;
             cp_async8(dst + (size_t)r * S + q, src + (size_t)r * d + q);
         }
     }
 }
 
+// release / acquire on shared-memory counters: the hand-off between the MMA warps and the
+// accumulator warps
+__device__ __forceinline__ void st_release_smem(int *p, int v) {
+    unsigned a = (unsigned)__cvta_generic_to_shared(p);
+    asm volatile("st.release.cta.shared.b32 [%0], %1;\n" ::"r"(a), "r"(v) : "memory");
+}
+__device__ __forceinline__ int ld_acquire_smem(const int *p) {
+    unsigned a = (unsigned)__cvta_generic_to_shared(p);
+    int v;
+    asm volatile("ld.acquire.cta.shared.b32 %0, [%1];\n" : "=r"(v) : "r"(a) : "memory");
+    return v;
+}
+__device__ __forceinline__ void spin_until_at_least(const int *p, int target) {
+    while (ld_acquire_smem(p) < target) __nanosleep(40);
+}
+__device__ __forceinline__ void mma_group_barrier(int nthreads) {
+    asm volatile("bar.sync 1, %0;\n" ::"r"(nthreads) : "memory");
+}
+
 // One accumulator chunk of a warp tile: 16 rows x (cnt <= 8) n8 tiles over the whole d.
 // xa0/xa1: this lane's A-fragment addresses for rows frow and frow+8; cb: its B-fragment
 // address in the first n8 tile; hcol: &h[first column this lane owns]; col0: that column.
-template <bool FULL>
+// NSQ: also accumulate |x|^2 of the lane's fragment elements (first chunk of a tile only).
+template <bool FULL, bool NSQ>
 __device__ __forceinline__ void mma_chunk(const double *xa0, const double *xa1, const double *cb, int S,
                                           int ksteps, int cnt, const double *hcol, int col0, Top2 &t0,
-                                          Top2 &t1) {
+                                          Top2 &t1, double &nsq0, double &nsq1) {
     double acc0[kChunkTiles][2], acc1[kChunkTiles][2];
 #pragma unroll
     for (int j = 0; j < kChunkTiles; j++) {
@@ -236,6 +262,10 @@ __device__ __forceinline__ void mma_chunk(const double *xa0, const double *xa1, 
 #pragma unroll 2
     for (int ks = 0; ks < ksteps; ks++) {
         const double a0 = xa0[ks * 4], a1 = xa1[ks * 4];
+        if (NSQ) {
+            nsq0 = fma(a0, a0, nsq0);
+            nsq1 = fma(a1, a1, nsq1);
+        }
 #pragma unroll
         for (int j = 0; j < kChunkTiles; j++) {
             if (FULL || j < cnt) {
@@ -257,269 +287,290 @@ __device__ __forceinline__ void mma_chunk(const double *xa0, const double *xa1, 
     }
 }
 
+// The assign (+ accumulate) kernel.  One persistent CTA per SM with two kinds of warps:
+//
+//   MMA warps (warp < mma_warps): each owns 16-row tiles gw, gw + GW, ...; copies a tile into
+//     its shared-memory buffer (cp.async), multiplies it against all centroids on the FP64 tensor
+//     cores keeping (best, second, index) per row, replays near-tie rows exactly, writes the
+//     labels and publishes the tile;
+//   accumulator warps (ACCUM only): each lane owns columns of the per-cluster sums; they consume
+//     the published tiles in the fixed order (round, warp) and do sums[label][c] += x[r][c] with
+//     plain loads and stores -- no atomics, and the same order of additions every run.
+//
+// Centroids are resident in shared memory when they fit (n_ctiles == 1); otherwise the MMA warps
+// stream centroid tiles from L2 through two buffers, in lock-step (named barrier 1).
 template <bool ACCUM>
 __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
-    const int nwarps = blockDim.x >> 5;
+    const int W = p.mma_warps;
+    const int A = ACCUM ? p.acc_warps : 0;
     const int S = p.S;
+    const int xs = p.xs;
     const int c_bufs = p.n_ctiles > 1 ? 2 : 1;
     const size_t ctile_elems = (size_t)p.nc_tile * S;
     const size_t xtile_elems = (size_t)kWarpRows * S;
+    const bool sums_smem = ACCUM && p.sums_in_smem;
 
     double *Cs = reinterpret_cast<double *>(smem_raw);
     double *hs = Cs + c_bufs * ctile_elems;
     double *Xall = hs + p.k_pad;
-    double *Xw = Xall + (size_t)warp * p.xs * xtile_elems;
-    double *sums_s = Xall + (size_t)nwarps * p.xs * xtile_elems;
-    const size_t sums_elems = (ACCUM && p.sums_in_smem) ? (size_t)p.k * p.d : 0;
+    double *sums_s = Xall + (size_t)W * xs * xtile_elems;
+    const size_t sums_elems = sums_smem ? (size_t)p.k * p.d : 0;
     int *counts_s = reinterpret_cast<int *>(sums_s + sums_elems);
-    int *lab_s = counts_s + ((ACCUM && p.sums_in_smem) ? p.k : 0) + warp * kWarpRows;
-
-    const bool vec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.x) & 15) == 0);
-    const bool cvec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15) == 0);
+    int *lab_all = counts_s + (sums_smem ? p.k : 0); // [W * xs][16]
+    int *rows_all = lab_all + W * xs * kWarpRows;    // [W * xs]
+    int *seq_ready = rows_all + W * xs;              // [W]
+    int *seq_done = seq_ready + W;                   // [W * A]
 
     // ---- one-time set-up: zero everything (pad columns and pad rows must read as 0) ----
     {
-        const size_t zero_elems = c_bufs * ctile_elems + p.k_pad + (size_t)nwarps * p.xs * xtile_elems + sums_elems;
+        const size_t zero_elems = c_bufs * ctile_elems + p.k_pad + (size_t)W * xs * xtile_elems + sums_elems;
         for (size_t i = threadIdx.x; i < zero_elems; i += blockDim.x) Cs[i] = 0.0;
-        if (ACCUM && p.sums_in_smem)
-            for (int i = threadIdx.x; i < p.k; i += blockDim.x) counts_s[i] = 0;
+        const int zero_ints = (sums_smem ? p.k : 0) + W * xs * kWarpRows + W * xs + W + W * A;
+        for (int i = threadIdx.x; i < zero_ints; i += blockDim.x) counts_s[i] = 0;
     }
     __syncthreads();
+    const bool cvec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15) == 0);
     for (int i = threadIdx.x; i < p.k_pad; i += blockDim.x) hs[i] = p.h[i];
     if (p.n_ctiles == 1) {
         // resident centroids: k rows of d doubles, rows k..nc_tile-1 stay zero (their h is +inf)
-        if (cvec16) {
-            const int cpr = p.d >> 1, total = p.k * cpr;
-            for (int i = threadIdx.x; i < total; i += blockDim.x) {
-                const int r = i / cpr, q = i - r * cpr;
-                cp_async16(Cs + (size_t)r * S + 2 * q, p.c + (size_t)r * p.d + 2 * q);
-            }
-        } else {
-            const int total = p.k * p.d;
-            for (int i = threadIdx.x; i < total; i += blockDim.x) {
-                const int r = i / p.d, q = i - r * p.d;
-                cp_async8(Cs + (size_t)r * S + q, p.c + (size_t)r * p.d + q);
-            }
-        }
+        load_rows_async(Cs, p.c, p.k, p.d, S, threadIdx.x, blockDim.x, cvec16);
         cp_async_commit();
         cp_async_wait<0>();
     }
     __syncthreads();
 
-    const double cmax2 = *p.cmax2;
     const int64_t total_tiles = (p.n + kWarpRows - 1) / kWarpRows;
-    const int64_t gw = (int64_t)blockIdx.x * nwarps + warp;
-    const int64_t GW = (int64_t)gridDim.x * nwarps;
+    const int64_t GW = (int64_t)gridDim.x * W;
     const int64_t rounds = (total_tiles + GW - 1) / GW;
-    const int frow = lane >> 2; // fragment row / B-fragment column within an 8-tile
-    const int fk = lane & 3;    // fragment k index
-    unsigned long long local_rechecks = 0;
 
-    // streaming mode bookkeeping: which buffer holds the C tile of the current step
-    int cbuf = 0;
-    if (p.n_ctiles > 1) {
-        // prefetch C tile 0 into buffer 0
-        const int rows0 = min(p.nc_tile, p.k);
-        const int cpr = cvec16 ? (p.d >> 1) : p.d;
-        const int total = rows0 * cpr;
-        for (int i = threadIdx.x; i < total; i += blockDim.x) {
-            const int r = i / cpr, q = i - r * cpr;
-            if (cvec16) cp_async16(Cs + (size_t)r * S + 2 * q, p.c + (size_t)r * p.d + 2 * q);
-            else cp_async8(Cs + (size_t)r * S + q, p.c + (size_t)r * p.d + q);
+    if (warp < W) {
+        // =============================== MMA warp ===============================
+        const bool vec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.x) & 15) == 0);
+        const double cmax2 = *p.cmax2;
+        const int64_t gw = (int64_t)blockIdx.x * W + warp;
+        const int frow = lane >> 2; // fragment row / B-fragment column within an 8-tile
+        const int fk = lane & 3;    // fragment k index
+        const int mma_threads = W * 32;
+        double *Xw = Xall + (size_t)warp * xs * xtile_elems;
+        unsigned long long local_rechecks = 0;
+        int cbuf = 0;
+
+        if (p.n_ctiles > 1) {
+            // prefetch centroid tile 0 into buffer 0 (rows past k stay zero)
+            load_rows_async(Cs, p.c, min(p.nc_tile, p.k), p.d, S, threadIdx.x, mma_threads, cvec16);
+            cp_async_commit();
         }
-        cp_async_commit();
-    }
-
-    // resident mode with two stages: start the first tile's load
-    if (p.xs == 2 && gw < total_tiles) {
-        const int64_t row0 = gw * kWarpRows;
-        const int rows = (int)min((int64_t)kWarpRows, p.n - row0);
-        warp_load_rows(Xw, p.x + row0 * p.d, rows, p.d, S, lane, vec16);
-    }
-    if (p.xs == 2) cp_async_commit();
-
-    for (int64_t it = 0; it < rounds; it++) {
-        const int64_t tile = it * GW + gw;
-        const bool active = tile < total_tiles;
-        const int64_t row0 = tile * kWarpRows;
-        const int rows_valid = active ? (int)min((int64_t)kWarpRows, p.n - row0) : 0;
-        double *Xt = Xw + (p.xs == 2 ? (size_t)(it & 1) * xtile_elems : 0);
-
-        if (p.xs == 2) {
-            // prefetch the next round's tile into the other stage, then wait for this one
-            const int64_t ntile = tile + GW;
-            if (ntile < total_tiles) {
-                const int64_t nrow0 = ntile * kWarpRows;
-                const int nrows = (int)min((int64_t)kWarpRows, p.n - nrow0);
-                warp_load_rows(Xw + (size_t)((it + 1) & 1) * xtile_elems, p.x + nrow0 * p.d, nrows, p.d, S, lane,
-                               vec16);
+        if (xs == 2) {
+            if (gw < total_tiles) {
+                const int64_t row0 = gw * kWarpRows;
+                load_rows_async(Xw, p.x + row0 * p.d, (int)min((int64_t)kWarpRows, p.n - row0), p.d, S, lane, 32,
+                                vec16);
             }
             cp_async_commit();
-            cp_async_wait<1>();
-            __syncwarp();
-        } else {
-            if (active) warp_load_rows(Xt, p.x + row0 * p.d, rows_valid, p.d, S, lane, vec16);
-            cp_async_commit();
-            if (p.n_ctiles == 1) {
-                cp_async_wait<0>();
-                __syncwarp();
-            }
         }
 
-        Top2 t0 = {-INFINITY, -INFINITY, 0}, t1 = {-INFINITY, -INFINITY, 0};
-        double nsq0 = 0.0, nsq1 = 0.0;
+        for (int64_t it = 0; it < rounds; it++) {
+            const int64_t tile = it * GW + gw;
+            const bool active = tile < total_tiles;
+            const int64_t row0 = tile * kWarpRows;
+            const int rows_valid = active ? (int)min((int64_t)kWarpRows, p.n - row0) : 0;
+            const int stage = (xs == 2) ? (int)(it & 1) : 0;
+            double *Xt = Xw + (size_t)stage * xtile_elems;
+            int *lab_s = lab_all + (warp * xs + stage) * kWarpRows;
 
-        for (int ct = 0; ct < p.n_ctiles; ct++) {
-            const double *Ct = Cs + (size_t)cbuf * ctile_elems;
-            const int ct_base = ct * p.nc_tile; // first centroid of this tile
-            if (p.n_ctiles > 1) {
-                // my copies of this step's tile (and my row tile) have landed; after the barrier so
-                // have everyone's, and everyone is done reading the other buffer.
-                cp_async_wait<0>();
-                __syncthreads();
-                // prefetch the next step's C tile into the other buffer
-                int nct = ct + 1;
-                bool more = true;
-                if (nct == p.n_ctiles) {
-                    nct = 0;
-                    more = (it + 1 < rounds);
+            // the buffer about to be overwritten was last used by tile it-1: wait until the
+            // accumulator warps have consumed it
+            if (ACCUM && it >= 1)
+                for (int a = 0; a < A; a++) spin_until_at_least(&seq_done[warp * A + a], (int)it);
+
+            if (xs == 2) {
+                const int64_t ntile = tile + GW;
+                if (ntile < total_tiles) {
+                    const int64_t nrow0 = ntile * kWarpRows;
+                    load_rows_async(Xw + (size_t)(stage ^ 1) * xtile_elems, p.x + nrow0 * p.d,
+                                    (int)min((int64_t)kWarpRows, p.n - nrow0), p.d, S, lane, 32, vec16);
                 }
-                if (more) {
-                    const int nbase = nct * p.nc_tile;
-                    const int nrows = min(p.nc_tile, p.k - nbase);
-                    double *dstb = Cs + (size_t)(cbuf ^ 1) * ctile_elems;
-                    const int cpr = cvec16 ? (p.d >> 1) : p.d;
-                    const int total = p.nc_tile * cpr;
-                    for (int i = threadIdx.x; i < total; i += blockDim.x) {
-                        const int r = i / cpr, q = i - r * cpr;
-                        if (r < nrows) {
-                            if (cvec16)
-                                cp_async16(dstb + (size_t)r * S + 2 * q, p.c + (size_t)(nbase + r) * p.d + 2 * q);
-                            else
-                                cp_async8(dstb + (size_t)r * S + q, p.c + (size_t)(nbase + r) * p.d + q);
+                cp_async_commit();
+                cp_async_wait<1>();
+                __syncwarp();
+            } else {
+                if (active) load_rows_async(Xt, p.x + row0 * p.d, rows_valid, p.d, S, lane, 32, vec16);
+                cp_async_commit();
+                if (p.n_ctiles == 1) {
+                    cp_async_wait<0>();
+                    __syncwarp();
+                }
+            }
+
+            Top2 t0 = {-INFINITY, -INFINITY, 0}, t1 = {-INFINITY, -INFINITY, 0};
+            double nsq0 = 0.0, nsq1 = 0.0;
+
+            for (int ct = 0; ct < p.n_ctiles; ct++) {
+                const double *Ct = Cs + (size_t)cbuf * ctile_elems;
+                const int ct_base = ct * p.nc_tile; // first centroid of this tile
+                if (p.n_ctiles > 1) {
+                    // my copies of this step's tile (and my row tile) have landed; after the barrier so
+                    // have everyone's, and every MMA warp is done reading the other buffer
+                    cp_async_wait<0>();
+                    mma_group_barrier(mma_threads);
+                    int nct = ct + 1;
+                    bool more = true;
+                    if (nct == p.n_ctiles) {
+                        nct = 0;
+                        more = (it + 1 < rounds);
+                    }
+                    if (more) {
+                        const int nbase = nct * p.nc_tile;
+                        const int nrows = min(p.nc_tile, p.k - nbase);
+                        double *dstb = Cs + (size_t)(cbuf ^ 1) * ctile_elems;
+                        load_rows_async(dstb, p.c + (size_t)nbase * p.d, nrows, p.d, S, threadIdx.x, mma_threads,
+                                        cvec16);
+                        // rows past k in the last tile read as zero (their h is +inf)
+                        for (int i = nrows * p.d + threadIdx.x; i < p.nc_tile * p.d; i += mma_threads) {
+                            const int r = i / p.d, q = i - r * p.d;
+                            dstb[(size_t)r * S + q] = 0.0;
+                        }
+                    }
+                    cp_async_commit();
+                }
+
+                if (active) {
+                    const double *xa0 = Xt + (size_t)frow * S + fk;
+                    const double *xa1 = xa0 + (size_t)8 * S;
+                    const int tiles_here = (min(p.nc_tile, p.k_pad - ct_base)) >> 3; // n8 tiles in this C tile
+                    for (int ch = 0; ch < tiles_here; ch += kChunkTiles) {
+                        const int cnt = min(kChunkTiles, tiles_here - ch);
+                        const double *cb = Ct + (size_t)(ch * 8 + frow) * S + fk;
+                        const int col0 = ct_base + ch * 8 + fk * 2;
+                        const bool first = (ct == 0 && ch == 0); // |x|^2 rides along with the first chunk
+                        if (cnt == kChunkTiles) {
+                            if (first) mma_chunk<true, true>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1);
+                            else mma_chunk<true, false>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1);
                         } else {
-                            // rows past k in the last tile: zero (their h is +inf)
-                            if (cvec16) {
-                                dstb[(size_t)r * S + 2 * q] = 0.0;
-                                dstb[(size_t)r * S + 2 * q + 1] = 0.0;
-                            } else {
-                                dstb[(size_t)r * S + q] = 0.0;
-                            }
+                            if (first) mma_chunk<false, true>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1);
+                            else mma_chunk<false, false>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1);
                         }
                     }
                 }
-                cp_async_commit();
+                if (p.n_ctiles > 1) cbuf ^= 1;
             }
 
             if (active) {
-                const double *xa0 = Xt + (size_t)frow * S + fk;
-                const double *xa1 = xa0 + (size_t)8 * S;
-                if (ct == 0) {
-                    // |x|^2 of the two rows this quad owns (any order: only feeds the threshold)
-                    for (int ks = 0; ks < p.ksteps; ks++) {
-                        const double a0 = xa0[ks * 4], a1 = xa1[ks * 4];
-                        nsq0 = fma(a0, a0, nsq0);
-                        nsq1 = fma(a1, a1, nsq1);
-                    }
-                }
-                const int tiles_here = (min(p.nc_tile, p.k_pad - ct_base)) >> 3; // n8 tiles in this C tile
-                for (int ch = 0; ch < tiles_here; ch += kChunkTiles) {
-                    const int cnt = min(kChunkTiles, tiles_here - ch);
-                    const double *cb = Ct + (size_t)(ch * 8 + frow) * S + fk;
-                    const int col0 = ct_base + ch * 8 + fk * 2;
-                    if (cnt == kChunkTiles) mma_chunk<true>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1);
-                    else mma_chunk<false>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1);
-                }
-            }
-            if (p.n_ctiles > 1) cbuf ^= 1;
-        }
+                // combine the four lanes of each quad (same rows, different columns)
+                top2_merge_xor(t0, 1);
+                top2_merge_xor(t0, 2);
+                top2_merge_xor(t1, 1);
+                top2_merge_xor(t1, 2);
+                nsq0 += __shfl_xor_sync(0xffffffffu, nsq0, 1);
+                nsq0 += __shfl_xor_sync(0xffffffffu, nsq0, 2);
+                nsq1 += __shfl_xor_sync(0xffffffffu, nsq1, 1);
+                nsq1 += __shfl_xor_sync(0xffffffffu, nsq1, 2);
 
-        if (active) {
-            // combine the four lanes of each quad (same rows, different columns)
-            top2_merge_xor(t0, 1);
-            top2_merge_xor(t0, 2);
-            top2_merge_xor(t1, 1);
-            top2_merge_xor(t1, 2);
-            nsq0 += __shfl_xor_sync(0xffffffffu, nsq0, 1);
-            nsq0 += __shfl_xor_sync(0xffffffffu, nsq0, 2);
-            nsq1 += __shfl_xor_sync(0xffffffffu, nsq1, 1);
-            nsq1 += __shfl_xor_sync(0xffffffffu, nsq1, 2);
-
-            // decision margin in squared-distance units: D = |x|^2 - 2 v
-            const bool ok0 = 2.0 * (t0.best - t0.second) > p.thr_coef * (nsq0 + cmax2);
-            const bool ok1 = 2.0 * (t1.best - t1.second) > p.thr_coef * (nsq1 + cmax2);
-            const bool flag0 = !ok0 && (frow < rows_valid);
-            const bool flag1 = !ok1 && (frow + 8 < rows_valid);
-            if (fk == 0) {
-                lab_s[frow] = t0.idx;
-                lab_s[frow + 8] = t1.idx;
-            }
-            // bit r of `flagged`: row r of the tile needs the exact replay
-            unsigned f0 = __ballot_sync(0xffffffffu, flag0 && fk == 0);
-            unsigned f1 = __ballot_sync(0xffffffffu, flag1 && fk == 0);
-            unsigned flagged = 0;
+                // decision margin in squared-distance units: D = |x|^2 - 2 v
+                const bool ok0 = 2.0 * (t0.best - t0.second) > p.thr_coef * (nsq0 + cmax2);
+                const bool ok1 = 2.0 * (t1.best - t1.second) > p.thr_coef * (nsq1 + cmax2);
+                const bool flag0 = !ok0 && (frow < rows_valid);
+                const bool flag1 = !ok1 && (frow + 8 < rows_valid);
+                if (fk == 0) {
+                    lab_s[frow] = t0.idx;
+                    lab_s[frow + 8] = t1.idx;
+                }
+                // bit r of `flagged`: row r of the tile needs the exact replay
+                const unsigned f0 = __ballot_sync(0xffffffffu, flag0 && fk == 0);
+                const unsigned f1 = __ballot_sync(0xffffffffu, flag1 && fk == 0);
+                unsigned flagged = 0;
 #pragma unroll
-            for (int r = 0; r < 8; r++) {
-                flagged |= ((f0 >> (4 * r)) & 1u) << r;
-                flagged |= ((f1 >> (4 * r)) & 1u) << (r + 8);
-            }
-            __syncwarp();
-            while (flagged) {
-                const int r = __ffs(flagged) - 1;
-                flagged &= flagged - 1;
-                const int lab = exact_find_closest(Xt + (size_t)r * S, p.c, p.cn, p.k, p.d, p.fma_mode);
-                if (lane == 0) {
-                    lab_s[r] = lab;
-                    local_rechecks++;
+                for (int r = 0; r < 8; r++) {
+                    flagged |= ((f0 >> (4 * r)) & 1u) << r;
+                    flagged |= ((f1 >> (4 * r)) & 1u) << (r + 8);
                 }
-            }
-            __syncwarp();
-
-            if (p.labels != nullptr && lane < rows_valid) p.labels[row0 + lane] = lab_s[lane];
-
-            if (ACCUM) {
-                // sums[label] += row, counts[label]++ (KMeans.java:293-294), rows of one label first
-                // added together in registers so each (label, column) costs one atomic per tile
-                const int my_lab = (lane < rows_valid) ? lab_s[lane] : -1;
-                unsigned pending = (rows_valid >= 32) ? 0xffffffffu : ((1u << rows_valid) - 1u);
-                while (pending) {
-                    const int r0 = __ffs(pending) - 1;
-                    const int L = __shfl_sync(0xffffffffu, my_lab, r0);
-                    const unsigned grp = __ballot_sync(0xffffffffu, my_lab == L) & pending;
-                    pending &= ~grp;
-                    for (int c = lane; c < p.d; c += 32) {
-                        double a = 0.0;
-                        unsigned g = grp;
-                        while (g) {
-                            const int r = __ffs(g) - 1;
-                            g &= g - 1;
-                            a += Xt[(size_t)r * S + c];
-                        }
-                        if (p.sums_in_smem) atomicAdd(&sums_s[(size_t)L * p.d + c], a);
-                        else atomicAdd(&p.partials[(size_t)L * p.d + c], a);
-                    }
+                __syncwarp();
+                while (flagged) {
+                    const int r = __ffs(flagged) - 1;
+                    flagged &= flagged - 1;
+                    const int lab = exact_find_closest(Xt + (size_t)r * S, p.c, p.cn, p.k, p.d, p.fma_mode);
                     if (lane == 0) {
-                        if (p.sums_in_smem) atomicAdd(&counts_s[L], __popc(grp));
-                        else atomicAdd(&p.partials[(size_t)p.k * p.d + L], (double)__popc(grp));
+                        lab_s[r] = lab;
+                        local_rechecks++;
                     }
                 }
+                __syncwarp();
+                if (p.labels != nullptr && lane < rows_valid) p.labels[row0 + lane] = lab_s[lane];
             }
-            __syncwarp(); // the tile buffer and lab_s are reused next round
+            if (ACCUM) {
+                // publish the tile (labels + rows) to the accumulator warps
+                __syncwarp();
+                if (lane == 0) {
+                    rows_all[warp * xs + stage] = rows_valid;
+                    st_release_smem(&seq_ready[warp], (int)it + 1);
+                }
+            } else {
+                __syncwarp(); // the tile buffer and lab_s are reused next round
+            }
+        }
+        cp_async_wait<0>();
+        if (lane == 0 && local_rechecks && p.recheck_count) atomicAdd(p.recheck_count, local_rechecks);
+    } else if (ACCUM) {
+        // =========================== accumulator warp ===========================
+        // sums[label] += row, counts[label]++ (KMeans.java:293-294).  Lane l of accumulator a owns
+        // columns a*32 + l, + 32*A, ...: no two threads ever touch the same cell.
+        const int a = warp - W;
+        const int cstride = 32 * A;
+        const int c0 = a * 32 + lane;
+        for (int64_t it = 0; it < rounds; it++) {
+            const int stage = (xs == 2) ? (int)(it & 1) : 0;
+            for (int w = 0; w < W; w++) {
+                spin_until_at_least(&seq_ready[w], (int)it + 1);
+                const int rows = rows_all[w * xs + stage];
+                const double *Xt = Xall + (size_t)(w * xs + stage) * xtile_elems;
+                const int *lab = lab_all + (w * xs + stage) * kWarpRows;
+                if (rows > 0) {
+                    if (sums_smem) {
+                        for (int c = c0; c < p.d; c += cstride) {
+                            int r = 0;
+                            for (; r + 1 < rows; r += 2) {
+                                const int L0 = lab[r], L1 = lab[r + 1];
+                                const double x0 = Xt[(size_t)r * S + c], x1 = Xt[(size_t)(r + 1) * S + c];
+                                double *s0 = sums_s + (size_t)L0 * p.d + c;
+                                if (L0 != L1) { // independent cells: both read-modify-writes in flight
+                                    double *s1 = sums_s + (size_t)L1 * p.d + c;
+                                    const double v0 = *s0, v1 = *s1;
+                                    *s0 = v0 + x0;
+                                    *s1 = v1 + x1;
+                                } else {
+                                    *s0 = (*s0 + x0) + x1;
+                                }
+                            }
+                            if (r < rows) {
+                                double *s0 = sums_s + (size_t)lab[r] * p.d + c;
+                                *s0 = *s0 + Xt[(size_t)r * S + c];
+                            }
+                        }
+                        if (a == 0 && lane < rows) atomicAdd(&counts_s[lab[lane]], 1);
+                    } else {
+                        // sums too large for shared memory: one global accumulator (L2 atomics)
+                        for (int c = c0; c < p.d; c += cstride)
+                            for (int r = 0; r < rows; r++)
+                                atomicAdd(&p.partials[(size_t)lab[r] * p.d + c], Xt[(size_t)r * S + c]);
+                        if (a == 0 && lane < rows) atomicAdd(&p.partials[(size_t)p.k * p.d + lab[lane]], 1.0);
+                    }
+                }
+                __syncwarp();
+                if (lane == 0) st_release_smem(&seq_done[w * A + a], (int)it + 1);
+            }
         }
     }
-    cp_async_wait<0>();
 
-    if (ACCUM && p.sums_in_smem) {
+    if (sums_smem) {
         // this CTA's partial, added to its own slot (plain read-modify-write: slot b belongs to CTA b)
         __syncthreads();
         double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
         for (int i = threadIdx.x; i < p.k * p.d; i += blockDim.x) slot[i] += sums_s[i];
         for (int i = threadIdx.x; i < p.k; i += blockDim.x) slot[(size_t)p.k * p.d + i] += (double)counts_s[i];
     }
-    if (lane == 0 && local_rechecks && p.recheck_count) atomicAdd(p.recheck_count, local_rechecks);
 }
 
 // ------------------------------------------------------------------------------------------
