@@ -174,8 +174,8 @@ int stride_for(int d) {
 // Shared memory the assign kernel needs for a geometry (must mirror the carve-up in assign_kernel).
 size_t smem_bytes(int warps, int acc, int xs, int S, int k, int d, int k_pad, int nc_tile, int n_ctiles, bool sums) {
     size_t dbl = (size_t)(n_ctiles > 1 ? 2 : 1) * nc_tile * S + k_pad + (size_t)warps * xs * kWarpRows * S +
-                 (sums ? (size_t)k * d : 0);
-    size_t ints = (sums ? (size_t)k : 0) + (size_t)warps * xs * kWarpRows + (size_t)warps * xs + warps +
+                 (sums ? (((size_t)(k + 1) * d + 1) & ~(size_t)1) : 0);
+    size_t ints = (sums ? (size_t)k : 0) + 2 * (size_t)warps * xs * kWarpRows + (size_t)warps * xs + warps +
                   (size_t)warps * acc;
     return dbl * 8 + ints * 4;
 }

@@ -134,7 +134,7 @@ __device__ __forceinline__ double ref_dist2(double pn, double cn, double dot) {
 // strict <, first index wins) is then replayed in index order over each group of 32.  A group
 // in which no distance is below the running best cannot change it and is skipped.
 // x: the row (shared or global memory), c/cn: global.  All lanes return the label.
-__device__ int exact_find_closest(const double *x, const double *c, const double *cn, int k, int d,
+__device__ __noinline__ int exact_find_closest(const double *x, const double *c, const double *cn, int k, int d,
                                   int fma_mode) {
     const int lane = threadIdx.x & 31;
     const double pn = sqrt(ref_sumsq(x, d, fma_mode)); // correctly rounded, as Math.sqrt
@@ -196,7 +196,7 @@ __device__ __forceinline__ void top2_merge_xor(Top2 &t, int off) {
 
 // Copies `rows` rows of d doubles (contiguous in global memory) into shared rows of stride S, by
 // `nthreads` cooperating threads of which this is number `tid`.  vec16: d even, source 16-byte aligned.
-__device__ __forceinline__ void load_rows_async(double *dst, const double *src, int rows, int d, int S, int tid,
+__device__ __noinline__ void load_rows_async(double *dst, const double *src, int rows, int d, int S, int tid,
                                                 int nthreads, bool vec16) {
     if (vec16) {
         const int cpr = d >> 1; // 16-byte chunks per row
@@ -241,11 +241,11 @@ __device__ __forceinline__ void mma_group_barrier(int nthreads) {
 // One accumulator chunk of a warp tile: 16 rows x (cnt <= 8) n8 tiles over the whole d.
 // xa0/xa1: this lane's A-fragment addresses for rows frow and frow+8; cb: its B-fragment
 // address in the first n8 tile; hcol: &h[first column this lane owns]; col0: that column.
-// NSQ: also accumulate |x|^2 of the lane's fragment elements (first chunk of a tile only).
-template <bool FULL, bool NSQ>
+// with_nsq (warp-uniform): also accumulate |x|^2 of the lane's fragment elements (first chunk of a tile).
+template <bool FULL>
 __device__ __forceinline__ void mma_chunk(const double *xa0, const double *xa1, const double *cb, int S,
-                                          int ksteps, int cnt, const double *hcol, int col0, Top2 &t0,
-                                          Top2 &t1, double &nsq0, double &nsq1) {
+                                       int ksteps, int cnt, const double *hcol, int col0, Top2 &t0,
+                                       Top2 &t1, double &nsq0, double &nsq1, bool with_nsq) {
     double acc0[kChunkTiles][2], acc1[kChunkTiles][2];
 #pragma unroll
     for (int j = 0; j < kChunkTiles; j++) {
@@ -262,7 +262,7 @@ __device__ __forceinline__ void mma_chunk(const double *xa0, const double *xa1, 
 #pragma unroll 2
     for (int ks = 0; ks < ksteps; ks++) {
         const double a0 = xa0[ks * 4], a1 = xa1[ks * 4];
-        if (NSQ) {
+        if (with_nsq) {
             nsq0 = fma(a0, a0, nsq0);
             nsq1 = fma(a1, a1, nsq1);
         }
@@ -317,19 +317,21 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
     double *hs = Cs + c_bufs * ctile_elems;
     double *Xall = hs + p.k_pad;
     double *sums_s = Xall + (size_t)W * xs * xtile_elems;
-    const size_t sums_elems = sums_smem ? (size_t)p.k * p.d : 0;
-    int *counts_s = reinterpret_cast<int *>(sums_s + sums_elems);
-    int *lab_all = counts_s + (sums_smem ? p.k : 0); // [W * xs][16]
-    int *rows_all = lab_all + W * xs * kWarpRows;    // [W * xs]
-    int *seq_ready = rows_all + W * xs;              // [W]
-    int *seq_done = seq_ready + W;                   // [W * A]
+    // k rows of sums plus one scratch row that absorbs the updates of rows handled in pass 2
+    const size_t sums_elems = sums_smem ? (((size_t)(p.k + 1) * p.d + 1) & ~(size_t)1) : 0; // even: keeps off_all 16-byte aligned
+    int *off_all = reinterpret_cast<int *>(sums_s + sums_elems); // [W * xs][16], 16-byte aligned
+    int *lab_all = off_all + W * xs * kWarpRows;                 // [W * xs][16]
+    int *counts_s = lab_all + W * xs * kWarpRows;                // [k] when the sums are in shared memory
+    int *rows_all = counts_s + (sums_smem ? p.k : 0);            // [W * xs]
+    int *seq_ready = rows_all + W * xs;                          // [W]
+    int *seq_done = seq_ready + W;                               // [W * A]
 
     // ---- one-time set-up: zero everything (pad columns and pad rows must read as 0) ----
     {
         const size_t zero_elems = c_bufs * ctile_elems + p.k_pad + (size_t)W * xs * xtile_elems + sums_elems;
         for (size_t i = threadIdx.x; i < zero_elems; i += blockDim.x) Cs[i] = 0.0;
-        const int zero_ints = (sums_smem ? p.k : 0) + W * xs * kWarpRows + W * xs + W + W * A;
-        for (int i = threadIdx.x; i < zero_ints; i += blockDim.x) counts_s[i] = 0;
+        const int zero_ints = 2 * W * xs * kWarpRows + (sums_smem ? p.k : 0) + W * xs + W + W * A;
+        for (int i = threadIdx.x; i < zero_ints; i += blockDim.x) off_all[i] = 0;
     }
     __syncthreads();
     const bool cvec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15) == 0);
@@ -446,13 +448,10 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                         const double *cb = Ct + (size_t)(ch * 8 + frow) * S + fk;
                         const int col0 = ct_base + ch * 8 + fk * 2;
                         const bool first = (ct == 0 && ch == 0); // |x|^2 rides along with the first chunk
-                        if (cnt == kChunkTiles) {
-                            if (first) mma_chunk<true, true>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1);
-                            else mma_chunk<true, false>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1);
-                        } else {
-                            if (first) mma_chunk<false, true>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1);
-                            else mma_chunk<false, false>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1);
-                        }
+                        if (cnt == kChunkTiles)
+                            mma_chunk<true>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1, first);
+                        else
+                            mma_chunk<false>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1, first);
                     }
                 }
                 if (p.n_ctiles > 1) cbuf ^= 1;
@@ -501,7 +500,25 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 if (p.labels != nullptr && lane < rows_valid) p.labels[row0 + lane] = lab_s[lane];
             }
             if (ACCUM) {
-                // publish the tile (labels + rows) to the accumulator warps
+                // publish the tile to the accumulator warps.  Rows whose label already occurred earlier
+                // in the tile are first folded into that earlier row (in row order, in this warp's own
+                // buffer), so every row left points at a distinct sums row; folded rows and rows past
+                // the end of the data point at the scratch row.
+                __syncwarp();
+                const int my_lab = (lane < rows_valid) ? lab_s[lane] : -1 - lane;
+                const unsigned same = __match_any_sync(0xffffffffu, my_lab);
+                const int firstrow = __ffs(same) - 1;
+                const bool is_dup = (lane < rows_valid) && (firstrow != lane);
+                unsigned dupmask = __ballot_sync(0xffffffffu, is_dup);
+                if (lane < kWarpRows)
+                    off_all[(warp * xs + stage) * kWarpRows + lane] =
+                        ((lane < rows_valid && !is_dup) ? my_lab : p.k) * p.d;
+                while (dupmask) { // warp-uniform
+                    const int r = __ffs(dupmask) - 1;
+                    dupmask &= dupmask - 1;
+                    const int f = __shfl_sync(0xffffffffu, firstrow, r);
+                    for (int c = lane; c < p.d; c += 32) Xt[(size_t)f * S + c] += Xt[(size_t)r * S + c];
+                }
                 __syncwarp();
                 if (lane == 0) {
                     rows_all[warp * xs + stage] = rows_valid;
@@ -528,33 +545,34 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 const double *Xt = Xall + (size_t)(w * xs + stage) * xtile_elems;
                 const int *lab = lab_all + (w * xs + stage) * kWarpRows;
                 if (rows > 0) {
+                    const int *offp = off_all + (w * xs + stage) * kWarpRows;
                     if (sums_smem) {
+                        // every row of the tile, four at a time: rows that count update four distinct
+                        // cells, the others fall into the scratch row (whose content is never read)
                         for (int c = c0; c < p.d; c += cstride) {
-                            int r = 0;
-                            for (; r + 1 < rows; r += 2) {
-                                const int L0 = lab[r], L1 = lab[r + 1];
-                                const double x0 = Xt[(size_t)r * S + c], x1 = Xt[(size_t)(r + 1) * S + c];
-                                double *s0 = sums_s + (size_t)L0 * p.d + c;
-                                if (L0 != L1) { // independent cells: both read-modify-writes in flight
-                                    double *s1 = sums_s + (size_t)L1 * p.d + c;
-                                    const double v0 = *s0, v1 = *s1;
-                                    *s0 = v0 + x0;
-                                    *s1 = v1 + x1;
-                                } else {
-                                    *s0 = (*s0 + x0) + x1;
-                                }
-                            }
-                            if (r < rows) {
-                                double *s0 = sums_s + (size_t)lab[r] * p.d + c;
-                                *s0 = *s0 + Xt[(size_t)r * S + c];
+                            const double *xb = Xt + c;
+                            double *sb = sums_s + c;
+#pragma unroll 1
+                            for (int r = 0; r < kWarpRows; r += 4) {
+                                const int4 o = *reinterpret_cast<const int4 *>(offp + r);
+                                const double x0 = xb[(size_t)r * S], x1 = xb[(size_t)(r + 1) * S];
+                                const double x2 = xb[(size_t)(r + 2) * S], x3 = xb[(size_t)(r + 3) * S];
+                                const double s0 = sb[o.x], s1 = sb[o.y], s2 = sb[o.z], s3 = sb[o.w];
+                                sb[o.x] = s0 + x0;
+                                sb[o.y] = s1 + x1;
+                                sb[o.z] = s2 + x2;
+                                sb[o.w] = s3 + x3;
                             }
                         }
                         if (a == 0 && lane < rows) atomicAdd(&counts_s[lab[lane]], 1);
                     } else {
                         // sums too large for shared memory: one global accumulator (L2 atomics)
+                        const int trash = p.k * p.d;
                         for (int c = c0; c < p.d; c += cstride)
-                            for (int r = 0; r < rows; r++)
-                                atomicAdd(&p.partials[(size_t)lab[r] * p.d + c], Xt[(size_t)r * S + c]);
+                            for (int r = 0; r < rows; r++) {
+                                const int o = offp[r];
+                                if (o != trash) atomicAdd(&p.partials[(size_t)o + c], Xt[(size_t)r * S + c]);
+                            }
                         if (a == 0 && lane < rows) atomicAdd(&p.partials[(size_t)p.k * p.d + lab[lane]], 1.0);
                     }
                 }
