@@ -9,6 +9,7 @@
 #include <dlfcn.h>
 #include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -85,8 +86,15 @@ struct Chunk {
 
 struct LaunchCfg {
     int warps, acc_warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid;
+    int acc_order, spin_ns;
     size_t smem;
 };
+
+// Tuning overrides for experiments (environment; unset in normal use).
+int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
 
 thread_local std::string g_static_error;
 
@@ -173,15 +181,17 @@ int stride_for(int d) {
 
 // Shared memory the assign kernel needs for a geometry (must mirror the carve-up in assign_kernel).
 size_t smem_bytes(int warps, int acc, int xs, int S, int k, int d, int k_pad, int nc_tile, int n_ctiles, bool sums) {
-    size_t dbl = (size_t)(n_ctiles > 1 ? 2 : 1) * nc_tile * S + k_pad + (size_t)warps * xs * kWarpRows * S +
+    size_t dbl = (size_t)(n_ctiles > 1 ? 2 : 1) * nc_tile * S + k_pad + (size_t)warps * xs /* mbarriers */ +
+                 (size_t)warps * xs * kWarpRows * S +
                  (sums ? (((size_t)(k + 1) * d + 1) & ~(size_t)1) : 0);
     size_t ints = (sums ? (size_t)k : 0) + 2 * (size_t)warps * xs * kWarpRows + (size_t)warps * xs + warps +
                   (size_t)warps * acc;
     return dbl * 8 + ints * 4;
 }
 
-// accumulator warps: one per 32 columns, at most 4 (lanes then take several columns each)
-int acc_warps_for(int d) { return std::min(4, (d + 31) / 32); }
+// accumulator warps: one per 32 columns, at most 2 (lanes then take several columns each); with 10
+// MMA warps that is 384 threads
+int acc_warps_for(int d) { return std::min(2, (d + 31) / 32); }
 
 // Picks the launch geometry for (k, d).  Preference order: centroids resident in shared memory with
 // block-private sums; resident centroids with global-atomic sums; centroid tiles streamed from L2.
@@ -192,21 +202,27 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     c.k_pad = (k + 7) & ~7;
     c.grid = ctx->sm_count;
     c.acc_warps = accum ? acc_warps_for(d) : 0;
+    c.acc_order = env_int("FMLK_TUNE_ORDER", (ctx->flags & FMLK_FLAG_DETERMINISTIC) ? 0 : 1);
+    c.spin_ns = env_int("FMLK_TUNE_SPIN_NS", 40);
+    const int force_w = env_int("FMLK_TUNE_W", 0), force_xs = env_int("FMLK_TUNE_XS", 0);
     const size_t budget = ctx->smem_optin;
     // few centroids: HBM-bound, favour a prefetched second row tile per warp;
     // many centroids: FP64-bound, three MMA warps per scheduler with one tile each
-    static const int small_k[][2] = {{12, 2}, {12, 1}, {8, 1}, {4, 1}};
-    static const int large_k[][2] = {{12, 1}, {8, 1}, {4, 1}, {4, 1}};
+    // (at most 12 warps of 32 threads: the kernel is built for 384 threads so that each may hold 160
+    // registers -- the double-buffered fragments of the MMA loop need more than 128)
+    static const int small_k[][2] = {{10, 2}, {10, 1}, {8, 1}, {4, 1}};
+    static const int large_k[][2] = {{10, 1}, {8, 1}, {4, 1}, {4, 1}};
     const int(*cand)[2] = (c.k_pad <= 32) ? small_k : large_k;
     const int ncand = 4;
     for (int pass = 0; pass < 2; pass++) {
         const bool sums = accum && pass == 0;
         if (!accum && pass == 1) break;
         for (int i = 0; i < ncand; i++) {
-            size_t need = smem_bytes(cand[i][0], c.acc_warps, cand[i][1], c.S, k, d, c.k_pad, c.k_pad, 1, sums);
+            const int cw = force_w ? force_w : cand[i][0], cx = force_xs ? force_xs : cand[i][1];
+            size_t need = smem_bytes(cw, c.acc_warps, cx, c.S, k, d, c.k_pad, c.k_pad, 1, sums);
             if (need <= budget) {
-                c.warps = cand[i][0];
-                c.xs = cand[i][1];
+                c.warps = cw;
+                c.xs = cx;
                 c.nc_tile = c.k_pad;
                 c.n_ctiles = 1;
                 c.sums_in_smem = sums ? 1 : 0;
@@ -362,6 +378,8 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.xs = cfg.xs;
     p.mma_warps = cfg.warps;
     p.acc_warps = cfg.acc_warps;
+    p.acc_order = cfg.acc_order;
+    p.spin_ns = cfg.spin_ns;
     p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
     p.recheck_count = ctx->recheck;
     const int64_t tiles = (n + kWarpRows - 1) / kWarpRows;
@@ -1026,12 +1044,16 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
     LaunchCfg c;
     int rc = choose_cfg(ctx, k, d, accumulate != 0, &c);
     if (rc) return rc;
+    cudaFuncAttributes fa{};
+    if (accumulate) cudaFuncGetAttributes(&fa, assign_kernel<true>);
+    else cudaFuncGetAttributes(&fa, assign_kernel<false>);
     snprintf(out, (size_t)out_len,
-             "grid=%d block=%d smem=%zu mma_warps=%d acc_warps=%d xs=%d S=%d ksteps=%d k_pad=%d nc_tile=%d n_ctiles=%d "
-             "sums_in_smem=%d n_partials=%d",
-             c.grid, (c.warps + c.acc_warps) * 32, c.smem, c.warps, c.acc_warps, c.xs, c.S, c.ksteps, c.k_pad,
+             "regs=%d max_threads=%d local=%zu grid=%d block=%d smem=%zu mma_warps=%d acc_warps=%d xs=%d S=%d ksteps=%d k_pad=%d nc_tile=%d n_ctiles=%d "
+             "sums_in_smem=%d n_partials=%d acc_order=%d",
+             fa.numRegs, fa.maxThreadsPerBlock, fa.localSizeBytes, c.grid, (c.warps + c.acc_warps) * 32, c.smem, c.warps,
+             c.acc_warps, c.xs, c.S, c.ksteps, c.k_pad,
              c.nc_tile, c.n_ctiles,
-             c.sums_in_smem, c.n_partials);
+             c.sums_in_smem, c.n_partials, c.acc_order);
     return FMLK_OK;
 }
 

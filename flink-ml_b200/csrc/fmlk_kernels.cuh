@@ -54,6 +54,9 @@ struct AssignParams {
     int32_t xs;       // row-tile stages per MMA warp (1 or 2; 2 only when n_ctiles == 1)
     int32_t mma_warps; // warps that load + multiply + label
     int32_t acc_warps; // warps that own columns of the sums (accumulate launches only)
+    int32_t acc_order; // 0: tiles are accumulated in the fixed order (round, warp): bit-reproducible sums
+                       // 1: in arrival order: no head-of-line waiting, last bits vary from run to run
+    int32_t spin_ns;   // back-off of the hand-off spin loops
     int32_t fma_mode; // exact path follows the JDK>=11 netlib variant
     unsigned long long *recheck_count;
 };
@@ -73,6 +76,52 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() {
     asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory");
+}
+
+// 64-bit load from a 32-bit shared-memory address (+ constant byte offset folded by the compiler).
+// volatile: the loads and the DMMAs below keep the order they are written in, which is the
+// software pipeline of mma_chunk.
+__device__ __forceinline__ double lds_f64(unsigned addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];\n" : "=d"(v) : "r"(addr));
+    return v;
+}
+
+// mbarrier + bulk asynchronous copy (TMA engine; SASS: UBLKCP): row tiles travel HBM -> shared
+// memory without passing through registers, and completion is counted in bytes on the barrier.
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(unsigned bar, unsigned parity) {
+    unsigned ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 28)) __trap(); // a lost copy must not hang the device
+    }
+}
+// orders this thread's earlier generic-proxy accesses to shared memory (and those it has
+// synchronised with) before its later asynchronous-proxy (bulk copy) accesses
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+__device__ __forceinline__ void bulk_copy_g2s(unsigned dst_smem, const void *src_gmem, unsigned bytes, unsigned bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst_smem),
+                 "l"(__cvta_generic_to_global(src_gmem)), "r"(bytes), "r"(bar)
+                 : "memory");
 }
 
 // D(8x8) += A(8x4, row) * B(4x8, col), FP64 tensor core (SASS: DMMA.8x8x4).
@@ -231,22 +280,27 @@ __device__ __forceinline__ int ld_acquire_smem(const int *p) {
     asm volatile("ld.acquire.cta.shared.b32 %0, [%1];\n" : "=r"(v) : "r"(a) : "memory");
     return v;
 }
-__device__ __forceinline__ void spin_until_at_least(const int *p, int target) {
-    while (ld_acquire_smem(p) < target) __nanosleep(40);
+__device__ __forceinline__ void spin_until_at_least(const int *p, int target, unsigned ns) {
+    while (ld_acquire_smem(p) < target) __nanosleep(ns);
 }
 __device__ __forceinline__ void mma_group_barrier(int nthreads) {
     asm volatile("bar.sync 1, %0;\n" ::"r"(nthreads) : "memory");
 }
 
 // One accumulator chunk of a warp tile: 16 rows x (cnt <= 8) n8 tiles over the whole d.
-// xa0/xa1: this lane's A-fragment addresses for rows frow and frow+8; cb: its B-fragment
-// address in the first n8 tile; hcol: &h[first column this lane owns]; col0: that column.
+// xa0/xa1: shared-memory byte addresses of this lane's A fragments (rows frow, frow+8, k index fk);
+// cb: of its B fragment in the chunk's first n8 tile; tstride: bytes between n8 tiles;
+// hcol: &h[first column this lane owns]; col0: that column.
 // with_nsq (warp-uniform): also accumulate |x|^2 of the lane's fragment elements (first chunk of a tile).
+//
+// Software pipeline: the fragments of k-step s+1 are loaded while the 16 DMMAs of k-step s issue,
+// one load next to each pair of DMMAs, so the FP64 tensor pipe never waits for shared memory.
 template <bool FULL>
-__device__ __forceinline__ void mma_chunk(const double *xa0, const double *xa1, const double *cb, int S,
-                                       int ksteps, int cnt, const double *hcol, int col0, Top2 &t0,
-                                       Top2 &t1, double &nsq0, double &nsq1, bool with_nsq) {
+__device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned cb, unsigned tstride, int ksteps,
+                                          int cnt, const double *hcol, int col0, Top2 &t0, Top2 &t1, double &nsq0,
+                                          double &nsq1, bool with_nsq) {
     double acc0[kChunkTiles][2], acc1[kChunkTiles][2];
+    unsigned bj[kChunkTiles];
 #pragma unroll
     for (int j = 0; j < kChunkTiles; j++) {
         // accumulators start at -|c|^2/2, so the tile comes out as x.c - |c|^2/2
@@ -257,24 +311,58 @@ __device__ __forceinline__ void mma_chunk(const double *xa0, const double *xa1, 
         acc0[j][1] = h1;
         acc1[j][0] = h0;
         acc1[j][1] = h1;
+        bj[j] = cb + (on ? j : 0) * tstride; // unused tiles alias tile 0 (loaded, never multiplied)
     }
-    const size_t tstride = (size_t)8 * S;
-#pragma unroll 2
-    for (int ks = 0; ks < ksteps; ks++) {
-        const double a0 = xa0[ks * 4], a1 = xa1[ks * 4];
+    double a0c, a1c, bc[kChunkTiles], a0n, a1n, bn[kChunkTiles];
+    a0c = lds_f64(xa0);
+    a1c = lds_f64(xa1);
+#pragma unroll
+    for (int j = 0; j < kChunkTiles; j++) bc[j] = lds_f64(bj[j]);
+
+    // one k-step: multiply with the `cur` fragments while loading the `nxt` ones from byte offset `off`
+#define FMLK_KSTEP(A0C, A1C, BC, A0N, A1N, BN, OFF)                                      \
+    {                                                                                     \
+        if (with_nsq) {                                                                   \
+            nsq0 = fma(A0C, A0C, nsq0);                                                   \
+            nsq1 = fma(A1C, A1C, nsq1);                                                   \
+        }                                                                                 \
+        A0N = lds_f64(xa0 + (OFF));                                                       \
+        A1N = lds_f64(xa1 + (OFF));                                                       \
+        _Pragma("unroll") for (int j = 0; j < kChunkTiles; j++) {                         \
+            BN[j] = lds_f64(bj[j] + (OFF));                                               \
+            if (FULL || j < cnt) {                                                        \
+                dmma884(acc0[j][0], acc0[j][1], A0C, BC[j]);                              \
+                dmma884(acc1[j][0], acc1[j][1], A1C, BC[j]);                              \
+            }                                                                             \
+        }                                                                                 \
+    }
+
+    int ks = 0;
+#pragma unroll 1
+    for (; ks + 2 <= ksteps; ks += 2) {
+        FMLK_KSTEP(a0c, a1c, bc, a0n, a1n, bn, 32u)
+        // the loads of this second step run one k-step past the end on the last trip: they stay
+        // inside the CTA's shared memory (row padding / the next array) and are never used
+        FMLK_KSTEP(a0n, a1n, bn, a0c, a1c, bc, 64u)
+        xa0 += 64u;
+        xa1 += 64u;
+#pragma unroll
+        for (int j = 0; j < kChunkTiles; j++) bj[j] += 64u;
+    }
+    if (ks < ksteps) { // odd number of k-steps: the last one is already in the `c` fragments
         if (with_nsq) {
-            nsq0 = fma(a0, a0, nsq0);
-            nsq1 = fma(a1, a1, nsq1);
+            nsq0 = fma(a0c, a0c, nsq0);
+            nsq1 = fma(a1c, a1c, nsq1);
         }
 #pragma unroll
         for (int j = 0; j < kChunkTiles; j++) {
             if (FULL || j < cnt) {
-                const double b = cb[j * tstride + ks * 4];
-                dmma884(acc0[j][0], acc0[j][1], a0, b);
-                dmma884(acc1[j][0], acc1[j][1], a1, b);
+                dmma884(acc0[j][0], acc0[j][1], a0c, bc[j]);
+                dmma884(acc1[j][0], acc1[j][1], a1c, bc[j]);
             }
         }
     }
+#undef FMLK_KSTEP
 #pragma unroll
     for (int j = 0; j < kChunkTiles; j++) {
         if (FULL || j < cnt) {
@@ -300,7 +388,7 @@ __device__ __forceinline__ void mma_chunk(const double *xa0, const double *xa1, 
 // Centroids are resident in shared memory when they fit (n_ctiles == 1); otherwise the MMA warps
 // stream centroid tiles from L2 through two buffers, in lock-step (named barrier 1).
 template <bool ACCUM>
-__global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
+__global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -315,7 +403,8 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
 
     double *Cs = reinterpret_cast<double *>(smem_raw);
     double *hs = Cs + c_bufs * ctile_elems;
-    double *Xall = hs + p.k_pad;
+    unsigned long long *xbar = reinterpret_cast<unsigned long long *>(hs + p.k_pad); // [W * xs] mbarriers
+    double *Xall = hs + p.k_pad + W * xs;
     double *sums_s = Xall + (size_t)W * xs * xtile_elems;
     // k rows of sums plus one scratch row that absorbs the updates of rows handled in pass 2
     const size_t sums_elems = sums_smem ? (((size_t)(p.k + 1) * p.d + 1) & ~(size_t)1) : 0; // even: keeps off_all 16-byte aligned
@@ -328,12 +417,14 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
 
     // ---- one-time set-up: zero everything (pad columns and pad rows must read as 0) ----
     {
-        const size_t zero_elems = c_bufs * ctile_elems + p.k_pad + (size_t)W * xs * xtile_elems + sums_elems;
+        const size_t zero_elems = c_bufs * ctile_elems + p.k_pad + W * xs + (size_t)W * xs * xtile_elems + sums_elems;
         for (size_t i = threadIdx.x; i < zero_elems; i += blockDim.x) Cs[i] = 0.0;
         const int zero_ints = 2 * W * xs * kWarpRows + (sums_smem ? p.k : 0) + W * xs + W + W * A;
         for (int i = threadIdx.x; i < zero_ints; i += blockDim.x) off_all[i] = 0;
     }
     __syncthreads();
+    if (threadIdx.x < W * xs) mbar_init((unsigned)__cvta_generic_to_shared(&xbar[threadIdx.x]), 1u);
+    mbar_fence_init();
     const bool cvec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15) == 0);
     for (int i = threadIdx.x; i < p.k_pad; i += blockDim.x) hs[i] = p.h[i];
     if (p.n_ctiles == 1) {
@@ -359,19 +450,46 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         double *Xw = Xall + (size_t)warp * xs * xtile_elems;
         unsigned long long local_rechecks = 0;
         int cbuf = 0;
+        // row tiles: bulk asynchronous copies (one per row, issued by the lane of that row) that
+        // complete on this warp's mbarrier; rows of odd length fall back to 8-byte cp.async
+        const bool use_tma = vec16;
+        const unsigned row_bytes = (unsigned)p.d * 8u;
+        unsigned uses0 = 0, uses1 = 0; // completed phases of the stage barriers (parity = uses & 1)
+        auto x_issue = [&](int stage, int64_t row0, int rows) {
+            double *dst = Xw + (size_t)stage * xtile_elems;
+            if (use_tma) {
+                const unsigned bar = (unsigned)__cvta_generic_to_shared(&xbar[warp * xs + stage]);
+                fence_proxy_async_smem(); // the buffer was read (and zeroed at start) through the generic proxy
+                if (lane == 0) mbar_arrive_expect_tx(bar, row_bytes * (unsigned)rows);
+                __syncwarp();
+                if (lane < rows)
+                    bulk_copy_g2s((unsigned)__cvta_generic_to_shared(dst + (size_t)lane * S),
+                                  p.x + (row0 + lane) * p.d, row_bytes, bar);
+            } else {
+                load_rows_async(dst, p.x + row0 * p.d, rows, p.d, S, lane, 32, false);
+                cp_async_commit();
+            }
+        };
+        auto x_wait = [&](int stage) {
+            if (use_tma) {
+                const unsigned bar = (unsigned)__cvta_generic_to_shared(&xbar[warp * xs + stage]);
+                unsigned &u = stage ? uses1 : uses0;
+                mbar_wait(bar, u & 1u);
+                u++;
+            } else {
+                cp_async_wait<0>();
+                __syncwarp();
+            }
+        };
 
         if (p.n_ctiles > 1) {
             // prefetch centroid tile 0 into buffer 0 (rows past k stay zero)
             load_rows_async(Cs, p.c, min(p.nc_tile, p.k), p.d, S, threadIdx.x, mma_threads, cvec16);
             cp_async_commit();
         }
-        if (xs == 2) {
-            if (gw < total_tiles) {
-                const int64_t row0 = gw * kWarpRows;
-                load_rows_async(Xw, p.x + row0 * p.d, (int)min((int64_t)kWarpRows, p.n - row0), p.d, S, lane, 32,
-                                vec16);
-            }
-            cp_async_commit();
+        if (xs == 2 && gw < total_tiles) {
+            const int64_t row0 = gw * kWarpRows;
+            x_issue(0, row0, (int)min((int64_t)kWarpRows, p.n - row0));
         }
 
         for (int64_t it = 0; it < rounds; it++) {
@@ -386,26 +504,19 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
             // the buffer about to be overwritten was last used by tile it-1: wait until the
             // accumulator warps have consumed it
             if (ACCUM && it >= 1)
-                for (int a = 0; a < A; a++) spin_until_at_least(&seq_done[warp * A + a], (int)it);
+                for (int a = 0; a < A; a++) spin_until_at_least(&seq_done[warp * A + a], (int)it, (unsigned)p.spin_ns);
 
             if (xs == 2) {
+                // prefetch the next round's tile into the other stage, then wait for this one
                 const int64_t ntile = tile + GW;
                 if (ntile < total_tiles) {
                     const int64_t nrow0 = ntile * kWarpRows;
-                    load_rows_async(Xw + (size_t)(stage ^ 1) * xtile_elems, p.x + nrow0 * p.d,
-                                    (int)min((int64_t)kWarpRows, p.n - nrow0), p.d, S, lane, 32, vec16);
+                    x_issue(stage ^ 1, nrow0, (int)min((int64_t)kWarpRows, p.n - nrow0));
                 }
-                cp_async_commit();
-                cp_async_wait<1>();
-                __syncwarp();
-            } else {
-                if (active) load_rows_async(Xt, p.x + row0 * p.d, rows_valid, p.d, S, lane, 32, vec16);
-                cp_async_commit();
-                if (p.n_ctiles == 1) {
-                    cp_async_wait<0>();
-                    __syncwarp();
-                }
+            } else if (active) {
+                x_issue(0, row0, rows_valid);
             }
+            if (active) x_wait(stage);
 
             Top2 t0 = {-INFINITY, -INFINITY, 0}, t1 = {-INFINITY, -INFINITY, 0};
             double nsq0 = 0.0, nsq1 = 0.0;
@@ -440,18 +551,20 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 }
 
                 if (active) {
-                    const double *xa0 = Xt + (size_t)frow * S + fk;
-                    const double *xa1 = xa0 + (size_t)8 * S;
+                    const unsigned xa0 = (unsigned)__cvta_generic_to_shared(Xt + (size_t)frow * S + fk);
+                    const unsigned xa1 = xa0 + 8u * (unsigned)S * 8u;
+                    const unsigned ctile = (unsigned)__cvta_generic_to_shared(Ct + (size_t)frow * S + fk);
+                    const unsigned tstride = 8u * (unsigned)S * 8u;
                     const int tiles_here = (min(p.nc_tile, p.k_pad - ct_base)) >> 3; // n8 tiles in this C tile
                     for (int ch = 0; ch < tiles_here; ch += kChunkTiles) {
                         const int cnt = min(kChunkTiles, tiles_here - ch);
-                        const double *cb = Ct + (size_t)(ch * 8 + frow) * S + fk;
+                        const unsigned cb = ctile + (unsigned)ch * tstride;
                         const int col0 = ct_base + ch * 8 + fk * 2;
                         const bool first = (ct == 0 && ch == 0); // |x|^2 rides along with the first chunk
                         if (cnt == kChunkTiles)
-                            mma_chunk<true>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1, first);
+                            mma_chunk<true>(xa0, xa1, cb, tstride, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1, first);
                         else
-                            mma_chunk<false>(xa0, xa1, cb, S, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1, first);
+                            mma_chunk<false>(xa0, xa1, cb, tstride, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1, first);
                     }
                 }
                 if (p.n_ctiles > 1) cbuf ^= 1;
@@ -537,10 +650,34 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         const int a = warp - W;
         const int cstride = 32 * A;
         const int c0 = a * 32 + lane;
-        for (int64_t it = 0; it < rounds; it++) {
-            const int stage = (xs == 2) ? (int)(it & 1) : 0;
-            for (int w = 0; w < W; w++) {
-                spin_until_at_least(&seq_ready[w], (int)it + 1);
+        // lane w < W keeps the number of tiles of MMA warp w consumed so far
+        int consumed = 0;
+        const int64_t total_tiles_cta = rounds * W;
+        int next_w = 0;
+        for (int64_t done_tiles = 0; done_tiles < total_tiles_cta; done_tiles++) {
+            int w;
+            if (p.acc_order == 0) {
+                w = next_w;
+                next_w = (next_w + 1 == W) ? 0 : next_w + 1;
+                spin_until_at_least(&seq_ready[w], __shfl_sync(0xffffffffu, consumed, w) + 1, (unsigned)p.spin_ns);
+            } else {
+                unsigned avail;
+                while (true) {
+                    const bool ready = (lane < W) && (ld_acquire_smem(&seq_ready[lane]) > consumed);
+                    avail = __ballot_sync(0xffffffffu, ready);
+                    if (avail) break;
+                    __nanosleep((unsigned)p.spin_ns);
+                }
+                // rotate the starting point so no warp is favoured
+                const unsigned rot = (avail >> next_w) | (avail << ((32 - next_w) & 31));
+                w = (next_w + __ffs(next_w ? rot : avail) - 1) % 32;
+                if (w >= W) w = __ffs(avail) - 1;
+                next_w = (w + 1 == W) ? 0 : w + 1;
+            }
+            const int it_w = __shfl_sync(0xffffffffu, consumed, w);
+            if (lane == w) consumed++;
+            const int stage = (xs == 2) ? (it_w & 1) : 0;
+            {
                 const int rows = rows_all[w * xs + stage];
                 const double *Xt = Xall + (size_t)(w * xs + stage) * xtile_elems;
                 const int *lab = lab_all + (w * xs + stage) * kWarpRows;
@@ -577,7 +714,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                     }
                 }
                 __syncwarp();
-                if (lane == 0) st_release_smem(&seq_done[w * A + a], (int)it + 1);
+                if (lane == 0) st_release_smem(&seq_done[w * A + a], it_w + 1);
             }
         }
     }
