@@ -86,7 +86,7 @@ struct Chunk {
 
 struct LaunchCfg {
     int warps, acc_warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid;
-    int acc_order, spin_ns;
+    int acc_order, spin_ns, stagger_ns;
     size_t smem;
 };
 
@@ -117,6 +117,7 @@ struct fmlk_ctx {
     int32_t k_cap = 0;
     size_t kd_cap = 0;
     double *centroids = nullptr; // k*d
+    double *c_mma = nullptr;     // k*d: centroids for the tensor-core pass (dead ones zeroed)
     double *weights = nullptr;   // k
     double *cn = nullptr;        // k
     double *h = nullptr;         // k_pad
@@ -204,6 +205,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     c.acc_warps = accum ? acc_warps_for(d) : 0;
     c.acc_order = env_int("FMLK_TUNE_ORDER", (ctx->flags & FMLK_FLAG_DETERMINISTIC) ? 0 : 1);
     c.spin_ns = env_int("FMLK_TUNE_SPIN_NS", 40);
+    c.stagger_ns = env_int("FMLK_TUNE_STAGGER_NS", 0);
     const int force_w = env_int("FMLK_TUNE_W", 0), force_xs = env_int("FMLK_TUNE_XS", 0);
     const size_t budget = ctx->smem_optin;
     // few centroids: HBM-bound, favour a prefetched second row tile per warp;
@@ -265,6 +267,7 @@ int ensure_model(fmlk_ctx *ctx, int k, int d) {
     // buffers are sized by element count: a model with no more centroids and no more elements fits
     if (k <= ctx->k_cap && (size_t)k * d <= ctx->kd_cap) return FMLK_OK;
     dev_free(ctx->centroids);
+    dev_free(ctx->c_mma);
     dev_free(ctx->weights);
     dev_free(ctx->cn);
     dev_free(ctx->h);
@@ -272,6 +275,7 @@ int ensure_model(fmlk_ctx *ctx, int k, int d) {
     dev_free(ctx->red);
     dev_free(ctx->local_model);
     dev_free(ctx->gathered);
+    ctx->c_mma = nullptr;
     ctx->centroids = ctx->weights = ctx->cn = ctx->h = ctx->cmax2 = ctx->red = ctx->local_model = ctx->gathered =
         nullptr;
     ctx->k_cap = 0;
@@ -279,6 +283,7 @@ int ensure_model(fmlk_ctx *ctx, int k, int d) {
     const size_t kd = (size_t)k * d, len = kd + k;
     int rc;
     if ((rc = dev_alloc(ctx, &ctx->centroids, kd))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->c_mma, kd))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->weights, (size_t)k))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->cn, (size_t)k))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->h, (size_t)k + 8))) return rc;
@@ -347,7 +352,7 @@ int prep_centroids(fmlk_ctx *ctx) {
     const int k_pad = (ctx->k + 7) & ~7;
     prep_centroids_kernel<<<1, 256, 0, ctx->stream>>>(ctx->centroids, ctx->k, k_pad, ctx->md,
                                                      (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0, ctx->cn, ctx->h,
-                                                     ctx->cmax2);
+                                                     ctx->cmax2, ctx->c_mma);
     ctx->total_launches++;
     CK(ctx, cudaGetLastError());
     return FMLK_OK;
@@ -363,6 +368,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.S = cfg.S;
     p.ksteps = cfg.ksteps;
     p.c = ctx->centroids;
+    p.c_mma = ctx->c_mma;
     p.cn = ctx->cn;
     p.h = ctx->h;
     p.cmax2 = ctx->cmax2;
@@ -380,6 +386,8 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.acc_warps = cfg.acc_warps;
     p.acc_order = cfg.acc_order;
     p.spin_ns = cfg.spin_ns;
+    p.stagger_ns = cfg.stagger_ns;
+    p.debug_skip = env_int("FMLK_TUNE_DEBUG_SKIP", 0);
     p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
     p.recheck_count = ctx->recheck;
     const int64_t tiles = (n + kWarpRows - 1) / kWarpRows;
@@ -584,6 +592,7 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     for (Chunk &c : ctx->chunks)
         if (c.owned) dev_free(c.ptr);
     dev_free(ctx->centroids);
+    dev_free(ctx->c_mma);
     dev_free(ctx->weights);
     dev_free(ctx->cn);
     dev_free(ctx->h);

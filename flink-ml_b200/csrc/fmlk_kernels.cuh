@@ -38,7 +38,8 @@ struct AssignParams {
     int32_t d;
     int32_t S;      // shared-memory row stride in doubles; S % 8 == 4 keeps 64-bit fragment loads conflict-free
     int32_t ksteps; // ceil(d/4)
-    const double *c;     // k x d centroids
+    const double *c;     // k x d centroids (as given: the exact replay reads these)
+    const double *c_mma; // k x d centroids for the tensor-core pass: dead ones replaced by zero rows
     const double *cn;    // k norms, reference arithmetic
     const double *h;     // k_pad: |c|^2/2 ; +inf beyond k
     const double *cmax2; // max finite |c|^2
@@ -57,6 +58,8 @@ struct AssignParams {
     int32_t acc_order; // 0: tiles are accumulated in the fixed order (round, warp): bit-reproducible sums
                        // 1: in arrival order: no head-of-line waiting, last bits vary from run to run
     int32_t spin_ns;   // back-off of the hand-off spin loops
+    int32_t stagger_ns; // initial delay between the MMA warps of one scheduler (see assign_kernel)
+    int32_t debug_skip; // experiments only: 1 = skip the per-element selection, 2 = also skip row loads
     int32_t fma_mode; // exact path follows the JDK>=11 netlib variant
     unsigned long long *recheck_count;
 };
@@ -85,6 +88,12 @@ __device__ __forceinline__ double lds_f64(unsigned addr) {
     double v;
     asm volatile("ld.shared.f64 %0, [%1];\n" : "=d"(v) : "r"(addr));
     return v;
+}
+// Same, into a variable that keeps its register: the "+d" constraint ties the old and the new value
+// together, so the allocator cannot hand the load the register a DMMA has only just read (a
+// write-after-read stall); each fragment register is rewritten a whole k-step after its last use.
+__device__ __forceinline__ void lds_f64_into(double &v, unsigned addr) {
+    asm volatile("ld.shared.f64 %0, [%1];\n" : "+d"(v) : "r"(addr));
 }
 
 // mbarrier + bulk asynchronous copy (TMA engine; SASS: UBLKCP): row tiles travel HBM -> shared
@@ -216,31 +225,51 @@ __device__ __noinline__ int exact_find_closest(const double *x, const double *c,
 // ------------------------------------------------------------------------------------------
 // assign (+ accumulate) kernel
 
+// Running (best, second-best, index of best) of the scores of one row, kept as order-preserving
+// integer keys: comparing and selecting then runs on the integer pipes and never queues behind the
+// DMMAs on the FP64 pipe (a DSETP issued next to another warp's DMMA stream waits ~50 cycles).
+//   key(v) = bits(v) for v >= 0, bits(v) with the low 63 bits flipped for v < 0   (an involution)
+// Scores are never NaN for rows and centroids that are finite (dead centroids are replaced by a
+// zero row with h = +inf in prep_centroids_kernel, so they score -inf); rows that are not finite
+// fail the margin test through |x|^2 and go to the exact replay.
 struct Top2 {
-    double best, second;
+    long long best, second;
     int idx;
 };
 
-// Branch-free update with explicit compares: a NaN score (NaN centroid, NaN row) never wins and
-// never becomes the runner-up, as in the Java scan.
+__device__ __forceinline__ long long score_key(double v) {
+    const long long b = __double_as_longlong(v);
+    return b ^ ((b >> 63) & 0x7fffffffffffffffLL);
+}
+__device__ __forceinline__ double key_score(long long k) {
+    return __longlong_as_double(k ^ ((k >> 63) & 0x7fffffffffffffffLL));
+}
+__device__ __forceinline__ Top2 top2_init() {
+    const long long ninf = score_key(-INFINITY);
+    Top2 t = {ninf, ninf, 0};
+    return t;
+}
+
 __device__ __forceinline__ void top2_push(Top2 &t, double v, int col) {
-    const bool gt = v > t.best;
-    const bool gs = v > t.second;
-    t.second = gt ? t.best : (gs ? v : t.second);
+    const long long k = score_key(v);
+    const bool gt = k > t.best;
+    const bool gs = k > t.second;
+    t.second = gt ? t.best : (gs ? k : t.second);
     t.idx = gt ? col : t.idx;
-    t.best = gt ? v : t.best;
+    t.best = gt ? k : t.best;
 }
 
 __device__ __forceinline__ void top2_merge_xor(Top2 &t, int off) {
-    const double ob = __shfl_xor_sync(0xffffffffu, t.best, off);
-    const double os = __shfl_xor_sync(0xffffffffu, t.second, off);
+    const long long ob = __shfl_xor_sync(0xffffffffu, t.best, off);
+    const long long os = __shfl_xor_sync(0xffffffffu, t.second, off);
     const int oi = __shfl_xor_sync(0xffffffffu, t.idx, off);
-    const double loser = ob > t.best ? t.best : ob; // neither is NaN
+    const long long loser = ob > t.best ? t.best : ob;
     if (ob > t.best || (ob == t.best && oi < t.idx)) {
         t.best = ob;
         t.idx = oi;
     }
-    t.second = fmax(fmax(t.second, os), loser);
+    long long s2 = t.second > os ? t.second : os;
+    t.second = s2 > loser ? s2 : loser;
 }
 
 // Copies `rows` rows of d doubles (contiguous in global memory) into shared rows of stride S, by
@@ -287,7 +316,9 @@ __device__ __forceinline__ void mma_group_barrier(int nthreads) {
     asm volatile("bar.sync 1, %0;\n" ::"r"(nthreads) : "memory");
 }
 
-// One accumulator chunk of a warp tile: 16 rows x (cnt <= 8) n8 tiles over the whole d.
+// One accumulator chunk of a warp tile: 16 rows x CNT (1..8) n8 tiles over the whole d.  CNT is a
+// template parameter: a DMMA that is merely predicated off still blocks its warp for a DMMA's issue
+// time, so the last, partial chunk of a centroid tile gets code with exactly its number of tiles.
 // xa0/xa1: shared-memory byte addresses of this lane's A fragments (rows frow, frow+8, k index fk);
 // cb: of its B fragment in the chunk's first n8 tile; tstride: bytes between n8 tiles;
 // hcol: &h[first column this lane owns]; col0: that column.
@@ -295,29 +326,30 @@ __device__ __forceinline__ void mma_group_barrier(int nthreads) {
 //
 // Software pipeline: the fragments of k-step s+1 are loaded while the 16 DMMAs of k-step s issue,
 // one load next to each pair of DMMAs, so the FP64 tensor pipe never waits for shared memory.
-template <bool FULL>
+template <int CNT>
 __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned cb, unsigned tstride, int ksteps,
-                                          int cnt, const double *hcol, int col0, Top2 &t0, Top2 &t1, double &nsq0,
-                                          double &nsq1, bool with_nsq) {
-    double acc0[kChunkTiles][2], acc1[kChunkTiles][2];
-    unsigned bj[kChunkTiles];
+                                          const double *hcol, int col0, Top2 &t0, Top2 &t1, double &nsq0,
+                                          double &nsq1, bool with_nsq, int debug_skip = 0) {
+    double acc0[CNT][2], acc1[CNT][2];
+    unsigned bj[CNT];
 #pragma unroll
-    for (int j = 0; j < kChunkTiles; j++) {
+    for (int j = 0; j < CNT; j++) {
         // accumulators start at -|c|^2/2, so the tile comes out as x.c - |c|^2/2
-        const bool on = FULL || j < cnt;
-        const double h0 = on ? -hcol[j * 8] : 0.0;
-        const double h1 = on ? -hcol[j * 8 + 1] : 0.0;
+        const double h0 = -hcol[j * 8];
+        const double h1 = -hcol[j * 8 + 1];
         acc0[j][0] = h0;
         acc0[j][1] = h1;
         acc1[j][0] = h0;
         acc1[j][1] = h1;
-        bj[j] = cb + (on ? j : 0) * tstride; // unused tiles alias tile 0 (loaded, never multiplied)
+        bj[j] = cb + j * tstride;
     }
-    double a0c, a1c, bc[kChunkTiles], a0n, a1n, bn[kChunkTiles];
+    double a0c, a1c, bc[CNT], a0n = 0.0, a1n = 0.0, bn[CNT];
+#pragma unroll
+    for (int j = 0; j < CNT; j++) bn[j] = 0.0;
     a0c = lds_f64(xa0);
     a1c = lds_f64(xa1);
 #pragma unroll
-    for (int j = 0; j < kChunkTiles; j++) bc[j] = lds_f64(bj[j]);
+    for (int j = 0; j < CNT; j++) bc[j] = lds_f64(bj[j]);
 
     // one k-step: multiply with the `cur` fragments while loading the `nxt` ones from byte offset `off`
 #define FMLK_KSTEP(A0C, A1C, BC, A0N, A1N, BN, OFF)                                      \
@@ -326,14 +358,12 @@ __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned c
             nsq0 = fma(A0C, A0C, nsq0);                                                   \
             nsq1 = fma(A1C, A1C, nsq1);                                                   \
         }                                                                                 \
-        A0N = lds_f64(xa0 + (OFF));                                                       \
-        A1N = lds_f64(xa1 + (OFF));                                                       \
-        _Pragma("unroll") for (int j = 0; j < kChunkTiles; j++) {                         \
-            BN[j] = lds_f64(bj[j] + (OFF));                                               \
-            if (FULL || j < cnt) {                                                        \
-                dmma884(acc0[j][0], acc0[j][1], A0C, BC[j]);                              \
-                dmma884(acc1[j][0], acc1[j][1], A1C, BC[j]);                              \
-            }                                                                             \
+        lds_f64_into(A0N, xa0 + (OFF));                                                   \
+        lds_f64_into(A1N, xa1 + (OFF));                                                   \
+        _Pragma("unroll") for (int j = 0; j < CNT; j++) {                         \
+            lds_f64_into(BN[j], bj[j] + (OFF));                                           \
+            dmma884(acc0[j][0], acc0[j][1], A0C, BC[j]);                                  \
+            dmma884(acc1[j][0], acc1[j][1], A1C, BC[j]);                                  \
         }                                                                                 \
     }
 
@@ -347,7 +377,7 @@ __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned c
         xa0 += 64u;
         xa1 += 64u;
 #pragma unroll
-        for (int j = 0; j < kChunkTiles; j++) bj[j] += 64u;
+        for (int j = 0; j < CNT; j++) bj[j] += 64u;
     }
     if (ks < ksteps) { // odd number of k-steps: the last one is already in the `c` fragments
         if (with_nsq) {
@@ -355,23 +385,26 @@ __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned c
             nsq1 = fma(a1c, a1c, nsq1);
         }
 #pragma unroll
-        for (int j = 0; j < kChunkTiles; j++) {
-            if (FULL || j < cnt) {
-                dmma884(acc0[j][0], acc0[j][1], a0c, bc[j]);
-                dmma884(acc1[j][0], acc1[j][1], a1c, bc[j]);
-            }
+        for (int j = 0; j < CNT; j++) {
+            dmma884(acc0[j][0], acc0[j][1], a0c, bc[j]);
+            dmma884(acc1[j][0], acc1[j][1], a1c, bc[j]);
         }
     }
 #undef FMLK_KSTEP
+    if (debug_skip) { // experiments: keep the accumulators alive at almost no cost
+        double sum = 0.0;
 #pragma unroll
-    for (int j = 0; j < kChunkTiles; j++) {
-        if (FULL || j < cnt) {
-            const int col = col0 + j * 8;
-            top2_push(t0, acc0[j][0], col);
-            top2_push(t0, acc0[j][1], col + 1);
-            top2_push(t1, acc1[j][0], col);
-            top2_push(t1, acc1[j][1], col + 1);
-        }
+        for (int j = 0; j < CNT; j++) sum += acc0[j][0] + acc0[j][1] + acc1[j][0] + acc1[j][1];
+        if (sum == 1.2345e300) t0.idx = 1;
+        return;
+    }
+#pragma unroll
+    for (int j = 0; j < CNT; j++) {
+        const int col = col0 + j * 8;
+        top2_push(t0, acc0[j][0], col);
+        top2_push(t0, acc0[j][1], col + 1);
+        top2_push(t1, acc1[j][0], col);
+        top2_push(t1, acc1[j][1], col + 1);
     }
 }
 
@@ -425,11 +458,11 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
     __syncthreads();
     if (threadIdx.x < W * xs) mbar_init((unsigned)__cvta_generic_to_shared(&xbar[threadIdx.x]), 1u);
     mbar_fence_init();
-    const bool cvec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.c) & 15) == 0);
+    const bool cvec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.c_mma) & 15) == 0);
     for (int i = threadIdx.x; i < p.k_pad; i += blockDim.x) hs[i] = p.h[i];
     if (p.n_ctiles == 1) {
         // resident centroids: k rows of d doubles, rows k..nc_tile-1 stay zero (their h is +inf)
-        load_rows_async(Cs, p.c, p.k, p.d, S, threadIdx.x, blockDim.x, cvec16);
+        load_rows_async(Cs, p.c_mma, p.k, p.d, S, threadIdx.x, blockDim.x, cvec16);
         cp_async_commit();
         cp_async_wait<0>();
     }
@@ -482,9 +515,16 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
             }
         };
 
+        // The MMA warps of one scheduler share its FP64 tensor pipe.  Left alone they run in lock-step
+        // (same work, same start): all in the DMMA loop together, then all out of it together, and the
+        // pipe idles while they load, select and publish.  Starting them a fraction of a tile apart
+        // keeps some warps in the loop while others are between tiles.
+        if (p.stagger_ns > 0 && p.n_ctiles == 1) {
+            for (int i = 0; i < (warp >> 2); i++) __nanosleep((unsigned)p.stagger_ns);
+        }
         if (p.n_ctiles > 1) {
             // prefetch centroid tile 0 into buffer 0 (rows past k stay zero)
-            load_rows_async(Cs, p.c, min(p.nc_tile, p.k), p.d, S, threadIdx.x, mma_threads, cvec16);
+            load_rows_async(Cs, p.c_mma, min(p.nc_tile, p.k), p.d, S, threadIdx.x, mma_threads, cvec16);
             cp_async_commit();
         }
         if (xs == 2 && gw < total_tiles) {
@@ -513,12 +553,12 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
                     const int64_t nrow0 = ntile * kWarpRows;
                     x_issue(stage ^ 1, nrow0, (int)min((int64_t)kWarpRows, p.n - nrow0));
                 }
-            } else if (active) {
+            } else if (active && !(p.debug_skip >= 2 && it > 0)) {
                 x_issue(0, row0, rows_valid);
             }
-            if (active) x_wait(stage);
+            if (active && !(p.debug_skip >= 2 && it > 0 && xs == 1)) x_wait(stage);
 
-            Top2 t0 = {-INFINITY, -INFINITY, 0}, t1 = {-INFINITY, -INFINITY, 0};
+            Top2 t0 = top2_init(), t1 = top2_init();
             double nsq0 = 0.0, nsq1 = 0.0;
 
             for (int ct = 0; ct < p.n_ctiles; ct++) {
@@ -539,7 +579,7 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
                         const int nbase = nct * p.nc_tile;
                         const int nrows = min(p.nc_tile, p.k - nbase);
                         double *dstb = Cs + (size_t)(cbuf ^ 1) * ctile_elems;
-                        load_rows_async(dstb, p.c + (size_t)nbase * p.d, nrows, p.d, S, threadIdx.x, mma_threads,
+                        load_rows_async(dstb, p.c_mma + (size_t)nbase * p.d, nrows, p.d, S, threadIdx.x, mma_threads,
                                         cvec16);
                         // rows past k in the last tile read as zero (their h is +inf)
                         for (int i = nrows * p.d + threadIdx.x; i < p.nc_tile * p.d; i += mma_threads) {
@@ -561,10 +601,13 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
                         const unsigned cb = ctile + (unsigned)ch * tstride;
                         const int col0 = ct_base + ch * 8 + fk * 2;
                         const bool first = (ct == 0 && ch == 0); // |x|^2 rides along with the first chunk
-                        if (cnt == kChunkTiles)
-                            mma_chunk<true>(xa0, xa1, cb, tstride, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1, first);
-                        else
-                            mma_chunk<false>(xa0, xa1, cb, tstride, p.ksteps, cnt, hs + col0, col0, t0, t1, nsq0, nsq1, first);
+#define FMLK_CHUNK(N) \
+    case N: mma_chunk<N>(xa0, xa1, cb, tstride, p.ksteps, hs + col0, col0, t0, t1, nsq0, nsq1, first, p.debug_skip); break;
+                        switch (cnt) {
+                            FMLK_CHUNK(8) FMLK_CHUNK(7) FMLK_CHUNK(6) FMLK_CHUNK(5)
+                            FMLK_CHUNK(4) FMLK_CHUNK(3) FMLK_CHUNK(2) FMLK_CHUNK(1)
+                        }
+#undef FMLK_CHUNK
                     }
                 }
                 if (p.n_ctiles > 1) cbuf ^= 1;
@@ -582,10 +625,10 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
                 nsq1 += __shfl_xor_sync(0xffffffffu, nsq1, 2);
 
                 // decision margin in squared-distance units: D = |x|^2 - 2 v
-                const bool ok0 = 2.0 * (t0.best - t0.second) > p.thr_coef * (nsq0 + cmax2);
-                const bool ok1 = 2.0 * (t1.best - t1.second) > p.thr_coef * (nsq1 + cmax2);
-                const bool flag0 = !ok0 && (frow < rows_valid);
-                const bool flag1 = !ok1 && (frow + 8 < rows_valid);
+                const bool ok0 = 2.0 * (key_score(t0.best) - key_score(t0.second)) > p.thr_coef * (nsq0 + cmax2);
+                const bool ok1 = 2.0 * (key_score(t1.best) - key_score(t1.second)) > p.thr_coef * (nsq1 + cmax2);
+                const bool flag0 = !ok0 && (frow < rows_valid) && !p.debug_skip;
+                const bool flag1 = !ok1 && (frow + 8 < rows_valid) && !p.debug_skip;
                 if (fk == 0) {
                     lab_s[frow] = t0.idx;
                     lab_s[frow + 8] = t1.idx;
@@ -731,18 +774,24 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
 // ------------------------------------------------------------------------------------------
 // per-round small kernels
 
-// VectorWithNorm of every centroid (KMeans.java:279-282) in reference arithmetic, plus the
-// values the assign kernel needs: h = |c|^2/2 (+inf for padding) and the largest finite |c|^2.
+// VectorWithNorm of every centroid (KMeans.java:279-282) in reference arithmetic, plus what the
+// assign kernel's tensor-core pass needs: h = |c|^2/2 (+inf for padding) and the largest finite
+// |c|^2.  A centroid whose |c|^2 is not finite (NaN after its cluster emptied, Inf, or an overflow)
+// can never win the Java scan (its distance is NaN or +Inf, and `<` is strict): it is "dead".  For
+// the tensor-core pass a dead centroid becomes a zero row with h = +inf in c_mma, so it scores -inf
+// instead of NaN; the exact replay keeps reading the original centroids.
 __global__ void prep_centroids_kernel(const double *c, int k, int k_pad, int d, int fma_mode, double *cn,
-                                      double *h, double *cmax2) {
+                                      double *h, double *cmax2, double *c_mma) {
     __shared__ double red[256];
     double mx = 0.0;
     for (int j = threadIdx.x; j < k_pad; j += blockDim.x) {
         if (j < k) {
             const double ss = ref_sumsq(c + (size_t)j * d, d, fma_mode);
             cn[j] = sqrt(ss);
-            h[j] = 0.5 * ss;
-            if (isfinite(ss) && ss > mx) mx = ss;
+            const bool live = isfinite(ss);
+            h[j] = live ? 0.5 * ss : INFINITY;
+            if (live && ss > mx) mx = ss;
+            for (int i = 0; i < d; i++) c_mma[(size_t)j * d + i] = live ? c[(size_t)j * d + i] : 0.0;
         } else {
             h[j] = INFINITY;
         }
