@@ -203,7 +203,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     c.k_pad = (k + 7) & ~7;
     c.grid = ctx->sm_count;
     c.acc_warps = accum ? acc_warps_for(d) : 0;
-    c.acc_order = env_int("FMLK_TUNE_ORDER", (ctx->flags & FMLK_FLAG_DETERMINISTIC) ? 0 : 1);
+    c.acc_order = env_int("FMLK_TUNE_ORDER", 0); // fixed order: reproducible sums (and measured faster)
     c.spin_ns = env_int("FMLK_TUNE_SPIN_NS", 40);
     c.stagger_ns = env_int("FMLK_TUNE_STAGGER_NS", 0);
     const int force_w = env_int("FMLK_TUNE_W", 0), force_xs = env_int("FMLK_TUNE_XS", 0);

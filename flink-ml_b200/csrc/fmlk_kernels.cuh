@@ -225,33 +225,42 @@ __device__ __noinline__ int exact_find_closest(const double *x, const double *c,
 // ------------------------------------------------------------------------------------------
 // assign (+ accumulate) kernel
 
-// Running (best, second-best, index of best) of the scores of one row, kept as order-preserving
-// integer keys: comparing and selecting then runs on the integer pipes and never queues behind the
-// DMMAs on the FP64 pipe (a DSETP issued next to another warp's DMMA stream waits ~50 cycles).
-//   key(v) = bits(v) for v >= 0, bits(v) with the low 63 bits flipped for v < 0   (an involution)
+// Running (best, second-best, index of best) of the scores of one row.  The hot path keeps only
+// the HIGH 32 bits of an order-preserving integer key of each score (sign, exponent, 20 mantissa
+// bits): comparing and selecting then costs 8 integer instructions per score and never queues
+// behind the DMMAs on the FP64 pipe (a DSETP issued next to another warp's DMMA stream waits
+// ~50 cycles).
+//   key(v) = bits(v) for v >= 0, bits(v) with the low 63 bits flipped for v < 0   (monotonic in v)
+// Dropping the low word rounds a score DOWN by less than one unit of its 20-bit mantissa, so
+//   lower(best) = value(best_hi : 00000000) <= best,   upper(second) = value(second_hi : ffffffff) >= second
+// and a row is decided when lower(best) - upper(second) clears the rounding threshold; rows whose
+// two best scores agree to ~6 digits (about one in 10^4..10^5) simply take the exact replay.
 // Scores are never NaN for rows and centroids that are finite (dead centroids are replaced by a
 // zero row with h = +inf in prep_centroids_kernel, so they score -inf); rows that are not finite
 // fail the margin test through |x|^2 and go to the exact replay.
 struct Top2 {
-    long long best, second;
+    int best, second; // high words of the keys
     int idx;
 };
 
-__device__ __forceinline__ long long score_key(double v) {
-    const long long b = __double_as_longlong(v);
-    return b ^ ((b >> 63) & 0x7fffffffffffffffLL);
+__device__ __forceinline__ int score_key_hi(double v) {
+    const int hi = __double2hiint(v);
+    return hi ^ ((hi >> 31) & 0x7fffffff);
 }
-__device__ __forceinline__ double key_score(long long k) {
-    return __longlong_as_double(k ^ ((k >> 63) & 0x7fffffffffffffffLL));
+__device__ __forceinline__ double key_hi_value(int khi, unsigned lo_bits) {
+    // inverse of the key map for (khi : lo_bits); for negative values the low word flips too
+    const int hi = khi ^ ((khi >> 31) & 0x7fffffff);
+    const unsigned lo = (khi < 0) ? ~lo_bits : lo_bits;
+    return __hiloint2double(hi, (int)lo);
 }
 __device__ __forceinline__ Top2 top2_init() {
-    const long long ninf = score_key(-INFINITY);
+    const int ninf = score_key_hi(-INFINITY);
     Top2 t = {ninf, ninf, 0};
     return t;
 }
 
 __device__ __forceinline__ void top2_push(Top2 &t, double v, int col) {
-    const long long k = score_key(v);
+    const int k = score_key_hi(v);
     const bool gt = k > t.best;
     const bool gs = k > t.second;
     t.second = gt ? t.best : (gs ? k : t.second);
@@ -260,16 +269,20 @@ __device__ __forceinline__ void top2_push(Top2 &t, double v, int col) {
 }
 
 __device__ __forceinline__ void top2_merge_xor(Top2 &t, int off) {
-    const long long ob = __shfl_xor_sync(0xffffffffu, t.best, off);
-    const long long os = __shfl_xor_sync(0xffffffffu, t.second, off);
+    const int ob = __shfl_xor_sync(0xffffffffu, t.best, off);
+    const int os = __shfl_xor_sync(0xffffffffu, t.second, off);
     const int oi = __shfl_xor_sync(0xffffffffu, t.idx, off);
-    const long long loser = ob > t.best ? t.best : ob;
+    const int loser = ob > t.best ? t.best : ob;
     if (ob > t.best || (ob == t.best && oi < t.idx)) {
         t.best = ob;
         t.idx = oi;
     }
-    long long s2 = t.second > os ? t.second : os;
-    t.second = s2 > loser ? s2 : loser;
+    t.second = max(max(t.second, os), loser);
+}
+
+// conservative decision margin of a row in score units: lower(best) - upper(second)
+__device__ __forceinline__ double top2_margin(const Top2 &t) {
+    return key_hi_value(t.best, 0u) - key_hi_value(t.second, 0xffffffffu);
 }
 
 // Copies `rows` rows of d doubles (contiguous in global memory) into shared rows of stride S, by
@@ -625,8 +638,8 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
                 nsq1 += __shfl_xor_sync(0xffffffffu, nsq1, 2);
 
                 // decision margin in squared-distance units: D = |x|^2 - 2 v
-                const bool ok0 = 2.0 * (key_score(t0.best) - key_score(t0.second)) > p.thr_coef * (nsq0 + cmax2);
-                const bool ok1 = 2.0 * (key_score(t1.best) - key_score(t1.second)) > p.thr_coef * (nsq1 + cmax2);
+                const bool ok0 = 2.0 * top2_margin(t0) > p.thr_coef * (nsq0 + cmax2);
+                const bool ok1 = 2.0 * top2_margin(t1) > p.thr_coef * (nsq1 + cmax2);
                 const bool flag0 = !ok0 && (frow < rows_valid) && !p.debug_skip;
                 const bool flag1 = !ok1 && (frow + 8 < rows_valid) && !p.debug_skip;
                 if (fk == 0) {
@@ -727,22 +740,29 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
                 if (rows > 0) {
                     const int *offp = off_all + (w * xs + stage) * kWarpRows;
                     if (sums_smem) {
-                        // every row of the tile, four at a time: rows that count update four distinct
-                        // cells, the others fall into the scratch row (whose content is never read)
+                        // every row of the tile: rows that count update distinct cells, the others fall
+                        // into the scratch row (whose content is never read)
                         for (int c = c0; c < p.d; c += cstride) {
                             const double *xb = Xt + c;
                             double *sb = sums_s + c;
-#pragma unroll 1
-                            for (int r = 0; r < kWarpRows; r += 4) {
-                                const int4 o = *reinterpret_cast<const int4 *>(offp + r);
-                                const double x0 = xb[(size_t)r * S], x1 = xb[(size_t)(r + 1) * S];
-                                const double x2 = xb[(size_t)(r + 2) * S], x3 = xb[(size_t)(r + 3) * S];
-                                const double s0 = sb[o.x], s1 = sb[o.y], s2 = sb[o.z], s3 = sb[o.w];
-                                sb[o.x] = s0 + x0;
-                                sb[o.y] = s1 + x1;
-                                sb[o.z] = s2 + x2;
-                                sb[o.w] = s3 + x3;
+                            int off[kWarpRows];
+                            double xv[kWarpRows], sv[kWarpRows];
+#pragma unroll
+                            for (int q = 0; q < kWarpRows / 4; q++) {
+                                const int4 o = *reinterpret_cast<const int4 *>(offp + 4 * q);
+                                off[4 * q + 0] = o.x;
+                                off[4 * q + 1] = o.y;
+                                off[4 * q + 2] = o.z;
+                                off[4 * q + 3] = o.w;
                             }
+                            // all loads, then all adds and stores: the 16 cells are distinct (or the
+                            // scratch row), so the updates are independent and their latencies overlap
+#pragma unroll
+                            for (int r = 0; r < kWarpRows; r++) xv[r] = xb[(size_t)r * S];
+#pragma unroll
+                            for (int r = 0; r < kWarpRows; r++) sv[r] = sb[off[r]];
+#pragma unroll
+                            for (int r = 0; r < kWarpRows; r++) sb[off[r]] = sv[r] + xv[r];
                         }
                         if (a == 0 && lane < rows) atomicAdd(&counts_s[lab[lane]], 1);
                     } else {

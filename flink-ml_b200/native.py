@@ -16,7 +16,6 @@ OK = 0
 ERR_INVALID_ARG, ERR_STATE, ERR_DIM, ERR_CUDA, ERR_NCCL, ERR_NOMEM = -1, -2, -3, -4, -5, -6
 FLAG_PROFILE = 0x1
 FLAG_BLAS_FMA = 0x2
-FLAG_DETERMINISTIC = 0x4
 NCCL_ID_BYTES = 128
 
 

@@ -42,8 +42,6 @@ typedef enum fmlk_status {
 /* fmlk_create flags */
 #define FMLK_FLAG_PROFILE 0x1  /* time every assign-kernel launch with CUDA events (fmlk_get_profile) */
 #define FMLK_FLAG_BLAS_FMA 0x2 /* exact paths follow netlib's JDK>=11 (Math.fma) variant instead of JDK 8 */
-#define FMLK_FLAG_DETERMINISTIC 0x4 /* per-cluster sums are added in a fixed order: bit-identical results run to run
-                                       (assignments are always exact; this only pins the last bits of the sums) */
 
 #define FMLK_NCCL_ID_BYTES 128
 
