@@ -1067,3 +1067,115 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
 }
 
 } // extern "C"
+
+// ------------------------------------------------------------------------------------------
+// Allocation-free variant of the local training round.
+//
+// Everything the round needs besides the caller's inputs and outputs -- the per-CTA partial sums,
+// the reduced [sums | counts] vector, the centroid norms and the sanitised centroid copy -- lives in
+// this one file-scope device array, so the call never reaches cudaMalloc / cudaFree.  The array is
+// part of the library image: every GPU that loads the library holds these ~10.8 MB until exit.
+namespace {
+constexpr size_t kNoAllocMaxModel = 8192; // limit on k*d + k (doubles)
+constexpr int kNoAllocMaxSlots = 160;     // per-CTA partial slots (one CTA per SM)
+constexpr int kNoAllocMaxK = 2048;
+constexpr size_t kNoAllocPartials = (size_t)kNoAllocMaxSlots * kNoAllocMaxModel;
+constexpr size_t kNoAllocDoubles = kNoAllocPartials      /* partials            */
+                                   + kNoAllocMaxModel    /* red: [sums | counts] */
+                                   + kNoAllocMaxModel    /* c_mma                */
+                                   + kNoAllocMaxK        /* cn                   */
+                                   + (kNoAllocMaxK + 8)  /* h                    */
+                                   + 8;                  /* cmax2, recheck count */
+constexpr int kNoAllocMaxDevices = 16;
+} // namespace
+
+static __device__ __align__(256) double g_noalloc_scratch[kNoAllocDoubles];
+
+namespace {
+struct NoAllocDevice {
+    bool ready = false;
+    fmlk_ctx ctx; // a context whose device buffers are slices of g_noalloc_scratch (owns nothing)
+};
+NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
+
+// Once per device, with that device current: resolve the DEVICE address of the scratch array.
+// In host code the name g_noalloc_scratch is only a handle for the runtime, not a device pointer;
+// the address a kernel can use comes from cudaGetSymbolAddress.
+int noalloc_setup(int device) {
+    NoAllocDevice &nd = g_noalloc_dev[device];
+    if (nd.ready) return FMLK_OK;
+    double *base = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void **)&base, g_noalloc_scratch);
+    if (e != cudaSuccess || base == nullptr) {
+        cudaGetLastError();
+        return fail(nullptr, FMLK_ERR_CUDA, std::string("cudaGetSymbolAddress(scratch): ") + cudaGetErrorString(e));
+    }
+    int smem = 0, sms = 0, major = 0;
+    e = cudaDeviceGetAttribute(&smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+    if (e == cudaSuccess && major == 10)
+        e = cudaFuncSetAttribute(assign_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, std::string("device set-up: ") + cudaGetErrorString(e));
+    if (major != 10) return fail(nullptr, FMLK_ERR_CUDA, "this build targets sm_100a (B200) only");
+    if (sms > kNoAllocMaxSlots) return fail(nullptr, FMLK_ERR_INVALID_ARG, "device has more SMs than the scratch array has slots");
+    fmlk_ctx &c = nd.ctx;
+    c.device = device;
+    c.rank = 0;
+    c.world = 1;
+    c.flags = 0;
+    c.own_stream = false;
+    c.sm_count = sms;
+    c.smem_optin = (size_t)smem;
+    c.partials = base;
+    c.partials_cap = kNoAllocPartials;
+    c.red = base + kNoAllocPartials;
+    c.c_mma = c.red + kNoAllocMaxModel;
+    c.cn = c.c_mma + kNoAllocMaxModel;
+    c.h = c.cn + kNoAllocMaxK;
+    c.cmax2 = c.h + (kNoAllocMaxK + 8);
+    c.recheck = reinterpret_cast<unsigned long long *>(c.cmax2 + 1);
+    nd.ready = true;
+    return FMLK_OK;
+}
+} // namespace
+
+extern "C" int32_t fmlk_local_partials_noalloc(int32_t device, void *cuda_stream, const double *rows_dev, int64_t n,
+                                               int32_t d, const double *centroids_dev, int32_t k,
+                                               double *out_sums_dev, double *out_counts_dev) {
+    if (device < 0 || device >= kNoAllocMaxDevices) return fail(nullptr, FMLK_ERR_INVALID_ARG, "device index out of range");
+    if (k < 1 || d < 1 || n < 0) return fail(nullptr, FMLK_ERR_INVALID_ARG, "bad k / d / n");
+    if ((size_t)k * d + k > kNoAllocMaxModel || k > kNoAllocMaxK)
+        return fail(nullptr, FMLK_ERR_INVALID_ARG,
+                    "model too large for the allocation-free entry point: k*d + k must be <= 8192 and k <= 2048; "
+                    "use fmlk_local_partials on a context instead");
+    if (!centroids_dev || !out_sums_dev || !out_counts_dev || (n > 0 && !rows_dev))
+        return fail(nullptr, FMLK_ERR_INVALID_ARG, "null device pointer");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, cudaGetErrorString(e));
+    int rc = noalloc_setup(device);
+    if (rc) return rc;
+    fmlk_ctx *ctx = &g_noalloc_dev[device].ctx;
+    ctx->stream = (cudaStream_t)cuda_stream;
+    ctx->k = k;
+    ctx->md = d;
+    ctx->d = d;
+    ctx->n_total = 0;
+    ctx->centroids = const_cast<double *>(centroids_dev); // read only
+    const size_t kd = (size_t)k * d;
+    // the array keeps whatever the previous call left: the partial sums are cleared inside
+    // local_round, the replay counter here
+    CK(nullptr, cudaMemsetAsync(ctx->recheck, 0, sizeof(unsigned long long), ctx->stream));
+    if (n > 0) {
+        if ((rc = local_round(ctx, rows_dev, n))) {
+            g_static_error = ctx->err;
+            return rc;
+        }
+    } else {
+        CK(nullptr, cudaMemsetAsync(ctx->red, 0, (kd + k) * sizeof(double), ctx->stream));
+    }
+    CK(nullptr, cudaMemcpyAsync(out_sums_dev, ctx->red, kd * sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream));
+    CK(nullptr, cudaMemcpyAsync(out_counts_dev, ctx->red + kd, (size_t)k * sizeof(double), cudaMemcpyDeviceToDevice,
+                            ctx->stream));
+    return FMLK_OK;
+}

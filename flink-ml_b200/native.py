@@ -54,6 +54,7 @@ SIGNATURES = {
     "fmlk_train_round": (_i32, [_vp, _vp, _vp]),
     "fmlk_fit": (_i32, [_vp, _i32, _vp, _vp]),
     "fmlk_local_partials": (_i32, [_vp, _vp, _vp]),
+    "fmlk_local_partials_noalloc": (_i32, [_i32, _vp, _vp, _i64, _i32, _vp, _i32, _vp, _vp]),
     "fmlk_get_model": (_i32, [_vp, _vp, _vp]),
     "fmlk_predict": (_i32, [_vp, _vp, _i64, _i32, _vp]),
     "fmlk_predict_dev": (_i32, [_vp, _vp, _i64, _i32, _vp]),
@@ -124,6 +125,13 @@ def measure_fp64_peaks(device=0, ms=200.0):
     a, b = _f64(), _f64()
     _check(lib().fmlk_measure_fp64_peaks(int(device), float(ms), C.byref(a), C.byref(b)))
     return a.value, b.value
+
+
+def local_partials_noalloc(device, stream, rows_ptr, n, d, centroids_ptr, k, out_sums_ptr, out_counts_ptr):
+    """fmlk_local_partials_noalloc: (sums, counts) of n device rows against k device centroids without
+    any device allocation (fixed scratch inside the library; k*d + k <= 8192).  Asynchronous on `stream`."""
+    _check(lib().fmlk_local_partials_noalloc(int(device), stream, rows_ptr, int(n), int(d), centroids_ptr, int(k),
+                                             out_sums_ptr, out_counts_ptr))
 
 
 def rows_on_task(num_values, task, num_tasks):

@@ -112,6 +112,32 @@ int32_t fmlk_fit(fmlk_ctx *ctx, int32_t max_iter, double *out_centroids, double 
  * reduction: the record emitted at KMeans.java:297.  Does not change the centroids. */
 int32_t fmlk_local_partials(fmlk_ctx *ctx, double *out_sums, int64_t *out_counts);
 
+/* The same (sums, counts) for callers that must not allocate device memory.  It has no counterpart
+ * in the reference; it exists for two kinds of host:
+ *   - a task manager that has handed the GPU's whole memory budget to its own pool (Flink-style
+ *     managed memory, RMM, a framework's caching allocator): a cudaMalloc made behind that pool's
+ *     back can fail, or succeed and starve the pool;
+ *   - a latency-critical operator thread: cudaMalloc and cudaFree synchronise the whole device,
+ *     which stalls every other stream the process is running.
+ * The call allocates nothing and frees nothing.  All scratch (per-CTA partial sums, centroid
+ * norms, a sanitised centroid copy) is a fixed array inside the library, about 10.8 MB that every
+ * GPU which loads the library holds until the process exits.  In exchange the model is limited:
+ * k*d + k <= 8192 and k <= 2048 (e.g. k=100 x d=64, k=1000 x d=7); larger models are rejected with
+ * FMLK_ERR_INVALID_ARG and should use fmlk_local_partials on a context.
+ *   rows_dev        n x d rows, device memory (caller-owned, only read)
+ *   centroids_dev   k x d centroids, device memory (only read)
+ *   out_sums_dev    k x d sums, device memory; out_counts_dev: k counts as doubles, device memory
+ * The work is enqueued on cuda_stream (NULL: the default stream) and the outputs are valid once
+ * that stream has completed; the call itself does not wait.  The first call on each device also
+ * looks up the device address of the scratch array and sets a kernel attribute: make that first
+ * call before any stream capture begins.  Every call uses the same array, which still holds the
+ * previous call's data: what must start at zero is cleared on the stream first, and two calls whose
+ * GPU work overlaps (different streams, or different threads) race on it -- keep them ordered.
+ * Errors are reported through fmlk_last_error(NULL) of the calling thread. */
+int32_t fmlk_local_partials_noalloc(int32_t device, void *cuda_stream, const double *rows_dev, int64_t n,
+                                    int32_t d, const double *centroids_dev, int32_t k,
+                                    double *out_sums_dev, double *out_counts_dev);
+
 /* Current centroids (k x d) and weights (k) as held on the device. */
 int32_t fmlk_get_model(fmlk_ctx *ctx, double *out_centroids, double *out_weights);
 

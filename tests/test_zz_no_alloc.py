@@ -1,0 +1,76 @@
+"""The allocation-free entry point (fmlk_local_partials_noalloc) against the ordinary one.
+
+Some hosts of this library cannot let it call cudaMalloc: a task manager that has given the whole
+GPU memory budget to its own pool, or an operator thread that cannot afford the device-wide
+synchronisation cudaMalloc/cudaFree imply.  For them the library keeps a fixed scratch array of its
+own (about 10.8 MB per GPU) and offers one entry point that uses only that array plus the caller's
+input and output buffers.  This test calls it through the C ABI twice in a row -- the second call
+with a different shape, so anything the first call left in the shared array would show -- and
+checks both results against fmlk_local_partials on a context (counts equal, sums to 1e-12
+relative: the two paths add in the same order, the tolerance is the one the other tests use).
+
+Collected last (file name) so that a failure here cannot hide any other test under -x."""
+import numpy as np
+import pytest
+
+from flink_ml_b200 import native
+
+pytestmark = pytest.mark.gpu
+
+SUM_RTOL = 1e-12
+
+
+def _reference(x, cent):
+    with native.Context(0) as ctx:
+        ctx.append_points(x)
+        ctx.set_centroids(cent)
+        return ctx.local_partials()
+
+
+def _noalloc(torch, x, cent):
+    dev = torch.device("cuda", 0)
+    xd = torch.from_numpy(x).to(dev)
+    cd = torch.from_numpy(cent).to(dev)
+    k, d = cent.shape
+    sums = torch.full((k, d), float("nan"), dtype=torch.float64, device=dev)
+    counts = torch.full((k,), float("nan"), dtype=torch.float64, device=dev)
+    torch.cuda.synchronize()
+    free_before, _ = torch.cuda.mem_get_info(0)
+    stream = torch.cuda.current_stream()
+    native.local_partials_noalloc(0, stream.cuda_stream, xd.data_ptr(), x.shape[0], d, cd.data_ptr(), k,
+                                  sums.data_ptr(), counts.data_ptr())
+    stream.synchronize()
+    free_after, _ = torch.cuda.mem_get_info(0)
+    return sums.cpu().numpy(), counts.cpu().numpy(), free_before, free_after
+
+
+def test_noalloc_matches_context_path_twice():
+    import torch
+    rng = np.random.default_rng(3)
+    # warm-up call: the first call on a device does the one-time set-up
+    _noalloc(torch, rng.random((64, 8)), rng.random((4, 8)))
+    shapes = [(30000, 64, 100), (4099, 7, 5)]  # config-2 shape, then a smaller ragged one
+    for n, d, k in shapes:
+        x = rng.random((n, d))
+        cent = x[rng.choice(n, k, replace=False)].copy()
+        cent[0] = cent[1]  # an exact tie: rows equal to these centroids take the exact replay
+        want_sums, want_counts = _reference(x, cent)
+        sums, counts, free_before, free_after = _noalloc(torch, x, cent)
+        assert np.array_equal(counts, want_counts.astype(np.float64))
+        assert np.allclose(sums, want_sums, rtol=SUM_RTOL, atol=0)
+        assert free_after == free_before  # nothing was allocated or freed on the device
+    # an empty batch gives zeros, not the previous call's numbers
+    sums, counts, _, _ = _noalloc(torch, np.empty((0, 7)), rng.random((5, 7)))
+    assert not sums.any() and not counts.any()
+
+
+def test_noalloc_rejects_models_beyond_the_limit():
+    import torch
+    dev = torch.device("cuda", 0)
+    x = torch.zeros((16, 64), dtype=torch.float64, device=dev)
+    cent = torch.zeros((200, 64), dtype=torch.float64, device=dev)  # 200*64 + 200 > 8192
+    out_s = torch.zeros((200, 64), dtype=torch.float64, device=dev)
+    out_c = torch.zeros((200,), dtype=torch.float64, device=dev)
+    with pytest.raises(native.IllegalArgumentError, match="too large for the allocation-free entry point"):
+        native.local_partials_noalloc(0, None, x.data_ptr(), 16, 64, cent.data_ptr(), 200, out_s.data_ptr(),
+                                      out_c.data_ptr())
