@@ -266,3 +266,33 @@ def test_g7_model_bytes_round_trip():
     # empty model
     c3, w3, _ = O.model_decode(O.model_encode(np.empty((0, 0)), np.empty(0)))
     assert c3.shape[0] == 0 and w3.size == 0
+
+
+# ---------------------------------------------------------------- the committed fixture file
+def test_committed_golden_fixture_file():
+    """tests/golden/reference_test_vectors.json holds the same literals (for readers and for
+    other language bindings); the oracle must reproduce every one of them."""
+    import json
+    import os
+    g = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden",
+                                    "reference_test_vectors.json")))
+    g1 = g["G1_DistanceMeasureTest"]
+    cent = np.array(g1["centroids"], dtype=float)
+    assert O.find_closest(cent, g1["point_a_sparse_densified"]) == g1["closest_a"]
+    assert O.find_closest(cent, g1["point_b"]) == g1["closest_b"]
+    assert O.distance(g1["point_a_sparse_densified"], g1["point_b"]) == pytest.approx(g1["distance_a_b"], abs=g1["tolerance"])
+    b = g["BLASTest"]
+    assert O.ddot(b["x"], b["y"]) == pytest.approx(b["dot"], abs=b["tolerance"])
+    assert O.dnrm2(b["x"]) ** 2 == pytest.approx(b["norm2_x_squared"], abs=1e-6)
+    g2 = g["G2_KMeansTest"]
+    data = np.array(g2["data"])
+    c, _ = O.fit([data], data[[0, 3]], g2["maxIter"])
+    assert np.allclose(c[np.argsort(c[:, 0])], g2["expected_centroids_sorted_by_x"], atol=g2["tolerance"])
+    g4 = g["G4_OnlineKMeansTest_getModelData"]
+    c0, w0 = O.random_model_data(2, 2, 0.0, 0)
+    assert c0.tolist() == g4["init_centroids_from_java_util_Random_0"]
+    c, w = O.online_round(np.array(g4["trainData1"]), c0, w0, g4["decayFactor"], g4["parallelism"])
+    assert np.allclose(c[np.argsort(c[:, 0])], g4["expected_centroids_sorted_by_x"], atol=g4["tolerance"])
+    assert np.allclose(w, g4["expected_weights"], atol=g4["tolerance"])
+    g8 = g["G8_param_defaults"]
+    assert O.KMEANS_DEFAULT_SEED == g8["KMeans"]["seed"] and O.ONLINE_KMEANS_DEFAULT_SEED == g8["OnlineKMeans"]["seed"]
