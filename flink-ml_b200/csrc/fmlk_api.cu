@@ -11,6 +11,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <cmath>
 #include <new>
 #include <string>
 #include <vector>
@@ -209,13 +210,16 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     const int force_w = env_int("FMLK_TUNE_W", 0), force_xs = env_int("FMLK_TUNE_XS", 0);
     const size_t budget = ctx->smem_optin;
     // few centroids: HBM-bound, favour a prefetched second row tile per warp;
-    // many centroids: FP64-bound, three MMA warps per scheduler with one tile each
-    // (at most 12 warps of 32 threads: the kernel is built for 384 threads so that each may hold 160
-    // registers -- the double-buffered fragments of the MMA loop need more than 128)
-    static const int small_k[][2] = {{10, 2}, {10, 1}, {8, 1}, {4, 1}};
-    static const int large_k[][2] = {{10, 1}, {8, 1}, {4, 1}, {4, 1}};
-    const int(*cand)[2] = (c.k_pad <= 32) ? small_k : large_k;
-    const int ncand = 4;
+    // many centroids: FP64-bound; a warp is blocked for ~20 cycles after each DMMA it issues, so the
+    // tensor pipe (one DMMA per 16 cycles) needs several warps per scheduler inside the MMA loop.
+    // (at most 16 warps of 32 threads: the kernel is built for 512 threads x 128 registers)
+    static const int small_acc[][2] = {{14, 2}, {14, 1}, {12, 1}, {8, 1}, {4, 1}};
+    static const int large_acc[][2] = {{14, 1}, {12, 1}, {10, 1}, {8, 1}, {4, 1}};
+    static const int small_pred[][2] = {{16, 2}, {16, 1}, {12, 1}, {8, 1}, {4, 1}};
+    static const int large_pred[][2] = {{16, 1}, {12, 1}, {8, 1}, {4, 1}, {4, 1}};
+    const bool small = c.k_pad <= 32;
+    const int(*cand)[2] = accum ? (small ? small_acc : large_acc) : (small ? small_pred : large_pred);
+    const int ncand = 5;
     for (int pass = 0; pass < 2; pass++) {
         const bool sums = accum && pass == 0;
         if (!accum && pass == 1) break;
@@ -235,19 +239,33 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
             }
         }
     }
-    // streaming: 8 MMA warps, one row stage, the rest of shared memory split into two centroid tiles
-    c.warps = 8;
+    // streaming: one row stage per MMA warp, the rest of shared memory split into two centroid tiles.
+    // More MMA warps keep the tensor pipe fed but leave less room for the centroid tiles (shorter
+    // lock-step phases, more barriers): take the warp count with the largest warps x min(tile, 64).
     c.xs = 1;
     c.sums_in_smem = 0;
     c.n_partials = 1;
-    size_t fixed = smem_bytes(c.warps, c.acc_warps, c.xs, c.S, k, d, c.k_pad, 0, 2, false);
-    if (fixed + 2 * 8 * (size_t)c.S * 8 > budget)
+    int best_w = 0, best_nc = 0, best_score = -1;
+    for (int w = 12; w >= 4; w -= 2) {
+        if (force_w && w != force_w) continue;
+        if ((w + c.acc_warps) * 32 > 512) continue;
+        size_t fixed = smem_bytes(w, c.acc_warps, c.xs, c.S, k, d, c.k_pad, 0, 2, false);
+        if (fixed + 2 * 8 * (size_t)c.S * 8 > budget) continue;
+        int nc = (int)((budget - fixed) / (2 * (size_t)c.S * 8));
+        nc &= ~7;
+        nc = std::min(nc, c.k_pad);
+        const int score = w * std::min(nc, 64);
+        if (score > best_score) {
+            best_score = score;
+            best_w = w;
+            best_nc = nc;
+        }
+    }
+    if (best_w == 0)
         return fail(ctx, FMLK_ERR_INVALID_ARG, "vector dimension too large for the shared-memory tiling");
-    int nc = (int)((budget - fixed) / (2 * (size_t)c.S * 8));
-    nc &= ~7;
-    nc = std::min(nc, c.k_pad);
-    c.nc_tile = nc;
-    c.n_ctiles = (c.k_pad + nc - 1) / nc;
+    c.warps = best_w;
+    c.nc_tile = best_nc;
+    c.n_ctiles = (c.k_pad + best_nc - 1) / best_nc;
     c.smem = smem_bytes(c.warps, c.acc_warps, c.xs, c.S, k, d, c.k_pad, c.nc_tile, c.n_ctiles, false);
     *out = c;
     return FMLK_OK;
@@ -287,7 +305,7 @@ int ensure_model(fmlk_ctx *ctx, int k, int d) {
     if ((rc = dev_alloc(ctx, &ctx->weights, (size_t)k))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->cn, (size_t)k))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->h, (size_t)k + 8))) return rc;
-    if ((rc = dev_alloc(ctx, &ctx->cmax2, (size_t)1))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->cmax2, (size_t)2))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->red, len))) return rc;
     if ((rc = dev_alloc(ctx, &ctx->local_model, len))) return rc;
     if (ctx->world > 1 && (rc = dev_alloc(ctx, &ctx->gathered, len * ctx->world))) return rc;
@@ -377,6 +395,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.nc_tile = cfg.nc_tile;
     p.n_ctiles = cfg.n_ctiles;
     p.thr_coef = 8.0 * (2.0 * ctx->md + 16.0) * 0x1.0p-53;
+    p.thr_coef_exp = ilogb(p.thr_coef) + 1;
     p.labels = labels;
     p.partials = accum ? ctx->partials : nullptr;
     p.n_partials = cfg.n_partials;
@@ -1134,7 +1153,7 @@ int noalloc_setup(int device) {
     c.cn = c.c_mma + kNoAllocMaxModel;
     c.h = c.cn + kNoAllocMaxK;
     c.cmax2 = c.h + (kNoAllocMaxK + 8);
-    c.recheck = reinterpret_cast<unsigned long long *>(c.cmax2 + 1);
+    c.recheck = reinterpret_cast<unsigned long long *>(c.cmax2 + 2);
     nd.ready = true;
     return FMLK_OK;
 }

@@ -41,13 +41,14 @@ struct AssignParams {
     const double *c;     // k x d centroids (as given: the exact replay reads these)
     const double *c_mma; // k x d centroids for the tensor-core pass: dead ones replaced by zero rows
     const double *cn;    // k norms, reference arithmetic
-    const double *h;     // k_pad: |c|^2/2 ; +inf beyond k
-    const double *cmax2; // max finite |c|^2
+    const double *h;     // k_pad: -|c|^2/2 ; -inf beyond k and for dead centroids
+    const double *cmax2; // max finite |c|^2 ; cmax2[1] holds ceil(log2(cmax2)) as a double
     int32_t k;
     int32_t k_pad;    // k rounded up to 8
     int32_t nc_tile;  // centroids per shared-memory tile (multiple of 8)
     int32_t n_ctiles; // 1: all centroids stay resident in shared memory
     double thr_coef;  // 8 (2d+16) 2^-53
+    int32_t thr_coef_exp; // ceil(log2(thr_coef))
     int32_t *labels;  // n, or null
     double *partials; // [n_partials][k*d + k], or null: no accumulation (predict)
     int32_t n_partials;
@@ -334,22 +335,23 @@ __device__ __forceinline__ void mma_group_barrier(int nthreads) {
 // time, so the last, partial chunk of a centroid tile gets code with exactly its number of tiles.
 // xa0/xa1: shared-memory byte addresses of this lane's A fragments (rows frow, frow+8, k index fk);
 // cb: of its B fragment in the chunk's first n8 tile; tstride: bytes between n8 tiles;
-// hcol: &h[first column this lane owns]; col0: that column.
-// with_nsq (warp-uniform): also accumulate |x|^2 of the lane's fragment elements (first chunk of a tile).
+// hcol: &(-h)[first column this lane owns]; col0: that column.
+// with_nsq (warp-uniform): also track the largest |x| (as the high word of its bits) over the lane's
+// fragment elements -- integer work; anything on the FP64 pipe outside the DMMAs waits behind them.
 //
 // Software pipeline: the fragments of k-step s+1 are loaded while the 16 DMMAs of k-step s issue,
 // one load next to each pair of DMMAs, so the FP64 tensor pipe never waits for shared memory.
 template <int CNT>
 __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned cb, unsigned tstride, int ksteps,
-                                          const double *hcol, int col0, Top2 &t0, Top2 &t1, double &nsq0,
-                                          double &nsq1, bool with_nsq, int debug_skip = 0) {
+                                          const double *hcol, int col0, Top2 &t0, Top2 &t1, int &mx0,
+                                          int &mx1, bool with_nsq, int debug_skip = 0) {
     double acc0[CNT][2], acc1[CNT][2];
     unsigned bj[CNT];
 #pragma unroll
     for (int j = 0; j < CNT; j++) {
         // accumulators start at -|c|^2/2, so the tile comes out as x.c - |c|^2/2
-        const double h0 = -hcol[j * 8];
-        const double h1 = -hcol[j * 8 + 1];
+        const double h0 = hcol[j * 8];
+        const double h1 = hcol[j * 8 + 1];
         acc0[j][0] = h0;
         acc0[j][1] = h1;
         acc1[j][0] = h0;
@@ -368,8 +370,8 @@ __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned c
 #define FMLK_KSTEP(A0C, A1C, BC, A0N, A1N, BN, OFF)                                      \
     {                                                                                     \
         if (with_nsq) {                                                                   \
-            nsq0 = fma(A0C, A0C, nsq0);                                                   \
-            nsq1 = fma(A1C, A1C, nsq1);                                                   \
+            mx0 = max(mx0, __double2hiint(A0C) & 0x7fffffff);                             \
+            mx1 = max(mx1, __double2hiint(A1C) & 0x7fffffff);                             \
         }                                                                                 \
         lds_f64_into(A0N, xa0 + (OFF));                                                   \
         lds_f64_into(A1N, xa1 + (OFF));                                                   \
@@ -394,8 +396,8 @@ __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned c
     }
     if (ks < ksteps) { // odd number of k-steps: the last one is already in the `c` fragments
         if (with_nsq) {
-            nsq0 = fma(a0c, a0c, nsq0);
-            nsq1 = fma(a1c, a1c, nsq1);
+            mx0 = max(mx0, __double2hiint(a0c) & 0x7fffffff);
+            mx1 = max(mx1, __double2hiint(a1c) & 0x7fffffff);
         }
 #pragma unroll
         for (int j = 0; j < CNT; j++) {
@@ -434,7 +436,7 @@ __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned c
 // Centroids are resident in shared memory when they fit (n_ctiles == 1); otherwise the MMA warps
 // stream centroid tiles from L2 through two buffers, in lock-step (named barrier 1).
 template <bool ACCUM>
-__global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
+__global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
@@ -488,7 +490,8 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
     if (warp < W) {
         // =============================== MMA warp ===============================
         const bool vec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.x) & 15) == 0);
-        const double cmax2 = *p.cmax2;
+        const int cmax2_exp = (int)p.cmax2[1]; // ceil(log2(max finite |c|^2))
+        const int dpad_exp = 32 - __clz(4 * p.ksteps); // > log2(d rounded up to 4)
         const int64_t gw = (int64_t)blockIdx.x * W + warp;
         const int frow = lane >> 2; // fragment row / B-fragment column within an 8-tile
         const int fk = lane & 3;    // fragment k index
@@ -572,7 +575,7 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
             if (active && !(p.debug_skip >= 2 && it > 0 && xs == 1)) x_wait(stage);
 
             Top2 t0 = top2_init(), t1 = top2_init();
-            double nsq0 = 0.0, nsq1 = 0.0;
+            int mx0 = 0, mx1 = 0; // high words of the largest |x| in the two rows this quad owns
 
             for (int ct = 0; ct < p.n_ctiles; ct++) {
                 const double *Ct = Cs + (size_t)cbuf * ctile_elems;
@@ -615,7 +618,7 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
                         const int col0 = ct_base + ch * 8 + fk * 2;
                         const bool first = (ct == 0 && ch == 0); // |x|^2 rides along with the first chunk
 #define FMLK_CHUNK(N) \
-    case N: mma_chunk<N>(xa0, xa1, cb, tstride, p.ksteps, hs + col0, col0, t0, t1, nsq0, nsq1, first, p.debug_skip); break;
+    case N: mma_chunk<N>(xa0, xa1, cb, tstride, p.ksteps, hs + col0, col0, t0, t1, mx0, mx1, first, p.debug_skip); break;
                         switch (cnt) {
                             FMLK_CHUNK(8) FMLK_CHUNK(7) FMLK_CHUNK(6) FMLK_CHUNK(5)
                             FMLK_CHUNK(4) FMLK_CHUNK(3) FMLK_CHUNK(2) FMLK_CHUNK(1)
@@ -632,14 +635,27 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
                 top2_merge_xor(t0, 2);
                 top2_merge_xor(t1, 1);
                 top2_merge_xor(t1, 2);
-                nsq0 += __shfl_xor_sync(0xffffffffu, nsq0, 1);
-                nsq0 += __shfl_xor_sync(0xffffffffu, nsq0, 2);
-                nsq1 += __shfl_xor_sync(0xffffffffu, nsq1, 1);
-                nsq1 += __shfl_xor_sync(0xffffffffu, nsq1, 2);
+                mx0 = max(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+                mx0 = max(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+                mx1 = max(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+                mx1 = max(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
 
-                // decision margin in squared-distance units: D = |x|^2 - 2 v
-                const bool ok0 = 2.0 * top2_margin(t0) > p.thr_coef * (nsq0 + cmax2);
-                const bool ok1 = 2.0 * top2_margin(t1) > p.thr_coef * (nsq1 + cmax2);
+                // Decision margin in score units (D = |x|^2 - 2 v, so 2 * margin_v is the gap in squared
+                // distance) against a power-of-two upper bound of the rounding threshold
+                //   thr = coef * (|x|^2 + |c|max^2) <= 2^(coef_exp + 1 + max(2(E+1) + log2 d, cmax2_exp)),
+                // E = exponent of the row's largest |x_i|.  Built from integer fields: one FP64
+                // subtract and one compare per row is all that touches the FP64 pipe here.
+                auto row_ok = [&](const Top2 &t, int mx) -> bool {
+                    if (mx >= 0x7ff00000) return false; // Inf / NaN in the row
+                    const int ex = 2 * ((mx >> 20) - 1023 + 1) + dpad_exp;
+                    int te = p.thr_coef_exp + 1 + max(ex, cmax2_exp) + 1023;
+                    if (te >= 2047) return false;
+                    te = max(te, 1);
+                    const double thr_ub = __hiloint2double(te << 20, 0);
+                    return 2.0 * top2_margin(t) > thr_ub;
+                };
+                const bool ok0 = row_ok(t0, mx0);
+                const bool ok1 = row_ok(t1, mx1);
                 const bool flag0 = !ok0 && (frow < rows_valid) && !p.debug_skip;
                 const bool flag1 = !ok1 && (frow + 8 < rows_valid) && !p.debug_skip;
                 if (fk == 0) {
@@ -795,10 +811,10 @@ __global__ void __launch_bounds__(384, 1) assign_kernel(const AssignParams p) {
 // per-round small kernels
 
 // VectorWithNorm of every centroid (KMeans.java:279-282) in reference arithmetic, plus what the
-// assign kernel's tensor-core pass needs: h = |c|^2/2 (+inf for padding) and the largest finite
+// assign kernel's tensor-core pass needs: h = -|c|^2/2 (-inf for padding) and the largest finite
 // |c|^2.  A centroid whose |c|^2 is not finite (NaN after its cluster emptied, Inf, or an overflow)
 // can never win the Java scan (its distance is NaN or +Inf, and `<` is strict): it is "dead".  For
-// the tensor-core pass a dead centroid becomes a zero row with h = +inf in c_mma, so it scores -inf
+// the tensor-core pass a dead centroid becomes a zero row with h = -inf in c_mma, so it scores -inf
 // instead of NaN; the exact replay keeps reading the original centroids.
 __global__ void prep_centroids_kernel(const double *c, int k, int k_pad, int d, int fma_mode, double *cn,
                                       double *h, double *cmax2, double *c_mma) {
@@ -809,11 +825,11 @@ __global__ void prep_centroids_kernel(const double *c, int k, int k_pad, int d, 
             const double ss = ref_sumsq(c + (size_t)j * d, d, fma_mode);
             cn[j] = sqrt(ss);
             const bool live = isfinite(ss);
-            h[j] = live ? 0.5 * ss : INFINITY;
+            h[j] = live ? -0.5 * ss : -INFINITY; // stored negated: the accumulators start from it
             if (live && ss > mx) mx = ss;
             for (int i = 0; i < d; i++) c_mma[(size_t)j * d + i] = live ? c[(size_t)j * d + i] : 0.0;
         } else {
-            h[j] = INFINITY;
+            h[j] = -INFINITY;
         }
     }
     red[threadIdx.x] = mx;
@@ -822,7 +838,11 @@ __global__ void prep_centroids_kernel(const double *c, int k, int k_pad, int d, 
         if (threadIdx.x < s) red[threadIdx.x] = fmax(red[threadIdx.x], red[threadIdx.x + s]);
         __syncthreads();
     }
-    if (threadIdx.x == 0) *cmax2 = red[0];
+    if (threadIdx.x == 0) {
+        cmax2[0] = red[0];
+        // ceil(log2(cmax2)) for the power-of-two threshold bound (very negative when there is no live centroid)
+        cmax2[1] = red[0] > 0.0 ? (double)(ilogb(red[0]) + 1) : -1100.0;
+    }
 }
 
 // out[i] = sum over CTA slots b = 0..n_partials-1 of partials[b][i], in slot order.

@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libflinkml_kmeans_cuda.so")
+LIB_PATH = os.environ.get("FMLK_LIB_PATH") or os.path.join(_HERE, "lib", "libflinkml_kmeans_cuda.so")
 
 OK = 0
 ERR_INVALID_ARG, ERR_STATE, ERR_DIM, ERR_CUDA, ERR_NCCL, ERR_NOMEM = -1, -2, -3, -4, -5, -6
