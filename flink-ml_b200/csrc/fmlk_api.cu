@@ -213,7 +213,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     // many centroids: FP64-bound; a warp is blocked for ~20 cycles after each DMMA it issues, so the
     // tensor pipe (one DMMA per 16 cycles) needs several warps per scheduler inside the MMA loop.
     // (at most 16 warps of 32 threads: the kernel is built for 512 threads x 128 registers)
-    static const int small_acc[][2] = {{14, 2}, {14, 1}, {12, 1}, {8, 1}, {4, 1}};
+    static const int small_acc[][2] = {{12, 2}, {12, 1}, {8, 2}, {8, 1}, {4, 1}};
     static const int large_acc[][2] = {{14, 1}, {12, 1}, {10, 1}, {8, 1}, {4, 1}};
     static const int small_pred[][2] = {{16, 2}, {16, 1}, {12, 1}, {8, 1}, {4, 1}};
     static const int large_pred[][2] = {{16, 1}, {12, 1}, {8, 1}, {4, 1}, {4, 1}};
@@ -241,7 +241,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     }
     // streaming: one row stage per MMA warp, the rest of shared memory split into two centroid tiles.
     // More MMA warps keep the tensor pipe fed but leave less room for the centroid tiles (shorter
-    // lock-step phases, more barriers): take the warp count with the largest warps x min(tile, 64).
+    // lock-step phases, more barriers): take the warp count with the largest warps x min(tile, 32).
     c.xs = 1;
     c.sums_in_smem = 0;
     c.n_partials = 1;
@@ -254,7 +254,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
         int nc = (int)((budget - fixed) / (2 * (size_t)c.S * 8));
         nc &= ~7;
         nc = std::min(nc, c.k_pad);
-        const int score = w * std::min(nc, 64);
+        const int score = w * std::min(nc, 32);
         if (score > best_score) {
             best_score = score;
             best_w = w;

@@ -753,11 +753,44 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 const int rows = rows_all[w * xs + stage];
                 const double *Xt = Xall + (size_t)(w * xs + stage) * xtile_elems;
                 const int *lab = lab_all + (w * xs + stage) * kWarpRows;
+                const int *offp = off_all + (w * xs + stage) * kWarpRows;
+                if (rows > 0 && sums_smem && p.d <= cstride) {
+                    // common case, one column per lane: copy what the tile contributes into registers
+                    // (row offsets, this lane's column of the 16 rows, the label for the count), hand the
+                    // buffer straight back to its MMA warp -- it can refill it while the sums are updated --
+                    // and only then do the read-modify-writes.
+                    const bool has_col = c0 < p.d;
+                    const double *xb = Xt + (has_col ? c0 : 0);
+                    double *sb = sums_s + (has_col ? c0 : 0);
+                    int off[kWarpRows];
+                    double xv[kWarpRows], sv[kWarpRows];
+#pragma unroll
+                    for (int q = 0; q < kWarpRows / 4; q++) {
+                        const int4 o = *reinterpret_cast<const int4 *>(offp + 4 * q);
+                        off[4 * q + 0] = o.x;
+                        off[4 * q + 1] = o.y;
+                        off[4 * q + 2] = o.z;
+                        off[4 * q + 3] = o.w;
+                    }
+#pragma unroll
+                    for (int r = 0; r < kWarpRows; r++) xv[r] = xb[(size_t)r * S];
+                    const int my_label = (a == 0 && lane < rows) ? lab[lane] : -1;
+                    __syncwarp();
+                    if (lane == 0) st_release_smem(&seq_done[w * A + a], it_w + 1);
+                    // rows that count update distinct cells, the others fall into the scratch row (never
+                    // read): the 16 updates are independent and their latencies overlap
+                    if (has_col) {
+#pragma unroll
+                        for (int r = 0; r < kWarpRows; r++) sv[r] = sb[off[r]];
+#pragma unroll
+                        for (int r = 0; r < kWarpRows; r++) sb[off[r]] = sv[r] + xv[r];
+                    }
+                    if (my_label >= 0) atomicAdd(&counts_s[my_label], 1);
+                    continue;
+                }
                 if (rows > 0) {
-                    const int *offp = off_all + (w * xs + stage) * kWarpRows;
                     if (sums_smem) {
-                        // every row of the tile: rows that count update distinct cells, the others fall
-                        // into the scratch row (whose content is never read)
+                        // several columns per lane (d > 64): same updates, column by column
                         for (int c = c0; c < p.d; c += cstride) {
                             const double *xb = Xt + c;
                             double *sb = sums_s + c;
@@ -771,8 +804,6 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                                 off[4 * q + 2] = o.z;
                                 off[4 * q + 3] = o.w;
                             }
-                            // all loads, then all adds and stores: the 16 cells are distinct (or the
-                            // scratch row), so the updates are independent and their latencies overlap
 #pragma unroll
                             for (int r = 0; r < kWarpRows; r++) xv[r] = xb[(size_t)r * S];
 #pragma unroll
