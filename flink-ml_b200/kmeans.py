@@ -18,6 +18,7 @@ flink-ml-cuda module sketched in INTEGRATION.md.
 import json
 import os
 import time
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 
@@ -402,12 +403,14 @@ class KMeansModel(_KMeansModelParams):
 # ------------------------------------------------------------------------------------------
 # KMeans
 
-def select_random_centroids(ctx, cluster, k, seed):
+def select_random_centroids(ctx, cluster, k, seed, ids=None):
     """KMeans.selectRandomCentroids (KMeans.java:310-327) = DataStreamUtils.sample
     (DataStreamUtils.java:212-227) over the points already in the contexts' caches: a reservoir
     per subtask from Random(seed), then one reservoir from a fresh Random(seed) over the
-    subtasks' picks concatenated in subtask order."""
-    ids = native.reservoir(ctx.num_points(), k, seed)
+    subtasks' picks concatenated in subtask order.  `ids`: this subtask's stage-1 picks if the
+    caller has computed them already (they depend only on the row count)."""
+    if ids is None:
+        ids = native.reservoir(ctx.num_points(), k, seed)
     mine = ctx.get_points(ids) if ids.size else np.empty((0, max(ctx.d, 0)))
     if cluster.world == 1:
         return mine  # the second stage sees <= k elements and passes them through
@@ -453,16 +456,21 @@ class KMeans(_KMeansModelParams, _HasSeed):
         points = to_matrix(inputs[0].column(self.get_features_col()))  # row -> toDense(), KMeans.java:92-94
         ctx = cluster.context()
         ctx.clear_points()
-        ctx.append_points(points)
-        md = self._fit_cached(ctx, cluster)
+        # the sampler's pass over the subtask's element count is pure host work (java.util.Random):
+        # run it while the rows are copied to the device
+        with ThreadPoolExecutor(max_workers=1) as pool:
+            ids_future = pool.submit(native.reservoir, points.shape[0], self.get_k(), self.get_seed())
+            ctx.append_points(points)
+            ids = ids_future.result()
+        md = self._fit_cached(ctx, cluster, ids)
         ctx.clear_points()  # onIterationTerminated, KMeans.java:302-307
         model = KMeansModel(cluster).set_model_data(md.to_table())
         self._copy_params_to(model)
         return model
 
-    def _fit_cached(self, ctx, cluster):
+    def _fit_cached(self, ctx, cluster, ids=None):
         """The part of fit() after ingestion: initial centroids, maxIter rounds, model data."""
-        init = select_random_centroids(ctx, cluster, self.get_k(), self.get_seed())
+        init = select_random_centroids(ctx, cluster, self.get_k(), self.get_seed(), ids)
         if init.shape[0] == 0:
             raise IllegalStateError("no input points")
         ctx.set_centroids(init)
