@@ -86,7 +86,7 @@ struct Chunk {
 };
 
 struct LaunchCfg {
-    int warps, acc_warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid;
+    int warps, acc_warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid, private_sums;
     int acc_order, spin_ns, stagger_ns;
     size_t smem;
 };
@@ -182,12 +182,13 @@ int stride_for(int d) {
 }
 
 // Shared memory the assign kernel needs for a geometry (must mirror the carve-up in assign_kernel).
-size_t smem_bytes(int warps, int acc, int xs, int S, int k, int d, int k_pad, int nc_tile, int n_ctiles, bool sums) {
+size_t smem_bytes(int warps, int acc, int xs, int S, int k, int d, int k_pad, int nc_tile, int n_ctiles, bool sums,
+                  bool priv = false) {
     size_t dbl = (size_t)(n_ctiles > 1 ? 2 : 1) * nc_tile * S + k_pad + (size_t)warps * xs /* mbarriers */ +
                  (size_t)warps * xs * kWarpRows * S +
-                 (sums ? (((size_t)(k + 1) * d + 1) & ~(size_t)1) : 0);
-    size_t ints = (sums ? (size_t)k : 0) + 2 * (size_t)warps * xs * kWarpRows + (size_t)warps * xs + warps +
-                  (size_t)warps * acc;
+                 (priv ? ((((size_t)warps * k * d) + 1) & ~(size_t)1) : sums ? (((size_t)(k + 1) * d + 1) & ~(size_t)1) : 0);
+    size_t ints = (priv ? (size_t)warps * k : sums ? (size_t)k : 0) + 2 * (size_t)warps * xs * kWarpRows +
+                  (size_t)warps * xs + warps + (size_t)warps * acc;
     return dbl * 8 + ints * 4;
 }
 
@@ -220,6 +221,27 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     const bool small = c.k_pad <= 32;
     const int(*cand)[2] = accum ? (small ? small_acc : large_acc) : (small ? small_pred : large_pred);
     const int ncand = 5;
+    if (accum && small) {
+        // few centroids: every MMA warp keeps private sums (no accumulator warps, no hand-off)
+        static const int priv_cand[][2] = {{16, 2}, {16, 1}, {12, 2}, {12, 1}, {10, 1}, {8, 1}, {6, 1}, {4, 1}};
+        for (int i = 0; i < 8; i++) {
+            const int cw = force_w ? force_w : priv_cand[i][0], cx = force_xs ? force_xs : priv_cand[i][1];
+            size_t need = smem_bytes(cw, 0, cx, c.S, k, d, c.k_pad, c.k_pad, 1, true, true);
+            if (need <= budget && env_int("FMLK_TUNE_PRIVATE", 1)) {
+                c.warps = cw;
+                c.acc_warps = 0;
+                c.xs = cx;
+                c.nc_tile = c.k_pad;
+                c.n_ctiles = 1;
+                c.sums_in_smem = 1;
+                c.private_sums = 1;
+                c.n_partials = c.grid;
+                c.smem = need;
+                *out = c;
+                return FMLK_OK;
+            }
+        }
+    }
     for (int pass = 0; pass < 2; pass++) {
         const bool sums = accum && pass == 0;
         if (!accum && pass == 1) break;
@@ -404,6 +426,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.mma_warps = cfg.warps;
     p.acc_warps = cfg.acc_warps;
     p.acc_order = cfg.acc_order;
+    p.private_sums = cfg.private_sums;
     p.spin_ns = cfg.spin_ns;
     p.stagger_ns = cfg.stagger_ns;
     p.debug_skip = env_int("FMLK_TUNE_DEBUG_SKIP", 0);
@@ -450,6 +473,17 @@ int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
     ctx->total_launches++;
     CK(ctx, cudaGetLastError());
     return FMLK_OK;
+}
+
+// Geometry for labelling rows with the current model.
+struct PredictPlan {
+    LaunchCfg cfg{};
+};
+
+int plan_predict(fmlk_ctx *ctx, PredictPlan *pl) { return choose_cfg(ctx, ctx->k, ctx->md, false, &pl->cfg); }
+
+int run_predict(fmlk_ctx *ctx, const PredictPlan &pl, const double *x, int64_t n, int32_t *labels) {
+    return launch_assign(ctx, pl.cfg, x, n, labels, false);
 }
 
 int one_train_round(fmlk_ctx *ctx) {
@@ -781,11 +815,11 @@ int32_t fmlk_get_model(fmlk_ctx *ctx, double *out_centroids, double *out_weights
 }
 
 static int32_t predict_impl(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t *labels_dev) {
-    LaunchCfg cfg;
-    int rc = choose_cfg(ctx, ctx->k, ctx->md, false, &cfg);
+    PredictPlan pl;
+    int rc = plan_predict(ctx, &pl);
     if (rc) return rc;
     if ((rc = prep_centroids(ctx))) return rc;
-    return launch_assign(ctx, cfg, rows_dev, n, labels_dev, false);
+    return run_predict(ctx, pl, rows_dev, n, labels_dev);
 }
 
 int32_t fmlk_predict_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d, int32_t *out_labels_dev) {
@@ -810,14 +844,14 @@ int32_t fmlk_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t 
     const int64_t max_rows = std::max<int64_t>(1, ((int64_t)256 << 20) / ((int64_t)d * 8));
     const int64_t step = std::min(n, max_rows);
     if ((rc = ensure_stage(ctx, (size_t)step * d, (size_t)step))) return rc;
-    LaunchCfg cfg;
-    if ((rc = choose_cfg(ctx, ctx->k, ctx->md, false, &cfg))) return rc;
+    PredictPlan pl;
+    if ((rc = plan_predict(ctx, &pl))) return rc;
     if ((rc = prep_centroids(ctx))) return rc;
     for (int64_t off = 0; off < n; off += step) {
         const int64_t m = std::min(step, n - off);
         CK(ctx, cudaMemcpyAsync(ctx->stage_rows, rows_host + off * d, (size_t)m * d * sizeof(double),
                                 cudaMemcpyHostToDevice, ctx->stream));
-        if ((rc = launch_assign(ctx, cfg, ctx->stage_rows, m, ctx->stage_labels, false))) return rc;
+        if ((rc = run_predict(ctx, pl, ctx->stage_rows, m, ctx->stage_labels))) return rc;
         CK(ctx, cudaMemcpyAsync(out_labels_host + off, ctx->stage_labels, (size_t)m * sizeof(int32_t),
                                 cudaMemcpyDeviceToHost, ctx->stream));
     }
@@ -835,12 +869,12 @@ int32_t fmlk_predict_cached(fmlk_ctx *ctx, int32_t *out_labels_host) {
     if (ctx->d != ctx->md) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
     if (!out_labels_host) return fail(ctx, FMLK_ERR_INVALID_ARG, "labels is null");
     if ((rc = ensure_stage(ctx, 0, (size_t)ctx->n_total))) return rc;
-    LaunchCfg cfg;
-    if ((rc = choose_cfg(ctx, ctx->k, ctx->md, false, &cfg))) return rc;
+    PredictPlan pl;
+    if ((rc = plan_predict(ctx, &pl))) return rc;
     if ((rc = prep_centroids(ctx))) return rc;
     int64_t off = 0;
     for (const Chunk &ch : ctx->chunks) {
-        if ((rc = launch_assign(ctx, cfg, ch.ptr, ch.rows, ctx->stage_labels + off, false))) return rc;
+        if ((rc = run_predict(ctx, pl, ch.ptr, ch.rows, ctx->stage_labels + off))) return rc;
         off += ch.rows;
     }
     CK(ctx, cudaMemcpyAsync(out_labels_host, ctx->stage_labels, (size_t)ctx->n_total * sizeof(int32_t),
@@ -1077,11 +1111,11 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
     else cudaFuncGetAttributes(&fa, assign_kernel<false>);
     snprintf(out, (size_t)out_len,
              "regs=%d max_threads=%d local=%zu grid=%d block=%d smem=%zu mma_warps=%d acc_warps=%d xs=%d S=%d ksteps=%d k_pad=%d nc_tile=%d n_ctiles=%d "
-             "sums_in_smem=%d n_partials=%d acc_order=%d",
+             "sums_in_smem=%d n_partials=%d acc_order=%d private_sums=%d",
              fa.numRegs, fa.maxThreadsPerBlock, fa.localSizeBytes, c.grid, (c.warps + c.acc_warps) * 32, c.smem, c.warps,
              c.acc_warps, c.xs, c.S, c.ksteps, c.k_pad,
              c.nc_tile, c.n_ctiles,
-             c.sums_in_smem, c.n_partials, c.acc_order);
+             c.sums_in_smem, c.n_partials, c.acc_order, c.private_sums);
     return FMLK_OK;
 }
 

@@ -56,6 +56,8 @@ struct AssignParams {
     int32_t xs;       // row-tile stages per MMA warp (1 or 2; 2 only when n_ctiles == 1)
     int32_t mma_warps; // warps that load + multiply + label
     int32_t acc_warps; // warps that own columns of the sums (accumulate launches only)
+    int32_t private_sums; // 1: few centroids -- every MMA warp keeps its own k x d sums in shared memory and
+                          //    adds its own tiles' rows itself (no accumulator warps, no hand-off)
     int32_t acc_order; // 0: tiles are accumulated in the fixed order (round, warp): bit-reproducible sums
                        // 1: in arrival order: no head-of-line waiting, last bits vary from run to run
     int32_t spin_ns;   // back-off of the hand-off spin loops
@@ -441,7 +443,8 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int W = p.mma_warps;
-    const int A = ACCUM ? p.acc_warps : 0;
+    const bool priv = ACCUM && p.private_sums;
+    const int A = (ACCUM && !priv) ? p.acc_warps : 0;
     const int S = p.S;
     const int xs = p.xs;
     const int c_bufs = p.n_ctiles > 1 ? 2 : 1;
@@ -455,11 +458,14 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
     double *Xall = hs + p.k_pad + W * xs;
     double *sums_s = Xall + (size_t)W * xs * xtile_elems;
     // k rows of sums plus one scratch row that absorbs the updates of rows handled in pass 2
-    const size_t sums_elems = sums_smem ? (((size_t)(p.k + 1) * p.d + 1) & ~(size_t)1) : 0; // even: keeps off_all 16-byte aligned
+    // shared sums: k rows plus one scratch row; private sums: one k x d copy per MMA warp
+    const size_t sums_elems = priv ? ((((size_t)W * p.k * p.d) + 1) & ~(size_t)1)
+                                   : (sums_smem ? (((size_t)(p.k + 1) * p.d + 1) & ~(size_t)1) : 0); // even: 16-byte alignment
     int *off_all = reinterpret_cast<int *>(sums_s + sums_elems); // [W * xs][16], 16-byte aligned
     int *lab_all = off_all + W * xs * kWarpRows;                 // [W * xs][16]
     int *counts_s = lab_all + W * xs * kWarpRows;                // [k] when the sums are in shared memory
-    int *rows_all = counts_s + (sums_smem ? p.k : 0);            // [W * xs]
+    const int count_ints = priv ? W * p.k : (sums_smem ? p.k : 0);
+    int *rows_all = counts_s + count_ints;                       // [W * xs]
     int *seq_ready = rows_all + W * xs;                          // [W]
     int *seq_done = seq_ready + W;                               // [W * A]
 
@@ -467,7 +473,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
     {
         const size_t zero_elems = c_bufs * ctile_elems + p.k_pad + W * xs + (size_t)W * xs * xtile_elems + sums_elems;
         for (size_t i = threadIdx.x; i < zero_elems; i += blockDim.x) Cs[i] = 0.0;
-        const int zero_ints = 2 * W * xs * kWarpRows + (sums_smem ? p.k : 0) + W * xs + W + W * A;
+        const int zero_ints = 2 * W * xs * kWarpRows + count_ints + W * xs + W + W * A;
         for (int i = threadIdx.x; i < zero_ints; i += blockDim.x) off_all[i] = 0;
     }
     __syncthreads();
@@ -684,7 +690,19 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 __syncwarp();
                 if (p.labels != nullptr && lane < rows_valid) p.labels[row0 + lane] = lab_s[lane];
             }
-            if (ACCUM) {
+            if (ACCUM && priv) {
+                // few centroids: this warp's own sums.  Lane l owns columns l, l+32, ...; rows are added
+                // in row order (several rows of a tile usually share a label: same cell, program order)
+                __syncwarp();
+                double *mine = sums_s + (size_t)warp * p.k * p.d;
+                for (int r = 0; r < rows_valid; r++) {
+                    double *srow = mine + (size_t)lab_s[r] * p.d;
+                    const double *xrow = Xt + (size_t)r * S;
+                    for (int c = lane; c < p.d; c += 32) srow[c] += xrow[c];
+                }
+                if (lane < rows_valid) atomicAdd(&counts_s[warp * p.k + lab_s[lane]], 1);
+                __syncwarp();
+            } else if (ACCUM) {
                 // publish the tile to the accumulator warps.  Rows whose label already occurred earlier
                 // in the tile are first folded into that earlier row (in row order, in this warp's own
                 // buffer), so every row left points at a distinct sums row; folded rows and rows past
@@ -829,7 +847,22 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         }
     }
 
-    if (sums_smem) {
+    if (priv) {
+        // the warps' private sums, combined in warp order, added to this CTA's slot
+        __syncthreads();
+        const int model = p.k * p.d;
+        double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)model + p.k);
+        for (int i = threadIdx.x; i < model; i += blockDim.x) {
+            double acc = sums_s[i];
+            for (int w = 1; w < W; w++) acc += sums_s[(size_t)w * model + i];
+            slot[i] += acc;
+        }
+        for (int i = threadIdx.x; i < p.k; i += blockDim.x) {
+            int c = 0;
+            for (int w = 0; w < W; w++) c += counts_s[w * p.k + i];
+            slot[(size_t)model + i] += (double)c;
+        }
+    } else if (sums_smem) {
         // this CTA's partial, added to its own slot (plain read-modify-write: slot b belongs to CTA b)
         __syncthreads();
         double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
