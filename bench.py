@@ -248,7 +248,7 @@ def run_ours(args):
         roofline = {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_frac,
                     "peak_source": peak_src}
     roofline.update({
-        "traffic": None, "kernel": "fmlk::assign_kernel<true>", "ms_per_launch": assign_ms,
+        "traffic": None, "kernel": "fmlk::assign_kernel<1> (MODE 1: assign + accumulate)", "ms_per_launch": assign_ms,
         "launches_timed": prof["assign_launches"], "share_of_step": prof["assign_ms"] / total_ms,
         "hbm": {"achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_frac, "peak_source": peak_src},
         "fp64_tensor": {"achieved": tf, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tensor_frac},

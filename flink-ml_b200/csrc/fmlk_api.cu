@@ -442,8 +442,9 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
         e1 = next_event(ctx);
         if (e0 && e1) cudaEventRecord(e0, ctx->stream);
     }
-    if (accum) assign_kernel<true><<<grid, (cfg.warps + cfg.acc_warps) * 32, cfg.smem, ctx->stream>>>(p);
-    else assign_kernel<false><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
+    if (accum && cfg.private_sums) assign_kernel<2><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
+    else if (accum) assign_kernel<1><<<grid, (cfg.warps + cfg.acc_warps) * 32, cfg.smem, ctx->stream>>>(p);
+    else assign_kernel<0><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
     if (prof && e0 && e1) cudaEventRecord(e1, ctx->stream);
     ctx->assign_launches++;
     ctx->total_launches++;
@@ -600,9 +601,11 @@ int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
     if (e == cudaSuccess && major == 10) {
         // the assign kernel sizes its shared memory per launch, up to the opt-in maximum
-        e = cudaFuncSetAttribute(assign_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        e = cudaFuncSetAttribute(assign_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(assign_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            e = cudaFuncSetAttribute(assign_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     }
     if (e != cudaSuccess) {
         std::string m = std::string("device set-up: ") + cudaGetErrorString(e);
@@ -1107,8 +1110,9 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
     int rc = choose_cfg(ctx, k, d, accumulate != 0, &c);
     if (rc) return rc;
     cudaFuncAttributes fa{};
-    if (accumulate) cudaFuncGetAttributes(&fa, assign_kernel<true>);
-    else cudaFuncGetAttributes(&fa, assign_kernel<false>);
+    if (accumulate && c.private_sums) cudaFuncGetAttributes(&fa, assign_kernel<2>);
+    else if (accumulate) cudaFuncGetAttributes(&fa, assign_kernel<1>);
+    else cudaFuncGetAttributes(&fa, assign_kernel<0>);
     snprintf(out, (size_t)out_len,
              "regs=%d max_threads=%d local=%zu grid=%d block=%d smem=%zu mma_warps=%d acc_warps=%d xs=%d S=%d ksteps=%d k_pad=%d nc_tile=%d n_ctiles=%d "
              "sums_in_smem=%d n_partials=%d acc_order=%d private_sums=%d",
@@ -1168,7 +1172,9 @@ int noalloc_setup(int device) {
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     if (e == cudaSuccess) e = cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
     if (e == cudaSuccess && major == 10)
-        e = cudaFuncSetAttribute(assign_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        e = cudaFuncSetAttribute(assign_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess && major == 10)
+        e = cudaFuncSetAttribute(assign_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, std::string("device set-up: ") + cudaGetErrorString(e));
     if (major != 10) return fail(nullptr, FMLK_ERR_CUDA, "this build targets sm_100a (B200) only");
     if (sms > kNoAllocMaxSlots) return fail(nullptr, FMLK_ERR_INVALID_ARG, "device has more SMs than the scratch array has slots");

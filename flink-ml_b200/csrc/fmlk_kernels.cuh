@@ -437,13 +437,18 @@ __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned c
 //
 // Centroids are resident in shared memory when they fit (n_ctiles == 1); otherwise the MMA warps
 // stream centroid tiles from L2 through two buffers, in lock-step (named barrier 1).
-template <bool ACCUM>
+//
+// MODE 0: predict (labels only); 1: accumulate through the accumulator warps (or global atomics);
+// 2: accumulate into warp-private sums (small k).  Separate instantiations: the modes do not share
+// registers or schedules (folding mode 2 into mode 1 as a run-time branch cost mode 1 6 %).
+template <int MODE>
 __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
+    constexpr bool ACCUM = MODE != 0;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int W = p.mma_warps;
-    const bool priv = ACCUM && p.private_sums;
+    constexpr bool priv = MODE == 2;
     const int A = (ACCUM && !priv) ? p.acc_warps : 0;
     const int S = p.S;
     const int xs = p.xs;
