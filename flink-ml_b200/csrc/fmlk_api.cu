@@ -192,9 +192,8 @@ size_t smem_bytes(int warps, int acc, int xs, int S, int k, int d, int k_pad, in
     return dbl * 8 + ints * 4;
 }
 
-// accumulator warps: one per 32 columns, at most 2 (lanes then take several columns each); with 10
-// MMA warps that is 384 threads
-int acc_warps_for(int d) { return std::min(2, (d + 31) / 32); }
+// accumulator warps: G = min(2, ceil(d / 32)) column groups x 2 row halves
+int acc_warps_for(int d) { return 2 * std::min(2, (d + 31) / 32); }
 
 // Picks the launch geometry for (k, d).  Preference order: centroids resident in shared memory with
 // block-private sums; resident centroids with global-atomic sums; centroid tiles streamed from L2.
@@ -205,7 +204,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     c.k_pad = (k + 7) & ~7;
     c.grid = ctx->sm_count;
     c.acc_warps = accum ? acc_warps_for(d) : 0;
-    c.acc_order = env_int("FMLK_TUNE_ORDER", 0); // fixed order: reproducible sums (and measured faster)
+    c.acc_order = 0; // tiles are accumulated in the fixed order (round, warp): reproducible sums
     c.spin_ns = env_int("FMLK_TUNE_SPIN_NS", 40);
     c.stagger_ns = env_int("FMLK_TUNE_STAGGER_NS", 0);
     const int force_w = env_int("FMLK_TUNE_W", 0), force_xs = env_int("FMLK_TUNE_XS", 0);
@@ -215,7 +214,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     // tensor pipe (one DMMA per 16 cycles) needs several warps per scheduler inside the MMA loop.
     // (at most 16 warps of 32 threads: the kernel is built for 512 threads x 128 registers)
     static const int small_acc[][2] = {{12, 2}, {12, 1}, {8, 2}, {8, 1}, {4, 1}};
-    static const int large_acc[][2] = {{14, 1}, {12, 1}, {10, 1}, {8, 1}, {4, 1}};
+    static const int large_acc[][2] = {{12, 1}, {12, 1}, {10, 1}, {8, 1}, {4, 1}};
     static const int small_pred[][2] = {{16, 2}, {16, 1}, {12, 1}, {8, 1}, {4, 1}};
     static const int large_pred[][2] = {{16, 1}, {12, 1}, {8, 1}, {4, 1}, {4, 1}};
     const bool small = c.k_pad <= 32;
@@ -248,6 +247,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
         for (int i = 0; i < ncand; i++) {
             const int cw = force_w ? force_w : cand[i][0], cx = force_xs ? force_xs : cand[i][1];
             size_t need = smem_bytes(cw, c.acc_warps, cx, c.S, k, d, c.k_pad, c.k_pad, 1, sums);
+            if ((cw + c.acc_warps) * 32 > 512) continue;
             if (need <= budget) {
                 c.warps = cw;
                 c.xs = cx;

@@ -58,8 +58,7 @@ struct AssignParams {
     int32_t acc_warps; // warps that own columns of the sums (accumulate launches only)
     int32_t private_sums; // 1: few centroids -- every MMA warp keeps its own k x d sums in shared memory and
                           //    adds its own tiles' rows itself (no accumulator warps, no hand-off)
-    int32_t acc_order; // 0: tiles are accumulated in the fixed order (round, warp): bit-reproducible sums
-                       // 1: in arrival order: no head-of-line waiting, last bits vary from run to run
+    int32_t acc_order; // always 0: tiles are accumulated in the fixed order (round, warp): bit-reproducible sums
     int32_t spin_ns;   // back-off of the hand-off spin loops
     int32_t stagger_ns; // initial delay between the MMA warps of one scheduler (see assign_kernel)
     int32_t debug_skip; // experiments only: 1 = skip the per-element selection, 2 = also skip row loads
@@ -328,6 +327,11 @@ __device__ __forceinline__ int ld_acquire_smem(const int *p) {
 __device__ __forceinline__ void spin_until_at_least(const int *p, int target, unsigned ns) {
     while (ld_acquire_smem(p) < target) __nanosleep(ns);
 }
+// named barrier 2: the accumulator warps of a CTA (count = 32 x their number)
+__device__ __forceinline__ void acc_group_barrier(int threads) {
+    asm volatile("bar.sync 2, %0;" ::"r"(threads) : "memory");
+}
+
 __device__ __forceinline__ void mma_group_barrier(int nthreads) {
     asm volatile("bar.sync 1, %0;\n" ::"r"(nthreads) : "memory");
 }
@@ -738,117 +742,111 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         }
         cp_async_wait<0>();
         if (lane == 0 && local_rechecks && p.recheck_count) atomicAdd(p.recheck_count, local_rechecks);
-    } else if (ACCUM) {
+    } else if (ACCUM && !priv) {
         // =========================== accumulator warp ===========================
-        // sums[label] += row, counts[label]++ (KMeans.java:293-294).  Lane l of accumulator a owns
-        // columns a*32 + l, + 32*A, ...: no two threads ever touch the same cell.
+        // sums[label] += row, counts[label]++ (KMeans.java:293-294).  The A = 2 G accumulator warps
+        // split a tile by columns (G groups of 32 lanes: lane l of group g owns columns g*32 + l,
+        // + 32 G, ...) and by rows (half h adds rows 8h .. 8h+7).  The rows of a published tile point
+        // at distinct sums rows, so the two halves never touch the same cell within a tile; a named
+        // barrier per tile keeps them from running a tile apart.  Every FP64 add issued here queues
+        // behind the MMA warps' DMMAs on the scheduler's FP64 pipe (~50-80 cycles each): the chain of
+        // adds per warp and tile, not their number, is what bounds the accumulators.
+        constexpr int RH = kWarpRows / 2; // rows per half
         const int a = warp - W;
-        const int cstride = 32 * A;
-        const int c0 = a * 32 + lane;
-        // lane w < W keeps the number of tiles of MMA warp w consumed so far
-        int consumed = 0;
+        const int G = A >> 1;
+        const int g = a % G, h = a / G;
+        const int cstride = 32 * G;
+        const int c0 = g * 32 + lane;
+        const int rbase = h * RH;
+        int w = 0, it_w = 0; // tiles are taken in the fixed order (round, warp): reproducible sums
         const int64_t total_tiles_cta = rounds * W;
-        int next_w = 0;
         for (int64_t done_tiles = 0; done_tiles < total_tiles_cta; done_tiles++) {
-            int w;
-            if (p.acc_order == 0) {
-                w = next_w;
-                next_w = (next_w + 1 == W) ? 0 : next_w + 1;
-                spin_until_at_least(&seq_ready[w], __shfl_sync(0xffffffffu, consumed, w) + 1, (unsigned)p.spin_ns);
-            } else {
-                unsigned avail;
-                while (true) {
-                    const bool ready = (lane < W) && (ld_acquire_smem(&seq_ready[lane]) > consumed);
-                    avail = __ballot_sync(0xffffffffu, ready);
-                    if (avail) break;
-                    __nanosleep((unsigned)p.spin_ns);
-                }
-                // rotate the starting point so no warp is favoured
-                const unsigned rot = (avail >> next_w) | (avail << ((32 - next_w) & 31));
-                w = (next_w + __ffs(next_w ? rot : avail) - 1) % 32;
-                if (w >= W) w = __ffs(avail) - 1;
-                next_w = (w + 1 == W) ? 0 : w + 1;
-            }
-            const int it_w = __shfl_sync(0xffffffffu, consumed, w);
-            if (lane == w) consumed++;
+            spin_until_at_least(&seq_ready[w], it_w + 1, (unsigned)p.spin_ns);
             const int stage = (xs == 2) ? (it_w & 1) : 0;
-            {
-                const int rows = rows_all[w * xs + stage];
-                const double *Xt = Xall + (size_t)(w * xs + stage) * xtile_elems;
-                const int *lab = lab_all + (w * xs + stage) * kWarpRows;
-                const int *offp = off_all + (w * xs + stage) * kWarpRows;
-                if (rows > 0 && sums_smem && p.d <= cstride) {
-                    // common case, one column per lane: copy what the tile contributes into registers
-                    // (row offsets, this lane's column of the 16 rows, the label for the count), hand the
-                    // buffer straight back to its MMA warp -- it can refill it while the sums are updated --
-                    // and only then do the read-modify-writes.
-                    const bool has_col = c0 < p.d;
-                    const double *xb = Xt + (has_col ? c0 : 0);
-                    double *sb = sums_s + (has_col ? c0 : 0);
-                    int off[kWarpRows];
-                    double xv[kWarpRows], sv[kWarpRows];
-#pragma unroll
-                    for (int q = 0; q < kWarpRows / 4; q++) {
-                        const int4 o = *reinterpret_cast<const int4 *>(offp + 4 * q);
-                        off[4 * q + 0] = o.x;
-                        off[4 * q + 1] = o.y;
-                        off[4 * q + 2] = o.z;
-                        off[4 * q + 3] = o.w;
-                    }
-#pragma unroll
-                    for (int r = 0; r < kWarpRows; r++) xv[r] = xb[(size_t)r * S];
-                    const int my_label = (a == 0 && lane < rows) ? lab[lane] : -1;
-                    __syncwarp();
-                    if (lane == 0) st_release_smem(&seq_done[w * A + a], it_w + 1);
-                    // rows that count update distinct cells, the others fall into the scratch row (never
-                    // read): the 16 updates are independent and their latencies overlap
-                    if (has_col) {
-#pragma unroll
-                        for (int r = 0; r < kWarpRows; r++) sv[r] = sb[off[r]];
-#pragma unroll
-                        for (int r = 0; r < kWarpRows; r++) sb[off[r]] = sv[r] + xv[r];
-                    }
-                    if (my_label >= 0) atomicAdd(&counts_s[my_label], 1);
-                    continue;
-                }
-                if (rows > 0) {
-                    if (sums_smem) {
-                        // several columns per lane (d > 64): same updates, column by column
-                        for (int c = c0; c < p.d; c += cstride) {
-                            const double *xb = Xt + c;
-                            double *sb = sums_s + c;
-                            int off[kWarpRows];
-                            double xv[kWarpRows], sv[kWarpRows];
-#pragma unroll
-                            for (int q = 0; q < kWarpRows / 4; q++) {
-                                const int4 o = *reinterpret_cast<const int4 *>(offp + 4 * q);
-                                off[4 * q + 0] = o.x;
-                                off[4 * q + 1] = o.y;
-                                off[4 * q + 2] = o.z;
-                                off[4 * q + 3] = o.w;
-                            }
-#pragma unroll
-                            for (int r = 0; r < kWarpRows; r++) xv[r] = xb[(size_t)r * S];
-#pragma unroll
-                            for (int r = 0; r < kWarpRows; r++) sv[r] = sb[off[r]];
-#pragma unroll
-                            for (int r = 0; r < kWarpRows; r++) sb[off[r]] = sv[r] + xv[r];
-                        }
-                        if (a == 0 && lane < rows) atomicAdd(&counts_s[lab[lane]], 1);
-                    } else {
-                        // sums too large for shared memory: one global accumulator (L2 atomics)
-                        const int trash = p.k * p.d;
-                        for (int c = c0; c < p.d; c += cstride)
-                            for (int r = 0; r < rows; r++) {
-                                const int o = offp[r];
-                                if (o != trash) atomicAdd(&p.partials[(size_t)o + c], Xt[(size_t)r * S + c]);
-                            }
-                        if (a == 0 && lane < rows) atomicAdd(&p.partials[(size_t)p.k * p.d + lab[lane]], 1.0);
-                    }
-                }
-                __syncwarp();
-                if (lane == 0) st_release_smem(&seq_done[w * A + a], it_w + 1);
+            const int rows = rows_all[w * xs + stage];
+            const double *Xt = Xall + (size_t)(w * xs + stage) * xtile_elems + (size_t)rbase * S;
+            const int *lab = lab_all + (w * xs + stage) * kWarpRows;
+            const int *offp = off_all + (w * xs + stage) * kWarpRows + rbase;
+            int *done_flag = &seq_done[w * A + a];
+            const int done_value = it_w + 1;
+            if (++w == W) {
+                w = 0;
+                it_w++;
             }
+            if (rows > 0 && sums_smem && p.d <= cstride) {
+                // common case, one column per lane: copy what the tile contributes into registers
+                // (row offsets, this lane's column of the 8 rows, the label for the count), hand the
+                // buffer straight back to its MMA warp -- it can refill it while the sums are updated --
+                // and only then do the read-modify-writes.
+                const bool has_col = c0 < p.d;
+                const double *xb = Xt + (has_col ? c0 : 0);
+                double *sb = sums_s + (has_col ? c0 : 0);
+                int off[RH];
+                double xv[RH], sv[RH];
+#pragma unroll
+                for (int q = 0; q < RH / 4; q++) {
+                    const int4 o = *reinterpret_cast<const int4 *>(offp + 4 * q);
+                    off[4 * q + 0] = o.x;
+                    off[4 * q + 1] = o.y;
+                    off[4 * q + 2] = o.z;
+                    off[4 * q + 3] = o.w;
+                }
+#pragma unroll
+                for (int r = 0; r < RH; r++) xv[r] = xb[(size_t)r * S];
+                const int my_label = (a == 0 && lane < rows) ? lab[lane] : -1;
+                __syncwarp();
+                if (lane == 0) st_release_smem(done_flag, done_value);
+                acc_group_barrier(A * 32); // both halves are done with the previous tile's cells
+                // rows that count update distinct cells, the others fall into the scratch row (never
+                // read): the 8 updates are independent and their latencies overlap
+                if (has_col) {
+#pragma unroll
+                    for (int r = 0; r < RH; r++) sv[r] = sb[off[r]];
+#pragma unroll
+                    for (int r = 0; r < RH; r++) sb[off[r]] = sv[r] + xv[r];
+                }
+                if (my_label >= 0) atomicAdd(&counts_s[my_label], 1);
+                continue;
+            }
+            if (rows > 0) {
+                if (sums_smem) {
+                    // several columns per lane (d > 64): same updates, column by column
+                    acc_group_barrier(A * 32);
+                    for (int c = c0; c < p.d; c += cstride) {
+                        const double *xb = Xt + c;
+                        double *sb = sums_s + c;
+                        int off[RH];
+                        double xv[RH], sv[RH];
+#pragma unroll
+                        for (int q = 0; q < RH / 4; q++) {
+                            const int4 o = *reinterpret_cast<const int4 *>(offp + 4 * q);
+                            off[4 * q + 0] = o.x;
+                            off[4 * q + 1] = o.y;
+                            off[4 * q + 2] = o.z;
+                            off[4 * q + 3] = o.w;
+                        }
+#pragma unroll
+                        for (int r = 0; r < RH; r++) xv[r] = xb[(size_t)r * S];
+#pragma unroll
+                        for (int r = 0; r < RH; r++) sv[r] = sb[off[r]];
+#pragma unroll
+                        for (int r = 0; r < RH; r++) sb[off[r]] = sv[r] + xv[r];
+                    }
+                    if (a == 0 && lane < rows) atomicAdd(&counts_s[lab[lane]], 1);
+                } else {
+                    // sums too large for shared memory: one global accumulator (L2 atomics)
+                    const int trash = p.k * p.d;
+                    const int rows_here = min(max(rows - rbase, 0), RH);
+                    for (int c = c0; c < p.d; c += cstride)
+                        for (int r = 0; r < rows_here; r++) {
+                            const int o = offp[r];
+                            if (o != trash) atomicAdd(&p.partials[(size_t)o + c], Xt[(size_t)r * S + c]);
+                        }
+                    if (a == 0 && lane < rows) atomicAdd(&p.partials[(size_t)p.k * p.d + lab[lane]], 1.0);
+                }
+            }
+            __syncwarp();
+            if (lane == 0) st_release_smem(done_flag, done_value);
         }
     }
 
