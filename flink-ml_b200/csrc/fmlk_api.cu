@@ -429,7 +429,6 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.private_sums = cfg.private_sums;
     p.spin_ns = cfg.spin_ns;
     p.stagger_ns = cfg.stagger_ns;
-    p.debug_skip = env_int("FMLK_TUNE_DEBUG_SKIP", 0);
     p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
     p.recheck_count = ctx->recheck;
     const int64_t tiles = (n + kWarpRows - 1) / kWarpRows;

@@ -61,7 +61,6 @@ struct AssignParams {
     int32_t acc_order; // always 0: tiles are accumulated in the fixed order (round, warp): bit-reproducible sums
     int32_t spin_ns;   // back-off of the hand-off spin loops
     int32_t stagger_ns; // initial delay between the MMA warps of one scheduler (see assign_kernel)
-    int32_t debug_skip; // experiments only: 1 = skip the per-element selection, 2 = also skip row loads
     int32_t fma_mode; // exact path follows the JDK>=11 netlib variant
     unsigned long long *recheck_count;
 };
@@ -264,10 +263,38 @@ __device__ __forceinline__ Top2 top2_init() {
 __device__ __forceinline__ void top2_push(Top2 &t, double v, int col) {
     const int k = score_key_hi(v);
     const bool gt = k > t.best;
-    const bool gs = k > t.second;
-    t.second = gt ? t.best : (gs ? k : t.second);
+    t.second = max(t.second, min(t.best, k));
     t.idx = gt ? col : t.idx;
-    t.best = gt ? k : t.best;
+    t.best = max(t.best, k);
+}
+
+// The scores of one fragment row of an accumulator chunk (8 n8 tiles x 2 columns; tiles the chunk
+// does not have are passed as -inf) pushed into the row's running Top2.  Deliberately NOT inlined:
+// selection is a quarter of the per-tile instructions, and the per-tile code of all the warps of a
+// CTA has to stay resident in the instruction cache (32 KB) -- one copy serves both fragment rows
+// and every chunk size.  Returns (best, second, idx).
+__device__ __noinline__ int3 select_chunk_row(int best, int second, int idx, int col0, double v0, double v1,
+                                              double v2, double v3, double v4, double v5, double v6, double v7,
+                                              double v8, double v9, double v10, double v11, double v12,
+                                              double v13, double v14, double v15) {
+    Top2 t = {best, second, idx};
+    top2_push(t, v0, col0);
+    top2_push(t, v1, col0 + 1);
+    top2_push(t, v2, col0 + 8);
+    top2_push(t, v3, col0 + 9);
+    top2_push(t, v4, col0 + 16);
+    top2_push(t, v5, col0 + 17);
+    top2_push(t, v6, col0 + 24);
+    top2_push(t, v7, col0 + 25);
+    top2_push(t, v8, col0 + 32);
+    top2_push(t, v9, col0 + 33);
+    top2_push(t, v10, col0 + 40);
+    top2_push(t, v11, col0 + 41);
+    top2_push(t, v12, col0 + 48);
+    top2_push(t, v13, col0 + 49);
+    top2_push(t, v14, col0 + 56);
+    top2_push(t, v15, col0 + 57);
+    return make_int3(t.best, t.second, t.idx);
 }
 
 __device__ __forceinline__ void top2_merge_xor(Top2 &t, int off) {
@@ -350,7 +377,7 @@ __device__ __forceinline__ void mma_group_barrier(int nthreads) {
 template <int CNT>
 __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned cb, unsigned tstride, int ksteps,
                                           const double *hcol, int col0, Top2 &t0, Top2 &t1, int &mx0,
-                                          int &mx1, bool with_nsq, int debug_skip = 0) {
+                                          int &mx1, bool with_nsq) {
     double acc0[CNT][2], acc1[CNT][2];
     unsigned bj[CNT];
 #pragma unroll
@@ -412,21 +439,23 @@ __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned c
         }
     }
 #undef FMLK_KSTEP
-    if (debug_skip) { // experiments: keep the accumulators alive at almost no cost
-        double sum = 0.0;
-#pragma unroll
-        for (int j = 0; j < CNT; j++) sum += acc0[j][0] + acc0[j][1] + acc1[j][0] + acc1[j][1];
-        if (sum == 1.2345e300) t0.idx = 1;
-        return;
+    constexpr double NI = -INFINITY;
+#define FMLK_V(A, J, E) ((J) < CNT ? A[(J) < CNT ? (J) : 0][E] : NI)
+#define FMLK_SELECT(T, A)                                                                                       \
+    {                                                                                                           \
+        const int3 r = select_chunk_row(T.best, T.second, T.idx, col0, FMLK_V(A, 0, 0), FMLK_V(A, 0, 1),        \
+                                        FMLK_V(A, 1, 0), FMLK_V(A, 1, 1), FMLK_V(A, 2, 0), FMLK_V(A, 2, 1),     \
+                                        FMLK_V(A, 3, 0), FMLK_V(A, 3, 1), FMLK_V(A, 4, 0), FMLK_V(A, 4, 1),     \
+                                        FMLK_V(A, 5, 0), FMLK_V(A, 5, 1), FMLK_V(A, 6, 0), FMLK_V(A, 6, 1),     \
+                                        FMLK_V(A, 7, 0), FMLK_V(A, 7, 1));                                      \
+        T.best = r.x;                                                                                           \
+        T.second = r.y;                                                                                         \
+        T.idx = r.z;                                                                                            \
     }
-#pragma unroll
-    for (int j = 0; j < CNT; j++) {
-        const int col = col0 + j * 8;
-        top2_push(t0, acc0[j][0], col);
-        top2_push(t0, acc0[j][1], col + 1);
-        top2_push(t1, acc1[j][0], col);
-        top2_push(t1, acc1[j][1], col + 1);
-    }
+    FMLK_SELECT(t0, acc0)
+    FMLK_SELECT(t1, acc1)
+#undef FMLK_SELECT
+#undef FMLK_V
 }
 
 // The assign (+ accumulate) kernel.  One persistent CTA per SM with two kinds of warps:
@@ -584,10 +613,10 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                     const int64_t nrow0 = ntile * kWarpRows;
                     x_issue(stage ^ 1, nrow0, (int)min((int64_t)kWarpRows, p.n - nrow0));
                 }
-            } else if (active && !(p.debug_skip >= 2 && it > 0)) {
+            } else if (active) {
                 x_issue(0, row0, rows_valid);
             }
-            if (active && !(p.debug_skip >= 2 && it > 0 && xs == 1)) x_wait(stage);
+            if (active) x_wait(stage);
 
             Top2 t0 = top2_init(), t1 = top2_init();
             int mx0 = 0, mx1 = 0; // high words of the largest |x| in the two rows this quad owns
@@ -633,7 +662,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                         const int col0 = ct_base + ch * 8 + fk * 2;
                         const bool first = (ct == 0 && ch == 0); // |x|^2 rides along with the first chunk
 #define FMLK_CHUNK(N) \
-    case N: mma_chunk<N>(xa0, xa1, cb, tstride, p.ksteps, hs + col0, col0, t0, t1, mx0, mx1, first, p.debug_skip); break;
+    case N: mma_chunk<N>(xa0, xa1, cb, tstride, p.ksteps, hs + col0, col0, t0, t1, mx0, mx1, first); break;
                         switch (cnt) {
                             FMLK_CHUNK(8) FMLK_CHUNK(7) FMLK_CHUNK(6) FMLK_CHUNK(5)
                             FMLK_CHUNK(4) FMLK_CHUNK(3) FMLK_CHUNK(2) FMLK_CHUNK(1)
@@ -671,8 +700,8 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 };
                 const bool ok0 = row_ok(t0, mx0);
                 const bool ok1 = row_ok(t1, mx1);
-                const bool flag0 = !ok0 && (frow < rows_valid) && !p.debug_skip;
-                const bool flag1 = !ok1 && (frow + 8 < rows_valid) && !p.debug_skip;
+                const bool flag0 = !ok0 && (frow < rows_valid);
+                const bool flag1 = !ok1 && (frow + 8 < rows_valid);
                 if (fk == 0) {
                     lab_s[frow] = t0.idx;
                     lab_s[frow + 8] = t1.idx;
