@@ -188,7 +188,7 @@ size_t smem_bytes(int warps, int acc, int xs, int S, int k, int d, int k_pad, in
                  (size_t)warps * xs * kWarpRows * S +
                  (priv ? ((((size_t)warps * k * d) + 1) & ~(size_t)1) : sums ? (((size_t)(k + 1) * d + 1) & ~(size_t)1) : 0);
     size_t ints = (priv ? (size_t)warps * k : sums ? (size_t)k : 0) + 2 * (size_t)warps * xs * kWarpRows +
-                  (size_t)warps * xs + warps + (size_t)warps * acc;
+                  (size_t)warps * xs + warps + (size_t)warps * acc + acc;
     return dbl * 8 + ints * 4;
 }
 
@@ -241,7 +241,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
             }
         }
     }
-    for (int pass = 0; pass < 2; pass++) {
+    for (int pass = env_int("FMLK_TUNE_GLOBAL_SUMS", 0) ? 1 : 0; pass < 2; pass++) {
         const bool sums = accum && pass == 0;
         if (!accum && pass == 1) break;
         for (int i = 0; i < ncand; i++) {
@@ -254,7 +254,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
                 c.nc_tile = c.k_pad;
                 c.n_ctiles = 1;
                 c.sums_in_smem = sums ? 1 : 0;
-                c.n_partials = sums ? c.grid : 1;
+                c.n_partials = sums ? c.grid : std::max(1, env_int("FMLK_TUNE_GLOBAL_SLOTS", 1));
                 c.smem = need;
                 *out = c;
                 return FMLK_OK;
@@ -429,6 +429,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.private_sums = cfg.private_sums;
     p.spin_ns = cfg.spin_ns;
     p.stagger_ns = cfg.stagger_ns;
+    p.no_bulk = env_int("FMLK_TUNE_NO_BULK", 0);
     p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
     p.recheck_count = ctx->recheck;
     const int64_t tiles = (n + kWarpRows - 1) / kWarpRows;
@@ -441,10 +442,31 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
         e1 = next_event(ctx);
         if (e0 && e1) cudaEventRecord(e0, ctx->stream);
     }
+#ifdef FMLK_TRACE
+    // debugging builds: FMLK_TRACE_FILE=path dumps the event timeline of CTA 0 of every launch (last one wins)
+    const char *trace_path = getenv("FMLK_TRACE_FILE");
+    const size_t trace_len = (size_t)16 * kTraceEvents;
+    if (trace_path) {
+        cudaMalloc((void **)&p.trace, trace_len * 8);
+        cudaMemsetAsync(p.trace, 0, trace_len * 8, ctx->stream);
+    }
+#endif
     if (accum && cfg.private_sums) assign_kernel<2><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
     else if (accum) assign_kernel<1><<<grid, (cfg.warps + cfg.acc_warps) * 32, cfg.smem, ctx->stream>>>(p);
     else assign_kernel<0><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
     if (prof && e0 && e1) cudaEventRecord(e1, ctx->stream);
+#ifdef FMLK_TRACE
+    if (trace_path) {
+        std::vector<unsigned long long> host(trace_len);
+        cudaMemcpyAsync(host.data(), p.trace, trace_len * 8, cudaMemcpyDeviceToHost, ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
+        if (FILE *f = fopen(trace_path, "wb")) {
+            fwrite(host.data(), 8, trace_len, f);
+            fclose(f);
+        }
+        cudaFree(p.trace);
+    }
+#endif
     ctx->assign_launches++;
     ctx->total_launches++;
     CK(ctx, cudaGetLastError());

@@ -61,6 +61,10 @@ struct AssignParams {
     int32_t acc_order; // always 0: tiles are accumulated in the fixed order (round, warp): bit-reproducible sums
     int32_t spin_ns;   // back-off of the hand-off spin loops
     int32_t stagger_ns; // initial delay between the MMA warps of one scheduler (see assign_kernel)
+#ifdef FMLK_TRACE
+    unsigned long long *trace; // [warps of CTA 0][kTraceEvents] (clock << 4 | event), debugging builds only
+#endif
+    int32_t no_bulk;  // tuning: 1 = row tiles with 16-byte cp.async instead of bulk copies
     int32_t fma_mode; // exact path follows the JDK>=11 netlib variant
     unsigned long long *recheck_count;
 };
@@ -309,9 +313,23 @@ __device__ __forceinline__ void top2_merge_xor(Top2 &t, int off) {
     t.second = max(max(t.second, os), loser);
 }
 
-// conservative decision margin of a row in score units: lower(best) - upper(second)
-__device__ __forceinline__ double top2_margin(const Top2 &t) {
-    return key_hi_value(t.best, 0u) - key_hi_value(t.second, 0xffffffffu);
+// Conservative margin test on the key high words alone (integer only: an FP64 subtract or compare
+// issued here would queue behind the other warps' DMMAs, and the longer a warp is held up between
+// tiles the more the warps of a scheduler fall into step).  True only if
+//   2 * (lower(best) - upper(second)) > 2^(te - 1023),     te = biased exponent of the threshold bound.
+// Same sign: with H, L the high words of the larger and smaller magnitude, the values are at least
+// (H - L - 1) high-word steps apart and a step is worth at least 2^(eL - 1043) (eL = biased exponent
+// of L; steps only grow with the magnitude).  Opposite signs: the margin is at least the larger
+// magnitude, which is at least 2^(e_max - 1023).
+__device__ __forceinline__ bool top2_margin_clears(const Top2 &t, int te) {
+    const int kb = t.best, ks = t.second; // kb >= ks
+    if (kb >= 0 && ks < 0) return (max(kb, ~ks) >> 20) >= te;
+    const int H = kb >= 0 ? kb : ~ks;
+    const int L = kb >= 0 ? ks : ~kb;
+    const int gap = H - L - 1;
+    const int sh = te - max(L >> 20, 1) + 19;
+    if (sh > 30) return false;
+    return gap > (sh < 0 ? 0 : (1 << sh));
 }
 
 // Copies `rows` rows of d doubles (contiguous in global memory) into shared rows of stride S, by
@@ -354,14 +372,22 @@ __device__ __forceinline__ int ld_acquire_smem(const int *p) {
 __device__ __forceinline__ void spin_until_at_least(const int *p, int target, unsigned ns) {
     while (ld_acquire_smem(p) < target) __nanosleep(ns);
 }
-// named barrier 2: the accumulator warps of a CTA (count = 32 x their number)
-__device__ __forceinline__ void acc_group_barrier(int threads) {
-    asm volatile("bar.sync 2, %0;" ::"r"(threads) : "memory");
-}
-
 __device__ __forceinline__ void mma_group_barrier(int nthreads) {
     asm volatile("bar.sync 1, %0;\n" ::"r"(nthreads) : "memory");
 }
+
+// Timeline tracing for performance work (compiled in only with -DFMLK_TRACE, see scripts/trace_timeline.py):
+// lane 0 of every warp of CTA 0 appends (clock << 4 | event) to its row of p.trace.
+#ifdef FMLK_TRACE
+constexpr int kTraceEvents = 2048;
+#define FMLK_TRACE_EVENT(EV)                                                                         \
+    if (p.trace && blockIdx.x == 0 && lane == 0 && trace_n < kTraceEvents)                           \
+        p.trace[(size_t)warp * kTraceEvents + trace_n++] = ((unsigned long long)clock64() << 4) | (EV);
+#define FMLK_TRACE_DECL int trace_n = 0;
+#else
+#define FMLK_TRACE_EVENT(EV)
+#define FMLK_TRACE_DECL
+#endif
 
 // One accumulator chunk of a warp tile: 16 rows x CNT (1..8) n8 tiles over the whole d.  CNT is a
 // template parameter: a DMMA that is merely predicated off still blocks its warp for a DMMA's issue
@@ -481,6 +507,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     const int W = p.mma_warps;
+    FMLK_TRACE_DECL
     constexpr bool priv = MODE == 2;
     const int A = (ACCUM && !priv) ? p.acc_warps : 0;
     const int S = p.S;
@@ -506,12 +533,13 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
     int *rows_all = counts_s + count_ints;                       // [W * xs]
     int *seq_ready = rows_all + W * xs;                          // [W]
     int *seq_done = seq_ready + W;                               // [W * A]
+    int *rmw_done = seq_done + W * A;                            // [A] tiles whose sums updates are complete
 
     // ---- one-time set-up: zero everything (pad columns and pad rows must read as 0) ----
     {
         const size_t zero_elems = c_bufs * ctile_elems + p.k_pad + W * xs + (size_t)W * xs * xtile_elems + sums_elems;
         for (size_t i = threadIdx.x; i < zero_elems; i += blockDim.x) Cs[i] = 0.0;
-        const int zero_ints = 2 * W * xs * kWarpRows + count_ints + W * xs + W + W * A;
+        const int zero_ints = 2 * W * xs * kWarpRows + count_ints + W * xs + W + W * A + A;
         for (int i = threadIdx.x; i < zero_ints; i += blockDim.x) off_all[i] = 0;
     }
     __syncthreads();
@@ -545,7 +573,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         int cbuf = 0;
         // row tiles: bulk asynchronous copies (one per row, issued by the lane of that row) that
         // complete on this warp's mbarrier; rows of odd length fall back to 8-byte cp.async
-        const bool use_tma = vec16;
+        const bool use_tma = vec16 && !p.no_bulk;
         const unsigned row_bytes = (unsigned)p.d * 8u;
         unsigned uses0 = 0, uses1 = 0; // completed phases of the stage barriers (parity = uses & 1)
         auto x_issue = [&](int stage, int64_t row0, int rows) {
@@ -603,6 +631,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
 
             // the buffer about to be overwritten was last used by tile it-1: wait until the
             // accumulator warps have consumed it
+            FMLK_TRACE_EVENT(0) // previous tile finished: waiting for the buffer
             if (ACCUM && it >= 1)
                 for (int a = 0; a < A; a++) spin_until_at_least(&seq_done[warp * A + a], (int)it, (unsigned)p.spin_ns);
 
@@ -616,7 +645,9 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
             } else if (active) {
                 x_issue(0, row0, rows_valid);
             }
+            FMLK_TRACE_EVENT(1) // tile start: buffer free, load issued
             if (active) x_wait(stage);
+            FMLK_TRACE_EVENT(2) // rows have landed: multiply starts
 
             Top2 t0 = top2_init(), t1 = top2_init();
             int mx0 = 0, mx1 = 0; // high words of the largest |x| in the two rows this quad owns
@@ -673,6 +704,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 if (p.n_ctiles > 1) cbuf ^= 1;
             }
 
+            FMLK_TRACE_EVENT(3) // multiply + selection done
             if (active) {
                 // combine the four lanes of each quad (same rows, different columns)
                 top2_merge_xor(t0, 1);
@@ -687,16 +719,15 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 // Decision margin in score units (D = |x|^2 - 2 v, so 2 * margin_v is the gap in squared
                 // distance) against a power-of-two upper bound of the rounding threshold
                 //   thr = coef * (|x|^2 + |c|max^2) <= 2^(coef_exp + 1 + max(2(E+1) + log2 d, cmax2_exp)),
-                // E = exponent of the row's largest |x_i|.  Built from integer fields: one FP64
-                // subtract and one compare per row is all that touches the FP64 pipe here.
+                // E = exponent of the row's largest |x_i|.  Integer arithmetic on exponent fields and key
+                // high words only: nothing here touches the FP64 pipe.
                 auto row_ok = [&](const Top2 &t, int mx) -> bool {
                     if (mx >= 0x7ff00000) return false; // Inf / NaN in the row
                     const int ex = 2 * ((mx >> 20) - 1023 + 1) + dpad_exp;
                     int te = p.thr_coef_exp + 1 + max(ex, cmax2_exp) + 1023;
                     if (te >= 2047) return false;
                     te = max(te, 1);
-                    const double thr_ub = __hiloint2double(te << 20, 0);
-                    return 2.0 * top2_margin(t) > thr_ub;
+                    return top2_margin_clears(t, te);
                 };
                 const bool ok0 = row_ok(t0, mx0);
                 const bool ok1 = row_ok(t1, mx1);
@@ -768,6 +799,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
             } else {
                 __syncwarp(); // the tile buffer and lab_s are reused next round
             }
+            FMLK_TRACE_EVENT(4) // labels written, tile published
         }
         cp_async_wait<0>();
         if (lane == 0 && local_rechecks && p.recheck_count) atomicAdd(p.recheck_count, local_rechecks);
@@ -776,21 +808,26 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         // sums[label] += row, counts[label]++ (KMeans.java:293-294).  The A = 2 G accumulator warps
         // split a tile by columns (G groups of 32 lanes: lane l of group g owns columns g*32 + l,
         // + 32 G, ...) and by rows (half h adds rows 8h .. 8h+7).  The rows of a published tile point
-        // at distinct sums rows, so the two halves never touch the same cell within a tile; a named
-        // barrier per tile keeps them from running a tile apart.  Every FP64 add issued here queues
-        // behind the MMA warps' DMMAs on the scheduler's FP64 pipe (~50-80 cycles each): the chain of
-        // adds per warp and tile, not their number, is what bounds the accumulators.
+        // at distinct sums rows, so the two halves never touch the same cell within a tile; across
+        // tiles a half starts the updates of tile t+1 only after its partner (same columns, other
+        // rows) has finished those of tile t (rmw_done).  Every FP64 add issued here queues behind
+        // the MMA warps' DMMAs on the scheduler's FP64 pipe (~100 cycles each): the chain of adds per
+        // warp and tile, not their number, is what bounds the accumulators.
         constexpr int RH = kWarpRows / 2; // rows per half
         const int a = warp - W;
-        const int G = A >> 1;
+        const int G = max(A >> 1, 1);
         const int g = a % G, h = a / G;
         const int cstride = 32 * G;
         const int c0 = g * 32 + lane;
         const int rbase = h * RH;
+        const int partner = (1 - h) * G + g;
+        int tiles_done = 0; // tiles whose sums updates this warp has completed
         int w = 0, it_w = 0; // tiles are taken in the fixed order (round, warp): reproducible sums
         const int64_t total_tiles_cta = rounds * W;
         for (int64_t done_tiles = 0; done_tiles < total_tiles_cta; done_tiles++) {
+            FMLK_TRACE_EVENT(5) // accumulator: waiting for the next tile
             spin_until_at_least(&seq_ready[w], it_w + 1, (unsigned)p.spin_ns);
+            FMLK_TRACE_EVENT(6) // accumulator: tile taken
             const int stage = (xs == 2) ? (it_w & 1) : 0;
             const int rows = rows_all[w * xs + stage];
             const double *Xt = Xall + (size_t)(w * xs + stage) * xtile_elems + (size_t)rbase * S;
@@ -825,7 +862,9 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 const int my_label = (a == 0 && lane < rows) ? lab[lane] : -1;
                 __syncwarp();
                 if (lane == 0) st_release_smem(done_flag, done_value);
-                acc_group_barrier(A * 32); // both halves are done with the previous tile's cells
+                FMLK_TRACE_EVENT(7) // accumulator: tile copied, buffer released
+                spin_until_at_least(&rmw_done[partner], tiles_done, 20u); // partner is done with the previous tile's cells
+                FMLK_TRACE_EVENT(8) // accumulator: partner is done with the previous tile
                 // rows that count update distinct cells, the others fall into the scratch row (never
                 // read): the 8 updates are independent and their latencies overlap
                 if (has_col) {
@@ -835,12 +874,15 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                     for (int r = 0; r < RH; r++) sb[off[r]] = sv[r] + xv[r];
                 }
                 if (my_label >= 0) atomicAdd(&counts_s[my_label], 1);
+                __syncwarp();
+                tiles_done++;
+                if (lane == 0) st_release_smem(&rmw_done[a], tiles_done);
                 continue;
             }
             if (rows > 0) {
                 if (sums_smem) {
                     // several columns per lane (d > 64): same updates, column by column
-                    acc_group_barrier(A * 32);
+                    spin_until_at_least(&rmw_done[partner], tiles_done, 20u);
                     for (int c = c0; c < p.d; c += cstride) {
                         const double *xb = Xt + c;
                         double *sb = sums_s + c;
@@ -863,19 +905,30 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                     }
                     if (a == 0 && lane < rows) atomicAdd(&counts_s[lab[lane]], 1);
                 } else {
-                    // sums too large for shared memory: one global accumulator (L2 atomics)
+                    // sums too large for shared memory: global accumulators (L2 atomics), slot by CTA
                     const int trash = p.k * p.d;
-                    const int rows_here = min(max(rows - rbase, 0), RH);
-                    for (int c = c0; c < p.d; c += cstride)
-                        for (int r = 0; r < rows_here; r++) {
-                            const int o = offp[r];
-                            if (o != trash) atomicAdd(&p.partials[(size_t)o + c], Xt[(size_t)r * S + c]);
+                    double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
+                    for (int c = c0; c < p.d; c += cstride) {
+                        int off[RH];
+                        double xv[RH];
+#pragma unroll
+                        for (int r = 0; r < RH; r++) {
+                            off[r] = offp[r];
+                            xv[r] = Xt[(size_t)r * S + c];
                         }
-                    if (a == 0 && lane < rows) atomicAdd(&p.partials[(size_t)p.k * p.d + lab[lane]], 1.0);
+#pragma unroll
+                        for (int r = 0; r < RH; r++)
+                            if (off[r] != trash) atomicAdd(&slot[(size_t)off[r] + c], xv[r]);
+                    }
+                    if (a == 0 && lane < rows) atomicAdd(&slot[(size_t)p.k * p.d + lab[lane]], 1.0);
                 }
             }
             __syncwarp();
-            if (lane == 0) st_release_smem(done_flag, done_value);
+            tiles_done++;
+            if (lane == 0) {
+                st_release_smem(&rmw_done[a], tiles_done);
+                st_release_smem(done_flag, done_value);
+            }
         }
     }
 
