@@ -131,6 +131,11 @@ struct fmlk_ctx {
     unsigned long long *recheck = nullptr;
 
     // staging for predict / online batches
+    uint8_t *ingest_buf = nullptr; // staging for serialized records
+    size_t ingest_cap = 0;
+    int *ingest_bad = nullptr;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_decoded[2] = {nullptr, nullptr};
     double *stage_rows = nullptr;
     size_t stage_rows_cap = 0; // doubles
     int32_t *stage_labels = nullptr;
@@ -681,6 +686,13 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     dev_free(ctx->recheck);
     dev_free(ctx->stage_rows);
     dev_free(ctx->stage_labels);
+    dev_free(ctx->ingest_buf);
+    dev_free(ctx->ingest_bad);
+    for (int b = 0; b < 2; b++) {
+        if (ctx->ev_copied[b]) cudaEventDestroy(ctx->ev_copied[b]);
+        if (ctx->ev_decoded[b]) cudaEventDestroy(ctx->ev_decoded[b]);
+    }
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
     cudaGetLastError();
@@ -740,6 +752,140 @@ int32_t fmlk_append_points(fmlk_ctx *ctx, const double *rows_host, int64_t n, in
 
 int32_t fmlk_append_points_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d) {
     return append_impl(ctx, rows_dev, n, d, cudaMemcpyDeviceToDevice);
+}
+
+// ---- ingest of the reference's serialized rows (DenseVectorSerializer / VectorSerializer /
+// VectorWithNormSerializer records): H2D of the raw bytes in pieces, decode_records_kernel into
+// the row cache
+static int record_layout(fmlk_ctx *ctx, int32_t format, int32_t d, int *hdr, int64_t *rec_bytes) {
+    if (d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "vector dimension must be positive");
+    switch (format) {
+    case FMLK_FMT_DENSE_VECTOR: *hdr = 4; *rec_bytes = 4 + 8 * (int64_t)d; return FMLK_OK;
+    case FMLK_FMT_VECTOR: *hdr = 5; *rec_bytes = 5 + 8 * (int64_t)d; return FMLK_OK;
+    case FMLK_FMT_VECTOR_WITH_NORM: *hdr = 5; *rec_bytes = 13 + 8 * (int64_t)d; return FMLK_OK;
+    }
+    return fail(ctx, FMLK_ERR_INVALID_ARG, "unknown record format");
+}
+
+static void launch_decode(cudaStream_t stream, int sms, const uint8_t *rec_dev, int64_t n, int d, int hdr,
+                          int64_t rec_bytes, double *out, int *bad_dev) {
+    const int threads = 256;
+    // groups of records staged through shared memory (~24 KB per block, 8 blocks per SM); records too
+    // long for that, or a base that is not 16-byte aligned, take the direct kernel
+    const int64_t group_rows = std::min<int64_t>(n, std::max<int64_t>(1, 24576 / rec_bytes));
+    const size_t smem = (size_t)(group_rows * rec_bytes) + 48;
+    if (smem <= 48 * 1024 && (reinterpret_cast<uintptr_t>(rec_dev) & 15) == 0) {
+        const int64_t groups = (n + group_rows - 1) / group_rows;
+        const int grid = (int)std::min<int64_t>(groups, (int64_t)sms * 8);
+        decode_records_smem_kernel<<<grid, threads, smem, stream>>>(rec_dev, n, d, hdr, (int)rec_bytes, (int)group_rows,
+                                                                     out, bad_dev);
+        return;
+    }
+    const int64_t total = n * d;
+    const int grid = (int)std::min<int64_t>((total + threads - 1) / threads, (int64_t)sms * 8);
+    decode_records_kernel<<<grid, threads, 0, stream>>>(rec_dev, n, d, hdr, (int)rec_bytes, out, bad_dev);
+}
+
+static int decode_status(fmlk_ctx *ctx, int bad) {
+    if (bad == 1) return fail(ctx, FMLK_ERR_INVALID_ARG, "sparse or unknown vector tag in a serialized record (densify first, KMeans.java:94)");
+    if (bad == 2) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
+    return FMLK_OK;
+}
+
+int32_t fmlk_append_points_serialized(fmlk_ctx *ctx, const uint8_t *records_host, int64_t nbytes, int32_t format,
+                                      int32_t d, int64_t *out_rows) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    int hdr = 0;
+    int64_t rec = 0;
+    if ((rc = record_layout(ctx, format, d, &hdr, &rec))) return rc;
+    if (nbytes < 0 || (nbytes > 0 && !records_host)) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad records / nbytes");
+    if (nbytes % rec != 0) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
+    if ((rc = check_dim(ctx, d))) return rc;
+    const int64_t n = nbytes / rec;
+    if (out_rows) *out_rows = n;
+    if (n == 0) return FMLK_OK;
+    // what to undo if a record turns out to be malformed
+    const size_t chunks_before = ctx->chunks.size();
+    const int64_t last_rows_before = chunks_before ? ctx->chunks.back().rows : 0, total_before = ctx->n_total;
+    const int d_before = ctx->d;
+    ctx->d = d;
+    double *dst = nullptr;
+    if ((rc = grow_points(ctx, n, &dst))) {
+        ctx->d = d_before;
+        return rc;
+    }
+    // two staging buffers: the copy of piece i+1 (copy stream) runs while piece i is unpacked
+    const int64_t piece_rows = std::max<int64_t>(1, ((int64_t)32 << 20) / rec);
+    const size_t piece_bytes = ((size_t)(piece_rows * rec) + 16 + 255) & ~(size_t)255;
+    if (2 * piece_bytes > ctx->ingest_cap) {
+        dev_free(ctx->ingest_buf);
+        ctx->ingest_buf = nullptr;
+        ctx->ingest_cap = 0;
+        if ((rc = dev_alloc(ctx, &ctx->ingest_buf, 2 * piece_bytes))) return rc;
+        ctx->ingest_cap = 2 * piece_bytes;
+    }
+    if (!ctx->ingest_bad && (rc = dev_alloc(ctx, &ctx->ingest_bad, 1))) return rc;
+    if (!ctx->copy_stream) {
+        CK(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; b++) {
+            CK(ctx, cudaEventCreateWithFlags(&ctx->ev_copied[b], cudaEventDisableTiming));
+            CK(ctx, cudaEventCreateWithFlags(&ctx->ev_decoded[b], cudaEventDisableTiming));
+        }
+    }
+    CK(ctx, cudaMemsetAsync(ctx->ingest_bad, 0, sizeof(int), ctx->stream));
+    int64_t piece = 0;
+    for (int64_t r0 = 0; r0 < n; r0 += piece_rows, piece++) {
+        const int64_t rows = std::min(piece_rows, n - r0);
+        const int b = (int)(piece & 1);
+        uint8_t *buf = ctx->ingest_buf + (size_t)b * piece_bytes;
+        if (piece >= 2) CK(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_decoded[b], 0));
+        CK(ctx, cudaMemcpyAsync(buf, records_host + r0 * rec, (size_t)(rows * rec), cudaMemcpyHostToDevice,
+                                ctx->copy_stream));
+        CK(ctx, cudaEventRecord(ctx->ev_copied[b], ctx->copy_stream));
+        CK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[b], 0));
+        launch_decode(ctx->stream, ctx->sm_count, buf, rows, d, hdr, rec, dst + r0 * d, ctx->ingest_bad);
+        CK(ctx, cudaEventRecord(ctx->ev_decoded[b], ctx->stream));
+        ctx->total_launches++;
+    }
+    int bad = 0;
+    CK(ctx, cudaMemcpyAsync(&bad, ctx->ingest_bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    // the caller may reuse its buffer as soon as we return (Flink object reuse)
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    CK(ctx, cudaGetLastError());
+    if (bad) {
+        while (ctx->chunks.size() > chunks_before) {
+            if (ctx->chunks.back().owned) dev_free(ctx->chunks.back().ptr);
+            ctx->chunks.pop_back();
+        }
+        if (chunks_before) ctx->chunks.back().rows = last_rows_before;
+        ctx->n_total = total_before;
+        ctx->d = d_before;
+        return decode_status(ctx, bad);
+    }
+    return FMLK_OK;
+}
+
+int32_t fmlk_decode_rows_dev(int32_t device, void *cuda_stream, const uint8_t *records_dev, int64_t n, int32_t d,
+                             int32_t format, double *out_rows_dev, int32_t *out_bad_dev) {
+    int hdr = 0;
+    int64_t rec = 0;
+    int rc = record_layout(nullptr, format, d, &hdr, &rec);
+    if (rc) return rc;
+    if (n < 0 || (n > 0 && (!records_dev || !out_rows_dev)) || !out_bad_dev)
+        return fail(nullptr, FMLK_ERR_INVALID_ARG, "bad arguments");
+    if ((reinterpret_cast<uintptr_t>(records_dev) & 7) != 0)
+        return fail(nullptr, FMLK_ERR_INVALID_ARG, "records_dev must be 8-byte aligned");
+    if (n == 0) return FMLK_OK;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, cudaGetErrorString(e));
+    int sms = 0;
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    launch_decode((cudaStream_t)cuda_stream, sms, records_dev, n, d, hdr, rec, out_rows_dev, out_bad_dev);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, cudaGetErrorString(e));
+    return FMLK_OK;
 }
 
 int32_t fmlk_adopt_points_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d) {

@@ -1105,6 +1105,122 @@ __global__ void generate_dense_kernel(unsigned long long seed_state, int64_t cou
 }
 
 // ------------------------------------------------------------------------------------------
+// Ingest: the reference's serialized rows -> the row-major FP64 cache
+//
+// Record layouts, all big-endian (DataOutputView / Bits.putLong, CORE/util/Bits.java:54-66):
+//   format 0  DenseVectorSerializer.serialize      (DenseVectorSerializer.java:78-93):  int32 len | len x double
+//   format 1  VectorSerializer.serialize           (VectorSerializer.java:80-88):       byte tag (0 = dense) | format 0
+//   format 2  VectorWithNormSerializer.serialize   (VectorWithNormSerializer.java:74-78): format 1 | double l2Norm
+// Every record of a call has len == d, so record r starts at r * rec_bytes and its doubles at
+// + hdr (4 or 5): nothing in a record is aligned to more than a byte.  One thread per output
+// double: the 8 source bytes are taken from the two or three aligned 32-bit words that hold them
+// (funnel shift), byte-swapped, and stored coalesced.  The thread of column 0 also checks its
+// record's tag and length field; *bad = 1: sparse / unknown tag, 2: len != d.  The stored l2Norm
+// is not read: norms are recomputed on the fly from the rows (VectorWithNorm.java:32-39 defines it
+// as BLAS.norm2(vector), so it carries no extra information).
+// HBM-bound: rec_bytes read + 8 d written per row.
+__device__ __forceinline__ unsigned load_be32_unaligned(const unsigned char *base, int64_t byte_off) {
+    const uintptr_t addr = reinterpret_cast<uintptr_t>(base) + (uintptr_t)byte_off;
+    const unsigned *w = reinterpret_cast<const unsigned *>(addr & ~(uintptr_t)3);
+    const unsigned sh = (unsigned)(addr & 3) * 8u;
+    const unsigned lo = w[0];
+    const unsigned v = sh ? __funnelshift_r(lo, w[1], sh) : lo; // little-endian view of the 4 bytes
+    return __byte_perm(v, 0, 0x0123);                           // big-endian value
+}
+
+__global__ void __launch_bounds__(256) decode_records_kernel(const unsigned char *rec, int64_t n, int d, int hdr,
+                                                               int rec_bytes, double *out, int *bad) {
+    const int64_t total = n * d;
+    for (int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; e < total; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t r = e / d;
+        const int j = (int)(e - r * d);
+        const int64_t off = r * rec_bytes + hdr + 8 * (int64_t)j;
+        const uintptr_t addr = reinterpret_cast<uintptr_t>(rec) + (uintptr_t)off;
+        const unsigned *w = reinterpret_cast<const unsigned *>(addr & ~(uintptr_t)3);
+        const unsigned sh = (unsigned)(addr & 3) * 8u;
+        const unsigned w0 = w[0], w1 = w[1];
+        unsigned b0 = w0, b1 = w1; // bytes 0-3 and 4-7 of the big-endian double, little-endian views
+        if (sh) {
+            // the third word reaches up to 3 bytes past this double: never read it past the end of
+            // the buffer (the last double of the last record of formats 0 and 1 ends there)
+            unsigned w2 = 0;
+            if (e + 1 < total || rec_bytes > hdr + 8 * d) {
+                w2 = w[2];
+            } else {
+                const unsigned char *tail = reinterpret_cast<const unsigned char *>(w + 2);
+                for (unsigned q = 0; q * 8u < sh; q++) w2 |= (unsigned)tail[q] << (8u * q);
+            }
+            b0 = __funnelshift_r(w0, w1, sh);
+            b1 = __funnelshift_r(w1, w2, sh);
+        }
+        out[e] = __hiloint2double((int)__byte_perm(b0, 0, 0x0123), (int)__byte_perm(b1, 0, 0x0123));
+        if (j == 0) {
+            int flag = 0;
+            if (hdr == 5 && rec[r * rec_bytes] != 0) flag = 1;
+            if ((int)load_be32_unaligned(rec, r * rec_bytes + (hdr - 4)) != d) flag = max(flag, 2);
+            if (flag) atomicMax(bad, flag);
+        }
+    }
+}
+
+// Same unpacking through shared memory (the one the library launches whenever a group of records
+// fits): a block takes `group_rows` consecutive records -- one contiguous byte range -- with
+// coalesced 16-byte loads, then every thread picks the 8 bytes of its output double out of shared
+// memory.  Global traffic is then exactly the record bytes in and the doubles out.
+// rec must be 16-byte aligned.  Dynamic shared memory: group_rows * rec_bytes + 48 bytes.
+__global__ void __launch_bounds__(256) decode_records_smem_kernel(const unsigned char *rec, int64_t n, int d, int hdr,
+                                                                    int rec_bytes, int group_rows, double *out, int *bad) {
+    extern __shared__ uint4 stage4[];
+    const int64_t total_bytes = n * rec_bytes;
+    const int64_t groups = (n + group_rows - 1) / group_rows;
+    for (int64_t g = blockIdx.x; g < groups; g += gridDim.x) {
+        const int64_t r0 = g * group_rows;
+        const int rows = (int)min((int64_t)group_rows, n - r0);
+        const int64_t b0 = r0 * rec_bytes;
+        const int mis = (int)(b0 & 15);
+        const int64_t a0 = b0 - mis; // 16-byte aligned start of the range to load
+        const int nvec = (mis + rows * rec_bytes + 15) >> 4;
+        for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+            const int64_t at = a0 + 16 * (int64_t)i;
+            if (at + 16 <= total_bytes) {
+                stage4[i] = *reinterpret_cast<const uint4 *>(rec + at);
+            } else { // the last, partial vector of the whole buffer
+                unsigned char *dst = reinterpret_cast<unsigned char *>(stage4 + i);
+                for (int q = 0; q < 16; q++) dst[q] = at + q < total_bytes ? rec[at + q] : 0;
+            }
+        }
+        __syncthreads();
+        const unsigned char *sb = reinterpret_cast<const unsigned char *>(stage4) + mis;
+        const int elems = rows * d;
+        for (int idx = threadIdx.x; idx < elems; idx += blockDim.x) {
+            const int rr = idx / d;
+            const int j = idx - rr * d;
+            const unsigned char *p8 = sb + rr * rec_bytes + hdr + 8 * j;
+            const uintptr_t a = reinterpret_cast<uintptr_t>(p8);
+            const unsigned *w = reinterpret_cast<const unsigned *>(a & ~(uintptr_t)3);
+            const unsigned sh = (unsigned)(a & 3) * 8u;
+            unsigned b0w = w[0], b1w = w[1];
+            if (sh) {
+                const unsigned w2 = w[2]; // inside the staging buffer (16 spare bytes at its end)
+                b0w = __funnelshift_r(b0w, b1w, sh);
+                b1w = __funnelshift_r(b1w, w2, sh);
+            }
+            out[(r0 + rr) * d + j] =
+                __hiloint2double((int)__byte_perm(b0w, 0, 0x0123), (int)__byte_perm(b1w, 0, 0x0123));
+            if (j == 0) {
+                const unsigned char *h = sb + rr * rec_bytes;
+                int flag = (hdr == 5 && h[0] != 0) ? 1 : 0;
+                const unsigned char *l = h + (hdr - 4);
+                const int len = (int)(((unsigned)l[0] << 24) | ((unsigned)l[1] << 16) | ((unsigned)l[2] << 8) | (unsigned)l[3]);
+                if (len != d) flag = max(flag, 2);
+                if (flag) atomicMax(bad, flag);
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // FP64 peak microbenchmarks (register-resident; the roofline denominators for the assign kernel)
 
 __global__ void __launch_bounds__(256) dmma_peak_kernel(double *out, int iters) {

@@ -93,3 +93,49 @@ def to_matrix(column):
         if r.size != d:
             raise ValueError("Vector size mismatched.")  # BLAS.java:36,70
     return np.ascontiguousarray(np.stack(rows), dtype=np.float64)
+
+
+# ------------------------------------------------------------------------------------------
+# The reference serializers' byte format (host side; the device unpacks it, see fmlk.h)
+
+FMT_DENSE_VECTOR, FMT_VECTOR, FMT_VECTOR_WITH_NORM = 0, 1, 2
+
+
+def record_bytes(fmt, d):
+    """Size of one serialized row of dimension d."""
+    return {FMT_DENSE_VECTOR: 4, FMT_VECTOR: 5, FMT_VECTOR_WITH_NORM: 13}[fmt] + 8 * int(d)
+
+
+def serialize_rows(matrix, fmt=FMT_VECTOR_WITH_NORM, norms=None):
+    """The bytes the reference writes for the rows of an n x d matrix, back to back:
+    DenseVectorSerializer.serialize (DenseVectorSerializer.java:78-93: big-endian int32 length, then
+    the doubles big-endian), VectorSerializer.serialize (VectorSerializer.java:80-88: a 0 tag byte
+    first) or VectorWithNormSerializer.serialize (VectorWithNormSerializer.java:74-78: the l2Norm
+    after the vector; pass `norms` or it is computed as sqrt(sum of squares))."""
+    m = np.ascontiguousarray(matrix, dtype=np.float64)
+    n, d = m.shape
+    rec = record_bytes(fmt, d)
+    out = np.zeros((n, rec), dtype=np.uint8)
+    hdr = 4 if fmt == FMT_DENSE_VECTOR else 5
+    out[:, hdr - 4:hdr] = np.frombuffer(np.array([d], dtype=">i4").tobytes(), dtype=np.uint8)
+    out[:, hdr:hdr + 8 * d] = m.astype(">f8").view(np.uint8).reshape(n, 8 * d)
+    if fmt == FMT_VECTOR_WITH_NORM:
+        nv = np.sqrt((m * m).sum(axis=1)) if norms is None else np.asarray(norms, dtype=np.float64)
+        out[:, hdr + 8 * d:] = nv.astype(">f8").view(np.uint8).reshape(n, 8)
+    return out.reshape(-1)
+
+
+def deserialize_rows(buf, fmt, d):
+    """Inverse of serialize_rows for records that all have dimension d (host reference decode)."""
+    rec = record_bytes(fmt, d)
+    b = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
+    if b.size % rec:
+        raise ValueError("Vector size mismatched.")
+    b = b.reshape(-1, rec)
+    hdr = 4 if fmt == FMT_DENSE_VECTOR else 5
+    lens = np.ascontiguousarray(b[:, hdr - 4:hdr]).view(">i4").reshape(-1)
+    if (lens != d).any():
+        raise ValueError("Vector size mismatched.")
+    if hdr == 5 and b[:, 0].any():
+        raise ValueError("sparse or unknown vector tag")
+    return np.ascontiguousarray(b[:, hdr:hdr + 8 * d]).view(">f8").astype(np.float64).reshape(-1, d)

@@ -16,6 +16,8 @@ OK = 0
 ERR_INVALID_ARG, ERR_STATE, ERR_DIM, ERR_CUDA, ERR_NCCL, ERR_NOMEM = -1, -2, -3, -4, -5, -6
 FLAG_PROFILE = 0x1
 FLAG_BLAS_FMA = 0x2
+# record formats of the reference's serializers (include/fmlk.h)
+FMT_DENSE_VECTOR, FMT_VECTOR, FMT_VECTOR_WITH_NORM = 0, 1, 2
 NCCL_ID_BYTES = 128
 
 
@@ -47,6 +49,8 @@ SIGNATURES = {
     "fmlk_reserve_points": (_i32, [_vp, _i64, _i32]),
     "fmlk_append_points": (_i32, [_vp, _vp, _i64, _i32]),
     "fmlk_append_points_dev": (_i32, [_vp, _vp, _i64, _i32]),
+    "fmlk_append_points_serialized": (_i32, [_vp, _vp, _i64, _i32, _i32, C.POINTER(_i64)]),
+    "fmlk_decode_rows_dev": (_i32, [_i32, _vp, _vp, _i64, _i32, _i32, _vp, _vp]),
     "fmlk_adopt_points_dev": (_i32, [_vp, _vp, _i64, _i32]),
     "fmlk_clear_points": (_i32, [_vp]),
     "fmlk_num_points": (_i64, [_vp]),
@@ -127,6 +131,11 @@ def measure_fp64_peaks(device=0, ms=200.0):
     return a.value, b.value
 
 
+def decode_rows_dev(device, stream, records_ptr, n, d, fmt, out_ptr, bad_ptr):
+    """The unpack kernel alone, device to device (see fmlk_decode_rows_dev)."""
+    _check(lib().fmlk_decode_rows_dev(int(device), stream, records_ptr, int(n), int(d), int(fmt), out_ptr, bad_ptr))
+
+
 def local_partials_noalloc(device, stream, rows_ptr, n, d, centroids_ptr, k, out_sums_ptr, out_counts_ptr):
     """fmlk_local_partials_noalloc: (sums, counts) of n device rows against k device centroids without
     any device allocation (fixed scratch inside the library; k*d + k <= 8192).  Asynchronous on `stream`."""
@@ -205,6 +214,22 @@ class Context:
         """Host rows given as a raw address (e.g. a pinned torch tensor's data_ptr())."""
         self._ck(lib().fmlk_append_points(self._h, host_ptr, int(n), int(d)))
         self.d = int(d)
+
+    def append_points_serialized(self, records, fmt, d):
+        """Rows still in the reference serializer's bytes (bytes / bytearray / uint8 array or a raw
+        (address, nbytes) pair of a pinned buffer); returns the number of rows appended."""
+        if isinstance(records, tuple):
+            addr, nbytes = int(records[0]), int(records[1])
+            keep = None
+        else:
+            keep = np.frombuffer(records, dtype=np.uint8) if not isinstance(records, np.ndarray) else \
+                np.ascontiguousarray(records, dtype=np.uint8)
+            addr, nbytes = keep.ctypes.data, keep.size
+        rows = _i64()
+        self._ck(lib().fmlk_append_points_serialized(self._h, addr, nbytes, int(fmt), int(d), C.byref(rows)))
+        if rows.value:
+            self.d = int(d)
+        return int(rows.value)
 
     def append_points_dev(self, dev_ptr, n, d):
         self._ck(lib().fmlk_append_points_dev(self._h, dev_ptr, int(n), int(d)))

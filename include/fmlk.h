@@ -82,6 +82,33 @@ int32_t fmlk_append_points(fmlk_ctx *ctx, const double *rows_host, int64_t n, in
 /* Same with the rows already on this context's device (device-to-device copy). */
 int32_t fmlk_append_points_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d);
 
+/* Record formats of the reference's serializers, all big-endian (CORE/util/Bits.java:54-66):
+ *   FMLK_FMT_DENSE_VECTOR      int32 len | len x double        DenseVectorSerializer.java:78-93
+ *   FMLK_FMT_VECTOR            byte tag (0 = dense) | the above   VectorSerializer.java:80-88
+ *   FMLK_FMT_VECTOR_WITH_NORM  the above | double l2Norm        VectorWithNormSerializer.java:74-78
+ * The last one is what ListStateWithCache<VectorWithNorm> holds for the KMeans point cache
+ * (KMeans.java:238-246) and what the operator re-reads every round (KMeans.java:291). */
+#define FMLK_FMT_DENSE_VECTOR 0
+#define FMLK_FMT_VECTOR 1
+#define FMLK_FMT_VECTOR_WITH_NORM 2
+
+/* processElement1 for rows still in the serializer's byte format: `nbytes` of back-to-back
+ * records of `format`, every one of dimension d, are copied to the device as they are and
+ * unpacked there (byte swap, header strip) into the HBM-resident cache -- replaces the per-row
+ * DenseVectorSerializer.deserialize (DenseVectorSerializer.java:96-116) on the ingest path.
+ * *out_rows = rows appended.  A record with another length, or nbytes not a multiple of the
+ * record size: FMLK_ERR_DIM "Vector size mismatched."; a sparse tag: FMLK_ERR_INVALID_ARG
+ * (the reference densifies before caching, KMeans.java:94).  On error the cache is unchanged.
+ * The stored l2Norm is not used (it is BLAS.norm2 of the same values, VectorWithNorm.java:32-39). */
+int32_t fmlk_append_points_serialized(fmlk_ctx *ctx, const uint8_t *records_host, int64_t nbytes,
+                                      int32_t format, int32_t d, int64_t *out_rows);
+
+/* The unpack kernel alone, device to device, asynchronous on `cuda_stream`: n records at
+ * records_dev (8-byte aligned) -> n x d native doubles at out_rows_dev.  *out_bad_dev (device
+ * int, zeroed by the caller) becomes 1 (sparse / unknown tag) or 2 (a record's len != d). */
+int32_t fmlk_decode_rows_dev(int32_t device, void *cuda_stream, const uint8_t *records_dev, int64_t n,
+                             int32_t d, int32_t format, double *out_rows_dev, int32_t *out_bad_dev);
+
 /* Zero-copy variant: the context reads caller-owned device memory in place; the caller
  * keeps it alive and unchanged until fmlk_clear_points / fmlk_destroy. */
 int32_t fmlk_adopt_points_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d);

@@ -614,6 +614,56 @@ ORC_API int64_t orc_model_decode(const uint8_t *in, int64_t len, int32_t *k_out,
 }
 
 /* ------------------------------------------------------------------ */
+/* Serialized rows (the ingest side of the hot path)                   */
+/* format 0: DenseVectorSerializer.serialize (CORE/linalg/typeinfo/DenseVectorSerializer.java:78-93):
+ *           writeInt(len), then Bits.putDouble per value (CORE/util/Bits.java:54-70, big-endian);
+ * format 1: VectorSerializer.serialize (VectorSerializer.java:80-88): writeByte(0) for a dense
+ *           vector, then format 0;
+ * format 2: VectorWithNormSerializer.serialize (VectorWithNormSerializer.java:74-78): format 1,
+ *           then writeDouble(l2Norm), l2Norm = BLAS.norm2(vector) (VectorWithNorm.java:32-39). */
+ORC_API int64_t orc_record_bytes(int32_t format, int32_t d) {
+    return (format == 0 ? 4 : format == 1 ? 5 : 13) + 8 * (int64_t)d;
+}
+
+ORC_API int64_t orc_encode_rows(int64_t n, int32_t d, const double *rows, int32_t format, uint8_t *out) {
+    uint8_t *q = out;
+    for (int64_t i = 0; i < n; i++) {
+        const double *x = rows + (size_t)i * d;
+        if (format >= 1) *q++ = 0;
+        put_be32(q, d);
+        q += 4;
+        for (int32_t j = 0; j < d; j++, q += 8) put_be64(q, x[j]);
+        if (format == 2) {
+            put_be64(q, orc_dnrm2(d, x));
+            q += 8;
+        }
+    }
+    return (int64_t)(q - out);
+}
+
+/* DenseVectorSerializer.deserialize (DenseVectorSerializer.java:96-116) and its wrappers, for
+ * records that must all have dimension d.  Returns rows decoded, -1: sparse / unknown tag,
+ * -2: a length other than d or a truncated buffer ("Vector size mismatched."). */
+ORC_API int64_t orc_decode_rows(const uint8_t *in, int64_t len, int32_t format, int32_t d, double *rows,
+                                double *norms) {
+    const int64_t rec = orc_record_bytes(format, d);
+    if (len % rec) return -2;
+    const int64_t n = len / rec;
+    const uint8_t *q = in;
+    for (int64_t i = 0; i < n; i++) {
+        if (format >= 1 && *q++ != 0) return -1;
+        if (get_be32(q) != d) return -2;
+        q += 4;
+        for (int32_t j = 0; j < d; j++, q += 8) rows[(size_t)i * d + j] = get_be64(q);
+        if (format == 2) {
+            if (norms) norms[i] = get_be64(q);
+            q += 8;
+        }
+    }
+    return n;
+}
+
+/* ------------------------------------------------------------------ */
 /* Timed CPU baseline: one training round with the rows split over `threads`
  * contiguous shards (the reference's data parallelism at parallelism = threads),
  * partials reduced in shard order.  Same arithmetic as orc_train_local. */

@@ -70,6 +70,9 @@ def lib():
         "orc_model_encode": (C.c_int64, [C.c_int32, C.c_int32, _f64p, _f64p, _u8p]),
         "orc_model_decode": (C.c_int64, [C.c_void_p, C.c_int64, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                          C.c_void_p, C.c_void_p]),
+        "orc_record_bytes": (C.c_int64, [C.c_int32, C.c_int32]),
+        "orc_encode_rows": (C.c_int64, [C.c_int64, C.c_int32, _f64p, C.c_int32, _u8p]),
+        "orc_decode_rows": (C.c_int64, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
         "orc_train_round_mt": (None, [C.c_int64, C.c_int32, _f64p, C.c_int32, _f64p, _f64p, _i32p, C.c_int32]),
         "orc_max_threads": (C.c_int32, []),
     }
@@ -292,6 +295,32 @@ def online_round(batch, centroids, weights, decay, p):
     lib().orc_online_round(batch.shape[0], batch.shape[1], batch.reshape(-1), c.shape[0], c.reshape(-1), w,
                            float(decay), int(p))
     return c, w
+
+
+FMT_DENSE_VECTOR, FMT_VECTOR, FMT_VECTOR_WITH_NORM = 0, 1, 2
+
+
+def encode_rows(points, fmt):
+    """The reference serializers' bytes for the rows of `points`, back to back."""
+    points = _rows(points)
+    n, d = points.shape
+    out = np.empty(int(lib().orc_record_bytes(fmt, d)) * n, dtype=np.uint8)
+    m = lib().orc_encode_rows(n, d, points.reshape(-1), fmt, out)
+    assert m == out.size
+    return out
+
+
+def decode_rows(data, fmt, d, want_norms=False):
+    buf = np.frombuffer(data, dtype=np.uint8) if not isinstance(data, np.ndarray) else np.ascontiguousarray(data)
+    rec = int(lib().orc_record_bytes(fmt, d))
+    rows = np.empty((buf.size // rec, d), dtype=np.float64)
+    norms = np.empty(rows.shape[0], dtype=np.float64)
+    n = lib().orc_decode_rows(buf.ctypes.data, buf.size, fmt, d, rows.ctypes.data, norms.ctypes.data)
+    if n == -1:
+        raise ValueError("sparse or unknown vector tag")
+    if n < 0:
+        raise ValueError("Vector size mismatched.")
+    return (rows, norms) if want_norms else rows
 
 
 def model_encode(centroids, weights):
