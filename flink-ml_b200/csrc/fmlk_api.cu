@@ -28,8 +28,8 @@ typedef struct {
     char internal[FMLK_NCCL_ID_BYTES];
 } ncclUniqueId;
 enum { ncclSuccess = 0 };
-enum { ncclSum = 0 };
-enum { ncclFloat64 = 8 };
+enum { ncclSum = 0, ncclMax = 2 };
+enum { ncclInt64 = 4, ncclFloat64 = 8 };
 
 struct NcclApi {
     void *handle = nullptr;
@@ -1123,6 +1123,51 @@ struct JRandom {
     }
 };
 } // namespace
+
+int32_t fmlk_all_reduce_sum_dev(fmlk_ctx *ctx, double *values_dev_inout, int64_t len) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if (len < 0 || (len > 0 && !values_dev_inout)) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad values / len");
+    if (ctx->world == 1 || len == 0) return FMLK_OK;
+    CKN(ctx, nccl().AllReduce(values_dev_inout, values_dev_inout, (size_t)len, ncclFloat64, ncclSum, ctx->comm,
+                              ctx->stream));
+    return FMLK_OK;
+}
+
+int32_t fmlk_all_reduce_sum(fmlk_ctx *ctx, double *values_host_inout, int64_t len) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if (len < 0 || (len > 0 && !values_host_inout)) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad values / len");
+    if (ctx->world == 1) return FMLK_OK;
+    // agree on the length first: max over ranks of (len, -len) gives the largest and the smallest
+    long long *probe = nullptr;
+    if ((rc = dev_alloc(ctx, &probe, 2))) return rc;
+    const long long mine[2] = {(long long)len, -(long long)len};
+    long long got[2] = {0, 0};
+    cudaError_t e = cudaMemcpyAsync(probe, mine, sizeof(mine), cudaMemcpyHostToDevice, ctx->stream);
+    int nrc = e == cudaSuccess ? nccl().AllReduce(probe, probe, 2, ncclInt64, ncclMax, ctx->comm, ctx->stream) : 0;
+    if (e == cudaSuccess && nrc == ncclSuccess)
+        e = cudaMemcpyAsync(got, probe, sizeof(got), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && nrc == ncclSuccess) e = cudaStreamSynchronize(ctx->stream);
+    dev_free(probe);
+    if (nrc != ncclSuccess) return fail(ctx, FMLK_ERR_NCCL, "ncclAllReduce failed");
+    if (e != cudaSuccess) return fail(ctx, FMLK_ERR_CUDA, cudaGetErrorString(e));
+    if (got[0] != -got[1]) return fail(ctx, FMLK_ERR_INVALID_ARG, "The input double array must have same length.");
+    if (len == 0) return FMLK_OK;
+    double *buf = nullptr;
+    if ((rc = dev_alloc(ctx, &buf, (size_t)len))) return rc;
+    e = cudaMemcpyAsync(buf, values_host_inout, (size_t)len * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
+    if (e == cudaSuccess) nrc = nccl().AllReduce(buf, buf, (size_t)len, ncclFloat64, ncclSum, ctx->comm, ctx->stream);
+    if (e == cudaSuccess && nrc == ncclSuccess)
+        e = cudaMemcpyAsync(values_host_inout, buf, (size_t)len * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess && nrc == ncclSuccess) e = cudaStreamSynchronize(ctx->stream);
+    dev_free(buf);
+    if (nrc != ncclSuccess) return fail(ctx, FMLK_ERR_NCCL, "ncclAllReduce failed");
+    if (e != cudaSuccess) return fail(ctx, FMLK_ERR_CUDA, cudaGetErrorString(e));
+    return FMLK_OK;
+}
 
 int32_t fmlk_reservoir(int64_t n, int32_t k, int64_t seed, int64_t *out_ids) {
     if (n < 0 || k < 0 || (k > 0 && !out_ids)) return fail(nullptr, FMLK_ERR_INVALID_ARG, "bad reservoir arguments");

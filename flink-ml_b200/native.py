@@ -51,6 +51,8 @@ SIGNATURES = {
     "fmlk_append_points_dev": (_i32, [_vp, _vp, _i64, _i32]),
     "fmlk_append_points_serialized": (_i32, [_vp, _vp, _i64, _i32, _i32, C.POINTER(_i64)]),
     "fmlk_decode_rows_dev": (_i32, [_i32, _vp, _vp, _i64, _i32, _i32, _vp, _vp]),
+    "fmlk_all_reduce_sum": (_i32, [_vp, _vp, _i64]),
+    "fmlk_all_reduce_sum_dev": (_i32, [_vp, _vp, _i64]),
     "fmlk_adopt_points_dev": (_i32, [_vp, _vp, _i64, _i32]),
     "fmlk_clear_points": (_i32, [_vp]),
     "fmlk_num_points": (_i64, [_vp]),
@@ -324,6 +326,16 @@ class Context:
                                          float(decay), c.ctypes.data, w.ctypes.data))
         self.k, self.md = k, d
         return c, w
+
+    # -- DataStreamUtils.allReduceSum
+    def all_reduce_sum(self, values):
+        """Element-wise sum of one double array per subtask, returned on every subtask."""
+        v = np.array(values, dtype=np.float64, copy=True).reshape(-1)
+        self._ck(lib().fmlk_all_reduce_sum(self._h, v.ctypes.data if v.size else None, v.size))
+        return v
+
+    def all_reduce_sum_dev(self, dev_ptr, n):
+        self._ck(lib().fmlk_all_reduce_sum_dev(self._h, dev_ptr, int(n)))
 
     # -- measurement
     def profile(self):

@@ -192,6 +192,21 @@ int32_t fmlk_predict_cached(fmlk_ctx *ctx, int32_t *out_labels_host);
 int32_t fmlk_online_round(fmlk_ctx *ctx, const double *local_batch_host, int64_t n_local, int32_t d,
                           int32_t k, double decay, double *centroids_inout, double *weights_inout);
 
+/* ---- DataStreamUtils.allReduceSum (CORE/common/datastream/DataStreamUtils.java:102-104,
+ *      AllReduceImpl.java:71-302) ---- */
+
+/* Every subtask contributes one double[len]; every subtask receives the element-wise sum (the
+ * reference splits the array into 4096-element chunks reduced on subtask chunk mod p in arrival
+ * order; here it is one ncclAllReduce over NVLink on the context's stream, identical on every
+ * rank).  values_host_inout: in = this subtask's array, out = the sum.  Lengths that differ
+ * between subtasks: FMLK_ERR_INVALID_ARG "The input double array must have same length."
+ * (AllReduceImpl.java:196-198) on every rank.  world == 1: the array is returned unchanged. */
+int32_t fmlk_all_reduce_sum(fmlk_ctx *ctx, double *values_host_inout, int64_t len);
+
+/* Same on device memory, in place, asynchronous on the context's stream; the caller guarantees
+ * equal lengths on all ranks (no check, no host synchronisation). */
+int32_t fmlk_all_reduce_sum_dev(fmlk_ctx *ctx, double *values_dev_inout, int64_t len);
+
 /* ---- initial centroids: KMeans.selectRandomCentroids (KMeans.java:310-327) ---- */
 
 /* One SamplingOperator (CORE/common/datastream/DataStreamUtils.java:633-704) over a stream of

@@ -12,7 +12,7 @@ import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
 import flink_ml_b200 as F  # noqa: E402
-from flink_ml_b200 import kmeans as K  # noqa: E402
+from flink_ml_b200 import kmeans as K, native  # noqa: E402
 from oracle import oracle as O  # noqa: E402
 
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
@@ -56,6 +56,31 @@ flags = [None] * world
 dist.all_gather_object(flags, lab_ok, group=host)
 if rank == 0:
     print("labels bit-exact on every rank:", all(flags))
+    ok = ok and all(flags)
+# DataStreamUtils.allReduceSum: AllReduceImplTest.java:66-110 sizes (0, half a chunk, p/2 and 1.5 p chunks),
+# every worker contributes [0, 1, ..., n-1]; then unequal lengths must raise on every rank
+ctx = cluster.context()
+ar_ok = True
+for numel in (0, 2048, 4096 * world // 2, 4096 * world * 3 // 2, 1_000_003):
+    got = ctx.all_reduce_sum(np.arange(numel, dtype=np.float64))
+    ar_ok = ar_ok and got.shape == (numel,) and bool(np.array_equal(got, np.arange(numel, dtype=np.float64) * world))
+rnd = np.random.default_rng(100 + rank).standard_normal(300_000)
+allr = [None] * world
+dist.all_gather_object(allr, rnd, group=host)
+got = ctx.all_reduce_sum(rnd)
+ar_ok = ar_ok and bool(np.allclose(got, np.sum(allr, axis=0), rtol=1e-12, atol=1e-12))
+same_everywhere = [None] * world
+dist.all_gather_object(same_everywhere, got.tobytes(), group=host)
+ar_ok = ar_ok and all(b == same_everywhere[0] for b in same_everywhere)
+try:
+    ctx.all_reduce_sum(np.zeros(10 + rank))
+    ar_ok = False
+except native.IllegalArgumentError as e:
+    ar_ok = ar_ok and "The input double array must have same length." in str(e)
+flags = [None] * world
+dist.all_gather_object(flags, ar_ok, group=host)
+if rank == 0:
+    print("allReduceSum on every rank:", all(flags))
     ok = ok and all(flags)
 dist.barrier()
 cluster.close()

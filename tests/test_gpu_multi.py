@@ -22,3 +22,4 @@ def test_two_rank_fit_matches_oracle():
     out = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
     assert out.returncode == 0, out.stdout[-2000:] + out.stderr[-2000:]
     assert "OK" in out.stdout and "labels bit-exact on every rank: True" in out.stdout
+    assert "allReduceSum on every rank: True" in out.stdout

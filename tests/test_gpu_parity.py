@@ -352,3 +352,11 @@ def test_predict_dev_and_adopt(ctx):
 def test_fp64_peaks_are_plausible():
     dmma, dfma = native.measure_fp64_peaks(0, 50.0)
     assert 5.0 < dmma < 100.0 and 5.0 < dfma < 100.0
+
+
+def test_all_reduce_sum_single_subtask_is_identity(ctx):
+    """DataStreamUtils.allReduceSum at parallelism 1 (AllReduceImplTest.java:66-110 with one worker);
+    the N > 1 case runs in tests/test_gpu_multi.py."""
+    for numel in (0, 2048, 6144):
+        v = np.arange(numel, dtype=np.float64)
+        assert np.array_equal(ctx.all_reduce_sum(v), v)
