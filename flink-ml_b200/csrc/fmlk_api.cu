@@ -434,6 +434,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.private_sums = cfg.private_sums;
     p.spin_ns = cfg.spin_ns;
     p.stagger_ns = cfg.stagger_ns;
+    p.acc_dmma = env_int("FMLK_TUNE_ACC_DMMA", 1);
     p.no_bulk = env_int("FMLK_TUNE_NO_BULK", 0);
     p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
     p.recheck_count = ctx->recheck;

@@ -64,6 +64,7 @@ struct AssignParams {
 #ifdef FMLK_TRACE
     unsigned long long *trace; // [warps of CTA 0][kTraceEvents] (clock << 4 | event), debugging builds only
 #endif
+    int32_t acc_dmma; // 1: accumulator warps add on the FP64 tensor pipe (d = 32 x column groups, finite rows)
     int32_t no_bulk;  // tuning: 1 = row tiles with 16-byte cp.async instead of bulk copies
     int32_t fma_mode; // exact path follows the JDK>=11 netlib variant
     unsigned long long *recheck_count;
@@ -570,6 +571,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         const int mma_threads = W * 32;
         double *Xw = Xall + (size_t)warp * xs * xtile_elems;
         unsigned long long local_rechecks = 0;
+        bool seen_nonfinite = false; // sticky: a row with Inf / NaN has been in this warp's buffer
         int cbuf = 0;
         // row tiles: bulk asynchronous copies (one per row, issued by the lane of that row) that
         // complete on this warp's mbarrier; rows of odd length fall back to 8-byte cp.async
@@ -583,6 +585,8 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 fence_proxy_async_smem(); // the buffer was read (and zeroed at start) through the generic proxy
                 if (lane == 0) mbar_arrive_expect_tx(bar, row_bytes * (unsigned)rows);
                 __syncwarp();
+                // (measured: issuing all the copies from one lane instead is slower, 2.4 k against 1.65 k
+                // cycles per tile -- either way the uniform-datapath copy costs ~100 cycles per row)
                 if (lane < rows)
                     bulk_copy_g2s((unsigned)__cvta_generic_to_shared(dst + (size_t)lane * S),
                                   p.x + (row0 + lane) * p.d, row_bytes, bar);
@@ -715,6 +719,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 mx0 = max(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
                 mx1 = max(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
                 mx1 = max(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+                if (ACCUM && __any_sync(0xffffffffu, max(mx0, mx1) >= 0x7ff00000)) seen_nonfinite = true;
 
                 // Decision margin in score units (D = |x|^2 - 2 v, so 2 * margin_v is the gap in squared
                 // distance) against a power-of-two upper bound of the rounding threshold
@@ -793,7 +798,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 }
                 __syncwarp();
                 if (lane == 0) {
-                    rows_all[warp * xs + stage] = rows_valid;
+                    rows_all[warp * xs + stage] = rows_valid | (seen_nonfinite ? 0x100 : 0);
                     st_release_smem(&seq_ready[warp], (int)it + 1);
                 }
             } else {
@@ -829,7 +834,8 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
             spin_until_at_least(&seq_ready[w], it_w + 1, (unsigned)p.spin_ns);
             FMLK_TRACE_EVENT(6) // accumulator: tile taken
             const int stage = (xs == 2) ? (it_w & 1) : 0;
-            const int rows = rows_all[w * xs + stage];
+            const int packed_rows = rows_all[w * xs + stage];
+            const int rows = packed_rows & 0xff;
             const double *Xt = Xall + (size_t)(w * xs + stage) * xtile_elems + (size_t)rbase * S;
             const int *lab = lab_all + (w * xs + stage) * kWarpRows;
             const int *offp = off_all + (w * xs + stage) * kWarpRows + rbase;
@@ -838,6 +844,46 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
             if (++w == W) {
                 w = 0;
                 it_w++;
+            }
+            if (rows > 0 && sums_smem && p.acc_dmma && p.d == cstride && !(packed_rows & 0x100) &&
+                (reinterpret_cast<uintptr_t>(sums_s) & 15) == 0) {
+                // d = 32 G and every row seen so far finite: the eight adds of this warp's 8 rows x 32
+                // columns go through the FP64 tensor pipe as D = I x X + C (m8n8k4: A selects row
+                // 4s + k for output row m, products 1.0 * x and 0.0 * x are exact, so each cell gets
+                // exactly one rounded addition, the same as sums + x).  A DMMA from this warp takes its
+                // turn among the MMA warps' DMMAs; a plain FP64 add waits two to three times longer.
+                // (0.0 * x needs x finite: tiles after a non-finite row take the scalar path below.)
+                const int m = lane >> 2, kq = lane & 3;
+                const int my_off = offp[m];
+                const double *xb = Xt + g * 32 + m;
+                double bfr[2][4];
+#pragma unroll
+                for (int s2 = 0; s2 < 2; s2++)
+#pragma unroll
+                    for (int nt = 0; nt < 4; nt++) bfr[s2][nt] = xb[(size_t)(4 * s2 + kq) * S + 8 * nt];
+                const int my_label = (a == 0 && lane < rows) ? lab[lane] : -1;
+                __syncwarp();
+                if (lane == 0) st_release_smem(done_flag, done_value);
+                FMLK_TRACE_EVENT(7) // accumulator: tile copied, buffer released
+                spin_until_at_least(&rmw_done[partner], tiles_done, 20u); // partner is done with the previous tile's cells
+                FMLK_TRACE_EVENT(8) // accumulator: partner is done with the previous tile
+                double2 *crow = reinterpret_cast<double2 *>(sums_s + my_off + g * 32 + 2 * kq);
+                const double a0 = (m == kq) ? 1.0 : 0.0, a1 = (m == 4 + kq) ? 1.0 : 0.0;
+                double2 cf[4];
+#pragma unroll
+                for (int nt = 0; nt < 4; nt++) cf[nt] = crow[4 * nt];
+#pragma unroll
+                for (int nt = 0; nt < 4; nt++) {
+                    dmma884(cf[nt].x, cf[nt].y, a0, bfr[0][nt]);
+                    dmma884(cf[nt].x, cf[nt].y, a1, bfr[1][nt]);
+                }
+#pragma unroll
+                for (int nt = 0; nt < 4; nt++) crow[4 * nt] = cf[nt];
+                if (my_label >= 0) atomicAdd(&counts_s[my_label], 1);
+                __syncwarp();
+                tiles_done++;
+                if (lane == 0) st_release_smem(&rmw_done[a], tiles_done);
+                continue;
             }
             if (rows > 0 && sums_smem && p.d <= cstride) {
                 // common case, one column per lane: copy what the tile contributes into registers

@@ -360,3 +360,28 @@ def test_all_reduce_sum_single_subtask_is_identity(ctx):
     for numel in (0, 2048, 6144):
         v = np.arange(numel, dtype=np.float64)
         assert np.array_equal(ctx.all_reduce_sum(v), v)
+
+
+@pytest.mark.parametrize("d", [32, 64])
+def test_tensor_pipe_accumulate_with_nonfinite_rows(ctx, d):
+    """d = 32 / 64 accumulate on the FP64 tensor pipe (D = I x X + C); a tile that holds or follows a
+    non-finite row must take the scalar path (0 * Inf would poison its neighbours' sums): the sums
+    of every cluster other than the ones those rows land in stay finite and match the oracle."""
+    rng = np.random.default_rng(11)
+    n, k = 60_000, 40
+    x = rng.standard_normal((n, d)) * 3.0
+    x[::7] = -x[::7]
+    x[12_345, 5] = np.inf
+    x[30_000] = np.nan
+    x[45_678, 0] = -np.inf
+    x[59_999, d - 1] = 1e308
+    cent = x[100:100 + k].copy()
+    _step_parity(ctx, x, cent)
+    ctx.clear_points()
+    ctx.append_points(x)
+    ctx.set_centroids(cent)
+    sums, counts = ctx.local_partials()
+    o_sums, o_counts = O.train_local(x, cent)[:2]
+    finite_rows = np.isfinite(o_sums).all(axis=1)
+    assert finite_rows.sum() >= k - 4 and np.array_equal(np.isfinite(sums).all(axis=1), finite_rows)
+    ctx.clear_points()
