@@ -87,7 +87,7 @@ struct Chunk {
 
 struct LaunchCfg {
     int warps, acc_warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid, private_sums;
-    int acc_order, spin_ns, stagger_ns;
+    int spin_ns, stagger_ns;
     size_t smem;
 };
 
@@ -209,7 +209,6 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     c.k_pad = (k + 7) & ~7;
     c.grid = ctx->sm_count;
     c.acc_warps = accum ? acc_warps_for(d) : 0;
-    c.acc_order = 0; // tiles are accumulated in the fixed order (round, warp): reproducible sums
     c.spin_ns = env_int("FMLK_TUNE_SPIN_NS", 40);
     c.stagger_ns = env_int("FMLK_TUNE_STAGGER_NS", 0);
     const int force_w = env_int("FMLK_TUNE_W", 0), force_xs = env_int("FMLK_TUNE_XS", 0);
@@ -430,7 +429,6 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.xs = cfg.xs;
     p.mma_warps = cfg.warps;
     p.acc_warps = cfg.acc_warps;
-    p.acc_order = cfg.acc_order;
     p.private_sums = cfg.private_sums;
     p.spin_ns = cfg.spin_ns;
     p.stagger_ns = cfg.stagger_ns;
@@ -1328,11 +1326,11 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
     else cudaFuncGetAttributes(&fa, assign_kernel<0>);
     snprintf(out, (size_t)out_len,
              "regs=%d max_threads=%d local=%zu grid=%d block=%d smem=%zu mma_warps=%d acc_warps=%d xs=%d S=%d ksteps=%d k_pad=%d nc_tile=%d n_ctiles=%d "
-             "sums_in_smem=%d n_partials=%d acc_order=%d private_sums=%d",
+             "sums_in_smem=%d n_partials=%d private_sums=%d",
              fa.numRegs, fa.maxThreadsPerBlock, fa.localSizeBytes, c.grid, (c.warps + c.acc_warps) * 32, c.smem, c.warps,
              c.acc_warps, c.xs, c.S, c.ksteps, c.k_pad,
              c.nc_tile, c.n_ctiles,
-             c.sums_in_smem, c.n_partials, c.acc_order, c.private_sums);
+             c.sums_in_smem, c.n_partials, c.private_sums);
     return FMLK_OK;
 }
 

@@ -58,7 +58,6 @@ struct AssignParams {
     int32_t acc_warps; // warps that own columns of the sums (accumulate launches only)
     int32_t private_sums; // 1: few centroids -- every MMA warp keeps its own k x d sums in shared memory and
                           //    adds its own tiles' rows itself (no accumulator warps, no hand-off)
-    int32_t acc_order; // always 0: tiles are accumulated in the fixed order (round, warp): bit-reproducible sums
     int32_t spin_ns;   // back-off of the hand-off spin loops
     int32_t stagger_ns; // initial delay between the MMA warps of one scheduler (see assign_kernel)
 #ifdef FMLK_TRACE
@@ -252,12 +251,6 @@ struct Top2 {
 __device__ __forceinline__ int score_key_hi(double v) {
     const int hi = __double2hiint(v);
     return hi ^ ((hi >> 31) & 0x7fffffff);
-}
-__device__ __forceinline__ double key_hi_value(int khi, unsigned lo_bits) {
-    // inverse of the key map for (khi : lo_bits); for negative values the low word flips too
-    const int hi = khi ^ ((khi >> 31) & 0x7fffffff);
-    const unsigned lo = (khi < 0) ? ~lo_bits : lo_bits;
-    return __hiloint2double(hi, (int)lo);
 }
 __device__ __forceinline__ Top2 top2_init() {
     const int ninf = score_key_hi(-INFINITY);

@@ -206,3 +206,24 @@ def test_two_stage_sampler_world2_gloo():
 def test_rows_on_task_matches_row_generator():
     for n, p in [(10, 4), (10 ** 9, 8), (7, 7), (3, 5)]:
         assert [native.rows_on_task(n, t, p) for t in range(p)] == [O.rows_on_task(n, t, p) for t in range(p)]
+
+
+def test_jni_shim_type_checks_against_the_header():
+    """integration/flink-ml-cuda/src/main/native/fmlk_jni.cc cannot be built here (no JDK); it must at
+    least parse and type-check against include/fmlk.h with a minimal stand-in for jni.h, and every
+    native method the Java class declares must have its JNI function."""
+    import re
+    import shutil
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    shim = os.path.join(root, "integration", "flink-ml-cuda", "src", "main", "native", "fmlk_jni.cc")
+    java = os.path.join(root, "integration", "flink-ml-cuda", "src", "main", "java", "org", "apache", "flink", "ml",
+                        "cuda", "KMeansNative.java")
+    gxx = shutil.which("g++")
+    assert gxx, "g++ not found"
+    out = subprocess.run([gxx, "-std=c++17", "-fsyntax-only", "-Wall", "-Werror", "-I" + os.path.join(root, "integration", "check"),
+                          "-I" + os.path.join(root, "include"), shim], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr[-2000:]
+    natives = set(re.findall(r"native\s+[\w\[\]]+\s+(\w+)\s*\(", open(java).read()))
+    exported = set(re.findall(r"Java_org_apache_flink_ml_cuda_KMeansNative_(\w+)\s*\(", open(shim).read()))
+    assert natives and natives == exported, (natives ^ exported)
