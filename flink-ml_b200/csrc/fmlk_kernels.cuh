@@ -64,6 +64,7 @@ struct AssignParams {
     unsigned long long *trace; // [warps of CTA 0][kTraceEvents] (clock << 4 | event), debugging builds only
 #endif
     int32_t acc_dmma; // 1: accumulator warps add on the FP64 tensor pipe (d = 32 x column groups, finite rows)
+    int32_t row_copies; // 1 = one bulk copy per row, 0 = one per tile (chosen by the host: see assign_kernel)
     int32_t no_bulk;  // tuning: 1 = row tiles with 16-byte cp.async instead of bulk copies
     int32_t fma_mode; // exact path follows the JDK>=11 netlib variant
     unsigned long long *recheck_count;
@@ -351,6 +352,37 @@ __device__ __noinline__ void load_rows_async(double *dst, const double *src, int
     }
 }
 
+// A row tile that arrived as ONE bulk copy lies densely (row r at r * d doubles) at the start of its
+// buffer; the MMA fragments want rows S doubles apart (S > d, the bank-conflict padding).  The warp
+// spreads the rows in place, from the last one down, R rows at a time through registers: the
+// destination of a group never reaches the source of the rows below it (S >= d), and within a
+// group every load precedes every store.  CH = 16-byte chunks per lane and row (d <= 64 * CH).
+template <int CH, int R>
+__device__ __forceinline__ void spread_rows_in_place(double *buf, int rows, int d, int S, int lane) {
+    const int cpr = d >> 1; // 16-byte chunks per row
+    for (int hi = rows; hi > 1; hi -= R) {
+        const int lo = max(1, hi - R);
+        double2 v[R][CH];
+#pragma unroll
+        for (int r = 0; r < R; r++)
+#pragma unroll
+            for (int c = 0; c < CH; c++) {
+                // always a valid address (clamped), so the staging values live in registers
+                const int q = min(lane + 32 * c, cpr - 1);
+                v[r][c] = reinterpret_cast<const double2 *>(buf + (size_t)min(lo + r, hi - 1) * d)[q];
+            }
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < R; r++)
+#pragma unroll
+            for (int c = 0; c < CH; c++) {
+                const int q = lane + 32 * c;
+                if (lo + r < hi && q < cpr) reinterpret_cast<double2 *>(buf + (size_t)(lo + r) * S)[q] = v[r][c];
+            }
+        __syncwarp();
+    }
+}
+
 // release / acquire on shared-memory counters: the hand-off between the MMA warps and the
 // accumulator warps
 __device__ __forceinline__ void st_release_smem(int *p, int v) {
@@ -566,9 +598,16 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         unsigned long long local_rechecks = 0;
         bool seen_nonfinite = false; // sticky: a row with Inf / NaN has been in this warp's buffer
         int cbuf = 0;
-        // row tiles: bulk asynchronous copies (one per row, issued by the lane of that row) that
-        // complete on this warp's mbarrier; rows of odd length fall back to 8-byte cp.async
+        // row tiles: bulk asynchronous copies (cp.async.bulk) completing on this warp's mbarrier.
+        // Either one copy per row, issued by the lane of that row straight into the padded layout
+        // (~100 cycles of issue per row -- the copy is a uniform-datapath instruction -- but the first
+        // rows are already in flight while the later ones issue), or ONE copy for the 16 contiguous
+        // rows, which lands densely and is then spread to the padded stride by the warp
+        // (spread_rows_in_place).  Measured: one copy per tile wins where the kernel is HBM-bound
+        // (few centroids: +7 % at k = 10, d = 100), one per row where it is bound by the tensor
+        // pipe (k = 100: 30.7 against 30.4 TFLOP/s).  Rows of odd length use 8-byte cp.async.
         const bool use_tma = vec16 && !p.no_bulk;
+        const bool one_copy = use_tma && p.d <= 128 && p.row_copies == 0;
         const unsigned row_bytes = (unsigned)p.d * 8u;
         unsigned uses0 = 0, uses1 = 0; // completed phases of the stage barriers (parity = uses & 1)
         auto x_issue = [&](int stage, int64_t row0, int rows) {
@@ -576,24 +615,36 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
             if (use_tma) {
                 const unsigned bar = (unsigned)__cvta_generic_to_shared(&xbar[warp * xs + stage]);
                 fence_proxy_async_smem(); // the buffer was read (and zeroed at start) through the generic proxy
-                if (lane == 0) mbar_arrive_expect_tx(bar, row_bytes * (unsigned)rows);
-                __syncwarp();
-                // (measured: issuing all the copies from one lane instead is slower, 2.4 k against 1.65 k
-                // cycles per tile -- either way the uniform-datapath copy costs ~100 cycles per row)
-                if (lane < rows)
-                    bulk_copy_g2s((unsigned)__cvta_generic_to_shared(dst + (size_t)lane * S),
-                                  p.x + (row0 + lane) * p.d, row_bytes, bar);
+                if (one_copy) {
+                    __syncwarp();
+                    if (lane == 0) {
+                        mbar_arrive_expect_tx(bar, row_bytes * (unsigned)rows);
+                        bulk_copy_g2s((unsigned)__cvta_generic_to_shared(dst), p.x + row0 * p.d, row_bytes * (unsigned)rows,
+                                      bar);
+                    }
+                } else {
+                    if (lane == 0) mbar_arrive_expect_tx(bar, row_bytes * (unsigned)rows);
+                    __syncwarp();
+                    if (lane < rows)
+                        bulk_copy_g2s((unsigned)__cvta_generic_to_shared(dst + (size_t)lane * S),
+                                      p.x + (row0 + lane) * p.d, row_bytes, bar);
+                }
             } else {
                 load_rows_async(dst, p.x + row0 * p.d, rows, p.d, S, lane, 32, false);
                 cp_async_commit();
             }
         };
-        auto x_wait = [&](int stage) {
+        auto x_wait = [&](int stage, int rows) {
             if (use_tma) {
                 const unsigned bar = (unsigned)__cvta_generic_to_shared(&xbar[warp * xs + stage]);
                 unsigned &u = stage ? uses1 : uses0;
                 mbar_wait(bar, u & 1u);
                 u++;
+                if (one_copy && S != p.d) {
+                    double *buf = Xw + (size_t)stage * xtile_elems;
+                    if (p.d <= 64) spread_rows_in_place<1, 4>(buf, rows, p.d, S, lane);
+                    else spread_rows_in_place<2, 2>(buf, rows, p.d, S, lane);
+                }
             } else {
                 cp_async_wait<0>();
                 __syncwarp();
@@ -643,7 +694,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 x_issue(0, row0, rows_valid);
             }
             FMLK_TRACE_EVENT(1) // tile start: buffer free, load issued
-            if (active) x_wait(stage);
+            if (active) x_wait(stage, rows_valid);
             FMLK_TRACE_EVENT(2) // rows have landed: multiply starts
 
             Top2 t0 = top2_init(), t1 = top2_init();
