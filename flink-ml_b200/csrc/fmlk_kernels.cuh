@@ -690,8 +690,8 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                     const int64_t nrow0 = ntile * kWarpRows;
                     x_issue(stage ^ 1, nrow0, (int)min((int64_t)kWarpRows, p.n - nrow0));
                 }
-            } else if (active) {
-                x_issue(0, row0, rows_valid);
+            } else if (active && (ACCUM || it == 0)) {
+                x_issue(0, row0, rows_valid); // (predict: tiles after the first were requested early, below)
             }
             FMLK_TRACE_EVENT(1) // tile start: buffer free, load issued
             if (active) x_wait(stage, rows_valid);
@@ -753,6 +753,15 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
             }
 
             FMLK_TRACE_EVENT(3) // multiply + selection done
+            if (!ACCUM && xs == 1) {
+                // predict: nothing below reads the row buffer (the rare exact replay fetches its row from
+                // global memory), so the next tile is requested now and lands during merge and labels
+                const int64_t ntile = tile + GW;
+                if (ntile < total_tiles) {
+                    const int64_t nrow0 = ntile * kWarpRows;
+                    x_issue(0, nrow0, (int)min((int64_t)kWarpRows, p.n - nrow0));
+                }
+            }
             if (active) {
                 // combine the four lanes of each quad (same rows, different columns)
                 top2_merge_xor(t0, 1);
@@ -799,7 +808,8 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 while (flagged) {
                     const int r = __ffs(flagged) - 1;
                     flagged &= flagged - 1;
-                    const int lab = exact_find_closest(Xt + (size_t)r * S, p.c, p.cn, p.k, p.d, p.fma_mode);
+                    const double *xrow = (!ACCUM && xs == 1) ? p.x + (row0 + r) * p.d : Xt + (size_t)r * S;
+                    const int lab = exact_find_closest(xrow, p.c, p.cn, p.k, p.d, p.fma_mode);
                     if (lane == 0) {
                         lab_s[r] = lab;
                         local_rechecks++;
