@@ -88,6 +88,7 @@ struct Chunk {
 struct LaunchCfg {
     int warps, acc_warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid, private_sums;
     int spin_ns, stagger_ns;
+    int wide; // rows too long for the shared-memory tiling: assign_wide_kernel
     size_t smem;
 };
 
@@ -217,13 +218,13 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     // many centroids: FP64-bound; a warp is blocked for ~20 cycles after each DMMA it issues, so the
     // tensor pipe (one DMMA per 16 cycles) needs several warps per scheduler inside the MMA loop.
     // (at most 16 warps of 32 threads: the kernel is built for 512 threads x 128 registers)
-    static const int small_acc[][2] = {{12, 2}, {12, 1}, {8, 2}, {8, 1}, {4, 1}};
-    static const int large_acc[][2] = {{12, 1}, {12, 1}, {10, 1}, {8, 1}, {4, 1}};
-    static const int small_pred[][2] = {{16, 2}, {16, 1}, {12, 1}, {8, 1}, {4, 1}};
-    static const int large_pred[][2] = {{16, 1}, {12, 1}, {8, 1}, {4, 1}, {4, 1}};
+    static const int small_acc[][2] = {{12, 2}, {12, 1}, {8, 2}, {8, 1}, {4, 1}, {2, 1}};
+    static const int large_acc[][2] = {{12, 1}, {12, 1}, {10, 1}, {8, 1}, {4, 1}, {2, 1}};
+    static const int small_pred[][2] = {{16, 2}, {16, 1}, {12, 1}, {8, 1}, {4, 1}, {2, 1}};
+    static const int large_pred[][2] = {{16, 1}, {12, 1}, {8, 1}, {4, 1}, {4, 1}, {2, 1}};
     const bool small = c.k_pad <= 32;
     const int(*cand)[2] = accum ? (small ? small_acc : large_acc) : (small ? small_pred : large_pred);
-    const int ncand = 5;
+    const int ncand = 6; // down to two MMA warps: long rows leave room for little else
     if (accum && small) {
         // few centroids: every MMA warp keeps private sums (no accumulator warps, no hand-off)
         static const int priv_cand[][2] = {{16, 2}, {16, 1}, {12, 2}, {12, 1}, {10, 1}, {8, 1}, {6, 1}, {4, 1}};
@@ -272,7 +273,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     c.sums_in_smem = 0;
     c.n_partials = 1;
     int best_w = 0, best_nc = 0, best_score = -1;
-    for (int w = 12; w >= 4; w -= 2) {
+    for (int w = 12; w >= 2; w -= 2) {
         if (force_w && w != force_w) continue;
         if ((w + c.acc_warps) * 32 > 512) continue;
         size_t fixed = smem_bytes(w, c.acc_warps, c.xs, c.S, k, d, c.k_pad, 0, 2, false);
@@ -287,8 +288,17 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
             best_nc = nc;
         }
     }
-    if (best_w == 0)
-        return fail(ctx, FMLK_ERR_INVALID_ARG, "vector dimension too large for the shared-memory tiling");
+    if (best_w == 0) {
+        // no tiling of the main kernel fits: the d-blocked kernel (no limit on d, global-atomic sums)
+        c.wide = 1;
+        c.warps = kWideWarps;
+        c.acc_warps = 0;
+        c.nc_tile = 8 * kChunkTiles;
+        c.n_ctiles = (c.k_pad + c.nc_tile - 1) / c.nc_tile;
+        c.smem = (size_t)2 * kWideStageElems * sizeof(double);
+        *out = c;
+        return FMLK_OK;
+    }
     c.warps = best_w;
     c.nc_tile = best_nc;
     c.n_ctiles = (c.k_pad + best_nc - 1) / best_nc;
@@ -457,7 +467,11 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
         cudaMemsetAsync(p.trace, 0, trace_len * 8, ctx->stream);
     }
 #endif
-    if (accum && cfg.private_sums) assign_kernel<2><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
+    if (cfg.wide) {
+        const int wgrid = (int)std::min<int64_t>(cfg.grid * 2, (tiles + kWideWarps - 1) / kWideWarps); // two CTAs per SM
+        if (accum) assign_wide_kernel<true><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
+        else assign_wide_kernel<false><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
+    } else if (accum && cfg.private_sums) assign_kernel<2><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
     else if (accum) assign_kernel<1><<<grid, (cfg.warps + cfg.acc_warps) * 32, cfg.smem, ctx->stream>>>(p);
     else assign_kernel<0><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
     if (prof && e0 && e1) cudaEventRecord(e1, ctx->stream);
@@ -633,6 +647,10 @@ int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *
             e = cudaFuncSetAttribute(assign_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(assign_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     }
     if (e != cudaSuccess) {
         std::string m = std::string("device set-up: ") + cudaGetErrorString(e);
@@ -1323,16 +1341,18 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
     int rc = choose_cfg(ctx, k, d, accumulate != 0, &c);
     if (rc) return rc;
     cudaFuncAttributes fa{};
-    if (accumulate && c.private_sums) cudaFuncGetAttributes(&fa, assign_kernel<2>);
+    if (c.wide && accumulate) cudaFuncGetAttributes(&fa, assign_wide_kernel<true>);
+    else if (c.wide) cudaFuncGetAttributes(&fa, assign_wide_kernel<false>);
+    else if (accumulate && c.private_sums) cudaFuncGetAttributes(&fa, assign_kernel<2>);
     else if (accumulate) cudaFuncGetAttributes(&fa, assign_kernel<1>);
     else cudaFuncGetAttributes(&fa, assign_kernel<0>);
     snprintf(out, (size_t)out_len,
              "regs=%d max_threads=%d local=%zu grid=%d block=%d smem=%zu mma_warps=%d acc_warps=%d xs=%d S=%d ksteps=%d k_pad=%d nc_tile=%d n_ctiles=%d "
-             "sums_in_smem=%d n_partials=%d private_sums=%d",
+             "sums_in_smem=%d n_partials=%d private_sums=%d wide=%d",
              fa.numRegs, fa.maxThreadsPerBlock, fa.localSizeBytes, c.grid, (c.warps + c.acc_warps) * 32, c.smem, c.warps,
              c.acc_warps, c.xs, c.S, c.ksteps, c.k_pad,
              c.nc_tile, c.n_ctiles,
-             c.sums_in_smem, c.n_partials, c.private_sums);
+             c.sums_in_smem, c.n_partials, c.private_sums, c.wide);
     return FMLK_OK;
 }
 
@@ -1388,6 +1408,8 @@ int noalloc_setup(int device) {
         e = cudaFuncSetAttribute(assign_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e == cudaSuccess && major == 10)
         e = cudaFuncSetAttribute(assign_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess && major == 10)
+        e = cudaFuncSetAttribute(assign_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, std::string("device set-up: ") + cudaGetErrorString(e));
     if (major != 10) return fail(nullptr, FMLK_ERR_CUDA, "this build targets sm_100a (B200) only");
     if (sms > kNoAllocMaxSlots) return fail(nullptr, FMLK_ERR_INVALID_ARG, "device has more SMs than the scratch array has slots");

@@ -1057,6 +1057,215 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
 }
 
 // ------------------------------------------------------------------------------------------
+// Rows too long for the shared-memory tiling of assign_kernel (a 16-row tile of d doubles per warp
+// plus centroid tiles): the same arithmetic, blocked along d.  A CTA of kWideWarps warps takes
+// 16 rows per warp; for each chunk of up to 64 centroids it walks the rows and the centroids in
+// blocks of kWideDk columns -- row blocks per warp, the centroid block shared by the CTA, both
+// brought in by cp.async (zero-filled past the ends) into two stages, so the next block loads
+// while the FP64 tensor cores work on this one -- keeping the chunk's scores in registers; then the
+// same selection, the same integer margin test and the same exact replay as assign_kernel.  Sums go
+// to a global accumulator with L2 atomics (rows re-read from global memory).  Rows are re-read once
+// per centroid chunk: this path trades reuse for having no limit on d, and is chosen only when
+// nothing of the main kernel fits.
+constexpr int kWideDk = 32;          // columns per block
+constexpr int kWideS = kWideDk + 4;  // padded shared-memory row stride (conflict-free fragments)
+constexpr int kWideWarps = 8;
+constexpr int kWideStageElems = (kWideWarps * kWarpRows + 8 * kChunkTiles) * kWideS; // doubles per stage
+
+// 16 or 8 bytes, of which only the first src_bytes come from memory (the rest reads as zero)
+__device__ __forceinline__ void cp_async16_zfill(void *smem_dst, const void *gmem_src, int src_bytes) {
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(s), "l"(gmem_src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async8_zfill(void *smem_dst, const void *gmem_src, int src_bytes) {
+    unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(s), "l"(gmem_src), "r"(src_bytes) : "memory");
+}
+
+// rows_pad x kWideDk doubles into dst (row stride kWideS): element (r, q) = src[r * ld + q] for
+// r < rows and q < cols, else zero; by nthreads cooperating threads.  vec16: 16-byte copies.
+__device__ __forceinline__ void wide_load_async(double *dst, const double *src, int64_t ld, int rows, int cols,
+                                                int rows_pad, bool vec16, int tid, int nthreads) {
+    if (vec16) {
+        constexpr int cpr = kWideDk / 2;
+        for (int i = tid; i < rows_pad * cpr; i += nthreads) {
+            const int r = i / cpr, q = 2 * (i - r * cpr);
+            const int have = (r < rows) ? max(0, min(2, cols - q)) * 8 : 0;
+            cp_async16_zfill(dst + r * kWideS + q, have ? src + (int64_t)r * ld + q : src, have);
+        }
+    } else {
+        for (int i = tid; i < rows_pad * kWideDk; i += nthreads) {
+            const int r = i / kWideDk, q = i - r * kWideDk;
+            const int have = (r < rows && q < cols) ? 8 : 0;
+            cp_async8_zfill(dst + r * kWideS + q, have ? src + (int64_t)r * ld + q : src, have);
+        }
+    }
+}
+
+template <int CNT>
+__device__ __forceinline__ void wide_block(const double *Xb, const double *Cb, int frow, int fk,
+                                           double (&acc0)[kChunkTiles][2], double (&acc1)[kChunkTiles][2], int &mx0,
+                                           int &mx1, bool with_nsq) {
+#pragma unroll 2
+    for (int ks = 0; ks < kWideDk / 4; ks++) {
+        const double a0 = Xb[frow * kWideS + 4 * ks + fk];
+        const double a1 = Xb[(frow + 8) * kWideS + 4 * ks + fk];
+        if (with_nsq) {
+            mx0 = max(mx0, __double2hiint(a0) & 0x7fffffff);
+            mx1 = max(mx1, __double2hiint(a1) & 0x7fffffff);
+        }
+#pragma unroll
+        for (int j = 0; j < CNT; j++) {
+            const double b = Cb[(j * 8 + frow) * kWideS + 4 * ks + fk];
+            dmma884(acc0[j][0], acc0[j][1], a0, b);
+            dmma884(acc1[j][0], acc1[j][1], a1, b);
+        }
+    }
+}
+
+template <bool ACCUM>
+__global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const AssignParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double *stage_base = reinterpret_cast<double *>(smem_raw);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int frow = lane >> 2, fk = lane & 3;
+    const int cmax2_exp = (int)p.cmax2[1];
+    const int dpad_exp = 32 - __clz(4 * p.ksteps);
+    const bool vec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.x) & 15) == 0) &&
+                       ((reinterpret_cast<uintptr_t>(p.c_mma) & 15) == 0);
+    constexpr int kCtaRows = kWideWarps * kWarpRows;
+    const int64_t total_ctiles = (p.n + kCtaRows - 1) / kCtaRows;
+    const int nkb = (p.d + kWideDk - 1) / kWideDk;
+    const int nchunks = (p.k_pad + 8 * kChunkTiles - 1) / (8 * kChunkTiles);
+    const int steps = nchunks * nkb; // (chunk, column block) pairs per CTA tile, chunk-major
+    unsigned long long local_rechecks = 0;
+    for (int64_t ctile = blockIdx.x; ctile < total_ctiles; ctile += gridDim.x) {
+        const int64_t crow0 = ctile * kCtaRows;
+        const int crows = (int)min((int64_t)kCtaRows, p.n - crow0);
+        const int64_t row0 = crow0 + warp * kWarpRows;
+        const int rows_valid = max(0, min(kWarpRows, crows - warp * kWarpRows));
+        // stage `st` <- step `s`: every warp's row block and the chunk's centroid block
+        auto issue = [&](int s, int st) {
+            const int ch = s / nkb, kb = (s - ch * nkb) * kWideDk;
+            const int ch0 = ch * 8 * kChunkTiles;
+            const int cnt8 = min(8 * kChunkTiles, p.k_pad - ch0);
+            double *Xs = stage_base + (size_t)st * kWideStageElems;
+            double *Cs2 = Xs + kCtaRows * kWideS;
+            wide_load_async(Xs, p.x + crow0 * p.d + kb, p.d, crows, p.d - kb, kCtaRows, vec16, threadIdx.x, blockDim.x);
+            wide_load_async(Cs2, p.c_mma + (int64_t)ch0 * p.d + kb, p.d, min(cnt8, p.k - ch0), p.d - kb, cnt8, vec16,
+                            threadIdx.x, blockDim.x);
+            cp_async_commit();
+        };
+        Top2 t0 = top2_init(), t1 = top2_init();
+        int mx0 = 0, mx1 = 0;
+        double acc0[kChunkTiles][2], acc1[kChunkTiles][2];
+        __syncthreads(); // every warp is done with both stages of the previous CTA tile
+        issue(0, 0);
+        for (int s = 0; s < steps; s++) {
+            const int ch = s / nkb, kbi = s - ch * nkb;
+            const int ch0 = ch * 8 * kChunkTiles;
+            const int cnt = min(kChunkTiles, (p.k_pad - ch0) >> 3);
+            const int col0 = ch0 + fk * 2;
+            if (kbi == 0) {
+#pragma unroll
+                for (int j = 0; j < kChunkTiles; j++) {
+                    // accumulators start at -|c|^2/2; tiles this chunk does not have score -inf
+                    const double h0 = j < cnt ? p.h[col0 + j * 8] : -INFINITY;
+                    const double h1 = j < cnt ? p.h[col0 + j * 8 + 1] : -INFINITY;
+                    acc0[j][0] = acc1[j][0] = h0;
+                    acc0[j][1] = acc1[j][1] = h1;
+                }
+            }
+            if (s + 1 < steps) {
+                issue(s + 1, (s + 1) & 1); // that stage was last read at step s - 1: see the barrier below
+                cp_async_wait<1>();
+            } else {
+                cp_async_wait<0>();
+            }
+            __syncthreads(); // step s has landed for every thread
+            {
+                const double *Xb = stage_base + (size_t)(s & 1) * kWideStageElems + (size_t)warp * kWarpRows * kWideS;
+                const double *Cb = stage_base + (size_t)(s & 1) * kWideStageElems + kCtaRows * kWideS;
+                const bool nsq = ch == 0; // the |x| bound rides along with the first chunk
+                switch (cnt) {
+                    case 8: wide_block<8>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 7: wide_block<7>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 6: wide_block<6>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 5: wide_block<5>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 4: wide_block<4>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 3: wide_block<3>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 2: wide_block<2>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    default: wide_block<1>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                }
+            }
+            __syncthreads(); // stage s & 1 may be refilled (by the issue of step s + 2 at step s + 1)
+            if (kbi == nkb - 1) {
+                int3 r0 = select_chunk_row(t0.best, t0.second, t0.idx, col0, acc0[0][0], acc0[0][1], acc0[1][0],
+                                           acc0[1][1], acc0[2][0], acc0[2][1], acc0[3][0], acc0[3][1], acc0[4][0],
+                                           acc0[4][1], acc0[5][0], acc0[5][1], acc0[6][0], acc0[6][1], acc0[7][0],
+                                           acc0[7][1]);
+                int3 r1 = select_chunk_row(t1.best, t1.second, t1.idx, col0, acc1[0][0], acc1[0][1], acc1[1][0],
+                                           acc1[1][1], acc1[2][0], acc1[2][1], acc1[3][0], acc1[3][1], acc1[4][0],
+                                           acc1[4][1], acc1[5][0], acc1[5][1], acc1[6][0], acc1[6][1], acc1[7][0],
+                                           acc1[7][1]);
+                t0.best = r0.x, t0.second = r0.y, t0.idx = r0.z;
+                t1.best = r1.x, t1.second = r1.y, t1.idx = r1.z;
+            }
+        }
+        top2_merge_xor(t0, 1);
+        top2_merge_xor(t0, 2);
+        top2_merge_xor(t1, 1);
+        top2_merge_xor(t1, 2);
+        mx0 = max(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+        mx0 = max(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = max(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+        mx1 = max(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        // the margin test of assign_kernel (see there)
+        auto row_ok = [&](const Top2 &t, int mx) -> bool {
+            if (mx >= 0x7ff00000) return false;
+            const int ex = 2 * ((mx >> 20) - 1023 + 1) + dpad_exp;
+            int te = p.thr_coef_exp + 1 + max(ex, cmax2_exp) + 1023;
+            if (te >= 2047) return false;
+            return top2_margin_clears(t, max(te, 1));
+        };
+        const bool flag0 = !row_ok(t0, mx0) && frow < rows_valid;
+        const bool flag1 = !row_ok(t1, mx1) && frow + 8 < rows_valid;
+        // lane r (r < 16) ends up holding the label of row r
+        const int lab_lo = __shfl_sync(0xffffffffu, t0.idx, (lane & 7) * 4);
+        const int lab_hi = __shfl_sync(0xffffffffu, t1.idx, (lane & 7) * 4);
+        int lab = (lane & 8) ? lab_hi : lab_lo;
+        unsigned flagged = 0;
+        {
+            const unsigned f0 = __ballot_sync(0xffffffffu, flag0 && fk == 0);
+            const unsigned f1 = __ballot_sync(0xffffffffu, flag1 && fk == 0);
+#pragma unroll
+            for (int r = 0; r < 8; r++) {
+                flagged |= ((f0 >> (4 * r)) & 1u) << r;
+                flagged |= ((f1 >> (4 * r)) & 1u) << (r + 8);
+            }
+        }
+        while (flagged) { // warp-uniform
+            const int r = __ffs(flagged) - 1;
+            flagged &= flagged - 1;
+            const int exact = exact_find_closest(p.x + (row0 + r) * p.d, p.c, p.cn, p.k, p.d, p.fma_mode);
+            if (lane == r) lab = exact;
+            local_rechecks++;
+        }
+        if (p.labels != nullptr && lane < rows_valid) p.labels[row0 + lane] = lab;
+        if (ACCUM) {
+            double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
+            for (int r = 0; r < rows_valid; r++) {
+                const int l = __shfl_sync(0xffffffffu, lab, r);
+                const double *xrow = p.x + (row0 + r) * p.d;
+                for (int c = lane; c < p.d; c += 32) atomicAdd(&slot[(size_t)l * p.d + c], xrow[c]);
+            }
+            if (lane < rows_valid) atomicAdd(&slot[(size_t)p.k * p.d + lab], 1.0);
+        }
+    }
+    if (lane == 0 && local_rechecks && p.recheck_count) atomicAdd(p.recheck_count, local_rechecks);
+}
+
+// ------------------------------------------------------------------------------------------
 // per-round small kernels
 
 // VectorWithNorm of every centroid (KMeans.java:279-282) in reference arithmetic, plus what the

@@ -125,6 +125,13 @@ SHAPES = [
     (6000, 64, 1000),    # config 4 shape
     (3000, 128, 1000),   # config 3 shape
     (2000, 128, 257),    # config 5's d with a ragged last centroid tile
+    # extremes of the tiling
+    (1500, 1000, 7),     # long rows: few MMA warps fit, several columns per accumulator lane
+    (600, 1531, 3),      # odd d close to the shared-memory limit of one row tile + centroids
+    (3000, 2, 3000),     # many more centroids than dimensions
+    (2500, 513, 33),     # odd d: 8-byte cp.async row loads, streamed centroids
+    (4000, 10, 2),       # config 1 shape
+    (4000, 100, 10),     # kmeans-benchmark.json shape
 ]
 
 
@@ -384,4 +391,15 @@ def test_tensor_pipe_accumulate_with_nonfinite_rows(ctx, d):
     o_sums, o_counts = O.train_local(x, cent)[:2]
     finite_rows = np.isfinite(o_sums).all(axis=1)
     assert finite_rows.sum() >= k - 4 and np.array_equal(np.isfinite(sums).all(axis=1), finite_rows)
+    ctx.clear_points()
+
+
+def test_rows_far_beyond_the_shared_memory_tiling(ctx):
+    """d = 20 000: nothing of the main kernel's tiling fits; the d-blocked kernel takes over with the
+    same labels, counts and sums (there is no limit on d and no fallback to the CPU)."""
+    n, d, k = 70, 20_000, 5
+    x = O.generate_dense(2, 0, 1, n, d)
+    cent = x[[3, 17, 30, 44, 69]].copy()
+    _step_parity(ctx, x, cent)
+    assert "wide=1" in ctx.describe_launch(k, d, True)
     ctx.clear_points()
