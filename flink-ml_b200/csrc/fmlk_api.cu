@@ -107,6 +107,7 @@ struct fmlk_ctx {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     int sm_count = 0;
+    int max_partial_slots = 0; // > 0: never use more per-CTA accumulators than this (borrowed scratch)
     size_t smem_optin = 0;
 
     int32_t d = 0;  // dimension of the cached rows (0: cache empty and nothing reserved)
@@ -214,6 +215,29 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     c.stagger_ns = env_int("FMLK_TUNE_STAGGER_NS", 0);
     const int force_w = env_int("FMLK_TUNE_W", 0), force_xs = env_int("FMLK_TUNE_XS", 0);
     const size_t budget = ctx->smem_optin;
+    auto take_wide = [&]() {
+        // the d-blocked kernel (no limit on d, global-atomic sums)
+        c.wide = 1;
+        c.warps = kWideWarps;
+        c.acc_warps = 0;
+        c.xs = 1;
+        c.sums_in_smem = 0;
+        // one accumulator per CTA while that stays under 64 MB: L2 atomics of different CTAs never meet
+        c.n_partials = (int)std::max<size_t>(1, std::min<size_t>((size_t)2 * ctx->sm_count,
+                                                                  ((size_t)64 << 20) / (((size_t)k * d + k) * sizeof(double))));
+        if (ctx->max_partial_slots > 0) c.n_partials = std::min(c.n_partials, ctx->max_partial_slots);
+        c.nc_tile = 8 * kChunkTiles;
+        c.n_ctiles = (c.k_pad + c.nc_tile - 1) / c.nc_tile;
+        c.smem = (size_t)2 * kWideStageElems * sizeof(double);
+        *out = c;
+        return FMLK_OK;
+    };
+    // measured: from d = 128 on the d-blocked kernel is the faster one (16 warps per SM share the
+    // centroid blocks; the main kernel's whole-row tiles leave room for 4-8 warps), e.g. d = 256,
+    // k = 100: 22.7 against 13.7 TFLOP/s; below that the main kernel wins (d = 64: 30.5 against 23.0)
+    const int force_wide = env_int("FMLK_TUNE_WIDE", -1);
+    // (few centroids, k <= 32, stay with the main kernel while it fits: 4.26 against 3.35 TB/s at k = 10, d = 128)
+    if (force_wide == 1 || (force_wide < 0 && d >= 128 && c.k_pad > 32)) return take_wide();
     // few centroids: HBM-bound, favour a prefetched second row tile per warp;
     // many centroids: FP64-bound; a warp is blocked for ~20 cycles after each DMMA it issues, so the
     // tensor pipe (one DMMA per 16 cycles) needs several warps per scheduler inside the MMA loop.
@@ -288,17 +312,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
             best_nc = nc;
         }
     }
-    if (best_w == 0) {
-        // no tiling of the main kernel fits: the d-blocked kernel (no limit on d, global-atomic sums)
-        c.wide = 1;
-        c.warps = kWideWarps;
-        c.acc_warps = 0;
-        c.nc_tile = 8 * kChunkTiles;
-        c.n_ctiles = (c.k_pad + c.nc_tile - 1) / c.nc_tile;
-        c.smem = (size_t)2 * kWideStageElems * sizeof(double);
-        *out = c;
-        return FMLK_OK;
-    }
+    if (best_w == 0) return take_wide(); // no tiling of the main kernel fits
     c.warps = best_w;
     c.nc_tile = best_nc;
     c.n_ctiles = (c.k_pad + best_nc - 1) / best_nc;
@@ -1423,6 +1437,7 @@ int noalloc_setup(int device) {
     c.smem_optin = (size_t)smem;
     c.partials = base;
     c.partials_cap = kNoAllocPartials;
+    c.max_partial_slots = kNoAllocMaxSlots;
     c.red = base + kNoAllocPartials;
     c.c_mma = c.red + kNoAllocMaxModel;
     c.cn = c.c_mma + kNoAllocMaxModel;

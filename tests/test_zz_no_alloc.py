@@ -49,7 +49,7 @@ def test_noalloc_matches_context_path_twice():
     rng = np.random.default_rng(3)
     # warm-up call: the first call on a device does the one-time set-up
     _noalloc(torch, rng.random((64, 8)), rng.random((4, 8)))
-    shapes = [(30000, 64, 100), (4099, 7, 5)]  # config-2 shape, then a smaller ragged one
+    shapes = [(30000, 64, 100), (4099, 7, 5), (9000, 256, 31)]  # config-2 shape, a smaller ragged one, a long-row one (d-blocked kernel)
     for n, d, k in shapes:
         x = rng.random((n, d))
         cent = x[rng.choice(n, k, replace=False)].copy()
