@@ -1083,21 +1083,31 @@ __device__ __forceinline__ void cp_async8_zfill(void *smem_dst, const void *gmem
 }
 
 // rows_pad x kWideDk doubles into dst (row stride kWideS): element (r, q) = src[r * ld + q] for
-// r < rows and q < cols, else zero; by nthreads cooperating threads.  vec16: 16-byte copies.
+// r < rows and q < cols, else zero; by the 32 * kWideWarps threads of the CTA.  vec16: 16-byte
+// copies.  A thread always copies the same columns (q) of rows r0, r0 + step, ...: no index
+// arithmetic beyond two pointer increments per copy.
 __device__ __forceinline__ void wide_load_async(double *dst, const double *src, int64_t ld, int rows, int cols,
-                                                int rows_pad, bool vec16, int tid, int nthreads) {
+                                                int rows_pad, bool vec16, int tid) {
+    constexpr int nthreads = 32 * kWideWarps;
     if (vec16) {
-        constexpr int cpr = kWideDk / 2;
-        for (int i = tid; i < rows_pad * cpr; i += nthreads) {
-            const int r = i / cpr, q = 2 * (i - r * cpr);
-            const int have = (r < rows) ? max(0, min(2, cols - q)) * 8 : 0;
-            cp_async16_zfill(dst + r * kWideS + q, have ? src + (int64_t)r * ld + q : src, have);
+        constexpr int cpr = kWideDk / 2, step = nthreads / cpr;
+        const int q = 2 * (tid % cpr);
+        const int have_c = max(0, min(2, cols - q)) * 8;
+        const double *s = src + (int64_t)(tid / cpr) * ld + q;
+        double *t = dst + (tid / cpr) * kWideS + q;
+        for (int r = tid / cpr; r < rows_pad; r += step, s += (int64_t)step * ld, t += step * kWideS) {
+            const int have = r < rows ? have_c : 0;
+            cp_async16_zfill(t, have ? s : src, have);
         }
     } else {
-        for (int i = tid; i < rows_pad * kWideDk; i += nthreads) {
-            const int r = i / kWideDk, q = i - r * kWideDk;
-            const int have = (r < rows && q < cols) ? 8 : 0;
-            cp_async8_zfill(dst + r * kWideS + q, have ? src + (int64_t)r * ld + q : src, have);
+        constexpr int step = nthreads / kWideDk;
+        const int q = tid % kWideDk;
+        const int have_c = q < cols ? 8 : 0;
+        const double *s = src + (int64_t)(tid / kWideDk) * ld + q;
+        double *t = dst + (tid / kWideDk) * kWideS + q;
+        for (int r = tid / kWideDk; r < rows_pad; r += step, s += (int64_t)step * ld, t += step * kWideS) {
+            const int have = r < rows ? have_c : 0;
+            cp_async8_zfill(t, have ? s : src, have);
         }
     }
 }
@@ -1151,9 +1161,9 @@ __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const Assi
             const int cnt8 = min(8 * kChunkTiles, p.k_pad - ch0);
             double *Xs = stage_base + (size_t)st * kWideStageElems;
             double *Cs2 = Xs + kCtaRows * kWideS;
-            wide_load_async(Xs, p.x + crow0 * p.d + kb, p.d, crows, p.d - kb, kCtaRows, vec16, threadIdx.x, blockDim.x);
+            wide_load_async(Xs, p.x + crow0 * p.d + kb, p.d, crows, p.d - kb, kCtaRows, vec16, threadIdx.x);
             wide_load_async(Cs2, p.c_mma + (int64_t)ch0 * p.d + kb, p.d, min(cnt8, p.k - ch0), p.d - kb, cnt8, vec16,
-                            threadIdx.x, blockDim.x);
+                            threadIdx.x);
             cp_async_commit();
         };
         Top2 t0 = top2_init(), t1 = top2_init();
@@ -1176,13 +1186,9 @@ __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const Assi
                     acc0[j][1] = acc1[j][1] = h1;
                 }
             }
-            if (s + 1 < steps) {
-                issue(s + 1, (s + 1) & 1); // that stage was last read at step s - 1: see the barrier below
-                cp_async_wait<1>();
-            } else {
-                cp_async_wait<0>();
-            }
-            __syncthreads(); // step s has landed for every thread
+            cp_async_wait<0>();
+            __syncthreads(); // step s has landed for every thread, and every warp is done with step s - 1
+            if (s + 1 < steps) issue(s + 1, (s + 1) & 1); // into the stage step s - 1 used; lands during step s
             {
                 const double *Xb = stage_base + (size_t)(s & 1) * kWideStageElems + (size_t)warp * kWarpRows * kWideS;
                 const double *Cb = stage_base + (size_t)(s & 1) * kWideStageElems + kCtaRows * kWideS;
@@ -1198,7 +1204,6 @@ __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const Assi
                     default: wide_block<1>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
                 }
             }
-            __syncthreads(); // stage s & 1 may be refilled (by the issue of step s + 2 at step s + 1)
             if (kbi == nkb - 1) {
                 int3 r0 = select_chunk_row(t0.best, t0.second, t0.idx, col0, acc0[0][0], acc0[0][1], acc0[1][0],
                                            acc0[1][1], acc0[2][0], acc0[2][1], acc0[3][0], acc0[3][1], acc0[4][0],

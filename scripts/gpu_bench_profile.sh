@@ -13,5 +13,5 @@ echo "ncu launches rc=$?"
 # full capture of the dominant kernel at the bench shape
 CMD2="python scripts/run_assign.py 10000000 64 100 3"
 $CMD2 > gpurun_out/plain_c2full.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:assign_kernel -s 1 -c 1 -f -o gpurun_out/prof_c2full $CMD2 > gpurun_out/ncu_c2full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:assign_ -s 1 -c 1 -f -o gpurun_out/prof_c2full $CMD2 > gpurun_out/ncu_c2full.log 2>&1
 echo "ncu full rc=$?"; cat gpurun_out/plain_c2full.log | cut -c1-120
