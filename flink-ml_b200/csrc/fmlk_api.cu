@@ -290,6 +290,12 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
             }
         }
     }
+    // centroids do not stay resident.  When d is a multiple of the d-blocked kernel's 32-column block
+    // (no padding waste) that kernel is the better streamer (training / predict, TFLOP/s):
+    //   d = 64, k = 1000: 26.7 / 28.2 against 26.0 / 28.5     d = 64, k = 500: 25.6 / 27.9 against 23.3 / 26.8
+    //   d = 32, k = 1000: 24.5 / 25.6 against 22.5 / 25.8     d = 96, k = 300: 23.7 / 26.5 against 20.4 / 24.8
+    // with padding waste (d = 100, k = 1000: 21.0 against 24.8) this kernel's lock-step tiles win.
+    if (force_wide < 0 && d >= 32 && d % 32 == 0) return take_wide();
     // streaming: one row stage per MMA warp, the rest of shared memory split into two centroid tiles.
     // More MMA warps keep the tensor pipe fed but leave less room for the centroid tiles (shorter
     // lock-step phases, more barriers): take the warp count with the largest warps x min(tile, 32).
