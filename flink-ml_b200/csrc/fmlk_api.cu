@@ -489,8 +489,11 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
 #endif
     if (cfg.wide) {
         const int wgrid = (int)std::min<int64_t>(cfg.grid * 2, (tiles + kWideWarps - 1) / kWideWarps); // two CTAs per SM
-        if (accum) assign_wide_kernel<true><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
-        else assign_wide_kernel<false><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
+        const bool xres = ctx->md <= 2 * kWideDk; // rows of up to 64 columns stay resident per CTA tile
+        if (accum && xres) assign_wide_kernel<true, true><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
+        else if (accum) assign_wide_kernel<true, false><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
+        else if (xres) assign_wide_kernel<false, true><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
+        else assign_wide_kernel<false, false><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
     } else if (accum && cfg.private_sums) assign_kernel<2><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
     else if (accum) assign_kernel<1><<<grid, (cfg.warps + cfg.acc_warps) * 32, cfg.smem, ctx->stream>>>(p);
     else assign_kernel<0><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
@@ -668,9 +671,13 @@ int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(assign_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(assign_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            e = cudaFuncSetAttribute(assign_wide_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(assign_wide_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            e = cudaFuncSetAttribute(assign_wide_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_wide_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_wide_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     }
     if (e != cudaSuccess) {
         std::string m = std::string("device set-up: ") + cudaGetErrorString(e);
@@ -1361,8 +1368,8 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
     int rc = choose_cfg(ctx, k, d, accumulate != 0, &c);
     if (rc) return rc;
     cudaFuncAttributes fa{};
-    if (c.wide && accumulate) cudaFuncGetAttributes(&fa, assign_wide_kernel<true>);
-    else if (c.wide) cudaFuncGetAttributes(&fa, assign_wide_kernel<false>);
+    if (c.wide && accumulate) cudaFuncGetAttributes(&fa, assign_wide_kernel<true, false>);
+    else if (c.wide) cudaFuncGetAttributes(&fa, assign_wide_kernel<false, false>);
     else if (accumulate && c.private_sums) cudaFuncGetAttributes(&fa, assign_kernel<2>);
     else if (accumulate) cudaFuncGetAttributes(&fa, assign_kernel<1>);
     else cudaFuncGetAttributes(&fa, assign_kernel<0>);
@@ -1429,7 +1436,9 @@ int noalloc_setup(int device) {
     if (e == cudaSuccess && major == 10)
         e = cudaFuncSetAttribute(assign_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e == cudaSuccess && major == 10)
-        e = cudaFuncSetAttribute(assign_wide_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        e = cudaFuncSetAttribute(assign_wide_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess && major == 10)
+        e = cudaFuncSetAttribute(assign_wide_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, std::string("device set-up: ") + cudaGetErrorString(e));
     if (major != 10) return fail(nullptr, FMLK_ERR_CUDA, "this build targets sm_100a (B200) only");
     if (sms > kNoAllocMaxSlots) return fail(nullptr, FMLK_ERR_INVALID_ARG, "device has more SMs than the scratch array has slots");

@@ -1086,16 +1086,16 @@ __device__ __forceinline__ void cp_async8_zfill(void *smem_dst, const void *gmem
 // r < rows and q < cols, else zero; by the 32 * kWideWarps threads of the CTA.  vec16: 16-byte
 // copies.  A thread always copies the same columns (q) of rows r0, r0 + step, ...: no index
 // arithmetic beyond two pointer increments per copy.
-__device__ __forceinline__ void wide_load_async(double *dst, const double *src, int64_t ld, int rows, int cols,
-                                                int rows_pad, bool vec16, int tid) {
+__device__ __forceinline__ void wide_load_async_strided(double *dst, int dstride, const double *src, int64_t ld, int rows,
+                                                        int cols, int rows_pad, bool vec16, int tid) {
     constexpr int nthreads = 32 * kWideWarps;
     if (vec16) {
         constexpr int cpr = kWideDk / 2, step = nthreads / cpr;
         const int q = 2 * (tid % cpr);
         const int have_c = max(0, min(2, cols - q)) * 8;
         const double *s = src + (int64_t)(tid / cpr) * ld + q;
-        double *t = dst + (tid / cpr) * kWideS + q;
-        for (int r = tid / cpr; r < rows_pad; r += step, s += (int64_t)step * ld, t += step * kWideS) {
+        double *t = dst + (tid / cpr) * dstride + q;
+        for (int r = tid / cpr; r < rows_pad; r += step, s += (int64_t)step * ld, t += step * dstride) {
             const int have = r < rows ? have_c : 0;
             cp_async16_zfill(t, have ? s : src, have);
         }
@@ -1104,22 +1104,27 @@ __device__ __forceinline__ void wide_load_async(double *dst, const double *src, 
         const int q = tid % kWideDk;
         const int have_c = q < cols ? 8 : 0;
         const double *s = src + (int64_t)(tid / kWideDk) * ld + q;
-        double *t = dst + (tid / kWideDk) * kWideS + q;
-        for (int r = tid / kWideDk; r < rows_pad; r += step, s += (int64_t)step * ld, t += step * kWideS) {
+        double *t = dst + (tid / kWideDk) * dstride + q;
+        for (int r = tid / kWideDk; r < rows_pad; r += step, s += (int64_t)step * ld, t += step * dstride) {
             const int have = r < rows ? have_c : 0;
             cp_async8_zfill(t, have ? s : src, have);
         }
     }
 }
 
+__device__ __forceinline__ void wide_load_async(double *dst, const double *src, int64_t ld, int rows, int cols,
+                                                int rows_pad, bool vec16, int tid) {
+    wide_load_async_strided(dst, kWideS, src, ld, rows, cols, rows_pad, vec16, tid);
+}
+
 template <int CNT>
-__device__ __forceinline__ void wide_block(const double *Xb, const double *Cb, int frow, int fk,
+__device__ __forceinline__ void wide_block(const double *Xb, int xstride, const double *Cb, int frow, int fk,
                                            double (&acc0)[kChunkTiles][2], double (&acc1)[kChunkTiles][2], int &mx0,
                                            int &mx1, bool with_nsq) {
 #pragma unroll 2
     for (int ks = 0; ks < kWideDk / 4; ks++) {
-        const double a0 = Xb[frow * kWideS + 4 * ks + fk];
-        const double a1 = Xb[(frow + 8) * kWideS + 4 * ks + fk];
+        const double a0 = Xb[frow * xstride + 4 * ks + fk];
+        const double a1 = Xb[(frow + 8) * xstride + 4 * ks + fk];
         if (with_nsq) {
             mx0 = max(mx0, __double2hiint(a0) & 0x7fffffff);
             mx1 = max(mx1, __double2hiint(a1) & 0x7fffffff);
@@ -1133,7 +1138,10 @@ __device__ __forceinline__ void wide_block(const double *Xb, const double *Cb, i
     }
 }
 
-template <bool ACCUM>
+// XRES (d <= 64): the CTA's 128 rows stay in shared memory for all centroid chunks (loaded once per
+// CTA tile, row stride kWideXresS); only the centroid blocks stream through the two stages.
+constexpr int kWideXresS = 2 * kWideDk + 4;
+template <bool ACCUM, bool XRES>
 __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const AssignParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double *stage_base = reinterpret_cast<double *>(smem_raw);
@@ -1159,9 +1167,10 @@ __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const Assi
             const int ch = s / nkb, kb = (s - ch * nkb) * kWideDk;
             const int ch0 = ch * 8 * kChunkTiles;
             const int cnt8 = min(8 * kChunkTiles, p.k_pad - ch0);
-            double *Xs = stage_base + (size_t)st * kWideStageElems;
-            double *Cs2 = Xs + kCtaRows * kWideS;
-            wide_load_async(Xs, p.x + crow0 * p.d + kb, p.d, crows, p.d - kb, kCtaRows, vec16, threadIdx.x);
+            double *Xs = XRES ? nullptr : stage_base + (size_t)st * kWideStageElems;
+            double *Cs2 = XRES ? stage_base + kCtaRows * kWideXresS + (size_t)st * (8 * kChunkTiles * kWideS)
+                               : Xs + kCtaRows * kWideS;
+            if (!XRES) wide_load_async(Xs, p.x + crow0 * p.d + kb, p.d, crows, p.d - kb, kCtaRows, vec16, threadIdx.x);
             wide_load_async(Cs2, p.c_mma + (int64_t)ch0 * p.d + kb, p.d, min(cnt8, p.k - ch0), p.d - kb, cnt8, vec16,
                             threadIdx.x);
             cp_async_commit();
@@ -1169,7 +1178,13 @@ __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const Assi
         Top2 t0 = top2_init(), t1 = top2_init();
         int mx0 = 0, mx1 = 0;
         double acc0[kChunkTiles][2], acc1[kChunkTiles][2];
-        __syncthreads(); // every warp is done with both stages of the previous CTA tile
+        __syncthreads(); // every warp is done with both stages (and the rows) of the previous CTA tile
+        if (XRES) {
+            // the whole row tile, as two column halves of the same group as the first centroid block
+            for (int half = 0; half < 2; half++)
+                wide_load_async_strided(stage_base + half * kWideDk, kWideXresS, p.x + crow0 * p.d + half * kWideDk, p.d, crows,
+                                        p.d - half * kWideDk, kCtaRows, vec16, threadIdx.x);
+        }
         issue(0, 0);
         for (int s = 0; s < steps; s++) {
             const int ch = s / nkb, kbi = s - ch * nkb;
@@ -1190,18 +1205,21 @@ __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const Assi
             __syncthreads(); // step s has landed for every thread, and every warp is done with step s - 1
             if (s + 1 < steps) issue(s + 1, (s + 1) & 1); // into the stage step s - 1 used; lands during step s
             {
-                const double *Xb = stage_base + (size_t)(s & 1) * kWideStageElems + (size_t)warp * kWarpRows * kWideS;
-                const double *Cb = stage_base + (size_t)(s & 1) * kWideStageElems + kCtaRows * kWideS;
+                const int xstride = XRES ? kWideXresS : kWideS;
+                const double *Xb = XRES ? stage_base + (size_t)warp * kWarpRows * kWideXresS + kbi * kWideDk
+                                        : stage_base + (size_t)(s & 1) * kWideStageElems + (size_t)warp * kWarpRows * kWideS;
+                const double *Cb = XRES ? stage_base + kCtaRows * kWideXresS + (size_t)(s & 1) * (8 * kChunkTiles * kWideS)
+                                        : stage_base + (size_t)(s & 1) * kWideStageElems + kCtaRows * kWideS;
                 const bool nsq = ch == 0; // the |x| bound rides along with the first chunk
                 switch (cnt) {
-                    case 8: wide_block<8>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 7: wide_block<7>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 6: wide_block<6>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 5: wide_block<5>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 4: wide_block<4>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 3: wide_block<3>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 2: wide_block<2>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    default: wide_block<1>(Xb, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 8: wide_block<8>(Xb, xstride, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 7: wide_block<7>(Xb, xstride, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 6: wide_block<6>(Xb, xstride, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 5: wide_block<5>(Xb, xstride, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 4: wide_block<4>(Xb, xstride, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 3: wide_block<3>(Xb, xstride, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 2: wide_block<2>(Xb, xstride, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    default: wide_block<1>(Xb, xstride, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
                 }
             }
             if (kbi == nkb - 1) {
