@@ -247,12 +247,16 @@ def run_ours(args):
     else:
         roofline = {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_frac,
                     "peak_source": peak_src}
+    launch_desc = ctx.describe_launch(k, d, True)
+    kernel_name = ("fmlk::assign_wide_kernel<true> (d-blocked assign + accumulate)" if "wide=1" in launch_desc else
+                   "fmlk::assign_kernel<2> (assign + warp-private sums)" if "private_sums=1" in launch_desc else
+                   "fmlk::assign_kernel<1> (assign + accumulate)")
     roofline.update({
-        "traffic": None, "kernel": "fmlk::assign_kernel<1> (MODE 1: assign + accumulate)", "ms_per_launch": assign_ms,
+        "traffic": None, "kernel": kernel_name, "ms_per_launch": assign_ms,
         "launches_timed": prof["assign_launches"], "share_of_step": prof["assign_ms"] / total_ms,
         "hbm": {"achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_frac, "peak_source": peak_src},
         "fp64_tensor": {"achieved": tf, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tensor_frac},
-        "fp64_fma_peak_tflops": dfma_peak, "launch": ctx.describe_launch(k, d, True),
+        "fp64_fma_peak_tflops": dfma_peak, "launch": launch_desc,
     })
     ncu_traffic = os.path.join(ROOT, "profiles", "traffic_%s.json" % args.workload)
     if os.path.exists(ncu_traffic):
