@@ -523,6 +523,14 @@ int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
     int rc = choose_cfg(ctx, ctx->k, ctx->md, true, &cfg);
     if (rc) return rc;
     const size_t len = (size_t)ctx->k * ctx->md + ctx->k;
+    if (cfg.wide) {
+        // no more accumulators than the largest launch has CTAs (short online batches: less to clear and add up)
+        int64_t most = extra_rows ? extra_n : 0;
+        if (!extra_rows)
+            for (const Chunk &ch : ctx->chunks) most = std::max(most, ch.rows);
+        const int64_t ctas = (most + (int64_t)kWideWarps * kWarpRows - 1) / ((int64_t)kWideWarps * kWarpRows);
+        cfg.n_partials = (int)std::max<int64_t>(1, std::min<int64_t>(cfg.n_partials, ctas));
+    }
     if ((rc = ensure_partials(ctx, len * cfg.n_partials))) return rc;
     if ((rc = prep_centroids(ctx))) return rc;
     CK(ctx, cudaMemsetAsync(ctx->partials, 0, len * cfg.n_partials * sizeof(double), ctx->stream));
