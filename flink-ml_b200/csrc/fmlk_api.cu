@@ -88,6 +88,7 @@ struct Chunk {
 struct LaunchCfg {
     int warps, acc_warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid, private_sums;
     int spin_ns, stagger_ns;
+    int red_sums; // MMA warps add to a global accumulator per CTA (no accumulator warps)
     int wide; // rows too long for the shared-memory tiling: assign_wide_kernel
     size_t smem;
 };
@@ -270,13 +271,47 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
             }
         }
     }
+    const bool det = (ctx->flags & FMLK_FLAG_DETERMINISTIC) != 0;
+    auto try_red = [&]() -> bool {
+        if (!accum || !env_int("FMLK_TUNE_RED_SUMS", 1)) return false;
+
+        // resident centroids, every warp an MMA warp, sums by L2 atomics into one accumulator per CTA:
+        // measured faster than the accumulator warps (k = 100: d = 64 26.5 against 25.5 TFLOP/s, d = 32
+        // 20.1 against 17.5-19.3, d = 96 20.2 against 15.8; k = 200, d = 64 28.4) -- the additions happen
+        // in L2 and nothing queues on the FP64 pipe -- but the sums' last bits depend on arrival order;
+        // FMLK_FLAG_DETERMINISTIC keeps the fixed-order accumulator warps
+        static const int red_cand[][2] = {{16, 1}, {12, 1}, {8, 1}};
+        for (int i = 0; i < 3; i++) {
+            const int cw = force_w ? force_w : red_cand[i][0];
+            size_t need = smem_bytes(cw, 0, 1, c.S, k, d, c.k_pad, c.k_pad, 1, false);
+            if (need <= budget) {
+                c.warps = cw;
+                c.acc_warps = 0;
+                c.xs = 1;
+                c.nc_tile = c.k_pad;
+                c.n_ctiles = 1;
+                c.sums_in_smem = 0;
+                c.red_sums = 1;
+                c.n_partials = (int)std::max<size_t>(1, std::min<size_t>((size_t)c.grid, ((size_t)64 << 20) / (((size_t)k * d + k) * sizeof(double))));
+                if (ctx->max_partial_slots > 0) c.n_partials = std::min(c.n_partials, ctx->max_partial_slots);
+                c.smem = need;
+                *out = c;
+                return true;
+            }
+        }
+            return false;
+    };
+    if (!det && try_red()) return FMLK_OK;
     for (int pass = env_int("FMLK_TUNE_GLOBAL_SUMS", 0) ? 1 : 0; pass < 2; pass++) {
         const bool sums = accum && pass == 0;
         if (!accum && pass == 1) break;
+        if (pass == 1 && try_red()) return FMLK_OK; // sums do not fit in shared memory: no fixed order to keep
         for (int i = 0; i < ncand; i++) {
             const int cw = force_w ? force_w : cand[i][0], cx = force_xs ? force_xs : cand[i][1];
             size_t need = smem_bytes(cw, c.acc_warps, cx, c.S, k, d, c.k_pad, c.k_pad, 1, sums);
             if ((cw + c.acc_warps) * 32 > 512) continue;
+            // fixed-order sums are only worth their accumulator warps with enough MMA warps beside them
+            if (sums && cw < 8 && env_int("FMLK_TUNE_RED_SUMS", 1)) continue;
             if (need <= budget) {
                 c.warps = cw;
                 c.xs = cx;
@@ -494,7 +529,8 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
         else if (accum) assign_wide_kernel<true, false><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
         else if (xres) assign_wide_kernel<false, true><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
         else assign_wide_kernel<false, false><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
-    } else if (accum && cfg.private_sums) assign_kernel<2><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
+    } else if (accum && cfg.red_sums) assign_kernel<3><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
+    else if (accum && cfg.private_sums) assign_kernel<2><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
     else if (accum) assign_kernel<1><<<grid, (cfg.warps + cfg.acc_warps) * 32, cfg.smem, ctx->stream>>>(p);
     else assign_kernel<0><<<grid, cfg.warps * 32, cfg.smem, ctx->stream>>>(p);
     if (prof && e0 && e1) cudaEventRecord(e1, ctx->stream);
@@ -678,6 +714,8 @@ int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *
             e = cudaFuncSetAttribute(assign_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(assign_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(assign_wide_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
@@ -1378,16 +1416,17 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
     cudaFuncAttributes fa{};
     if (c.wide && accumulate) cudaFuncGetAttributes(&fa, assign_wide_kernel<true, false>);
     else if (c.wide) cudaFuncGetAttributes(&fa, assign_wide_kernel<false, false>);
+    else if (accumulate && c.red_sums) cudaFuncGetAttributes(&fa, assign_kernel<3>);
     else if (accumulate && c.private_sums) cudaFuncGetAttributes(&fa, assign_kernel<2>);
     else if (accumulate) cudaFuncGetAttributes(&fa, assign_kernel<1>);
     else cudaFuncGetAttributes(&fa, assign_kernel<0>);
     snprintf(out, (size_t)out_len,
              "regs=%d max_threads=%d local=%zu grid=%d block=%d smem=%zu mma_warps=%d acc_warps=%d xs=%d S=%d ksteps=%d k_pad=%d nc_tile=%d n_ctiles=%d "
-             "sums_in_smem=%d n_partials=%d private_sums=%d wide=%d",
+             "sums_in_smem=%d n_partials=%d private_sums=%d red_sums=%d wide=%d",
              fa.numRegs, fa.maxThreadsPerBlock, fa.localSizeBytes, c.grid, (c.warps + c.acc_warps) * 32, c.smem, c.warps,
              c.acc_warps, c.xs, c.S, c.ksteps, c.k_pad,
              c.nc_tile, c.n_ctiles,
-             c.sums_in_smem, c.n_partials, c.private_sums, c.wide);
+             c.sums_in_smem, c.n_partials, c.private_sums, c.red_sums, c.wide);
     return FMLK_OK;
 }
 
@@ -1443,6 +1482,8 @@ int noalloc_setup(int device) {
         e = cudaFuncSetAttribute(assign_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e == cudaSuccess && major == 10)
         e = cudaFuncSetAttribute(assign_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    if (e == cudaSuccess && major == 10)
+        e = cudaFuncSetAttribute(assign_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e == cudaSuccess && major == 10)
         e = cudaFuncSetAttribute(assign_wide_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e == cudaSuccess && major == 10)

@@ -524,7 +524,8 @@ __device__ __forceinline__ void mma_chunk(unsigned xa0, unsigned xa1, unsigned c
 // stream centroid tiles from L2 through two buffers, in lock-step (named barrier 1).
 //
 // MODE 0: predict (labels only); 1: accumulate through the accumulator warps (or global atomics);
-// 2: accumulate into warp-private sums (small k).  Separate instantiations: the modes do not share
+// 2: accumulate into warp-private sums (small k); 3: every warp an MMA warp, rows added to the
+// CTA's global accumulator with red.global.add.f64.  Separate instantiations: the modes do not share
 // registers or schedules (folding mode 2 into mode 1 as a run-time branch cost mode 1 6 %).
 template <int MODE>
 __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
@@ -535,7 +536,8 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
     const int W = p.mma_warps;
     FMLK_TRACE_DECL
     constexpr bool priv = MODE == 2;
-    const int A = (ACCUM && !priv) ? p.acc_warps : 0;
+    constexpr bool red = MODE == 3;
+    const int A = (ACCUM && !priv && !red) ? p.acc_warps : 0;
     const int S = p.S;
     const int xs = p.xs;
     const int c_bufs = p.n_ctiles > 1 ? 2 : 1;
@@ -830,6 +832,19 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 }
                 if (lane < rows_valid) atomicAdd(&counts_s[warp * p.k + lab_s[lane]], 1);
                 __syncwarp();
+            } else if (ACCUM && red) {
+                // no accumulator warps: this warp adds its rows to the CTA's accumulator in global memory
+                // with fire-and-forget L2 atomics (the additions happen in L2, nothing queues on the
+                // FP64 pipe); sums then depend on arrival order in their last bits
+                __syncwarp();
+                double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
+                for (int r = 0; r < rows_valid; r++) {
+                    double *srow = slot + (size_t)lab_s[r] * p.d;
+                    const double *xrow = Xt + (size_t)r * S;
+                    for (int c = lane; c < p.d; c += 32) atomicAdd(&srow[c], xrow[c]);
+                }
+                if (lane < rows_valid) atomicAdd(&slot[(size_t)p.k * p.d + lab_s[lane]], 1.0);
+                __syncwarp();
             } else if (ACCUM) {
                 // publish the tile to the accumulator warps.  Rows whose label already occurred earlier
                 // in the tile are first folded into that earlier row (in row order, in this warp's own
@@ -862,7 +877,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         }
         cp_async_wait<0>();
         if (lane == 0 && local_rechecks && p.recheck_count) atomicAdd(p.recheck_count, local_rechecks);
-    } else if (ACCUM && !priv) {
+    } else if (ACCUM && !priv && !red) {
         // =========================== accumulator warp ===========================
         // sums[label] += row, counts[label]++ (KMeans.java:293-294).  The A = 2 G accumulator warps
         // split a tile by columns (G groups of 32 lanes: lane l of group g owns columns g*32 + l,

@@ -16,6 +16,7 @@ OK = 0
 ERR_INVALID_ARG, ERR_STATE, ERR_DIM, ERR_CUDA, ERR_NCCL, ERR_NOMEM = -1, -2, -3, -4, -5, -6
 FLAG_PROFILE = 0x1
 FLAG_BLAS_FMA = 0x2
+FLAG_DETERMINISTIC = 0x4
 # record formats of the reference's serializers (include/fmlk.h)
 FMT_DENSE_VECTOR, FMT_VECTOR, FMT_VECTOR_WITH_NORM = 0, 1, 2
 NCCL_ID_BYTES = 128

@@ -61,7 +61,8 @@ def test_fit_on_serialized_rows_equals_fit_on_raw_rows(ctx):
     ctx.append_points_serialized(L.serialize_rows(x, L.FMT_VECTOR_WITH_NORM), L.FMT_VECTOR_WITH_NORM, d)
     ctx.set_centroids(cent)
     c1, w1 = ctx.fit(5)
-    assert np.array_equal(c0, c1) and np.array_equal(w0, w1)
+    # same rows in the cache either way; the default accumulation (L2 atomics) leaves only the last bits free
+    assert np.allclose(c0, c1, rtol=1e-12, atol=0) and np.array_equal(w0, w1)
     oc, ow = O.fit([x], cent, 5)
     assert np.allclose(c1, oc, rtol=1e-9, atol=0) and np.array_equal(w1, ow)
     ctx.clear_points()

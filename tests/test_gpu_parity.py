@@ -403,3 +403,29 @@ def test_rows_far_beyond_the_shared_memory_tiling(ctx):
     _step_parity(ctx, x, cent)
     assert "wide=1" in ctx.describe_launch(k, d, True)
     ctx.clear_points()
+
+
+def test_deterministic_flag_gives_bit_identical_sums():
+    """FMLK_FLAG_DETERMINISTIC: per-cluster sums are added in a fixed order (accumulator warps, sums in
+    shared memory): two rounds over the same rows give the same bits; the default (L2 atomics) agrees
+    with both to summation order, and labels / counts are bit-exact in either mode."""
+    n, d, k = 300_000, 64, 100
+    x = O.generate_dense(2, 0, 1, n, d)
+    cent = x[:k].copy()
+    results = {}
+    for name, flags in (("det", native.FLAG_DETERMINISTIC), ("fast", 0)):
+        with native.Context(0, flags=flags) as c:
+            c.append_points(x)
+            c.set_centroids(cent)
+            a = c.local_partials()
+            b = c.local_partials()
+            results[name] = (a, b, c.describe_launch(k, d, True))
+    (a, b, desc) = results["det"]
+    assert "sums_in_smem=1" in desc and "red_sums=0" in desc
+    assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
+    (fa, fb, fdesc) = results["fast"]
+    assert "red_sums=1" in fdesc
+    assert np.array_equal(fa[1], a[1]) and np.array_equal(fb[1], a[1])
+    assert np.allclose(fa[0], a[0], rtol=SUM_RTOL, atol=0) and np.allclose(fb[0], a[0], rtol=SUM_RTOL, atol=0)
+    o_sums, o_counts = O.train_local(x, cent)
+    assert np.array_equal(a[1], o_counts.astype(np.int64)) and np.allclose(a[0], o_sums, rtol=SUM_RTOL, atol=0)
