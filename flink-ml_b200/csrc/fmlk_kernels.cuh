@@ -838,12 +838,24 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 // FP64 pipe); sums then depend on arrival order in their last bits
                 __syncwarp();
                 double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
-                for (int r = 0; r < rows_valid; r++) {
-                    double *srow = slot + (size_t)lab_s[r] * p.d;
-                    const double *xrow = Xt + (size_t)r * S;
-                    for (int c = lane; c < p.d; c += 32) atomicAdd(&srow[c], xrow[c]);
+                const int my_lab = lane < rows_valid ? lab_s[lane] : 0;
+                for (int c = lane; c < p.d; c += 32) {
+                    // eight rows at a time: the loads of a group are in flight together, the atomics follow
+#pragma unroll 1
+                    for (int r0 = 0; r0 < rows_valid; r0 += 8) {
+                        double v[8];
+                        int off[8];
+#pragma unroll
+                        for (int q = 0; q < 8; q++) {
+                            v[q] = Xt[(size_t)min(r0 + q, kWarpRows - 1) * S + c];
+                            off[q] = lab_s[min(r0 + q, kWarpRows - 1)] * p.d; // (rows past the end: any valid label, not added)
+                        }
+#pragma unroll
+                        for (int q = 0; q < 8; q++)
+                            if (r0 + q < rows_valid) atomicAdd(&slot[(size_t)off[q] + c], v[q]);
+                    }
                 }
-                if (lane < rows_valid) atomicAdd(&slot[(size_t)p.k * p.d + lab_s[lane]], 1.0);
+                if (lane < rows_valid) atomicAdd(&slot[(size_t)p.k * p.d + my_lab], 1.0);
                 __syncwarp();
             } else if (ACCUM) {
                 // publish the tile to the accumulator warps.  Rows whose label already occurred earlier
@@ -1292,10 +1304,20 @@ __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const Assi
         if (p.labels != nullptr && lane < rows_valid) p.labels[row0 + lane] = lab;
         if (ACCUM) {
             double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
-            for (int r = 0; r < rows_valid; r++) {
-                const int l = __shfl_sync(0xffffffffu, lab, r);
-                const double *xrow = p.x + (row0 + r) * p.d;
-                for (int c = lane; c < p.d; c += 32) atomicAdd(&slot[(size_t)l * p.d + c], xrow[c]);
+            // eight rows at a time per column group: the loads are in flight together, the atomics follow
+            int64_t loff[kWarpRows]; // sums row of each of the warp's rows
+#pragma unroll
+            for (int r = 0; r < kWarpRows; r++) loff[r] = (int64_t)__shfl_sync(0xffffffffu, lab, r) * p.d;
+            for (int c = lane; c < p.d; c += 32) {
+#pragma unroll
+                for (int r0 = 0; r0 < kWarpRows; r0 += 8) {
+                    double v[8];
+#pragma unroll
+                    for (int q = 0; q < 8; q++) v[q] = (r0 + q < rows_valid) ? p.x[(row0 + r0 + q) * p.d + c] : 0.0;
+#pragma unroll
+                    for (int q = 0; q < 8; q++)
+                        if (r0 + q < rows_valid) atomicAdd(&slot[loff[r0 + q] + c], v[q]);
+                }
             }
             if (lane < rows_valid) atomicAdd(&slot[(size_t)p.k * p.d + lab], 1.0);
         }
