@@ -500,6 +500,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.acc_dmma = env_int("FMLK_TUNE_ACC_DMMA", 1);
     // few centroids (HBM-bound): one bulk copy per row tile; otherwise one per row
     p.row_copies = env_int("FMLK_TUNE_ROW_COPIES", cfg.k_pad <= 32 ? 0 : 1);
+    p.no_bulk_red = env_int("FMLK_TUNE_NO_BULK_RED", 0);
     p.no_bulk = env_int("FMLK_TUNE_NO_BULK", 0);
     p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
     p.recheck_count = ctx->recheck;

@@ -65,6 +65,7 @@ struct AssignParams {
 #endif
     int32_t acc_dmma; // 1: accumulator warps add on the FP64 tensor pipe (d = 32 x column groups, finite rows)
     int32_t row_copies; // 1 = one bulk copy per row, 0 = one per tile (chosen by the host: see assign_kernel)
+    int32_t no_bulk_red; // tuning: 1 = per-lane L2 atomics instead of bulk reductions
     int32_t no_bulk;  // tuning: 1 = row tiles with 16-byte cp.async instead of bulk copies
     int32_t fma_mode; // exact path follows the JDK>=11 netlib variant
     unsigned long long *recheck_count;
@@ -138,6 +139,20 @@ __device__ __forceinline__ void bulk_copy_g2s(unsigned dst_smem, const void *src
                  "l"(__cvta_generic_to_global(src_gmem)), "r"(bytes), "r"(bar)
                  : "memory");
 }
+
+// Bulk asynchronous reduction (TMA engine; SASS: UBLKRED.G.S.ADD.F64): global[dst .. dst + bytes) +=
+// shared[src .. src + bytes) as FP64 additions performed in L2 -- no lane touches the data.  The
+// issuing thread commits its reductions as a group and, before the shared source is overwritten,
+// waits until the group has been read.
+__device__ __forceinline__ void bulk_reduce_add_f64(void *dst_gmem, unsigned src_smem, unsigned bytes) {
+    asm volatile("cp.reduce.async.bulk.global.shared::cta.bulk_group.add.f64 [%0], [%1], %2;\n" ::"l"(
+                     __cvta_generic_to_global(dst_gmem)),
+                 "r"(src_smem), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_group_all() { asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_group_read() { asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory"); }
 
 // D(8x8) += A(8x4, row) * B(4x8, col), FP64 tensor core (SASS: DMMA.8x8x4).
 __device__ __forceinline__ void dmma884(double &c0, double &c1, double a, double b) {
@@ -610,6 +625,10 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         // pipe (k = 100: 30.7 against 30.4 TFLOP/s).  Rows of odd length use 8-byte cp.async.
         const bool use_tma = vec16 && !p.no_bulk;
         const bool one_copy = use_tma && p.d <= 128 && p.row_copies == 0;
+        // sums by bulk reductions: rows 16-byte granular and accumulators 16-byte aligned
+        // (accumulator b starts b * (k d + k) doubles in: even, or a single accumulator)
+        const bool red_bulk = red && vec16 && !p.no_bulk_red && ((reinterpret_cast<uintptr_t>(p.partials) & 15) == 0) &&
+                              (p.n_partials == 1 || (((size_t)p.k * p.d + p.k) & 1) == 0);
         const unsigned row_bytes = (unsigned)p.d * 8u;
         unsigned uses0 = 0, uses1 = 0; // completed phases of the stage barriers (parity = uses & 1)
         auto x_issue = [&](int stage, int64_t row0, int rows) {
@@ -685,6 +704,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
             if (ACCUM && it >= 1)
                 for (int a = 0; a < A; a++) spin_until_at_least(&seq_done[warp * A + a], (int)it, (unsigned)p.spin_ns);
 
+            if (red && red_bulk && it >= 1) bulk_wait_group_read(); // the tile's rows have been read by the reductions
             if (xs == 2) {
                 // prefetch the next round's tile into the other stage, then wait for this one
                 const int64_t ntile = tile + GW;
@@ -839,6 +859,15 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 __syncwarp();
                 double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
                 const int my_lab = lane < rows_valid ? lab_s[lane] : 0;
+                if (red_bulk) {
+                    // one bulk reduction per row, issued by the lane of that row: the TMA engine reads the
+                    // row out of this warp's tile and adds it to sums[label] in L2
+                    fence_proxy_async_smem();
+                    if (lane < rows_valid)
+                        bulk_reduce_add_f64(slot + (size_t)my_lab * p.d,
+                                            (unsigned)__cvta_generic_to_shared(Xt + (size_t)lane * S), row_bytes);
+                    bulk_commit_group();
+                } else
                 for (int c = lane; c < p.d; c += 32) {
                     // eight rows at a time: the loads of a group are in flight together, the atomics follow
 #pragma unroll 1
@@ -888,6 +917,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
             FMLK_TRACE_EVENT(4) // labels written, tile published
         }
         cp_async_wait<0>();
+        if (red && red_bulk) bulk_wait_group_all(); // this thread's reductions have been performed
         if (lane == 0 && local_rechecks && p.recheck_count) atomicAdd(p.recheck_count, local_rechecks);
     } else if (ACCUM && !priv && !red) {
         // =========================== accumulator warp ===========================
