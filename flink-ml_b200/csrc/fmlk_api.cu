@@ -568,9 +568,10 @@ int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
         const int64_t ctas = (most + (int64_t)kWideWarps * kWarpRows - 1) / ((int64_t)kWideWarps * kWarpRows);
         cfg.n_partials = (int)std::max<int64_t>(1, std::min<int64_t>(cfg.n_partials, ctas));
     }
-    if ((rc = ensure_partials(ctx, len * cfg.n_partials))) return rc;
+    const size_t stride = partial_stride(ctx->k, ctx->md); // len rounded up to even
+    if ((rc = ensure_partials(ctx, stride * cfg.n_partials))) return rc;
     if ((rc = prep_centroids(ctx))) return rc;
-    CK(ctx, cudaMemsetAsync(ctx->partials, 0, len * cfg.n_partials * sizeof(double), ctx->stream));
+    CK(ctx, cudaMemsetAsync(ctx->partials, 0, stride * cfg.n_partials * sizeof(double), ctx->stream));
     if (extra_rows) {
         if ((rc = launch_assign(ctx, cfg, extra_rows, extra_n, nullptr, true))) return rc;
     } else {
@@ -579,7 +580,7 @@ int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
     }
     const int threads = 256;
     reduce_partials_kernel<<<(unsigned)((len + threads - 1) / threads), threads, 0, ctx->stream>>>(
-        ctx->partials, cfg.n_partials, (int)len, ctx->red);
+        ctx->partials, cfg.n_partials, (int)len, stride, ctx->red);
     ctx->total_launches++;
     CK(ctx, cudaGetLastError());
     return FMLK_OK;

@@ -246,6 +246,10 @@ __device__ __noinline__ int exact_find_closest(const double *x, const double *c,
 // ------------------------------------------------------------------------------------------
 // assign (+ accumulate) kernel
 
+// Doubles between the per-CTA accumulators [k*d sums | k counts]: k*d + k rounded up to even, so that
+// every accumulator (and, d being even, every sums row) starts 16-byte aligned for the bulk reductions.
+__host__ __device__ __forceinline__ size_t partial_stride(int k, int d) { return ((size_t)k * d + k + 1) & ~(size_t)1; }
+
 // Running (best, second-best, index of best) of the scores of one row.  The hot path keeps only
 // the HIGH 32 bits of an order-preserving integer key of each score (sign, exponent, 20 mantissa
 // bits): comparing and selecting then costs 8 integer instructions per score and never queues
@@ -626,9 +630,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         const bool use_tma = vec16 && !p.no_bulk;
         const bool one_copy = use_tma && p.d <= 128 && p.row_copies == 0;
         // sums by bulk reductions: rows 16-byte granular and accumulators 16-byte aligned
-        // (accumulator b starts b * (k d + k) doubles in: even, or a single accumulator)
-        const bool red_bulk = red && vec16 && !p.no_bulk_red && ((reinterpret_cast<uintptr_t>(p.partials) & 15) == 0) &&
-                              (p.n_partials == 1 || (((size_t)p.k * p.d + p.k) & 1) == 0);
+        const bool red_bulk = red && vec16 && !p.no_bulk_red && ((reinterpret_cast<uintptr_t>(p.partials) & 15) == 0);
         const unsigned row_bytes = (unsigned)p.d * 8u;
         unsigned uses0 = 0, uses1 = 0; // completed phases of the stage barriers (parity = uses & 1)
         auto x_issue = [&](int stage, int64_t row0, int rows) {
@@ -857,7 +859,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 // with fire-and-forget L2 atomics (the additions happen in L2, nothing queues on the
                 // FP64 pipe); sums then depend on arrival order in their last bits
                 __syncwarp();
-                double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
+                double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d);
                 const int my_lab = lane < rows_valid ? lab_s[lane] : 0;
                 if (red_bulk) {
                     // one bulk reduction per row, issued by the lane of that row: the TMA engine reads the
@@ -1064,7 +1066,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 } else {
                     // sums too large for shared memory: global accumulators (L2 atomics), slot by CTA
                     const int trash = p.k * p.d;
-                    double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
+                    double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d);
                     for (int c = c0; c < p.d; c += cstride) {
                         int off[RH];
                         double xv[RH];
@@ -1093,7 +1095,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         // the warps' private sums, combined in warp order, added to this CTA's slot
         __syncthreads();
         const int model = p.k * p.d;
-        double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)model + p.k);
+        double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d);
         for (int i = threadIdx.x; i < model; i += blockDim.x) {
             double acc = sums_s[i];
             for (int w = 1; w < W; w++) acc += sums_s[(size_t)w * model + i];
@@ -1107,7 +1109,7 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
     } else if (sums_smem) {
         // this CTA's partial, added to its own slot (plain read-modify-write: slot b belongs to CTA b)
         __syncthreads();
-        double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
+        double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d);
         for (int i = threadIdx.x; i < p.k * p.d; i += blockDim.x) slot[i] += sums_s[i];
         for (int i = threadIdx.x; i < p.k; i += blockDim.x) slot[(size_t)p.k * p.d + i] += (double)counts_s[i];
     }
@@ -1208,6 +1210,7 @@ __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const Assi
     const int dpad_exp = 32 - __clz(4 * p.ksteps);
     const bool vec16 = ((p.d & 1) == 0) && ((reinterpret_cast<uintptr_t>(p.x) & 15) == 0) &&
                        ((reinterpret_cast<uintptr_t>(p.c_mma) & 15) == 0);
+    const bool wide_bulk = vec16 && !p.no_bulk_red && ((reinterpret_cast<uintptr_t>(p.partials) & 15) == 0);
     constexpr int kCtaRows = kWideWarps * kWarpRows;
     const int64_t total_ctiles = (p.n + kCtaRows - 1) / kCtaRows;
     const int nkb = (p.d + kWideDk - 1) / kWideDk;
@@ -1235,6 +1238,7 @@ __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const Assi
         Top2 t0 = top2_init(), t1 = top2_init();
         int mx0 = 0, mx1 = 0;
         double acc0[kChunkTiles][2], acc1[kChunkTiles][2];
+        if (XRES && ACCUM && wide_bulk) bulk_wait_group_read(); // the reductions have read the previous tile's rows
         __syncthreads(); // every warp is done with both stages (and the rows) of the previous CTA tile
         if (XRES) {
             // the whole row tile, as two column halves of the same group as the first centroid block
@@ -1333,7 +1337,18 @@ __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const Assi
         }
         if (p.labels != nullptr && lane < rows_valid) p.labels[row0 + lane] = lab;
         if (ACCUM) {
-            double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * ((size_t)p.k * p.d + p.k);
+            double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d);
+            if (XRES && wide_bulk) {
+                // the CTA's rows are resident in shared memory: one bulk reduction per row (see assign_kernel)
+                fence_proxy_async_smem();
+                if (lane < rows_valid)
+                    bulk_reduce_add_f64(slot + (size_t)lab * p.d,
+                                        (unsigned)__cvta_generic_to_shared(stage_base + (size_t)(warp * kWarpRows + lane) * kWideXresS),
+                                        (unsigned)p.d * 8u);
+                bulk_commit_group();
+                if (lane < rows_valid) atomicAdd(&slot[(size_t)p.k * p.d + lab], 1.0);
+                continue;
+            }
             // eight rows at a time per column group: the loads are in flight together, the atomics follow
             int64_t loff[kWarpRows]; // sums row of each of the warp's rows
 #pragma unroll
@@ -1352,6 +1367,7 @@ __global__ void __launch_bounds__(kWideWarps * 32) assign_wide_kernel(const Assi
             if (lane < rows_valid) atomicAdd(&slot[(size_t)p.k * p.d + lab], 1.0);
         }
     }
+    if (XRES && ACCUM && wide_bulk) bulk_wait_group_all(); // this thread's reductions have been performed
     if (lane == 0 && local_rechecks && p.recheck_count) atomicAdd(p.recheck_count, local_rechecks);
 }
 
@@ -1394,11 +1410,11 @@ __global__ void prep_centroids_kernel(const double *c, int k, int k_pad, int d, 
 }
 
 // out[i] = sum over CTA slots b = 0..n_partials-1 of partials[b][i], in slot order.
-__global__ void reduce_partials_kernel(const double *partials, int n_partials, int len, double *out) {
+__global__ void reduce_partials_kernel(const double *partials, int n_partials, int len, size_t stride, double *out) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= len) return;
     double s = partials[i];
-    for (int b = 1; b < n_partials; b++) s = __dadd_rn(s, partials[(size_t)b * len + i]);
+    for (int b = 1; b < n_partials; b++) s = __dadd_rn(s, partials[(size_t)b * stride + i]);
     out[i] = s;
 }
 
