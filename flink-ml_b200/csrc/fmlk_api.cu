@@ -108,6 +108,7 @@ struct fmlk_ctx {
     cudaStream_t stream = nullptr;
     bool own_stream = false;
     int sm_count = 0;
+    bool rows_aligned16 = true; // every cached chunk (or the rows of this call) starts 16-byte aligned
     int max_partial_slots = 0; // > 0: never use more per-CTA accumulators than this (borrowed scratch)
     size_t smem_optin = 0;
 
@@ -250,6 +251,43 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     const bool small = c.k_pad <= 32;
     const int(*cand)[2] = accum ? (small ? small_acc : large_acc) : (small ? small_pred : large_pred);
     const int ncand = 6; // down to two MMA warps: long rows leave room for little else
+    const bool det = (ctx->flags & FMLK_FLAG_DETERMINISTIC) != 0;
+    auto try_red = [&]() -> bool {
+        if (!accum || !env_int("FMLK_TUNE_RED_SUMS", 1)) return false;
+
+        // resident centroids, every warp an MMA warp, sums by L2 atomics into one accumulator per CTA:
+        // measured faster than the accumulator warps (k = 100: d = 64 26.5 against 25.5 TFLOP/s, d = 32
+        // 20.1 against 17.5-19.3, d = 96 20.2 against 15.8; k = 200, d = 64 28.4) -- the additions happen
+        // in L2 and nothing queues on the FP64 pipe -- but the sums' last bits depend on arrival order;
+        // FMLK_FLAG_DETERMINISTIC keeps the fixed-order accumulator warps
+        // (few centroids are HBM-bound: a second, prefetched row tile per warp where it fits)
+        static const int red_cand[][2] = {{16, 2}, {16, 1}, {12, 2}, {12, 1}, {8, 1}};
+        for (int i = 0; i < 5; i++) {
+            if (red_cand[i][1] == 2 && !small) continue;
+            const int cw = force_w ? force_w : red_cand[i][0], cx = force_xs ? force_xs : red_cand[i][1];
+            size_t need = smem_bytes(cw, 0, cx, c.S, k, d, c.k_pad, c.k_pad, 1, false);
+            if (need <= budget) {
+                c.warps = cw;
+                c.acc_warps = 0;
+                c.xs = cx;
+                c.nc_tile = c.k_pad;
+                c.n_ctiles = 1;
+                c.sums_in_smem = 0;
+                c.red_sums = 1;
+                c.n_partials = (int)std::max<size_t>(1, std::min<size_t>((size_t)c.grid, ((size_t)64 << 20) / (((size_t)k * d + k) * sizeof(double))));
+                if (ctx->max_partial_slots > 0) c.n_partials = std::min(c.n_partials, ctx->max_partial_slots);
+                c.smem = need;
+                *out = c;
+                return true;
+            }
+        }
+            return false;
+    };
+    // few centroids: with rows the TMA engine can reduce from (even d, 16-byte aligned) the sums go out as
+    // bulk reductions too -- measured at k = 10, d = 100 against warp-private sums in shared memory, whose
+    // 64 FP64 adds per tile each wait ~100 cycles next to the other warps' DMMAs; otherwise private sums
+    if (accum && small && !det && (d & 1) == 0 && ctx->rows_aligned16 && env_int("FMLK_TUNE_SMALL_RED", 1) && try_red())
+        return FMLK_OK;
     if (accum && small) {
         // few centroids: every MMA warp keeps private sums (no accumulator warps, no hand-off)
         static const int priv_cand[][2] = {{16, 2}, {16, 1}, {12, 2}, {12, 1}, {10, 1}, {8, 1}, {6, 1}, {4, 1}};
@@ -271,36 +309,6 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
             }
         }
     }
-    const bool det = (ctx->flags & FMLK_FLAG_DETERMINISTIC) != 0;
-    auto try_red = [&]() -> bool {
-        if (!accum || !env_int("FMLK_TUNE_RED_SUMS", 1)) return false;
-
-        // resident centroids, every warp an MMA warp, sums by L2 atomics into one accumulator per CTA:
-        // measured faster than the accumulator warps (k = 100: d = 64 26.5 against 25.5 TFLOP/s, d = 32
-        // 20.1 against 17.5-19.3, d = 96 20.2 against 15.8; k = 200, d = 64 28.4) -- the additions happen
-        // in L2 and nothing queues on the FP64 pipe -- but the sums' last bits depend on arrival order;
-        // FMLK_FLAG_DETERMINISTIC keeps the fixed-order accumulator warps
-        static const int red_cand[][2] = {{16, 1}, {12, 1}, {8, 1}};
-        for (int i = 0; i < 3; i++) {
-            const int cw = force_w ? force_w : red_cand[i][0];
-            size_t need = smem_bytes(cw, 0, 1, c.S, k, d, c.k_pad, c.k_pad, 1, false);
-            if (need <= budget) {
-                c.warps = cw;
-                c.acc_warps = 0;
-                c.xs = 1;
-                c.nc_tile = c.k_pad;
-                c.n_ctiles = 1;
-                c.sums_in_smem = 0;
-                c.red_sums = 1;
-                c.n_partials = (int)std::max<size_t>(1, std::min<size_t>((size_t)c.grid, ((size_t)64 << 20) / (((size_t)k * d + k) * sizeof(double))));
-                if (ctx->max_partial_slots > 0) c.n_partials = std::min(c.n_partials, ctx->max_partial_slots);
-                c.smem = need;
-                *out = c;
-                return true;
-            }
-        }
-            return false;
-    };
     if (!det && try_red()) return FMLK_OK;
     for (int pass = env_int("FMLK_TUNE_GLOBAL_SUMS", 0) ? 1 : 0; pass < 2; pass++) {
         const bool sums = accum && pass == 0;
@@ -557,6 +565,9 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
 int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
     if (!extra_rows && ctx->n_total > 0 && ctx->d != ctx->md) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
     LaunchCfg cfg;
+    ctx->rows_aligned16 = extra_rows ? (reinterpret_cast<uintptr_t>(extra_rows) & 15) == 0 : true;
+    if (!extra_rows)
+        for (const Chunk &ch : ctx->chunks) ctx->rows_aligned16 = ctx->rows_aligned16 && (reinterpret_cast<uintptr_t>(ch.ptr) & 15) == 0;
     int rc = choose_cfg(ctx, ctx->k, ctx->md, true, &cfg);
     if (rc) return rc;
     const size_t len = (size_t)ctx->k * ctx->md + ctx->k;
