@@ -250,7 +250,7 @@ def run_ours(args):
     launch_desc = ctx.describe_launch(k, d, True)
     kernel_name = ("fmlk::assign_wide_kernel<true> (d-blocked assign + accumulate)" if "wide=1" in launch_desc else
                    "fmlk::assign_kernel<2> (assign + warp-private sums)" if "private_sums=1" in launch_desc else
-                   "fmlk::assign_kernel<3> (assign + sums by L2 atomics, one accumulator per CTA)" if "red_sums=1" in launch_desc else
+                   "fmlk::assign_kernel<3> (assign + sums by bulk reductions into one accumulator per CTA)" if "red_sums=1" in launch_desc else
                    "fmlk::assign_kernel<1> (assign + accumulate)")
     roofline.update({
         "traffic": None, "kernel": kernel_name, "ms_per_launch": assign_ms,

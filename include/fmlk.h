@@ -44,7 +44,7 @@ typedef enum fmlk_status {
 #define FMLK_FLAG_BLAS_FMA 0x2 /* exact paths follow netlib's JDK>=11 (Math.fma) variant instead of JDK 8 */
 #define FMLK_FLAG_DETERMINISTIC 0x4 /* per-cluster sums added in a fixed order (bit-identical from run to run)
                                        wherever they fit in shared memory, at a few percent of throughput;
-                                       default: L2 atomics, last bits depend on arrival order.  Labels,
+                                       default: additions performed in L2 (bulk reductions), last bits depend on arrival order.  Labels,
                                        counts and weights are bit-exact either way. */
 
 #define FMLK_NCCL_ID_BYTES 128
