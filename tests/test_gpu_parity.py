@@ -429,3 +429,18 @@ def test_deterministic_flag_gives_bit_identical_sums():
     assert np.allclose(fa[0], a[0], rtol=SUM_RTOL, atol=0) and np.allclose(fb[0], a[0], rtol=SUM_RTOL, atol=0)
     o_sums, o_counts = O.train_local(x, cent)
     assert np.array_equal(a[1], o_counts.astype(np.int64)) and np.allclose(a[0], o_sums, rtol=SUM_RTOL, atol=0)
+
+
+@pytest.mark.parametrize("n,d,k", [(50_000, 100, 10), (30_000, 10, 2), (40_000, 64, 100), (20_000, 64, 250)])
+def test_deterministic_context_step_parity(n, d, k):
+    """The fixed-order paths (warp-private sums for few centroids, accumulator warps otherwise) against
+    the oracle, and bit-identical from one round to the next where the sums fit in shared memory."""
+    x = O.generate_dense(2, 0, 1, n, d)
+    cent = O.select_random_centroids([x], k, O.KMEANS_DEFAULT_SEED)
+    with native.Context(0, flags=native.FLAG_DETERMINISTIC | native.FLAG_PROFILE) as c:
+        _step_parity(c, x, cent)
+        a = c.local_partials()
+        b = c.local_partials()
+        assert np.array_equal(a[1], b[1])
+        if "sums_in_smem=1" in c.describe_launch(k, d, True):
+            assert np.array_equal(a[0], b[0])
