@@ -6,6 +6,9 @@
 //                      LIB/clustering/kmeans/KMeans.java:291-295 with
 //                      CORE/common/distance/EuclideanDistanceMeasure.java:41-73;
 //                      also PredictLabelFunction.map, LIB/clustering/kmeans/KMeansModel.java:129-144
+//   assign_wide_kernel the same, blocked along d (d >= 128, streamed centroids with d % 32 == 0, any d
+//                      the whole-row tiles cannot hold)
+//   decode_records_*   DenseVectorSerializer / VectorWithNormSerializer.deserialize on the ingest path
 //   prep_centroids     new VectorWithNorm(centroid), KMeans.java:279-282
 //   reduce_partials    CentroidsUpdateReducer, KMeans.java:185-198 (within one GPU)
 //   finalize_centroids ModelDataGenerator, KMeans.java:200-212
