@@ -177,6 +177,25 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
         host_group = dist.new_group(backend="gloo")
 
+    # ---- N > 1: every world > 1 code path against the CPU oracle at parallelism = world, before
+    # anything is timed (p-shard fit over the NCCL all-reduce, labels, the rank-ordered online merge,
+    # allReduceSum).  The oracle is the checker here, never the thing measured.  A mismatch ends the
+    # run with a non-zero exit code, so the driver's per-N record carries it.
+    parity = None
+    if world > 1 and not args.no_parity:
+        sys.path.insert(0, os.path.join(ROOT, "scripts"))
+        from multi_gpu_parity import run_checks
+        pc = K.Cluster(rank, world, local, host_group=host_group)
+        parity = run_checks(pc, host_group)
+        pc.close()
+        if not parity["ok"]:
+            if rank == 0:
+                print(json.dumps({"metric": METRIC, "value": None, "unit": UNIT, "n_gpus": world, "parity": parity,
+                                  "error": "world > 1 parity against the oracle failed; nothing was timed"}))
+            dist.barrier()
+            dist.destroy_process_group()
+            sys.exit(1)
+
     n, d, k, rounds, desc = WORKLOADS[args.workload]
     if args.rows:
         n = args.rows
@@ -310,7 +329,7 @@ def run_ours(args):
                        if n * d * 8 > 200e6 else "inputs fit in L2 (reference's own small config)",
                        "data_seed": DATA_SEED, "init": "reference sampler, KMeans default seed"},
             "clocks": clocks, "e2e": e2e, "gpu_launches": prof["total_launches"],
-            "roofline": roofline, "cpu_baseline": base,
+            "roofline": roofline, "cpu_baseline": base, "parity": parity,
             "wall_ms_per_step": wall / args.steps * 1e3, "rechecked_rows": prof["rechecked_rows"],
         }
         print(json.dumps(out))
@@ -331,6 +350,7 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the world > 1 parity leg (N > 1 only)")
     args = ap.parse_args()
     if args.impl == "ours":
         args.warmup = max(args.warmup, 3)  # timing rule: at least 3 warm-up steps

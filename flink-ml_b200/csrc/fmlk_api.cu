@@ -12,6 +12,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <cmath>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -43,11 +44,8 @@ struct NcclApi {
     bool ok = false;
 };
 
-NcclApi &nccl() {
-    static NcclApi api;
-    static bool tried = false;
-    if (tried) return api;
-    tried = true;
+NcclApi load_nccl() {
+    NcclApi api;
     const char *names[] = {"libnccl.so.2", "libnccl.so"};
     for (const char *nm : names) {
         api.handle = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
@@ -78,6 +76,13 @@ NcclApi &nccl() {
     return api;
 }
 
+// Loaded once, by whichever thread asks first; the others block until the table is complete
+// (sibling subtasks of one TaskManager call fmlk_create / fmlk_nccl_unique_id together at open()).
+NcclApi &nccl() {
+    static NcclApi api = load_nccl();
+    return api;
+}
+
 struct Chunk {
     double *ptr;
     int64_t rows;
@@ -93,10 +98,17 @@ struct LaunchCfg {
     size_t smem;
 };
 
-// Tuning overrides for experiments (environment; unset in normal use).
+// Tuning overrides for experiments: FMLK_TUNE_* environment variables are honoured only by a
+// -DFMLK_TUNING build (scripts/tune.sh); the shipped library always takes the measured defaults, so
+// a stray variable in a task manager's environment cannot change which kernel runs.
 int env_int(const char *name, int dflt) {
+#ifdef FMLK_TUNING
     const char *v = getenv(name);
     return (v && *v) ? atoi(v) : dflt;
+#else
+    (void)name;
+    return dflt;
+#endif
 }
 
 thread_local std::string g_static_error;
@@ -146,6 +158,13 @@ struct fmlk_ctx {
     size_t stage_labels_cap = 0;
 
     ncclComm_t comm = nullptr;
+    // allReduceSum staging, kept across calls (no allocation per call once warm)
+    long long *ar_probe = nullptr; // 2
+    double *ar_buf = nullptr;
+    size_t ar_cap = 0; // doubles
+    // fmlk_get_points: device table of row addresses + gathered rows
+    const double **gather_ptrs = nullptr;
+    size_t gather_ptrs_cap = 0;
 
     // profile
     std::vector<cudaEvent_t> ev_pool;
@@ -652,13 +671,21 @@ int grow_points(fmlk_ctx *ctx, int64_t n, double **dst) {
             return FMLK_OK;
         }
     }
-    // geometric growth keeps the chunk count (one kernel launch each per round) logarithmic
-    int64_t cap = std::max<int64_t>(n, std::min<int64_t>(std::max<int64_t>(ctx->n_total, 1 << 16), (int64_t)1 << 26));
+    // geometric growth keeps the chunk count (one kernel launch each per round) logarithmic.  Sized in
+    // bytes: at least 32 MB (or the request), at most 32 GB per chunk, never more than what is free;
+    // on failure halve towards the request instead of dropping straight to it.
+    const int64_t row_bytes = (int64_t)ctx->d * (int64_t)sizeof(double);
+    const int64_t min_rows = std::max<int64_t>(1, ((int64_t)32 << 20) / row_bytes);
+    const int64_t max_rows = std::max<int64_t>(1, ((int64_t)32 << 30) / row_bytes);
+    int64_t cap = std::max<int64_t>(n, std::min<int64_t>(std::max<int64_t>(ctx->n_total, min_rows), max_rows));
+    size_t free_b = 0, total_b = 0;
+    if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess && (int64_t)(free_b / 2) / row_bytes < cap)
+        cap = std::max<int64_t>(n, (int64_t)(free_b / 2) / row_bytes);
     double *p = nullptr;
     cudaError_t e = cudaMalloc((void **)&p, (size_t)cap * ctx->d * sizeof(double));
-    if (e != cudaSuccess && cap > n) {
+    while (e != cudaSuccess && cap > n) {
         cudaGetLastError();
-        cap = n;
+        cap = std::max<int64_t>(n, cap / 2);
         e = cudaMalloc((void **)&p, (size_t)cap * ctx->d * sizeof(double));
     }
     if (e != cudaSuccess) {
@@ -793,6 +820,9 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     dev_free(ctx->stage_labels);
     dev_free(ctx->ingest_buf);
     dev_free(ctx->ingest_bad);
+    dev_free(ctx->ar_probe);
+    dev_free(ctx->ar_buf);
+    dev_free(ctx->gather_ptrs);
     for (int b = 0; b < 2; b++) {
         if (ctx->ev_copied[b]) cudaEventDestroy(ctx->ev_copied[b]);
         if (ctx->ev_decoded[b]) cudaEventDestroy(ctx->ev_decoded[b]);
@@ -911,16 +941,7 @@ int32_t fmlk_append_points_serialized(fmlk_ctx *ctx, const uint8_t *records_host
     const int64_t n = nbytes / rec;
     if (out_rows) *out_rows = n;
     if (n == 0) return FMLK_OK;
-    // what to undo if a record turns out to be malformed
-    const size_t chunks_before = ctx->chunks.size();
-    const int64_t last_rows_before = chunks_before ? ctx->chunks.back().rows : 0, total_before = ctx->n_total;
-    const int d_before = ctx->d;
-    ctx->d = d;
-    double *dst = nullptr;
-    if ((rc = grow_points(ctx, n, &dst))) {
-        ctx->d = d_before;
-        return rc;
-    }
+    // staging, flags, stream and events first: nothing below that can fail leaves the cache changed.
     // two staging buffers: the copy of piece i+1 (copy stream) runs while piece i is unpacked
     const int64_t piece_rows = std::max<int64_t>(1, ((int64_t)32 << 20) / rec);
     const size_t piece_bytes = ((size_t)(piece_rows * rec) + 16 + 255) & ~(size_t)255;
@@ -939,27 +960,20 @@ int32_t fmlk_append_points_serialized(fmlk_ctx *ctx, const uint8_t *records_host
             CK(ctx, cudaEventCreateWithFlags(&ctx->ev_decoded[b], cudaEventDisableTiming));
         }
     }
-    CK(ctx, cudaMemsetAsync(ctx->ingest_bad, 0, sizeof(int), ctx->stream));
-    int64_t piece = 0;
-    for (int64_t r0 = 0; r0 < n; r0 += piece_rows, piece++) {
-        const int64_t rows = std::min(piece_rows, n - r0);
-        const int b = (int)(piece & 1);
-        uint8_t *buf = ctx->ingest_buf + (size_t)b * piece_bytes;
-        if (piece >= 2) CK(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_decoded[b], 0));
-        CK(ctx, cudaMemcpyAsync(buf, records_host + r0 * rec, (size_t)(rows * rec), cudaMemcpyHostToDevice,
-                                ctx->copy_stream));
-        CK(ctx, cudaEventRecord(ctx->ev_copied[b], ctx->copy_stream));
-        CK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[b], 0));
-        launch_decode(ctx->stream, ctx->sm_count, buf, rows, d, hdr, rec, dst + r0 * d, ctx->ingest_bad);
-        CK(ctx, cudaEventRecord(ctx->ev_decoded[b], ctx->stream));
-        ctx->total_launches++;
+    // what to undo if a record turns out to be malformed or a copy fails
+    const size_t chunks_before = ctx->chunks.size();
+    const int64_t last_rows_before = chunks_before ? ctx->chunks.back().rows : 0, total_before = ctx->n_total;
+    const int d_before = ctx->d;
+    ctx->d = d;
+    double *dst = nullptr;
+    if ((rc = grow_points(ctx, n, &dst))) {
+        ctx->d = d_before;
+        return rc;
     }
-    int bad = 0;
-    CK(ctx, cudaMemcpyAsync(&bad, ctx->ingest_bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
-    // the caller may reuse its buffer as soon as we return (Flink object reuse)
-    CK(ctx, cudaStreamSynchronize(ctx->stream));
-    CK(ctx, cudaGetLastError());
-    if (bad) {
+    auto roll_back = [&]() {
+        cudaStreamSynchronize(ctx->copy_stream);
+        cudaStreamSynchronize(ctx->stream);
+        cudaGetLastError();
         while (ctx->chunks.size() > chunks_before) {
             if (ctx->chunks.back().owned) dev_free(ctx->chunks.back().ptr);
             ctx->chunks.pop_back();
@@ -967,6 +981,37 @@ int32_t fmlk_append_points_serialized(fmlk_ctx *ctx, const uint8_t *records_host
         if (chunks_before) ctx->chunks.back().rows = last_rows_before;
         ctx->n_total = total_before;
         ctx->d = d_before;
+    };
+    // every CUDA call from here on goes through one exit that restores the cache
+    cudaError_t e = cudaMemsetAsync(ctx->ingest_bad, 0, sizeof(int), ctx->stream);
+    int64_t piece = 0;
+    for (int64_t r0 = 0; e == cudaSuccess && r0 < n; r0 += piece_rows, piece++) {
+        const int64_t rows = std::min(piece_rows, n - r0);
+        const int b = (int)(piece & 1);
+        uint8_t *buf = ctx->ingest_buf + (size_t)b * piece_bytes;
+        if (piece >= 2) e = cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_decoded[b], 0);
+        if (e == cudaSuccess)
+            e = cudaMemcpyAsync(buf, records_host + r0 * rec, (size_t)(rows * rec), cudaMemcpyHostToDevice,
+                                ctx->copy_stream);
+        if (e == cudaSuccess) e = cudaEventRecord(ctx->ev_copied[b], ctx->copy_stream);
+        if (e == cudaSuccess) e = cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[b], 0);
+        if (e != cudaSuccess) break;
+        launch_decode(ctx->stream, ctx->sm_count, buf, rows, d, hdr, rec, dst + r0 * d, ctx->ingest_bad);
+        e = cudaEventRecord(ctx->ev_decoded[b], ctx->stream);
+        ctx->total_launches++;
+    }
+    int bad = 0;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&bad, ctx->ingest_bad, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream);
+    // the caller may reuse its buffer as soon as we return (Flink object reuse)
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e == cudaSuccess) e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        roll_back();
+        return fail(ctx, e == cudaErrorMemoryAllocation ? FMLK_ERR_NOMEM : FMLK_ERR_CUDA,
+                    std::string("ingest of serialized rows: ") + cudaGetErrorString(e));
+    }
+    if (bad) {
+        roll_back();
         return decode_status(ctx, bad);
     }
     return FMLK_OK;
@@ -1247,8 +1292,8 @@ int32_t fmlk_all_reduce_sum(fmlk_ctx *ctx, double *values_host_inout, int64_t le
     if (len < 0 || (len > 0 && !values_host_inout)) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad values / len");
     if (ctx->world == 1) return FMLK_OK;
     // agree on the length first: max over ranks of (len, -len) gives the largest and the smallest
-    long long *probe = nullptr;
-    if ((rc = dev_alloc(ctx, &probe, 2))) return rc;
+    if (!ctx->ar_probe && (rc = dev_alloc(ctx, &ctx->ar_probe, 2))) return rc;
+    long long *probe = ctx->ar_probe;
     const long long mine[2] = {(long long)len, -(long long)len};
     long long got[2] = {0, 0};
     cudaError_t e = cudaMemcpyAsync(probe, mine, sizeof(mine), cudaMemcpyHostToDevice, ctx->stream);
@@ -1256,19 +1301,26 @@ int32_t fmlk_all_reduce_sum(fmlk_ctx *ctx, double *values_host_inout, int64_t le
     if (e == cudaSuccess && nrc == ncclSuccess)
         e = cudaMemcpyAsync(got, probe, sizeof(got), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess && nrc == ncclSuccess) e = cudaStreamSynchronize(ctx->stream);
-    dev_free(probe);
     if (nrc != ncclSuccess) return fail(ctx, FMLK_ERR_NCCL, "ncclAllReduce failed");
     if (e != cudaSuccess) return fail(ctx, FMLK_ERR_CUDA, cudaGetErrorString(e));
     if (got[0] != -got[1]) return fail(ctx, FMLK_ERR_INVALID_ARG, "The input double array must have same length.");
     if (len == 0) return FMLK_OK;
-    double *buf = nullptr;
-    if ((rc = dev_alloc(ctx, &buf, (size_t)len))) return rc;
+    // the staging buffer grows geometrically and stays with the context: a steady stream of
+    // equal-length calls (SGD's gradient, SGD.java:130) allocates once
+    if ((size_t)len > ctx->ar_cap) {
+        dev_free(ctx->ar_buf);
+        ctx->ar_buf = nullptr;
+        ctx->ar_cap = 0;
+        const size_t want = std::max<size_t>((size_t)len, 1024);
+        if ((rc = dev_alloc(ctx, &ctx->ar_buf, want))) return rc;
+        ctx->ar_cap = want;
+    }
+    double *buf = ctx->ar_buf;
     e = cudaMemcpyAsync(buf, values_host_inout, (size_t)len * sizeof(double), cudaMemcpyHostToDevice, ctx->stream);
     if (e == cudaSuccess) nrc = nccl().AllReduce(buf, buf, (size_t)len, ncclFloat64, ncclSum, ctx->comm, ctx->stream);
     if (e == cudaSuccess && nrc == ncclSuccess)
         e = cudaMemcpyAsync(values_host_inout, buf, (size_t)len * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream);
     if (e == cudaSuccess && nrc == ncclSuccess) e = cudaStreamSynchronize(ctx->stream);
-    dev_free(buf);
     if (nrc != ncclSuccess) return fail(ctx, FMLK_ERR_NCCL, "ncclAllReduce failed");
     if (e != cudaSuccess) return fail(ctx, FMLK_ERR_CUDA, cudaGetErrorString(e));
     return FMLK_OK;
@@ -1295,20 +1347,35 @@ int32_t fmlk_get_points(fmlk_ctx *ctx, const int64_t *row_ids, int32_t m, double
     int rc = use_device(ctx);
     if (rc) return rc;
     if (m < 0 || (m > 0 && (!row_ids || !out_rows_host))) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad row ids");
+    if (m == 0) return FMLK_OK;
+    // resolve every id to its device address on the host, gather on the device, one copy back
+    std::vector<const double *> srcs((size_t)m);
     for (int32_t i = 0; i < m; i++) {
         int64_t r = row_ids[i];
         if (r < 0 || r >= ctx->n_total) return fail(ctx, FMLK_ERR_INVALID_ARG, "row id out of range");
-        const Chunk *src = nullptr;
         for (const Chunk &ch : ctx->chunks) {
             if (r < ch.rows) {
-                src = &ch;
+                srcs[(size_t)i] = ch.ptr + r * ctx->d;
                 break;
             }
             r -= ch.rows;
         }
-        CK(ctx, cudaMemcpyAsync(out_rows_host + (size_t)i * ctx->d, src->ptr + r * ctx->d, (size_t)ctx->d * sizeof(double),
-                                cudaMemcpyDeviceToHost, ctx->stream));
     }
+    if ((size_t)m > ctx->gather_ptrs_cap) {
+        dev_free(ctx->gather_ptrs);
+        ctx->gather_ptrs = nullptr;
+        ctx->gather_ptrs_cap = 0;
+        if ((rc = dev_alloc(ctx, &ctx->gather_ptrs, (size_t)m))) return rc;
+        ctx->gather_ptrs_cap = (size_t)m;
+    }
+    if ((rc = ensure_stage(ctx, (size_t)m * ctx->d, 0))) return rc;
+    CK(ctx, cudaMemcpyAsync(ctx->gather_ptrs, srcs.data(), (size_t)m * sizeof(const double *), cudaMemcpyHostToDevice,
+                            ctx->stream));
+    gather_rows_kernel<<<m, 128, 0, ctx->stream>>>(ctx->gather_ptrs, ctx->d, ctx->stage_rows);
+    ctx->total_launches++;
+    CK(ctx, cudaGetLastError());
+    CK(ctx, cudaMemcpyAsync(out_rows_host, ctx->stage_rows, (size_t)m * ctx->d * sizeof(double), cudaMemcpyDeviceToHost,
+                            ctx->stream));
     CK(ctx, cudaStreamSynchronize(ctx->stream));
     return FMLK_OK;
 }
@@ -1470,7 +1537,8 @@ static __device__ __align__(256) double g_noalloc_scratch[kNoAllocDoubles];
 
 namespace {
 struct NoAllocDevice {
-    bool ready = false;
+    std::mutex mu;      // the first call on a device does the set-up exactly once, whichever thread it is
+    bool ready = false; // (guarded by mu)
     fmlk_ctx ctx; // a context whose device buffers are slices of g_noalloc_scratch (owns nothing)
 };
 NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
@@ -1480,6 +1548,7 @@ NoAllocDevice g_noalloc_dev[kNoAllocMaxDevices];
 // the address a kernel can use comes from cudaGetSymbolAddress.
 int noalloc_setup(int device) {
     NoAllocDevice &nd = g_noalloc_dev[device];
+    std::lock_guard<std::mutex> lock(nd.mu);
     if (nd.ready) return FMLK_OK;
     double *base = nullptr;
     cudaError_t e = cudaGetSymbolAddress((void **)&base, g_noalloc_scratch);

@@ -1481,6 +1481,14 @@ __global__ void online_merge_kernel(const double *gathered, int world, int k, in
     else weights[j] = w;
 }
 
+// out[i][0..d) = *rows[i][0..d): the sampled rows of fmlk_get_points (KMeans.selectRandomCentroids,
+// KMeans.java:310-327), gathered on the device so that one copy brings them to the host.
+__global__ void gather_rows_kernel(const double *const *rows, int d, double *out) {
+    const double *src = rows[blockIdx.x];
+    double *dst = out + (size_t)blockIdx.x * d;
+    for (int i = threadIdx.x; i < d; i += blockDim.x) dst[i] = src[i];
+}
+
 // ------------------------------------------------------------------------------------------
 // java.util.Random on the device (benchmark data; bit-identical to the JDK's LCG)
 

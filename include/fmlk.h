@@ -160,8 +160,9 @@ int32_t fmlk_local_partials(fmlk_ctx *ctx, double *out_sums, int64_t *out_counts
  *   out_sums_dev    k x d sums, device memory; out_counts_dev: k counts as doubles, device memory
  * The work is enqueued on cuda_stream (NULL: the default stream) and the outputs are valid once
  * that stream has completed; the call itself does not wait.  The first call on each device also
- * looks up the device address of the scratch array and sets a kernel attribute: make that first
- * call before any stream capture begins.  Every call uses the same array, which still holds the
+ * looks up the device address of the scratch array and sets a kernel attribute (under a lock, so
+ * two threads may race to be first): make that first call before any stream capture begins.
+ * Every call uses the same array, which still holds the
  * previous call's data: what must start at zero is cleared on the stream first, and two calls whose
  * GPU work overlaps (different streams, or different threads) race on it -- keep them ordered.
  * Errors are reported through fmlk_last_error(NULL) of the calling thread. */

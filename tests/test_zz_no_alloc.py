@@ -4,16 +4,20 @@ Some hosts of this library cannot let it call cudaMalloc: a task manager that ha
 GPU memory budget to its own pool, or an operator thread that cannot afford the device-wide
 synchronisation cudaMalloc/cudaFree imply.  For them the library keeps a fixed scratch array of its
 own (about 10.8 MB per GPU) and offers one entry point that uses only that array plus the caller's
-input and output buffers.  This test calls it through the C ABI twice in a row -- the second call
-with a different shape, so anything the first call left in the shared array would show -- and
-checks both results against fmlk_local_partials on a context (counts equal, sums to 1e-12
-relative: the two paths add in the same order, the tolerance is the one the other tests use).
+input and output buffers.  This test calls it through the C ABI several times in a row -- each call
+with a different shape, so anything the previous call left in the shared array would show -- and
+checks every result against the CPU oracle (the same checker the other parity tests use) and
+against fmlk_local_partials on a context: counts equal, sums to 1e-12 relative.  The tolerance is
+the one the other tests use; it covers the order of the additions, which differs from call to call
+because most shapes add in L2 (bulk reductions) in arrival order.  One shape (d = 128, k = 60) is
+chosen so that the d-blocked kernel, not only the main one, runs on the fixed scratch.
 
 Collected last (file name) so that a failure here cannot hide any other test under -x."""
 import numpy as np
 import pytest
 
 from flink_ml_b200 import native
+from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
 
@@ -49,14 +53,22 @@ def test_noalloc_matches_context_path_twice():
     rng = np.random.default_rng(3)
     # warm-up call: the first call on a device does the one-time set-up
     _noalloc(torch, rng.random((64, 8)), rng.random((4, 8)))
-    shapes = [(30000, 64, 100), (4099, 7, 5), (9000, 256, 31)]  # config-2 shape, a smaller ragged one, a long-row one (d-blocked kernel)
+    # config-2 shape, a smaller ragged one, a long-row one that stays on the main kernel (k <= 32),
+    # and one that takes the d-blocked kernel (d >= 128 with more than 32 centroids; 60*128 + 60 <= 8192)
+    shapes = [(30000, 64, 100), (4099, 7, 5), (9000, 256, 31), (9000, 128, 60)]
+    with native.Context(0) as probe:
+        assert "wide=1" in probe.describe_launch(60, 128, True)
+        assert "wide=0" in probe.describe_launch(100, 64, True)
     for n, d, k in shapes:
         x = rng.random((n, d))
         cent = x[rng.choice(n, k, replace=False)].copy()
         cent[0] = cent[1]  # an exact tie: rows equal to these centroids take the exact replay
+        o_sums, o_counts = O.train_local(x, cent)
         want_sums, want_counts = _reference(x, cent)
         sums, counts, free_before, free_after = _noalloc(torch, x, cent)
-        assert np.array_equal(counts, want_counts.astype(np.float64))
+        assert np.array_equal(counts, o_counts.astype(np.float64))  # against the oracle
+        assert np.allclose(sums, o_sums, rtol=SUM_RTOL, atol=0)
+        assert np.array_equal(counts, want_counts.astype(np.float64))  # and against the context path
         assert np.allclose(sums, want_sums, rtol=SUM_RTOL, atol=0)
         assert free_after == free_before  # nothing was allocated or freed on the device
     # an empty batch gives zeros, not the previous call's numbers
