@@ -199,96 +199,145 @@ def run_ours(args):
     n, d, k, rounds, desc = WORKLOADS[args.workload]
     if args.rows:
         n = args.rows
-    cluster = K.Cluster(rank, world, local, flags=native.FLAG_PROFILE, host_group=host_group)
-    ctx = cluster.context()
     stream = torch.cuda.current_stream()
-    ctx.set_stream(stream.cuda_stream)
-
-    # ---- synthetic data: DenseVectorGenerator shard `rank` of `world`, generated in HBM
-    total_rows = n * world
-    assert native.rows_on_task(total_rows, rank, world) == n
-    x = torch.empty((n, d), dtype=torch.float64, device=dev)
-    native.generate_dense_dev(local, stream.cuda_stream, DATA_SEED, rank, world, total_rows, d, x.data_ptr())
-    torch.cuda.synchronize()
-    ctx.adopt_points_dev(x.data_ptr(), n, d, keep=x)
-    est = F.KMeans(cluster).set_k(k).set_max_iter(rounds)
-    init = K.select_random_centroids(ctx, cluster, k, est.get_seed())
+    peaks, peak_src = read_peaks()
+    dmma_peak, dfma_peak = native.measure_fp64_peaks(local, 300.0)
+    if rank == 0:
+        # the FP64 denominators of this run, with the clock they were measured at (MEASURED_PEAKS.json has no FP64 entry)
+        try:
+            with open(os.path.join(ROOT, "profiles", "fp64_peaks.json"), "w") as f:
+                json.dump({"dmma_m8n8k4_tflops": dmma_peak, "dfma_tflops": dfma_peak, "gpu": torch.cuda.get_device_name(local),
+                           "how": "fmlk_measure_fp64_peaks: register-resident DMMA / DFMA loops, best of the repeats in 300 ms",
+                           "theoretical_dmma_tflops_at_1965MHz": 148 * 64 * 2 * 1.965e9 / 1e12}, f, indent=1)
+        except OSError:
+            pass
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def one_step():
-        ctx.set_centroids(init)
-        ctx.fit(rounds, want_model=False)
+    def generate(rows_per_gpu, dd):
+        total = rows_per_gpu * world
+        assert native.rows_on_task(total, rank, world) == rows_per_gpu
+        t = torch.empty((rows_per_gpu, dd), dtype=torch.float64, device=dev)
+        native.generate_dense_dev(local, stream.cuda_stream, DATA_SEED, rank, world, total, dd, t.data_ptr())
+        torch.cuda.synchronize()
+        return t
+
+    def timed_fits(flags, xt, kk, nrounds, steps, warmup, sample_clocks=False):
+        """`steps` KMeans fits of `nrounds` rounds over the device-resident rows xt, timed on the device
+        (CUDA events on the launching stream, barrier + synchronize on both sides, max over ranks)."""
+        nn, dd = xt.shape
+        cl = K.Cluster(rank, world, local, flags=flags | native.FLAG_PROFILE, host_group=host_group)
+        cx = cl.context()
+        cx.set_stream(stream.cuda_stream)
+        cx.adopt_points_dev(xt.data_ptr(), nn, dd, keep=xt)
+        est_ = F.KMeans(cl).set_k(kk).set_max_iter(nrounds)
+        init_ = K.select_random_centroids(cx, cl, kk, est_.get_seed())
+
+        def one_step():
+            cx.set_centroids(init_)
+            cx.fit(nrounds, want_model=False)
+
+        for _ in range(warmup):
+            one_step()
+        cx.reset_profile()
+        sampler = ClockSampler(local) if (sample_clocks and rank == 0) else None
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        t0 = time.perf_counter()
+        e0.record(stream)
+        for _ in range(steps):
+            one_step()
+        e1.record(stream)
+        barrier()
+        wall = time.perf_counter() - t0
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        total_ms = float(ms.item())
+        prof = cx.profile()
+        launches = max(prof["assign_launches"], 1)
+        assign_ms = prof["assign_ms"] / launches
+        desc_ = cx.describe_launch(kk, dd, True)
+        fast = "fast=1" in desc_ and cx.fast_launches() > 0
+        tf = 2.0 * kk * dd * nn / (assign_ms * 1e-3) * 1e-12        # SURVEY 8d: 2*k*d flop per point-iteration
+        gbs = 8.0 * dd * nn / (assign_ms * 1e-3) * 1e-9             # SURVEY 8d: 8*d bytes per point-iteration
+        hbm_frac = gbs / peaks["hbm_gbs"]
+        tensor_frac = tf / dmma_peak if dmma_peak > 0 else 0.0
+        hbm = {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_frac,
+               "peak_source": peak_src}
+        if fast:
+            # the contraction is on the tcgen05 pipe (three TF32 passes: 6*k*d flop per point-iteration);
+            # nothing FP64 is left on the critical path, so the row stream from HBM is what bounds it
+            roof = dict(hbm)
+            tf32_peak = peaks.get("bf16_tflops", 0.0) / 2.0
+            roof["tf32_tensor"] = {"achieved": 3.0 * tf, "peak": tf32_peak, "unit": "TFLOP/s",
+                                   "frac": 3.0 * tf / tf32_peak if tf32_peak else None,
+                                   "peak_source": "half of MEASURED_PEAKS.json's burst bf16 figure (TF32 runs at half the bf16 rate)"}
+            kern = "fmlk::assign_fast_kernel<true> (tcgen05 TF32x3 contraction, FP64 exact replay of near-tie rows, sums by bulk reductions)"
+        elif tensor_frac >= hbm_frac:
+            roof = {"bound": "tensor", "achieved": tf, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tensor_frac,
+                    "peak_source": "FP64 DMMA m8n8k4 microbenchmark run live by this bench, written to profiles/fp64_peaks.json "
+                                   "(MEASURED_PEAKS.json has no FP64 entry; datasheet 37-40 TFLOP/s)"}
+        else:
+            roof = dict(hbm)
+        if not fast:
+            kern = ("fmlk::assign_wide_kernel<true> (d-blocked assign + accumulate)" if "wide=1" in desc_ else
+                    "fmlk::assign_kernel<2> (assign + warp-private sums)" if "private_sums=1" in desc_ else
+                    "fmlk::assign_kernel<3> (assign + sums by bulk reductions into one accumulator per CTA)"
+                    if "red_sums=1" in desc_ else "fmlk::assign_kernel<1> (assign + accumulate)")
+        roof.update({"traffic": None, "kernel": kern, "ms_per_launch": assign_ms, "launches_timed": prof["assign_launches"],
+                     "share_of_step": prof["assign_ms"] / total_ms, "hbm": hbm,
+                     "fp64_tensor": {"achieved": tf, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tensor_frac},
+                     "fp64_fma_peak_tflops": dfma_peak, "launch": desc_})
+        model = cx.get_model()
+        res = {"value": float(nn) * world * nrounds * steps / (total_ms * 1e-3), "total_ms": total_ms, "wall": wall,
+               "prof": prof, "roofline": roof, "model": model, "clocks": sampler.stop() if sampler else None,
+               "fast": fast, "ms_per_round": total_ms / steps / nrounds}
+        cx.clear_points()
+        cl.close()
+        return res
 
     # ---- value: rows resident in HBM, K fits timed on the device
-    for _ in range(args.warmup):
-        one_step()
-    ctx.reset_profile()
-    sampler = ClockSampler(local)
-    if rank == 0:
-        sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    t0 = time.perf_counter()
-    e0.record(stream)
-    for _ in range(args.steps):
-        one_step()
-    e1.record(stream)
-    barrier()
-    wall = time.perf_counter() - t0
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    total_ms = float(ms.item())
-    clocks = sampler.stop() if rank == 0 else None
-    prof = ctx.profile()
-    value = float(total_rows) * rounds * args.steps / (total_ms * 1e-3)
-    model_c, model_w = ctx.get_model()
-
-    # ---- roofline of the dominant kernel (assign + accumulate), live CUDA-event durations
-    peaks, peak_src = read_peaks()
-    launches = max(prof["assign_launches"], 1)
-    assign_ms = prof["assign_ms"] / launches
-    flop_per_launch = 2.0 * k * d * n          # 2*k*d flop per point-iteration
-    bytes_per_launch = 8.0 * d * n             # 8*d bytes per point-iteration
-    dmma_peak, dfma_peak = native.measure_fp64_peaks(local, 300.0)
-    tf = flop_per_launch / (assign_ms * 1e-3) * 1e-12
-    gbs = bytes_per_launch / (assign_ms * 1e-3) * 1e-9
-    hbm_frac = gbs / peaks["hbm_gbs"]
-    tensor_frac = tf / dmma_peak if dmma_peak > 0 else 0.0
-    if tensor_frac >= hbm_frac:
-        roofline = {"bound": "tensor", "achieved": tf, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tensor_frac,
-                    "peak_source": "FP64 DMMA m8n8k4 microbenchmark run live by this bench "
-                                   "(MEASURED_PEAKS.json has no FP64 entry; datasheet 37-40 TFLOP/s)"}
-    else:
-        roofline = {"bound": "hbm", "achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_frac,
-                    "peak_source": peak_src}
-    launch_desc = ctx.describe_launch(k, d, True)
-    kernel_name = ("fmlk::assign_wide_kernel<true> (d-blocked assign + accumulate)" if "wide=1" in launch_desc else
-                   "fmlk::assign_kernel<2> (assign + warp-private sums)" if "private_sums=1" in launch_desc else
-                   "fmlk::assign_kernel<3> (assign + sums by bulk reductions into one accumulator per CTA)" if "red_sums=1" in launch_desc else
-                   "fmlk::assign_kernel<1> (assign + accumulate)")
-    roofline.update({
-        "traffic": None, "kernel": kernel_name, "ms_per_launch": assign_ms,
-        "launches_timed": prof["assign_launches"], "share_of_step": prof["assign_ms"] / total_ms,
-        "hbm": {"achieved": gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s", "frac": hbm_frac, "peak_source": peak_src},
-        "fp64_tensor": {"achieved": tf, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tensor_frac},
-        "fp64_fma_peak_tflops": dfma_peak, "launch": launch_desc,
-    })
-    ncu_traffic = os.path.join(ROOT, "profiles", "traffic_%s.json" % args.workload)
+    x = generate(n, d)
+    total_rows = n * world
+    main_flags = native.FLAG_FAST_TF32 if args.fast else 0
+    r = timed_fits(main_flags, x, k, rounds, args.steps, args.warmup, sample_clocks=True)
+    value, total_ms, wall, prof, roofline, clocks = r["value"], r["total_ms"], r["wall"], r["prof"], r["roofline"], r["clocks"]
+    model_c, model_w = r["model"]
+    ncu_traffic = os.path.join(ROOT, "profiles", "traffic_%s%s.json" % (args.workload, "_fast" if r["fast"] else ""))
     if os.path.exists(ncu_traffic):
         try:
             roofline["traffic"] = json.load(open(ncu_traffic)).get("dram_bytes_per_launch")
+            roofline["traffic_source"] = "ncu --set full capture of this kernel on this workload, committed as " + \
+                                         os.path.relpath(ncu_traffic, ROOT)
         except Exception:
             pass
 
+    # ---- the same workload in the other mode, beside (never instead of) the headline: the tcgen05 fast mode
+    fast_rec = None
+    if not args.fast and not args.no_fast:
+        fr = timed_fits(native.FLAG_FAST_TF32, x, k, rounds, max(1, min(args.steps, 3)), 3)
+        fc, fw = fr["model"]
+        fast_rec = {
+            "dtype": "tf32x3+f64-recheck", "value": fr["value"], "unit": UNIT, "ms_per_round": fr["ms_per_round"],
+            "speedup_over_f64_mode": fr["value"] / value, "took_tcgen05_kernel": fr["fast"],
+            "roofline": fr["roofline"], "rechecked_rows": fr["prof"]["rechecked_rows"],
+            "rechecked_fraction": fr["prof"]["rechecked_rows"] / float(n * rounds * max(1, min(args.steps, 3))),
+            "weights_bit_exact_vs_f64_mode": bool(np.array_equal(fw, model_w)),
+            "centroids_within_1e-9_of_f64_mode": bool(np.allclose(fc, model_c, rtol=1e-9, atol=0, equal_nan=True)),
+            "gpu_launches": fr["prof"]["total_launches"],
+        }
+
     # ---- e2e: the public API with HOST buffers: KMeans.fit(Table) -> model, H2D and D2H inside
     e2e = None
+    cluster = K.Cluster(rank, world, local, flags=main_flags | native.FLAG_PROFILE, host_group=host_group)
+    est = F.KMeans(cluster).set_k(k).set_max_iter(rounds)
     if not args.no_e2e:
-        ctx.clear_points()
         host = torch.empty((n, d), dtype=torch.float64, pin_memory=True)
         host.copy_(x)
         torch.cuda.synchronize()
@@ -312,6 +361,39 @@ def run_ours(args):
                "steps": e2e_steps, "ms_per_step": float(dt.item()) / e2e_steps * 1e3,
                "api": "flink_ml_b200.KMeans.fit(Table) from pinned host rows; timed on the host clock "
                       "around the calls (max over ranks)", "model_matches_device_run": ok}
+        del host, table
+    else:
+        del x
+        torch.cuda.empty_cache()
+    cluster.close()
+
+    # ---- the north-star shape (config 4: 1e9 x 64, k = 1000 over 8 GPUs): this GPU's share, a short run
+    north = None
+    if not args.no_north_star and args.workload == "c2":
+        nn, nd, nk, nrounds = args.north_rows, 64, 1000, 3
+        free_b, _ = torch.cuda.mem_get_info(local)
+        if free_b > nn * nd * 8 + (8 << 30):
+            xs = generate(nn, nd)
+            recs, models = {}, {}
+            for name, fl in (("f64", 0), ("tf32x3+f64-recheck", native.FLAG_FAST_TF32)):
+                if name != "f64" and args.no_fast:
+                    continue
+                nr = timed_fits(fl, xs, nk, nrounds, 1, 1)
+                models[name] = nr["model"]
+                recs[name] = {"value": nr["value"], "unit": UNIT, "ms_per_round": nr["ms_per_round"],
+                              "per_gpu_fp64_equivalent_tflops": nr["roofline"]["fp64_tensor"]["achieved"],
+                              "roofline": {kx: nr["roofline"][kx] for kx in ("bound", "achieved", "peak", "unit", "frac", "kernel")},
+                              "took_tcgen05_kernel": nr["fast"], "rechecked_rows": nr["prof"]["rechecked_rows"]}
+            if "tf32x3+f64-recheck" in recs:
+                recs["tf32x3+f64-recheck"]["weights_bit_exact_vs_f64_mode"] = bool(
+                    np.array_equal(models["f64"][1], models["tf32x3+f64-recheck"][1]))
+                recs["tf32x3+f64-recheck"]["centroids_within_1e-9_of_f64_mode"] = bool(
+                    np.allclose(models["f64"][0], models["tf32x3+f64-recheck"][0], rtol=1e-9, atol=0, equal_nan=True))
+            north = {"workload": "config 4's per-GPU share: %d x %d FP64 rows per GPU (%d in all), k=%d, %d rounds, "
+                                 "device-resident, warm-up 1 fit" % (nn, nd, nn * world, nk, nrounds),
+                     "scaling": "weak", "modes": recs}
+            del xs
+            torch.cuda.empty_cache()
 
     base = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -321,7 +403,7 @@ def run_ours(args):
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "scaling": "weak", "vs_baseline": None, "dtype": "tf32x3+f64-recheck" if r["fast"] else "f64", "data": "synthetic",
             "config": {"workload": desc, "rows_per_gpu": n, "rows_total": total_rows, "d": d, "k": k,
                        "rounds_per_step": rounds, "sharding": "rows by subtask as RowGenerator (rank = subtask)",
                        "collective": "ncclAllReduce of k*d+k FP64 per round" if world > 1 else "none (1 GPU)",
@@ -331,11 +413,11 @@ def run_ours(args):
             "clocks": clocks, "e2e": e2e, "gpu_launches": prof["total_launches"],
             "roofline": roofline, "cpu_baseline": base, "parity": parity,
             "wall_ms_per_step": wall / args.steps * 1e3, "rechecked_rows": prof["rechecked_rows"],
+            "fast_mode": fast_rec, "north_star": north,
         }
         print(json.dumps(out))
     if world > 1:
         dist.barrier()
-        cluster.close()
         dist.destroy_process_group()
 
 
@@ -351,6 +433,11 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-parity", action="store_true", help="skip the world > 1 parity leg (N > 1 only)")
+    ap.add_argument("--fast", action="store_true",
+                    help="headline line in the tcgen05 fast mode (FMLK_FLAG_FAST_TF32) instead of the FP64 mode")
+    ap.add_argument("--no-fast", action="store_true", help="skip the fast-mode sub-record of the default run")
+    ap.add_argument("--no-north-star", action="store_true", help="skip the config-4-share sub-record")
+    ap.add_argument("--north-rows", type=int, default=125_000_000, help="rows per GPU of the north-star sub-record")
     args = ap.parse_args()
     if args.impl == "ours":
         args.warmup = max(args.warmup, 3)  # timing rule: at least 3 warm-up steps

@@ -5,6 +5,7 @@
 // at run time, only when world > 1) for the per-round sum over subtasks.
 #include "../../include/fmlk.h"
 #include "fmlk_kernels.cuh"
+#include "fmlk_fast.cuh"
 
 #include <dlfcn.h>
 #include <algorithm>
@@ -156,6 +157,17 @@ struct fmlk_ctx {
     size_t stage_rows_cap = 0; // doubles
     int32_t *stage_labels = nullptr;
     size_t stage_labels_cap = 0;
+
+    // fast mode (FMLK_FLAG_FAST_TF32): the centroids as TF32 terms + their tensor maps, the bitmap of
+    // rows left to the exact replay
+    float *bt1 = nullptr, *bt2 = nullptr;
+    size_t bt_cap = 0; // floats in bt1 (bt2 is never larger)
+    alignas(64) CUtensorMap map1, map2;
+    int map_k_rows = 0, map_KB = 0, map_nacc = 0;
+    uint32_t *flag_words = nullptr;
+    size_t flag_cap = 0;
+    float *dbg_scores = nullptr, *dbg_full = nullptr; // fmlk_fast_debug (tests)
+    int64_t fast_launches = 0;
 
     ncclComm_t comm = nullptr;
     // allReduceSum staging, kept across calls (no allocation per call once warm)
@@ -484,6 +496,165 @@ void drain_events(fmlk_ctx *ctx) {
     ctx->ev_used = 0;
 }
 
+
+// ---- fast mode (fmlk_fast.cuh): geometry, per-round operand preparation, launch -------------------
+struct FastPlan {
+    int Kd, KB, k_rows, Nacc, nA, NS, stage_bytes, group_bytes;
+    size_t smem;
+};
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled() {
+    static EncodeTiledFn fn = []() -> EncodeTiledFn {
+        void *f = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &f, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            return nullptr;
+        return (EncodeTiledFn)f;
+    }();
+    return fn;
+}
+
+// Does the tcgen05 kernel take (k, d)?  First version: centroid terms resident in shared memory
+// (k <= 256 after rounding up to 16), rows of at most 128 columns, two row stages.
+bool fast_shape(const fmlk_ctx *ctx, int k, int d, FastPlan *out) {
+    if (!(ctx->flags & FMLK_FLAG_FAST_TF32)) return false;
+    if (d < 2 || (d & 1) || d > 128) return false;
+    FastPlan f{};
+    f.Kd = (d + 7) & ~7;
+    f.KB = (f.Kd + 31) / 32;
+    f.k_rows = (k + 15) & ~15;
+    if (f.k_rows > 256) return false;
+    f.Nacc = f.k_rows;
+    f.nA = (kFastACol + 2 * 2 * f.Kd + 2 * f.Nacc <= kFastTmemCols) ? 2 : 1;
+    if (kFastACol + f.nA * 2 * f.Kd + 2 * f.Nacc > kFastTmemCols) return false;
+    f.group_bytes = kFastGroupRows * d * 8 + 16;
+    f.stage_bytes = kFastGroups * f.group_bytes;
+    const size_t fixed = (size_t)(2 * f.KB + 1) * f.Nacc * 128 + 2 * kFastRows * sizeof(float) + (size_t)f.Nacc * sizeof(int) +
+                         24 * 8 + 16 + 1024 /* alignment slack */;
+    if (fixed + 2 * (size_t)f.stage_bytes > ctx->smem_optin) return false;
+    f.NS = (int)std::min<size_t>(4, (ctx->smem_optin - fixed) / f.stage_bytes);
+    f.smem = fixed + (size_t)f.NS * f.stage_bytes;
+    *out = f;
+    return true;
+}
+
+int ensure_fast(fmlk_ctx *ctx, const FastPlan &f) {
+    const size_t need = (size_t)f.k_rows * (32 * f.KB + 32);
+    int rc;
+    bool fresh = false;
+    if (need > ctx->bt_cap) {
+        dev_free(ctx->bt1);
+        dev_free(ctx->bt2);
+        ctx->bt1 = ctx->bt2 = nullptr;
+        ctx->bt_cap = 0;
+        if ((rc = dev_alloc(ctx, &ctx->bt1, need))) return rc;
+        if ((rc = dev_alloc(ctx, &ctx->bt2, need))) return rc;
+        ctx->bt_cap = need;
+        fresh = true;
+    }
+    if (fresh || ctx->map_k_rows != f.k_rows || ctx->map_KB != f.KB || ctx->map_nacc != f.Nacc) {
+        EncodeTiledFn enc = encode_tiled();
+        if (!enc) return fail(ctx, FMLK_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
+        // bt1: k_rows x (32 KB + 32) floats, bt2: k_rows x 32 KB floats; boxes of Nacc rows x 32 columns
+        // (128 bytes) land with the 128-byte swizzle, the layout the MMA's shared-memory descriptor names.
+        // Both maps cover buffers of this context, i.e. this GPU's own memory.
+        const cuuint32_t box[2] = {32u, (cuuint32_t)f.Nacc}, estr[2] = {1u, 1u};
+        for (int t = 0; t < 2; t++) {
+            const cuuint64_t ld = (cuuint64_t)(32 * f.KB + (t == 0 ? 32 : 0));
+            const cuuint64_t dims[2] = {ld, (cuuint64_t)f.k_rows}, strides[1] = {ld * sizeof(float)};
+            CUresult r = enc(t == 0 ? &ctx->map1 : &ctx->map2, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
+                             t == 0 ? (void *)ctx->bt1 : (void *)ctx->bt2, dims, strides, box, estr,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (r != CUDA_SUCCESS) return fail(ctx, FMLK_ERR_CUDA, "cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+        }
+        ctx->map_k_rows = f.k_rows;
+        ctx->map_KB = f.KB;
+        ctx->map_nacc = f.Nacc;
+    }
+    return FMLK_OK;
+}
+
+// Rows that take the tcgen05 kernel: the shape fits, 16-byte aligned rows, enough of them to fill the GPU.
+bool fast_rows_ok(const double *x, int64_t n) { return n >= 4096 && (reinterpret_cast<uintptr_t>(x) & 15) == 0; }
+
+int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, int32_t *labels, bool accum, int n_partials) {
+    const int64_t tiles = (n + kFastRows - 1) / kFastRows;
+    const size_t words = (size_t)tiles * 4;
+    int rc;
+    if (words > ctx->flag_cap) {
+        dev_free(ctx->flag_words);
+        ctx->flag_words = nullptr;
+        ctx->flag_cap = 0;
+        if ((rc = dev_alloc(ctx, &ctx->flag_words, words))) return rc;
+        ctx->flag_cap = words;
+    }
+    FastParams p{};
+    p.x = x;
+    p.n = n;
+    p.d = ctx->md;
+    p.Kd = f.Kd;
+    p.KB = f.KB;
+    p.k = ctx->k;
+    p.Nacc = f.Nacc;
+    p.nA = f.nA;
+    p.NS = f.NS;
+    p.stage_bytes = f.stage_bytes;
+    p.group_bytes = f.group_bytes;
+    p.coef = (float)(2.5 * (f.Kd / 8 + 6) * 0x1.0p-22);
+    p.cmax2 = ctx->cmax2;
+    p.c = ctx->centroids;
+    p.cn = ctx->cn;
+    p.labels = labels;
+    p.partials = accum ? ctx->partials : nullptr;
+    p.n_partials = n_partials;
+    p.flag_words = ctx->flag_words;
+    p.dbg_scores = ctx->dbg_scores;
+    p.dbg_full = ctx->dbg_full;
+    p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
+    const int grid = (int)std::min<int64_t>(ctx->sm_count, tiles);
+#ifdef FMLK_TRACE
+    const char *trace_path = getenv("FMLK_TRACE_FILE");
+    const size_t trace_len = (size_t)kFastWarps * kTraceEvents;
+    if (trace_path) {
+        cudaMalloc((void **)&p.trace, trace_len * 8);
+        cudaMemsetAsync(p.trace, 0, trace_len * 8, ctx->stream);
+    }
+#endif
+    if (accum) assign_fast_kernel<true><<<grid, kFastThreads, f.smem, ctx->stream>>>(p, ctx->map1, ctx->map2);
+    else assign_fast_kernel<false><<<grid, kFastThreads, f.smem, ctx->stream>>>(p, ctx->map1, ctx->map2);
+    CK(ctx, cudaGetLastError());
+#ifdef FMLK_TRACE
+    if (trace_path) {
+        std::vector<unsigned long long> host(trace_len);
+        cudaMemcpyAsync(host.data(), p.trace, trace_len * 8, cudaMemcpyDeviceToHost, ctx->stream);
+        cudaStreamSynchronize(ctx->stream);
+        if (FILE *f = fopen(trace_path, "wb")) {
+            fwrite(host.data(), 8, trace_len, f);
+            fclose(f);
+        }
+        cudaFree(p.trace);
+    }
+#endif
+    const int rgrid = (int)std::min<int64_t>((int64_t)ctx->sm_count * 8, ((int64_t)words + 7) / 8);
+    if (accum)
+        recheck_rows_kernel<true><<<rgrid, 256, 0, ctx->stream>>>(x, n, ctx->md, ctx->flag_words, (int64_t)words, ctx->centroids,
+                                                                   ctx->cn, ctx->k, p.fma_mode, labels, ctx->partials,
+                                                                   ctx->recheck);
+    else
+        recheck_rows_kernel<false><<<rgrid, 256, 0, ctx->stream>>>(x, n, ctx->md, ctx->flag_words, (int64_t)words,
+                                                                    ctx->centroids, ctx->cn, ctx->k, p.fma_mode, labels, nullptr,
+                                                                    ctx->recheck);
+    CK(ctx, cudaGetLastError());
+    ctx->total_launches += 2;
+    ctx->fast_launches++;
+    return FMLK_OK;
+}
+
 int prep_centroids(fmlk_ctx *ctx) {
     const int k_pad = (ctx->k + 7) & ~7;
     prep_centroids_kernel<<<1, 256, 0, ctx->stream>>>(ctx->centroids, ctx->k, k_pad, ctx->md,
@@ -491,12 +662,34 @@ int prep_centroids(fmlk_ctx *ctx) {
                                                      ctx->cmax2, ctx->c_mma);
     ctx->total_launches++;
     CK(ctx, cudaGetLastError());
+    FastPlan f;
+    if (fast_shape(ctx, ctx->k, ctx->md, &f)) {
+        int rc = ensure_fast(ctx, f);
+        if (rc) return rc;
+        const int total = f.k_rows * (32 * f.KB + 32);
+        prep_fast_kernel<<<(total + 255) / 256, 256, 0, ctx->stream>>>(ctx->c_mma, ctx->h, ctx->k, ctx->md, f.k_rows, f.KB,
+                                                                       ctx->bt1, ctx->bt2);
+        ctx->total_launches++;
+        CK(ctx, cudaGetLastError());
+    }
     return FMLK_OK;
 }
 
 // Launches the assign kernel over one block of rows.  partials != null: accumulate.
 int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t n, int32_t *labels, bool accum) {
     if (n <= 0) return FMLK_OK;
+    {
+        FastPlan f;
+        if (fast_rows_ok(x, n) && fast_shape(ctx, ctx->k, ctx->md, &f)) {
+            const bool prof = (ctx->flags & FMLK_FLAG_PROFILE) != 0;
+            cudaEvent_t e0 = prof ? next_event(ctx) : nullptr, e1 = prof ? next_event(ctx) : nullptr;
+            if (e0 && e1) cudaEventRecord(e0, ctx->stream);
+            int rc = launch_fast(ctx, f, x, n, labels, accum, cfg.n_partials);
+            if (e0 && e1) cudaEventRecord(e1, ctx->stream);
+            ctx->assign_launches++;
+            return rc;
+        }
+    }
     AssignParams p{};
     p.x = x;
     p.n = n;
@@ -764,6 +957,10 @@ int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *
             e = cudaFuncSetAttribute(assign_wide_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(assign_wide_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     }
     if (e != cudaSuccess) {
         std::string m = std::string("device set-up: ") + cudaGetErrorString(e);
@@ -820,6 +1017,9 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     dev_free(ctx->stage_labels);
     dev_free(ctx->ingest_buf);
     dev_free(ctx->ingest_bad);
+    dev_free(ctx->bt1);
+    dev_free(ctx->bt2);
+    dev_free(ctx->flag_words);
     dev_free(ctx->ar_probe);
     dev_free(ctx->ar_buf);
     dev_free(ctx->gather_ptrs);
@@ -1488,11 +1688,32 @@ int32_t fmlk_measure_fp64_peaks(int32_t device, double ms, double *dmma_tflops, 
     return FMLK_OK;
 }
 
+int32_t fmlk_fast_debug(fmlk_ctx *ctx, float *best_second_dev, float *all_scores_dev) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    ctx->dbg_scores = best_second_dev;
+    ctx->dbg_full = all_scores_dev;
+    return FMLK_OK;
+}
+
+int64_t fmlk_fast_launches(const fmlk_ctx *ctx) { return ctx ? ctx->fast_launches : 0; }
+
 int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumulate, char *out, int32_t out_len) {
     if (!ctx || !out || out_len <= 0) return FMLK_ERR_INVALID_ARG;
     LaunchCfg c;
     int rc = choose_cfg(ctx, k, d, accumulate != 0, &c);
     if (rc) return rc;
+    FastPlan f;
+    if (fast_shape(ctx, k, d, &f)) {
+        cudaFuncAttributes fa{};
+        if (accumulate) cudaFuncGetAttributes(&fa, assign_fast_kernel<true>);
+        else cudaFuncGetAttributes(&fa, assign_fast_kernel<false>);
+        snprintf(out, (size_t)out_len,
+                 "fast=1 regs=%d local=%zu grid=%d block=%d smem=%zu Kd=%d KB=%d Nacc=%d tmem_a_buffers=%d row_stages=%d "
+                 "n_partials=%d wide=0 (rows below 4096 or unaligned rows take the FP64 kernel)",
+                 fa.numRegs, fa.localSizeBytes, ctx->sm_count, kFastThreads, f.smem, f.Kd, f.KB, f.Nacc, f.nA, f.NS,
+                 c.n_partials);
+        return FMLK_OK;
+    }
     cudaFuncAttributes fa{};
     if (c.wide && accumulate) cudaFuncGetAttributes(&fa, assign_wide_kernel<true, false>);
     else if (c.wide) cudaFuncGetAttributes(&fa, assign_wide_kernel<false, false>);

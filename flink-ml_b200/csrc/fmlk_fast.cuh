@@ -1,0 +1,527 @@
+// fmlk_fast.cuh -- the tcgen05 fast mode of the assign step (FMLK_FLAG_FAST_TF32).
+//
+// Replaces the same reference loop as assign_kernel (findClosest + axpy + counts++,
+// LIB/clustering/kmeans/KMeans.java:291-295 with CORE/common/distance/EuclideanDistanceMeasure.java:41-73;
+// PredictLabelFunction.map, LIB/clustering/kmeans/KMeansModel.java:129-144): north_star allows a
+// TF32 tensor-core contraction provided near-tie rows are re-checked in FP64.
+//
+// The contraction v_j = x.c_j - |c_j|^2/2 runs on the 5th-generation tensor cores (tcgen05.mma,
+// kind::tf32, accumulators in TMEM) with every FP64 operand split into TF32 terms:
+//     x = xh + xl (+ e_x),  |xl| <= 2^-11 |x|,  |e_x| <= 1.25 * 2^-22 |x|      (split on the fly, per row tile)
+//     c = c1 + c2 (+ e_c),  |c2| <= 2^-11 |c|,  |e_c| <= 2^-22 |c|              (split once per round)
+//     -|c|^2/2 = h1 + h2 + h3 (to 2^-33), multiplied by a constant column of ones
+// and three passes accumulated into ONE TMEM accumulator, small terms first:
+//     xh.c2 ,  xl.c1 ,  xh.c1 + 1.h
+// Error of the score (S' = |x||c| + |c|^2/2 <= |x|^2 + |c|max^2):
+//   - dropped products xl.c2, x.e_c, e_x.c:            <= 3.3 * 2^-22 S'
+//   - FP32 accumulation in the tensor core: each tcgen05.mma step (K = 8) adds eight exact products
+//     to the accumulator with at most 2^-22 relative error of the largest magnitude involved (two
+//     FP32 ulps: alignment truncation + the final rounding).  The two small passes carry partial
+//     sums <= 2^-10 S'; only the Kd/8 + 1 steps of the last pass see S' itself.
+//   => |v_fast - v_exact| <= E = (Kd/8 + 6) * 2^-22 * S'
+// A row is decided by the tensor-core pass when best - second > 2.5 E (2E for the two scores, the
+// rest covers the FP32 subtraction, the FP32 row norm and the FP64 reference's own rounding, all
+// orders of magnitude smaller).  Every other row -- near ties, duplicates, NaN/Inf, magnitudes outside
+// the range where FP32 neither overflows nor underflows -- is flagged in a bitmap and replayed by
+// recheck_rows_kernel with exact_find_closest (the reference arithmetic, operation by operation), so
+// labels and counts stay bit-exact.  The FP32 accumulation model is checked by
+// tests/test_gpu_fast.py::test_score_error_within_model against float64 scores.
+//
+// Data flow of one CTA (persistent, one per SM, 128-row tiles):
+//   loader warp      cp.async.bulk: 16 copies of 8 rows each into a stage (16-byte pad between the
+//                    groups: conflict-free 128-bit reads for one thread per row)
+//   converter warps  one thread per row: FP64 -> (xh, xl) TF32, tcgen05.st into TMEM (the A operand
+//                    never touches shared memory), FP32 row norm -> decision threshold
+//   MMA warp         one thread: tcgen05.mma A(TMEM) x B(shared, 128-byte swizzle, staged once by
+//                    tensor-map TMA loads), tcgen05.commit -> mbarriers
+//   epilogue warps   one thread per row: tcgen05.ld, running (best, second, index), margin test,
+//                    label; training: one cp.reduce.async.bulk add.f64 of the FP64 row (still in the
+//                    stage) into sums[label] of the CTA's accumulator in global memory
+#pragma once
+#include "fmlk_kernels.cuh"
+#include <cuda.h>
+
+namespace fmlk {
+
+constexpr int kFastRows = 128;       // rows per tile = TMEM lanes = MMA M
+constexpr int kFastGroupRows = 8;    // rows per bulk copy
+constexpr int kFastGroups = kFastRows / kFastGroupRows;
+constexpr int kFastConvWarps = 4;    // warps 0..3   (TMEM lane quarter = warp % 4)
+constexpr int kFastEpiSets = 2;      // warps 4..11  two sets of four, alternating tiles
+constexpr int kFastLoaderWarp = 4 + 4 * kFastEpiSets;
+constexpr int kFastMmaWarp = kFastLoaderWarp + 1;
+constexpr int kFastWarps = kFastMmaWarp + 1;
+constexpr int kFastThreads = kFastWarps * 32;
+constexpr int kFastTmemCols = 512;
+constexpr int kFastOnesCol = 0;      // 8 columns [1,1,1,0,0,0,0,0] in every lane
+constexpr int kFastACol = 16;        // first A buffer
+
+struct FastParams {
+    const double *x;
+    int64_t n;
+    int32_t d;
+    int32_t Kd;       // d rounded up to 8 (MMA K granularity for tf32)
+    int32_t KB;       // 32-column blocks of B covering Kd
+    int32_t k;
+    int32_t Nacc;     // accumulator columns = centroids per pass (multiple of 16, <= 256)
+    int32_t nA;       // A buffers in TMEM (1 or 2)
+    int32_t NS;       // row stages in shared memory
+    int32_t stage_bytes;
+    int32_t group_bytes; // 8 * d * 8 + 16
+    float coef;       // 2.5 * (Kd/8 + 6) * 2^-22
+    const double *cmax2; // [0] max finite |c|^2, [1] ceil(log2) of it
+    const double *c;     // k x d centroids as given (exact replay)
+    const double *cn;
+    int32_t *labels;     // or null
+    double *partials;    // or null (predict)
+    int32_t n_partials;
+    uint32_t *flag_words; // [ceil(n / 128) * 4]
+    float *dbg_scores;    // or null: [n][2] = best, second (tests)
+    float *dbg_full;      // or null: [n][Nacc] every score (tests, small n)
+    int32_t fma_mode;
+#ifdef FMLK_TRACE
+    unsigned long long *trace; // [kFastWarps][kTraceEvents] (clock << 4 | event) of CTA 0, debugging builds only
+#endif
+};
+
+#ifdef FMLK_TRACE
+#define FAST_TRACE(EV)                                                                   \
+    if (p.trace && blockIdx.x == 0 && lane == 0 && trace_n < kTraceEvents)               \
+        p.trace[(size_t)warp * kTraceEvents + trace_n++] = ((unsigned long long)clock64() << 4) | (EV);
+#else
+#define FAST_TRACE(EV)
+#endif
+
+// ------------------------------------------------------------------------------------------
+// PTX wrappers: tcgen05 / TMEM / tensor-map TMA
+
+__device__ __forceinline__ void tmem_alloc(unsigned smem_slot, unsigned cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_slot), "r"(cols) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(unsigned taddr, unsigned cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(unsigned bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
+}
+// D(TMEM) (+)= A(TMEM, 128 lanes x 8 columns) * B(shared, N x 8 tf32, K-major)
+__device__ __forceinline__ void tc_mma_tf32_ts(unsigned d_tmem, unsigned a_tmem, uint64_t b_desc, unsigned idesc,
+                                               unsigned accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem),
+        "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st16(unsigned taddr, const unsigned (&v)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16};\n" ::"r"(taddr),
+        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]),
+        "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st8(unsigned taddr, const unsigned (&v)[16]) {
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};\n" ::"r"(taddr), "r"(v[0]), "r"(v[1]),
+                 "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory"); }
+__device__ __forceinline__ void tmem_ld16(unsigned taddr, unsigned (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]),
+          "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
+
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
+}
+// tensor-map TMA load of a 2-D box (SASS: UTMALDG); the map covers this GPU's memory only
+__device__ __forceinline__ void tma_load_2d(unsigned dst_smem, const CUtensorMap *map, int c0, int c1, unsigned bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n" ::"r"(
+                     dst_smem),
+                 "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(bar)
+                 : "memory");
+}
+
+// Shared-memory matrix descriptor of a K-major operand tile stored as rows of 128 bytes with the
+// 128-byte swizzle (what a tensor-map load with CU_TENSOR_MAP_SWIZZLE_128B writes): 8-row groups
+// 1024 bytes apart (stride byte offset), version 1, layout type 2.  A K step of 8 tf32 inside the
+// 128-byte row advances the start address by 32 bytes.
+__device__ __forceinline__ uint64_t umma_desc_sw128(unsigned smem_addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr >> 4) & 0x3fffu);
+    d |= (uint64_t)1 << 16;                    // leading byte offset (unused for swizzled K-major): 1
+    d |= (uint64_t)(1024 >> 4) << 32;          // stride byte offset
+    d |= (uint64_t)1 << 46;                    // descriptor version (sm_100)
+    d |= (uint64_t)2 << 61;                    // SWIZZLE_128B
+    return d;
+}
+// Instruction descriptor: D = F32, A = B = TF32, both K-major, M = 128, N = n.
+__host__ __device__ __forceinline__ unsigned umma_idesc_tf32(int n) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(n >> 3) << 17) | ((unsigned)(kFastRows >> 4) << 24);
+}
+
+// TMEM lane L of a tile holds tile row fast_row_of_lane(L): eight consecutive lanes read rows of
+// eight different 8-row copy groups, whose 16-byte pads put them in different banks.
+__host__ __device__ __forceinline__ int fast_row_of_lane(int L) { return (L & 15) * kFastGroupRows + (L >> 4); }
+
+__device__ __forceinline__ unsigned tf32_rn_bits(float v) { return (__float_as_uint(v) + 0x1000u) & 0xffffe000u; }
+
+// ------------------------------------------------------------------------------------------
+// Per round: the centroids as TF32 terms, row-major with rows of 32-column blocks, for the tensor-map loads.
+//   bt1[j][0 .. 32 KB)       = c1 = tf32(c)          bt1[j][32 KB + 0..2] = h1, h2, h3 (three-term -|c|^2/2)
+//   bt2[j][0 .. 32 KB)       = c2 = tf32(c - c1)
+// rows j >= k and dead centroids: zeros with h1 = -inf (they score -inf and never win).
+__global__ void prep_fast_kernel(const double *c_mma, const double *h, int k, int d, int k_rows, int KB, float *bt1,
+                                 float *bt2) {
+    const int ld1 = 32 * KB + 32, ld2 = 32 * KB;
+    const int total = k_rows * ld1;
+    for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
+        const int j = idx / ld1, i = idx - j * ld1;
+        float v1 = 0.f, v2 = 0.f;
+        if (i < d && j < k) {
+            const double cv = c_mma[(size_t)j * d + i];
+            v1 = __uint_as_float(tf32_rn_bits(__double2float_rn(cv)));
+            v2 = __uint_as_float(tf32_rn_bits(__double2float_rn(cv - (double)v1)));
+        } else if (i >= 32 * KB && i < 32 * KB + 3) {
+            const double hv = j < k ? h[j] : -INFINITY;
+            const int t = i - 32 * KB;
+            if (!isfinite(hv)) {
+                v1 = t == 0 ? -INFINITY : 0.f;
+            } else {
+                const float a = __uint_as_float(tf32_rn_bits(__double2float_rn(hv)));
+                const double r1 = hv - (double)a;
+                const float b = __uint_as_float(tf32_rn_bits(__double2float_rn(r1)));
+                const float cc = __uint_as_float(tf32_rn_bits(__double2float_rn(r1 - (double)b)));
+                v1 = t == 0 ? a : (t == 1 ? b : cc);
+            }
+        }
+        bt1[idx] = v1;
+        if (i < ld2) bt2[(size_t)j * ld2 + i] = v2;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+template <bool ACCUM>
+__global__ void __launch_bounds__(kFastThreads, 1)
+    assign_fast_kernel(const FastParams p, const __grid_constant__ CUtensorMap map1, const __grid_constant__ CUtensorMap map2) {
+    extern __shared__ __align__(1024) unsigned char fast_smem[];
+    // the swizzled B tiles want a 1024-byte aligned base (the launch reserves the slack)
+    unsigned char *smem_raw = fast_smem + ((1024u - ((unsigned)__cvta_generic_to_shared(fast_smem) & 1023u)) & 1023u);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#ifdef FMLK_TRACE
+    int trace_n = 0;
+#endif
+    // carve-up (the B tiles first: the swizzle wants 1024-byte alignment)
+    const int bblk = p.Nacc * 128; // bytes of one 32-column block of B
+    unsigned char *B1 = smem_raw;                      // (KB + 1) blocks of bt1
+    unsigned char *B2 = B1 + (size_t)(p.KB + 1) * bblk; // KB blocks of bt2
+    unsigned char *stage0 = B2 + (size_t)p.KB * bblk;
+    float *thr_s = reinterpret_cast<float *>(stage0 + (size_t)p.NS * p.stage_bytes); // [2][128]
+    int *counts_s = reinterpret_cast<int *>(thr_s + 2 * kFastRows);                  // [Nacc]
+    unsigned long long *bars = reinterpret_cast<unsigned long long *>(counts_s + p.Nacc);
+    unsigned *tmem_slot = reinterpret_cast<unsigned *>(bars + 24);
+    auto bar = [&](int i) { return (unsigned)__cvta_generic_to_shared(&bars[i]); };
+    // barrier indices
+    const int FULL_X = 0, X_EMPTY = 4, A_FULL = 8, A_EMPTY = 10, D_FULL = 12, D_EMPTY = 14, THR_FULL = 16, THR_EMPTY = 18,
+              B_FULL = 20;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < 4; s++) {
+            mbar_init(bar(FULL_X + s), 1);
+            mbar_init(bar(X_EMPTY + s), 4); // the four warps that are the last readers of a stage
+        }
+        for (int a = 0; a < 2; a++) {
+            mbar_init(bar(A_FULL + a), kFastConvWarps);
+            mbar_init(bar(A_EMPTY + a), 1);
+            mbar_init(bar(D_FULL + a), 1);
+            mbar_init(bar(D_EMPTY + a), 4);
+            mbar_init(bar(THR_FULL + a), kFastConvWarps);
+            mbar_init(bar(THR_EMPTY + a), 4);
+        }
+        mbar_init(bar(B_FULL), 1);
+        mbar_fence_init();
+    }
+    for (int i = threadIdx.x; i < p.Nacc; i += blockDim.x) counts_s[i] = 0;
+    if (warp == kFastMmaWarp) tmem_alloc((unsigned)__cvta_generic_to_shared(tmem_slot), kFastTmemCols);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const unsigned tmem = *tmem_slot;
+    const unsigned a_cols = 2u * (unsigned)p.Kd;
+    const unsigned d_col0 = kFastACol + (unsigned)p.nA * a_cols;
+
+    const int64_t total_tiles = (p.n + kFastRows - 1) / kFastRows;
+    const int64_t my_tiles = total_tiles > blockIdx.x ? (total_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+
+    if (warp < kFastConvWarps) {
+        // =========================== converter: FP64 row -> TF32 terms in TMEM ===========================
+        const int q = warp;
+        const int L = 32 * q + lane;
+        const int rho = fast_row_of_lane(L);
+        const unsigned lane_sel = (unsigned)(32 * q) << 16;
+        {
+            // the constant column block [1, 1, 1, 0, ...] that multiplies (h1, h2, h3)
+            unsigned ones[16];
+#pragma unroll
+            for (int i = 0; i < 16; i++) ones[i] = i < 3 ? __float_as_uint(1.0f) : 0u;
+            tmem_st8(tmem + lane_sel + kFastOnesCol, ones);
+            tmem_wait_st();
+        }
+        const int cexp = (int)p.cmax2[1];
+        const bool model_ok = cexp >= -120 && cexp <= 80;
+        const float cmax2f = model_ok ? __double2float_ru(p.cmax2[0]) : INFINITY;
+        const size_t row_off = (size_t)(rho >> 3) * p.group_bytes + (size_t)(rho & 7) * p.d * 8;
+        for (int64_t i = 0; i < my_tiles; i++) {
+            const int s = (int)(i % p.NS), a = (int)(i % p.nA), e = (int)(i & 1);
+            const int64_t row0 = (blockIdx.x + i * gridDim.x) * kFastRows;
+            const int rows_valid = (int)min((int64_t)kFastRows, p.n - row0);
+            FAST_TRACE(0)
+            mbar_wait(bar(FULL_X + s), (unsigned)((i / p.NS) & 1));
+            FAST_TRACE(1)
+            mbar_wait(bar(A_EMPTY + a), (unsigned)(((i / p.nA) & 1) ^ 1));
+            tc_fence_after();
+            FAST_TRACE(2)
+            const double2 *src = reinterpret_cast<const double2 *>(stage0 + (size_t)s * p.stage_bytes + row_off);
+            const unsigned a_hi = tmem + lane_sel + kFastACol + (unsigned)a * a_cols;
+            const unsigned a_lo = a_hi + (unsigned)p.Kd;
+            float nsq = 0.f;
+            unsigned mx = 0;
+            for (int c0 = 0; c0 < p.Kd; c0 += 16) {
+                unsigned hi[16], lo[16];
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const int col = c0 + 2 * j;
+                    double2 v = make_double2(0.0, 0.0);
+                    if (col < p.d) v = src[col >> 1];
+                    const float f0 = __double2float_rn(v.x), f1 = __double2float_rn(v.y);
+                    mx = max(mx, max(__float_as_uint(f0) & 0x7fffffffu, __float_as_uint(f1) & 0x7fffffffu));
+                    nsq = fmaf(f0, f0, nsq);
+                    nsq = fmaf(f1, f1, nsq);
+                    const unsigned h0 = tf32_rn_bits(f0), h1 = tf32_rn_bits(f1);
+                    hi[2 * j] = h0;
+                    hi[2 * j + 1] = h1;
+                    lo[2 * j] = tf32_rn_bits(f0 - __uint_as_float(h0));
+                    lo[2 * j + 1] = tf32_rn_bits(f1 - __uint_as_float(h1));
+                }
+                if (c0 + 16 <= p.Kd) {
+                    tmem_st16(a_hi + (unsigned)c0, hi);
+                    tmem_st16(a_lo + (unsigned)c0, lo);
+                } else {
+                    tmem_st8(a_hi + (unsigned)c0, hi);
+                    tmem_st8(a_lo + (unsigned)c0, lo);
+                }
+            }
+            tmem_wait_st();
+            FAST_TRACE(3)
+            // decision threshold of this row (see the header); rows whose magnitudes FP32 cannot carry
+            // safely -- Inf / NaN, |x_i| >= 2^40, a non-zero row below 2^-60 -- always take the exact replay
+            const int ex = (int)(mx >> 23) - 127;
+            const bool range_ok = mx == 0u || (ex >= -60 && ex < 40);
+            float thr = INFINITY;
+            if (rho < rows_valid && range_ok) thr = p.coef * (nsq * 1.0001f + cmax2f) * 1.001f;
+            mbar_wait(bar(THR_EMPTY + e), (unsigned)(((i >> 1) & 1) ^ 1));
+            thr_s[e * kFastRows + L] = thr;
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(bar(THR_FULL + e));
+                mbar_arrive(bar(A_FULL + a));
+                if (!ACCUM) mbar_arrive(bar(X_EMPTY + s)); // predict: the rows are not needed again
+            }
+            FAST_TRACE(4)
+        }
+    } else if (warp < kFastLoaderWarp) {
+        // =========================== epilogue: scores -> label (+ accumulate) ===========================
+        const int e = (warp - kFastConvWarps) >> 2, q = (warp - kFastConvWarps) & 3;
+        const int L = 32 * q + lane;
+        const int rho = fast_row_of_lane(L);
+        const unsigned lane_sel = (unsigned)(32 * q) << 16;
+        const unsigned d_tmem = tmem + lane_sel + d_col0 + (unsigned)e * (unsigned)p.Nacc;
+        const size_t row_off = (size_t)(rho >> 3) * p.group_bytes + (size_t)(rho & 7) * p.d * 8;
+        double *slot = ACCUM ? p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d) : nullptr;
+        for (int64_t i = e; i < my_tiles; i += 2) {
+            const int s = (int)(i % p.NS);
+            const int64_t tile = blockIdx.x + i * gridDim.x;
+            const int64_t row0 = tile * kFastRows;
+            const int rows_valid = (int)min((int64_t)kFastRows, p.n - row0);
+            const unsigned ph = (unsigned)((i >> 1) & 1);
+            FAST_TRACE(5)
+            mbar_wait(bar(THR_FULL + e), ph);
+            const float thr = thr_s[e * kFastRows + L];
+            mbar_wait(bar(D_FULL + e), ph);
+            tc_fence_after();
+            FAST_TRACE(6)
+            float best = -INFINITY, second = -INFINITY;
+            int idx = 0;
+            for (int c0 = 0; c0 < p.Nacc; c0 += 16) {
+                unsigned v[16];
+                tmem_ld16(d_tmem + (unsigned)c0, v);
+                tmem_wait_ld();
+                if (p.dbg_full && rho < rows_valid) {
+#pragma unroll
+                    for (int j = 0; j < 16; j++) p.dbg_full[(size_t)(row0 + rho) * p.Nacc + c0 + j] = __uint_as_float(v[j]);
+                }
+#pragma unroll
+                for (int j = 0; j < 16; j++) {
+                    const float sc = __uint_as_float(v[j]);
+                    const bool gt = sc > best;
+                    second = fmaxf(second, fminf(best, sc));
+                    idx = gt ? c0 + j : idx;
+                    best = fmaxf(best, sc);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                mbar_arrive(bar(D_EMPTY + e));
+                mbar_arrive(bar(THR_EMPTY + e));
+            }
+            FAST_TRACE(7)
+            const bool valid = rho < rows_valid;
+            const bool decided = (best - second) > thr; // false for NaN, for thr = +inf, for exact ties
+            const bool flagged = valid && !decided;
+            const unsigned word = __ballot_sync(0xffffffffu, flagged);
+            if (lane == 0) p.flag_words[tile * 4 + q] = word;
+            if (p.dbg_scores && valid) {
+                p.dbg_scores[2 * (row0 + rho)] = best;
+                p.dbg_scores[2 * (row0 + rho) + 1] = second;
+            }
+            if (p.labels != nullptr && valid) p.labels[row0 + rho] = idx;
+            if (ACCUM) {
+                // one bulk reduction per decided row: the TMA engine adds the FP64 row, still in its
+                // stage, to sums[label] of this CTA's accumulator; the additions happen in L2
+                if (valid && !flagged) {
+                    bulk_reduce_add_f64(slot + (size_t)idx * p.d,
+                                        (unsigned)__cvta_generic_to_shared(stage0 + (size_t)s * p.stage_bytes + row_off),
+                                        (unsigned)p.d * 8u);
+                    atomicAdd(&counts_s[idx], 1);
+                }
+                bulk_commit_group();
+                FAST_TRACE(8)
+                bulk_wait_group_read(); // the rows have been read: the stage may be refilled
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(X_EMPTY + s));
+            }
+            FAST_TRACE(9)
+        }
+        if (ACCUM) bulk_wait_group_all();
+    } else if (warp == kFastLoaderWarp) {
+        // =========================== loader ===========================
+        if (lane == 0) {
+            // the centroid terms, once: (KB + 1) + KB boxes of Nacc rows x 32 columns
+            const unsigned bytes_b = (unsigned)((2 * p.KB + 1) * bblk);
+            mbar_arrive_expect_tx(bar(B_FULL), bytes_b);
+            for (int b = 0; b <= p.KB; b++)
+                tma_load_2d((unsigned)__cvta_generic_to_shared(B1 + (size_t)b * bblk), &map1, 32 * b, 0, bar(B_FULL));
+            for (int b = 0; b < p.KB; b++)
+                tma_load_2d((unsigned)__cvta_generic_to_shared(B2 + (size_t)b * bblk), &map2, 32 * b, 0, bar(B_FULL));
+            const unsigned row_bytes = (unsigned)p.d * 8u;
+            for (int64_t i = 0; i < my_tiles; i++) {
+                const int s = (int)(i % p.NS);
+                const int64_t row0 = (blockIdx.x + i * gridDim.x) * kFastRows;
+                const int rows_valid = (int)min((int64_t)kFastRows, p.n - row0);
+                FAST_TRACE(10)
+                mbar_wait(bar(X_EMPTY + s), (unsigned)(((i / p.NS) & 1) ^ 1));
+                FAST_TRACE(11)
+                mbar_arrive_expect_tx(bar(FULL_X + s), row_bytes * (unsigned)rows_valid);
+                unsigned char *dst = stage0 + (size_t)s * p.stage_bytes;
+                for (int g = 0; g * kFastGroupRows < rows_valid; g++) {
+                    const int nr = min(kFastGroupRows, rows_valid - g * kFastGroupRows);
+                    bulk_copy_g2s((unsigned)__cvta_generic_to_shared(dst + (size_t)g * p.group_bytes),
+                                  p.x + (row0 + (int64_t)g * kFastGroupRows) * p.d, row_bytes * (unsigned)nr, bar(FULL_X + s));
+                }
+            }
+        }
+    } else {
+        // =========================== MMA issuer ===========================
+        if (lane == 0) {
+            const unsigned idesc = umma_idesc_tf32(p.Nacc);
+            const unsigned b1 = (unsigned)__cvta_generic_to_shared(B1), b2 = (unsigned)__cvta_generic_to_shared(B2);
+            const int slabs = p.Kd >> 3;
+            mbar_wait(bar(B_FULL), 0);
+            for (int64_t i = 0; i < my_tiles; i++) {
+                const int a = (int)(i % p.nA), e = (int)(i & 1);
+                FAST_TRACE(12)
+                mbar_wait(bar(A_FULL + a), (unsigned)((i / p.nA) & 1));
+                FAST_TRACE(13)
+                mbar_wait(bar(D_EMPTY + e), (unsigned)(((i >> 1) & 1) ^ 1));
+                tc_fence_after();
+                FAST_TRACE(14)
+                const unsigned a_hi = tmem + kFastACol + (unsigned)a * a_cols, a_lo = a_hi + (unsigned)p.Kd;
+                const unsigned dt = tmem + d_col0 + (unsigned)e * (unsigned)p.Nacc;
+                unsigned acc = 0;
+                // small terms first: xh.c2, then xl.c1
+                for (int sl = 0; sl < slabs; sl++) {
+                    tc_mma_tf32_ts(dt, a_hi + 8u * sl, umma_desc_sw128(b2 + (unsigned)(sl >> 2) * bblk + (unsigned)(sl & 3) * 32u), idesc, acc);
+                    acc = 1;
+                }
+                for (int sl = 0; sl < slabs; sl++)
+                    tc_mma_tf32_ts(dt, a_lo + 8u * sl, umma_desc_sw128(b1 + (unsigned)(sl >> 2) * bblk + (unsigned)(sl & 3) * 32u), idesc, 1);
+                // the main term xh.c1 and the constant column times (h1, h2, h3)
+                for (int sl = 0; sl < slabs; sl++)
+                    tc_mma_tf32_ts(dt, a_hi + 8u * sl, umma_desc_sw128(b1 + (unsigned)(sl >> 2) * bblk + (unsigned)(sl & 3) * 32u), idesc, 1);
+                tc_mma_tf32_ts(dt, tmem + kFastOnesCol, umma_desc_sw128(b1 + (unsigned)p.KB * bblk), idesc, 1);
+                tc_commit(bar(A_EMPTY + a)); // the A buffer may be overwritten once these MMAs have read it
+                tc_commit(bar(D_FULL + e));  // and the scores are complete
+                FAST_TRACE(15)
+            }
+        }
+    }
+
+    // ---- teardown: counts of this CTA, TMEM released by the warp that allocated it
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (ACCUM) {
+        double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d);
+        for (int i = threadIdx.x; i < p.k; i += blockDim.x)
+            if (counts_s[i]) atomicAdd(&slot[(size_t)p.k * p.d + i], (double)counts_s[i]);
+    }
+    if (warp == kFastMmaWarp) tmem_dealloc(tmem, kFastTmemCols);
+}
+
+// ------------------------------------------------------------------------------------------
+// The rows the tensor-core pass did not decide (bit l of word 4 t + q: TMEM lane 32 q + l of tile t),
+// replayed with the reference arithmetic: one warp per flagged row.
+template <bool ACCUM>
+__global__ void __launch_bounds__(256) recheck_rows_kernel(const double *x, int64_t n, int d, const uint32_t *flag_words,
+                                                            int64_t n_words, const double *c, const double *cn, int k,
+                                                            int fma_mode, int32_t *labels, double *slot,
+                                                            unsigned long long *recheck_count) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    unsigned long long mine = 0;
+    for (int64_t w = (((int64_t)blockIdx.x * blockDim.x) + threadIdx.x) >> 5; w < n_words; w += warps) {
+        unsigned mask = flag_words[w];
+        const int64_t tile = w >> 2;
+        const int q = (int)(w & 3);
+        while (mask) { // warp-uniform
+            const int l = __ffs(mask) - 1;
+            mask &= mask - 1;
+            const int64_t row = tile * kFastRows + fast_row_of_lane(32 * q + l);
+            if (row >= n) continue;
+            const double *xr = x + row * d;
+            const int lab = exact_find_closest(xr, c, cn, k, d, fma_mode);
+            mine++;
+            if (labels != nullptr && lane == 0) labels[row] = lab;
+            if (ACCUM) {
+                for (int col = lane; col < d; col += 32) atomicAdd(&slot[(size_t)lab * d + col], xr[col]);
+                if (lane == 0) atomicAdd(&slot[(size_t)k * d + lab], 1.0);
+            }
+        }
+    }
+    if (lane == 0 && mine && recheck_count) atomicAdd(recheck_count, mine);
+}
+
+} // namespace fmlk

@@ -17,6 +17,7 @@ ERR_INVALID_ARG, ERR_STATE, ERR_DIM, ERR_CUDA, ERR_NCCL, ERR_NOMEM = -1, -2, -3,
 FLAG_PROFILE = 0x1
 FLAG_BLAS_FMA = 0x2
 FLAG_DETERMINISTIC = 0x4
+FLAG_FAST_TF32 = 0x8
 # record formats of the reference's serializers (include/fmlk.h)
 FMT_DENSE_VECTOR, FMT_VECTOR, FMT_VECTOR_WITH_NORM = 0, 1, 2
 NCCL_ID_BYTES = 128
@@ -74,6 +75,8 @@ SIGNATURES = {
     "fmlk_reset_profile": (_i32, [_vp]),
     "fmlk_measure_fp64_peaks": (_i32, [_i32, _f64, C.POINTER(_f64), C.POINTER(_f64)]),
     "fmlk_describe_launch": (_i32, [_vp, _i32, _i32, _i32, C.c_char_p, _i32]),
+    "fmlk_fast_debug": (_i32, [_vp, _vp, _vp]),
+    "fmlk_fast_launches": (_i64, [_vp]),
 }
 
 _lib = None
@@ -347,6 +350,12 @@ class Context:
 
     def reset_profile(self):
         self._ck(lib().fmlk_reset_profile(self._h))
+
+    def fast_debug(self, best_second_ptr, all_scores_ptr=None):
+        self._ck(lib().fmlk_fast_debug(self._h, best_second_ptr, all_scores_ptr))
+
+    def fast_launches(self):
+        return int(lib().fmlk_fast_launches(self._h))
 
     def describe_launch(self, k, d, accumulate=True):
         buf = C.create_string_buffer(512)

@@ -47,6 +47,13 @@ typedef enum fmlk_status {
                                        default: additions performed in L2 (bulk reductions), last bits depend on arrival order.  Labels,
                                        counts and weights are bit-exact either way. */
 
+#define FMLK_FLAG_FAST_TF32 0x8 /* north_star's fast mode: the contraction x.c - |c|^2/2 runs on the tcgen05 tensor cores
+                                   with every FP64 operand split into TF32 terms (three passes, FP32 accumulators in
+                                   TMEM); rows whose two best scores are closer than the proven error bound of that
+                                   arithmetic are replayed exactly in FP64 (EuclideanDistanceMeasure.java:53-73), so
+                                   labels, counts and weights stay bit-exact; sums are FP64 as in the default mode.
+                                   Shapes the tcgen05 kernel does not take run on the FP64 kernels unchanged. */
+
 #define FMLK_NCCL_ID_BYTES 128
 
 /* Library / build identification ("fmlk <version> sm_100a"). */
@@ -241,6 +248,14 @@ int32_t fmlk_reset_profile(fmlk_ctx *ctx);
 /* Sustained FP64 tensor-core (DMMA m8n8k4) and FP64 FMA throughput of `device` in TFLOP/s,
  * from a register-resident microbenchmark run for about `ms` milliseconds each. */
 int32_t fmlk_measure_fp64_peaks(int32_t device, double ms, double *dmma_tflops, double *dfma_tflops);
+
+/* Fast mode only (tests): from now on the tcgen05 kernel also writes, for every row it labels, the two
+ * best scores x.c - |c|^2/2 as it computed them (best_second_dev: n x 2 floats) and, if all_scores_dev
+ * is not NULL, every score (n x Nacc floats, Nacc = k rounded up to 16).  NULL, NULL switches it off. */
+int32_t fmlk_fast_debug(fmlk_ctx *ctx, float *best_second_dev, float *all_scores_dev);
+
+/* Launches that went through the tcgen05 kernel since the context was created. */
+int64_t fmlk_fast_launches(const fmlk_ctx *ctx);
 
 /* Launch geometry the assign kernel would use for (k, d): for DESIGN.md / bench reporting. */
 int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumulate,

@@ -1,5 +1,5 @@
 """Small driver for profiling: a few training rounds of one workload shape on cuda:0.
-usage: python scripts/run_assign.py N D K ROUNDS [predict]"""
+usage: python scripts/run_assign.py N D K ROUNDS [predict]      (FMLK_FAST=1: tcgen05 fast mode, FMLK_DET=1: deterministic sums)"""
 import os
 import sys
 
@@ -12,7 +12,8 @@ predict = len(sys.argv) > 5 and sys.argv[5] == "predict"
 x = torch.empty((n, d), dtype=torch.float64, device="cuda:0")
 native.generate_dense_dev(0, torch.cuda.current_stream().cuda_stream, 2, 0, 1, n, d, x.data_ptr())
 torch.cuda.synchronize()
-ctx = native.Context(0, flags=native.FLAG_PROFILE | (native.FLAG_DETERMINISTIC if os.environ.get("FMLK_DET") == "1" else 0))
+ctx = native.Context(0, flags=native.FLAG_PROFILE | (native.FLAG_DETERMINISTIC if os.environ.get("FMLK_DET") == "1" else 0)
+                     | (native.FLAG_FAST_TF32 if os.environ.get("FMLK_FAST") == "1" else 0))
 ctx.adopt_points_dev(x.data_ptr(), n, d, keep=x)
 ctx.set_centroids(x[:k].cpu().numpy())
 if predict:
