@@ -161,7 +161,8 @@ struct fmlk_ctx {
     // fast mode (FMLK_FLAG_FAST_TF32): the centroids as TF32 terms + their tensor maps, the bitmap of
     // rows left to the exact replay
     float *bt1 = nullptr, *bt2 = nullptr;
-    size_t bt_cap = 0; // floats in bt1 (bt2 is never larger)
+    double *ct = nullptr; // the centroids transposed (d x k_rows) for the exact replay
+    size_t bt_cap = 0; // floats in bt1 (bt2 and ct are never larger)
     alignas(64) CUtensorMap map1, map2;
     int map_k_rows = 0, map_KB = 0, map_nacc = 0;
     uint32_t *flag_words = nullptr;
@@ -519,8 +520,8 @@ EncodeTiledFn encode_tiled() {
 }
 
 // Does the tcgen05 kernel take (k, d)?  First version: centroid terms resident in shared memory
-// (k <= 256 after rounding up to 16), rows of at most 128 columns, two row stages.
-bool fast_shape(const fmlk_ctx *ctx, int k, int d, FastPlan *out) {
+// (k <= 240 after rounding up to 16), rows of at most 128 columns, at least two 64-row half stages.
+bool fast_shape(const fmlk_ctx *ctx, int k, int d, bool accum, FastPlan *out) {
     if (!(ctx->flags & FMLK_FLAG_FAST_TF32)) return false;
     if (d < 2 || (d & 1) || d > 128) return false;
     FastPlan f{};
@@ -532,11 +533,13 @@ bool fast_shape(const fmlk_ctx *ctx, int k, int d, FastPlan *out) {
     f.nA = (kFastACol + 2 * 2 * f.Kd + 2 * f.Nacc <= kFastTmemCols) ? 2 : 1;
     if (kFastACol + f.nA * 2 * f.Kd + 2 * f.Nacc > kFastTmemCols) return false;
     f.group_bytes = kFastGroupRows * d * 8 + 16;
-    f.stage_bytes = kFastGroups * f.group_bytes;
-    const size_t fixed = (size_t)(2 * f.KB + 1) * f.Nacc * 128 + 2 * kFastRows * sizeof(float) + (size_t)f.Nacc * sizeof(int) +
-                         24 * 8 + 16 + 1024 /* alignment slack */;
-    if (fixed + 2 * (size_t)f.stage_bytes > ctx->smem_optin) return false;
-    f.NS = (int)std::min<size_t>(4, (ctx->smem_optin - fixed) / f.stage_bytes);
+    f.stage_bytes = kFastHalfGroups * f.group_bytes;
+    const size_t fixed = (size_t)(2 * f.KB + 1) * f.Nacc * 128 + 8 * kFastRows * sizeof(float) + (size_t)f.Nacc * sizeof(int) +
+                         40 * 8 + 16 + 1024 /* alignment slack */;
+    // training keeps a half stage until its rows have been added: a whole tile in flight beside the one in work
+    const int min_stages = accum ? 4 : 2;
+    if (fixed + (size_t)min_stages * f.stage_bytes > ctx->smem_optin) return false;
+    f.NS = (int)std::min<size_t>(kFastMaxStages, (ctx->smem_optin - fixed) / f.stage_bytes);
     f.smem = fixed + (size_t)f.NS * f.stage_bytes;
     *out = f;
     return true;
@@ -549,10 +552,13 @@ int ensure_fast(fmlk_ctx *ctx, const FastPlan &f) {
     if (need > ctx->bt_cap) {
         dev_free(ctx->bt1);
         dev_free(ctx->bt2);
+        dev_free(ctx->ct);
         ctx->bt1 = ctx->bt2 = nullptr;
+        ctx->ct = nullptr;
         ctx->bt_cap = 0;
         if ((rc = dev_alloc(ctx, &ctx->bt1, need))) return rc;
         if ((rc = dev_alloc(ctx, &ctx->bt2, need))) return rc;
+        if ((rc = dev_alloc(ctx, &ctx->ct, need))) return rc;
         ctx->bt_cap = need;
         fresh = true;
     }
@@ -590,9 +596,12 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
         dev_free(ctx->flag_words);
         ctx->flag_words = nullptr;
         ctx->flag_cap = 0;
-        if ((rc = dev_alloc(ctx, &ctx->flag_words, words))) return rc;
+        // the bitmap, the list of its non-zero words and, after them, the list's length
+        if ((rc = dev_alloc(ctx, &ctx->flag_words, 2 * words + 1))) return rc;
         ctx->flag_cap = words;
     }
+    uint32_t *flag_list = ctx->flag_words + ctx->flag_cap, *flag_count = flag_list + ctx->flag_cap;
+    CK(ctx, cudaMemsetAsync(flag_count, 0, sizeof(uint32_t), ctx->stream));
     FastParams p{};
     p.x = x;
     p.n = n;
@@ -605,7 +614,7 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
     p.NS = f.NS;
     p.stage_bytes = f.stage_bytes;
     p.group_bytes = f.group_bytes;
-    p.coef = (float)(2.5 * (f.Kd / 8 + 6) * 0x1.0p-22);
+    p.coef = (float)(2.5 * (f.Kd / 16.0 + 5.5) * 0x1.0p-22);
     p.cmax2 = ctx->cmax2;
     p.c = ctx->centroids;
     p.cn = ctx->cn;
@@ -613,6 +622,8 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
     p.partials = accum ? ctx->partials : nullptr;
     p.n_partials = n_partials;
     p.flag_words = ctx->flag_words;
+    p.flag_list = flag_list;
+    p.flag_count = flag_count;
     p.dbg_scores = ctx->dbg_scores;
     p.dbg_full = ctx->dbg_full;
     p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
@@ -640,15 +651,22 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
         cudaFree(p.trace);
     }
 #endif
-    const int rgrid = (int)std::min<int64_t>((int64_t)ctx->sm_count * 8, ((int64_t)words + 7) / 8);
-    if (accum)
-        recheck_rows_kernel<true><<<rgrid, 256, 0, ctx->stream>>>(x, n, ctx->md, ctx->flag_words, (int64_t)words, ctx->centroids,
-                                                                   ctx->cn, ctx->k, p.fma_mode, labels, ctx->partials,
-                                                                   ctx->recheck);
-    else
-        recheck_rows_kernel<false><<<rgrid, 256, 0, ctx->stream>>>(x, n, ctx->md, ctx->flag_words, (int64_t)words,
-                                                                    ctx->centroids, ctx->cn, ctx->k, p.fma_mode, labels, nullptr,
-                                                                    ctx->recheck);
+    // the list's length is only known on the device: a fixed grid, as many blocks per SM as fit
+    const size_t row_smem = (size_t)8 * ctx->md * sizeof(double), ct_smem = (size_t)ctx->md * f.k_rows * sizeof(double);
+    const bool ct_fits = row_smem + ct_smem <= 100 * 1024;
+    const size_t rsmem = row_smem + (ct_fits ? ct_smem : 0);
+    const int per_sm = ct_fits ? (int)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / rsmem)) : 8;
+    const int rgrid = ctx->sm_count * per_sm;
+#define FMLK_RECHECK(A, S)                                                                                          \
+    recheck_rows_kernel<A, S><<<rgrid, 256, rsmem, ctx->stream>>>(x, n, ctx->md, ctx->flag_words, flag_list, flag_count, \
+                                                                  ctx->ct, f.k_rows, ctx->cn, ctx->k, p.fma_mode, labels,    \
+                                                                  accum ? ctx->partials : nullptr, accum ? n_partials : 1,   \
+                                                                  ctx->recheck)
+    if (accum && ct_fits) FMLK_RECHECK(true, true);
+    else if (accum) FMLK_RECHECK(true, false);
+    else if (ct_fits) FMLK_RECHECK(false, true);
+    else FMLK_RECHECK(false, false);
+#undef FMLK_RECHECK
     CK(ctx, cudaGetLastError());
     ctx->total_launches += 2;
     ctx->fast_launches++;
@@ -663,12 +681,12 @@ int prep_centroids(fmlk_ctx *ctx) {
     ctx->total_launches++;
     CK(ctx, cudaGetLastError());
     FastPlan f;
-    if (fast_shape(ctx, ctx->k, ctx->md, &f)) {
+    if (fast_shape(ctx, ctx->k, ctx->md, false, &f)) {
         int rc = ensure_fast(ctx, f);
         if (rc) return rc;
         const int total = f.k_rows * (32 * f.KB + 32);
-        prep_fast_kernel<<<(total + 255) / 256, 256, 0, ctx->stream>>>(ctx->c_mma, ctx->h, ctx->k, ctx->md, f.k_rows, f.KB,
-                                                                       ctx->bt1, ctx->bt2);
+        prep_fast_kernel<<<(total + 255) / 256, 256, 0, ctx->stream>>>(ctx->centroids, ctx->c_mma, ctx->h, ctx->k, ctx->md,
+                                                                       f.k_rows, f.KB, ctx->bt1, ctx->bt2, ctx->ct);
         ctx->total_launches++;
         CK(ctx, cudaGetLastError());
     }
@@ -680,7 +698,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     if (n <= 0) return FMLK_OK;
     {
         FastPlan f;
-        if (fast_rows_ok(x, n) && fast_shape(ctx, ctx->k, ctx->md, &f)) {
+        if (fast_rows_ok(x, n) && fast_shape(ctx, ctx->k, ctx->md, accum, &f)) {
             const bool prof = (ctx->flags & FMLK_FLAG_PROFILE) != 0;
             cudaEvent_t e0 = prof ? next_event(ctx) : nullptr, e1 = prof ? next_event(ctx) : nullptr;
             if (e0 && e1) cudaEventRecord(e0, ctx->stream);
@@ -961,6 +979,10 @@ int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *
             e = cudaFuncSetAttribute(assign_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(assign_fast_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(recheck_rows_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 101 * 1024);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(recheck_rows_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 101 * 1024);
     }
     if (e != cudaSuccess) {
         std::string m = std::string("device set-up: ") + cudaGetErrorString(e);
@@ -1019,6 +1041,7 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     dev_free(ctx->ingest_bad);
     dev_free(ctx->bt1);
     dev_free(ctx->bt2);
+    dev_free(ctx->ct);
     dev_free(ctx->flag_words);
     dev_free(ctx->ar_probe);
     dev_free(ctx->ar_buf);
@@ -1703,15 +1726,14 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
     int rc = choose_cfg(ctx, k, d, accumulate != 0, &c);
     if (rc) return rc;
     FastPlan f;
-    if (fast_shape(ctx, k, d, &f)) {
+    if (fast_shape(ctx, k, d, accumulate != 0, &f)) {
         cudaFuncAttributes fa{};
         if (accumulate) cudaFuncGetAttributes(&fa, assign_fast_kernel<true>);
         else cudaFuncGetAttributes(&fa, assign_fast_kernel<false>);
         snprintf(out, (size_t)out_len,
-                 "fast=1 regs=%d local=%zu grid=%d block=%d smem=%zu Kd=%d KB=%d Nacc=%d tmem_a_buffers=%d row_stages=%d "
+                 "fast=1 regs=%d local=%zu grid=%d block=%d smem=%zu Kd=%d KB=%d Nacc=%d tmem_a_buffers=%d half_stages=%d "
                  "n_partials=%d wide=0 (rows below 4096 or unaligned rows take the FP64 kernel)",
-                 fa.numRegs, fa.localSizeBytes, ctx->sm_count, kFastThreads, f.smem, f.Kd, f.KB, f.Nacc, f.nA, f.NS,
-                 c.n_partials);
+                 fa.numRegs, fa.localSizeBytes, ctx->sm_count, kFastThreads, f.smem, f.Kd, f.KB, f.Nacc, f.nA, f.NS, c.n_partials);
         return FMLK_OK;
     }
     cudaFuncAttributes fa{};

@@ -15,10 +15,11 @@
 // Error of the score (S' = |x||c| + |c|^2/2 <= |x|^2 + |c|max^2):
 //   - dropped products xl.c2, x.e_c, e_x.c:            <= 3.3 * 2^-22 S'
 //   - FP32 accumulation in the tensor core: each tcgen05.mma step (K = 8) adds eight exact products
-//     to the accumulator with at most 2^-22 relative error of the largest magnitude involved (two
-//     FP32 ulps: alignment truncation + the final rounding).  The two small passes carry partial
-//     sums <= 2^-10 S'; only the Kd/8 + 1 steps of the last pass see S' itself.
-//   => |v_fast - v_exact| <= E = (Kd/8 + 6) * 2^-22 * S'
+//     to the accumulator and rounds or truncates once to FP32: at most one ulp, 2^-23 relative to the
+//     largest magnitude involved.  The two small passes carry partial sums <= 2^-10 S'; only the
+//     Kd/8 + 1 steps of the last pass see S' itself:   <= (Kd/16 + 0.5 + Kd * 2^-13) * 2^-22 S'
+//   - FP32 work of the epilogue (row norm, subtraction): <= 2^-22 S'
+//   => |v_fast - v_exact| <= E = (Kd/16 + 5.5) * 2^-22 * S'
 // A row is decided by the tensor-core pass when best - second > 2.5 E (2E for the two scores, the
 // rest covers the FP32 subtraction, the FP32 row norm and the FP64 reference's own rounding, all
 // orders of magnitude smaller).  Every other row -- near ties, duplicates, NaN/Inf, magnitudes outside
@@ -28,15 +29,21 @@
 // tests/test_gpu_fast.py::test_score_error_within_model against float64 scores.
 //
 // Data flow of one CTA (persistent, one per SM, 128-row tiles):
-//   loader warp      cp.async.bulk: 16 copies of 8 rows each into a stage (16-byte pad between the
-//                    groups: conflict-free 128-bit reads for one thread per row)
+//   loader warp      cp.async.bulk: a tile arrives as two 64-row half stages, each 8 copies of 8 rows
+//                    (16-byte pad between the groups: conflict-free 128-bit reads, one thread per row)
 //   converter warps  one thread per row: FP64 -> (xh, xl) TF32, tcgen05.st into TMEM (the A operand
 //                    never touches shared memory), FP32 row norm -> decision threshold
 //   MMA warp         one thread: tcgen05.mma A(TMEM) x B(shared, 128-byte swizzle, staged once by
 //                    tensor-map TMA loads), tcgen05.commit -> mbarriers
-//   epilogue warps   one thread per row: tcgen05.ld, running (best, second, index), margin test,
-//                    label; training: one cp.reduce.async.bulk add.f64 of the FP64 row (still in the
-//                    stage) into sums[label] of the CTA's accumulator in global memory
+//   epilogue warps   eight warps on every tile: one thread per row and column half runs tcgen05.ld and the
+//                    running (best, second, index); the halves meet in shared memory, then the margin
+//                    test and the label.  Training: sixteen lanes of each warp issue one
+//                    cp.reduce.async.bulk add.f64 per decided row -- the TMA engine adds the FP64 row,
+//                    still in its half stage, to sums[label] of the CTA's accumulator in global memory
+//                    (the additions happen in L2) -- and the half stage is refilled once they have been read
+// (Keeping the sums in shared memory and re-reading the decided rows from L2 was built and measured: rows
+// that arrived by bulk copy are not in L2 afterwards -- 6 % hit rate, DRAM traffic x 1.9, with or without an
+// evict-last hint or an explicit L2 prefetch -- so the rows have to be added while they are in shared memory.)
 #pragma once
 #include "fmlk_kernels.cuh"
 #include <cuda.h>
@@ -44,14 +51,18 @@
 namespace fmlk {
 
 constexpr int kFastRows = 128;       // rows per tile = TMEM lanes = MMA M
+constexpr int kFastHalfRows = 64;    // rows per half stage
 constexpr int kFastGroupRows = 8;    // rows per bulk copy
-constexpr int kFastGroups = kFastRows / kFastGroupRows;
-constexpr int kFastConvWarps = 4;    // warps 0..3   (TMEM lane quarter = warp % 4)
-constexpr int kFastEpiSets = 2;      // warps 4..11  two sets of four, alternating tiles
-constexpr int kFastLoaderWarp = 4 + 4 * kFastEpiSets;
+constexpr int kFastHalfGroups = kFastHalfRows / kFastGroupRows;
+constexpr int kFastConvSets = 2;     // warps 0..7   two sets of four (TMEM lane quarter = warp % 4), each half of the columns
+constexpr int kFastConvWarps = 4 * kFastConvSets;
+constexpr int kFastEpiWarp0 = kFastConvWarps; // warps 8..15  two sets of four, each half of the score columns
+constexpr int kFastEpiWarps = 8;
+constexpr int kFastLoaderWarp = kFastEpiWarp0 + kFastEpiWarps;
 constexpr int kFastMmaWarp = kFastLoaderWarp + 1;
 constexpr int kFastWarps = kFastMmaWarp + 1;
 constexpr int kFastThreads = kFastWarps * 32;
+constexpr int kFastMaxStages = 8;
 constexpr int kFastTmemCols = 512;
 constexpr int kFastOnesCol = 0;      // 8 columns [1,1,1,0,0,0,0,0] in every lane
 constexpr int kFastACol = 16;        // first A buffer
@@ -65,10 +76,10 @@ struct FastParams {
     int32_t k;
     int32_t Nacc;     // accumulator columns = centroids per pass (multiple of 16, <= 256)
     int32_t nA;       // A buffers in TMEM (1 or 2)
-    int32_t NS;       // row stages in shared memory
-    int32_t stage_bytes;
+    int32_t NS;       // 64-row half stages in shared memory (2 .. 8)
+    int32_t stage_bytes; // of one half stage
     int32_t group_bytes; // 8 * d * 8 + 16
-    float coef;       // 2.5 * (Kd/8 + 6) * 2^-22
+    float coef;       // 2.5 * (Kd/16 + 5.5) * 2^-22
     const double *cmax2; // [0] max finite |c|^2, [1] ceil(log2) of it
     const double *c;     // k x d centroids as given (exact replay)
     const double *cn;
@@ -76,6 +87,8 @@ struct FastParams {
     double *partials;    // or null (predict)
     int32_t n_partials;
     uint32_t *flag_words; // [ceil(n / 128) * 4]
+    uint32_t *flag_list;  // indices of the non-zero words, in arrival order ...
+    uint32_t *flag_count; // ... and how many (zeroed before the launch)
     float *dbg_scores;    // or null: [n][2] = best, second (tests)
     float *dbg_full;      // or null: [n][Nacc] every score (tests, small n)
     int32_t fma_mode;
@@ -87,7 +100,7 @@ struct FastParams {
 #ifdef FMLK_TRACE
 #define FAST_TRACE(EV)                                                                   \
     if (p.trace && blockIdx.x == 0 && lane == 0 && trace_n < kTraceEvents)               \
-        p.trace[(size_t)warp * kTraceEvents + trace_n++] = ((unsigned long long)clock64() << 4) | (EV);
+        p.trace[(size_t)warp * kTraceEvents + trace_n++] = ((unsigned long long)clock64() << 5) | (EV);
 #else
 #define FAST_TRACE(EV)
 #endif
@@ -142,8 +155,28 @@ __device__ __forceinline__ void tmem_ld16(unsigned taddr, unsigned (&v)[16]) {
 }
 __device__ __forceinline__ void tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
 
+// Waiting warps share their scheduler's issue slots with the working ones: after a few polls, back off.
+__device__ __forceinline__ void mbar_wait_relaxed(unsigned bar, unsigned parity) {
+    unsigned spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > 4u) __nanosleep(40);
+        if (spins > (1u << 26)) __trap(); // a lost arrival must not hang the device
+    }
+}
 __device__ __forceinline__ void mbar_arrive(unsigned bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"(bar) : "memory");
+}
+// one lane of a converged warp (the operands of the instruction it guards stay in uniform registers)
+__device__ __forceinline__ bool elect_one() {
+    unsigned pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred P;\n"
+        "elect.sync _|P, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, P;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
 }
 // tensor-map TMA load of a 2-D box (SASS: UTMALDG); the map covers this GPU's memory only
 __device__ __forceinline__ void tma_load_2d(unsigned dst_smem, const CUtensorMap *map, int c0, int c1, unsigned bar) {
@@ -171,9 +204,12 @@ __host__ __device__ __forceinline__ unsigned umma_idesc_tf32(int n) {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(n >> 3) << 17) | ((unsigned)(kFastRows >> 4) << 24);
 }
 
-// TMEM lane L of a tile holds tile row fast_row_of_lane(L): eight consecutive lanes read rows of
-// eight different 8-row copy groups, whose 16-byte pads put them in different banks.
-__host__ __device__ __forceinline__ int fast_row_of_lane(int L) { return (L & 15) * kFastGroupRows + (L >> 4); }
+// TMEM lane L of a tile holds tile row fast_row_of_lane(L): lanes 0..63 the first half stage, 64..127
+// the second; eight consecutive lanes read rows of eight different 8-row copy groups, whose 16-byte
+// pads put them in different banks.
+__host__ __device__ __forceinline__ int fast_row_of_lane(int L) {
+    return (L & 64) + (L & 7) * kFastGroupRows + ((L >> 3) & 7);
+}
 
 __device__ __forceinline__ unsigned tf32_rn_bits(float v) { return (__float_as_uint(v) + 0x1000u) & 0xffffe000u; }
 
@@ -182,8 +218,9 @@ __device__ __forceinline__ unsigned tf32_rn_bits(float v) { return (__float_as_u
 //   bt1[j][0 .. 32 KB)       = c1 = tf32(c)          bt1[j][32 KB + 0..2] = h1, h2, h3 (three-term -|c|^2/2)
 //   bt2[j][0 .. 32 KB)       = c2 = tf32(c - c1)
 // rows j >= k and dead centroids: zeros with h1 = -inf (they score -inf and never win).
-__global__ void prep_fast_kernel(const double *c_mma, const double *h, int k, int d, int k_rows, int KB, float *bt1,
-                                 float *bt2) {
+// ct[i][j] = c[j][i] (the centroids as given, transposed, rows of k_rows doubles): the exact replay reads it.
+__global__ void prep_fast_kernel(const double *c, const double *c_mma, const double *h, int k, int d, int k_rows, int KB,
+                                 float *bt1, float *bt2, double *ct) {
     const int ld1 = 32 * KB + 32, ld2 = 32 * KB;
     const int total = k_rows * ld1;
     for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
@@ -208,13 +245,19 @@ __global__ void prep_fast_kernel(const double *c_mma, const double *h, int k, in
         }
         bt1[idx] = v1;
         if (i < ld2) bt2[(size_t)j * ld2 + i] = v2;
+        if (i < d) ct[(size_t)i * k_rows + j] = j < k ? c[(size_t)j * d + i] : 0.0;
     }
 }
 
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void named_barrier(int id, int nthreads) {
+    asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
+}
+
 template <bool ACCUM>
 __global__ void __launch_bounds__(kFastThreads, 1)
     assign_fast_kernel(const FastParams p, const __grid_constant__ CUtensorMap map1, const __grid_constant__ CUtensorMap map2) {
+    constexpr int kLoaderWarp = kFastLoaderWarp, kMmaWarp = kFastMmaWarp;
     extern __shared__ __align__(1024) unsigned char fast_smem[];
     // the swizzled B tiles want a 1024-byte aligned base (the launch reserves the slack)
     unsigned char *smem_raw = fast_smem + ((1024u - ((unsigned)__cvta_generic_to_shared(fast_smem) & 1023u)) & 1023u);
@@ -224,28 +267,34 @@ __global__ void __launch_bounds__(kFastThreads, 1)
 #endif
     // carve-up (the B tiles first: the swizzle wants 1024-byte alignment)
     const int bblk = p.Nacc * 128; // bytes of one 32-column block of B
-    unsigned char *B1 = smem_raw;                      // (KB + 1) blocks of bt1
+    unsigned char *B1 = smem_raw;                       // (KB + 1) blocks of bt1
     unsigned char *B2 = B1 + (size_t)(p.KB + 1) * bblk; // KB blocks of bt2
-    unsigned char *stage0 = B2 + (size_t)p.KB * bblk;
-    float *thr_s = reinterpret_cast<float *>(stage0 + (size_t)p.NS * p.stage_bytes); // [2][128]
-    int *counts_s = reinterpret_cast<int *>(thr_s + 2 * kFastRows);                  // [Nacc]
+    unsigned char *stage0 = B2 + (size_t)p.KB * bblk;   // NS half stages
+    float *nsq_s = reinterpret_cast<float *>(stage0 + (size_t)p.NS * p.stage_bytes); // [2 tiles][2 column halves][128]
+    float *mrg_b = nsq_s + 4 * kFastRows;                                             // [128] second column half: best
+    float *mrg_s = mrg_b + kFastRows;                                                 // [128]                     second
+    int *mrg_i = reinterpret_cast<int *>(mrg_s + kFastRows);                          // [128]                     index
+    int *lab_s = mrg_i + kFastRows;                                                   // [128] label by TMEM lane, -1: not decided
+    int *counts_s = lab_s + kFastRows;                                                // [Nacc]
     unsigned long long *bars = reinterpret_cast<unsigned long long *>(counts_s + p.Nacc);
-    unsigned *tmem_slot = reinterpret_cast<unsigned *>(bars + 24);
+    unsigned *tmem_slot = reinterpret_cast<unsigned *>(bars + 40);
     auto bar = [&](int i) { return (unsigned)__cvta_generic_to_shared(&bars[i]); };
     // barrier indices
-    const int FULL_X = 0, X_EMPTY = 4, A_FULL = 8, A_EMPTY = 10, D_FULL = 12, D_EMPTY = 14, THR_FULL = 16, THR_EMPTY = 18,
-              B_FULL = 20;
+    const int FULL_X = 0, X_EMPTY = 8, A_FULL = 16, A_EMPTY = 18, D_FULL = 20, D_EMPTY = 22, THR_FULL = 24, THR_EMPTY = 26,
+              B_FULL = 32;
 
     if (threadIdx.x == 0) {
-        for (int s = 0; s < 4; s++) {
+        for (int s = 0; s < kFastMaxStages; s++) {
             mbar_init(bar(FULL_X + s), 1);
-            mbar_init(bar(X_EMPTY + s), 4); // the four warps that are the last readers of a stage
+            // the last readers of a half stage: training, the four epilogue warps whose rows it holds (they feed
+            // the bulk reductions from it); predict, the two converter warps of each column set
+            mbar_init(bar(X_EMPTY + s), 4);
         }
         for (int a = 0; a < 2; a++) {
             mbar_init(bar(A_FULL + a), kFastConvWarps);
             mbar_init(bar(A_EMPTY + a), 1);
             mbar_init(bar(D_FULL + a), 1);
-            mbar_init(bar(D_EMPTY + a), 4);
+            mbar_init(bar(D_EMPTY + a), kFastEpiWarps);
             mbar_init(bar(THR_FULL + a), kFastConvWarps);
             mbar_init(bar(THR_EMPTY + a), 4);
         }
@@ -253,7 +302,7 @@ __global__ void __launch_bounds__(kFastThreads, 1)
         mbar_fence_init();
     }
     for (int i = threadIdx.x; i < p.Nacc; i += blockDim.x) counts_s[i] = 0;
-    if (warp == kFastMmaWarp) tmem_alloc((unsigned)__cvta_generic_to_shared(tmem_slot), kFastTmemCols);
+    if (warp == kMmaWarp) tmem_alloc((unsigned)__cvta_generic_to_shared(tmem_slot), kFastTmemCols);
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -262,15 +311,17 @@ __global__ void __launch_bounds__(kFastThreads, 1)
     const unsigned d_col0 = kFastACol + (unsigned)p.nA * a_cols;
 
     const int64_t total_tiles = (p.n + kFastRows - 1) / kFastRows;
-    const int64_t my_tiles = total_tiles > blockIdx.x ? (total_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x : 0;
+    const int my_tiles = total_tiles > blockIdx.x ? (int)((total_tiles - blockIdx.x + gridDim.x - 1) / gridDim.x) : 0;
+    const int last_rows = (int)(p.n - (total_tiles - 1) * kFastRows); // rows of the very last tile
 
     if (warp < kFastConvWarps) {
         // =========================== converter: FP64 row -> TF32 terms in TMEM ===========================
-        const int q = warp;
+        // two sets of four warps; set `cs` converts the 16-column steps [step_lo, step_hi) of every tile
+        const int cs = warp >> 2, q = warp & 3;
         const int L = 32 * q + lane;
         const int rho = fast_row_of_lane(L);
         const unsigned lane_sel = (unsigned)(32 * q) << 16;
-        {
+        if (cs == 0) {
             // the constant column block [1, 1, 1, 0, ...] that multiplies (h1, h2, h3)
             unsigned ones[16];
 #pragma unroll
@@ -278,26 +329,25 @@ __global__ void __launch_bounds__(kFastThreads, 1)
             tmem_st8(tmem + lane_sel + kFastOnesCol, ones);
             tmem_wait_st();
         }
-        const int cexp = (int)p.cmax2[1];
-        const bool model_ok = cexp >= -120 && cexp <= 80;
-        const float cmax2f = model_ok ? __double2float_ru(p.cmax2[0]) : INFINITY;
-        const size_t row_off = (size_t)(rho >> 3) * p.group_bytes + (size_t)(rho & 7) * p.d * 8;
-        for (int64_t i = 0; i < my_tiles; i++) {
-            const int s = (int)(i % p.NS), a = (int)(i % p.nA), e = (int)(i & 1);
-            const int64_t row0 = (blockIdx.x + i * gridDim.x) * kFastRows;
-            const int rows_valid = (int)min((int64_t)kFastRows, p.n - row0);
+        const int steps = (p.Kd + 15) >> 4;
+        const int step_lo = cs == 0 ? 0 : (steps + 1) >> 1, step_hi = cs == 0 ? (steps + 1) >> 1 : steps;
+        const size_t row_off = (size_t)((rho & 63) >> 3) * p.group_bytes + (size_t)(rho & 7) * p.d * 8;
+        int hs = (q >> 1) % p.NS, a = 0; // this warp's rows are in half (q >> 1) of every tile
+        unsigned ph_x = ((q >> 1) / p.NS) & 1, ph_a = 1; // FULL_X: phase of this use; A_EMPTY: the phase before
+        for (int i = 0; i < my_tiles; i++) {
+            const int e = i & 1;
             FAST_TRACE(0)
-            mbar_wait(bar(FULL_X + s), (unsigned)((i / p.NS) & 1));
+            mbar_wait_relaxed(bar(FULL_X + hs), ph_x);
             FAST_TRACE(1)
-            mbar_wait(bar(A_EMPTY + a), (unsigned)(((i / p.nA) & 1) ^ 1));
+            mbar_wait_relaxed(bar(A_EMPTY + a), ph_a);
             tc_fence_after();
             FAST_TRACE(2)
-            const double2 *src = reinterpret_cast<const double2 *>(stage0 + (size_t)s * p.stage_bytes + row_off);
+            const double2 *src = reinterpret_cast<const double2 *>(stage0 + (size_t)hs * p.stage_bytes + row_off);
             const unsigned a_hi = tmem + lane_sel + kFastACol + (unsigned)a * a_cols;
             const unsigned a_lo = a_hi + (unsigned)p.Kd;
-            float nsq = 0.f;
-            unsigned mx = 0;
-            for (int c0 = 0; c0 < p.Kd; c0 += 16) {
+            float n0 = 0.f, n1 = 0.f, n2 = 0.f, n3 = 0.f;
+            for (int st = step_lo; st < step_hi; st++) {
+                const int c0 = st << 4;
                 unsigned hi[16], lo[16];
 #pragma unroll
                 for (int j = 0; j < 8; j++) {
@@ -305,9 +355,13 @@ __global__ void __launch_bounds__(kFastThreads, 1)
                     double2 v = make_double2(0.0, 0.0);
                     if (col < p.d) v = src[col >> 1];
                     const float f0 = __double2float_rn(v.x), f1 = __double2float_rn(v.y);
-                    mx = max(mx, max(__float_as_uint(f0) & 0x7fffffffu, __float_as_uint(f1) & 0x7fffffffu));
-                    nsq = fmaf(f0, f0, nsq);
-                    nsq = fmaf(f1, f1, nsq);
+                    if (j & 1) {
+                        n2 = fmaf(f0, f0, n2);
+                        n3 = fmaf(f1, f1, n3);
+                    } else {
+                        n0 = fmaf(f0, f0, n0);
+                        n1 = fmaf(f1, f1, n1);
+                    }
                     const unsigned h0 = tf32_rn_bits(f0), h1 = tf32_rn_bits(f1);
                     hi[2 * j] = h0;
                     hi[2 * j + 1] = h1;
@@ -324,157 +378,250 @@ __global__ void __launch_bounds__(kFastThreads, 1)
             }
             tmem_wait_st();
             FAST_TRACE(3)
-            // decision threshold of this row (see the header); rows whose magnitudes FP32 cannot carry
-            // safely -- Inf / NaN, |x_i| >= 2^40, a non-zero row below 2^-60 -- always take the exact replay
-            const int ex = (int)(mx >> 23) - 127;
-            const bool range_ok = mx == 0u || (ex >= -60 && ex < 40);
-            float thr = INFINITY;
-            if (rho < rows_valid && range_ok) thr = p.coef * (nsq * 1.0001f + cmax2f) * 1.001f;
-            mbar_wait(bar(THR_EMPTY + e), (unsigned)(((i >> 1) & 1) ^ 1));
-            thr_s[e * kFastRows + L] = thr;
+            // this set's share of |x|^2 in FP32 (Inf / NaN / overflow propagate: such rows are never decided here)
+            mbar_wait_relaxed(bar(THR_EMPTY + e), (unsigned)(((i >> 1) & 1) ^ 1));
+            nsq_s[(e * 2 + cs) * kFastRows + L] = (n0 + n1) + (n2 + n3);
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
                 mbar_arrive(bar(THR_FULL + e));
                 mbar_arrive(bar(A_FULL + a));
-                if (!ACCUM) mbar_arrive(bar(X_EMPTY + s)); // predict: the rows are not needed again
+                if (!ACCUM) mbar_arrive(bar(X_EMPTY + hs)); // predict: the staged rows are not needed again
             }
             FAST_TRACE(4)
+            hs += 2;
+            if (hs >= p.NS) {
+                hs -= p.NS;
+                ph_x ^= 1u;
+            }
+            if (++a == p.nA) {
+                a = 0;
+                ph_a ^= 1u;
+            }
         }
     } else if (warp < kFastLoaderWarp) {
         // =========================== epilogue: scores -> label (+ accumulate) ===========================
-        const int e = (warp - kFastConvWarps) >> 2, q = (warp - kFastConvWarps) & 3;
+        // warp (ec, q): TMEM lanes 32 q .. 32 q + 31, score columns of half ec of every tile
+        const int ec = (warp - kFastEpiWarp0) >> 2, q = (warp - kFastEpiWarp0) & 3;
         const int L = 32 * q + lane;
         const int rho = fast_row_of_lane(L);
         const unsigned lane_sel = (unsigned)(32 * q) << 16;
-        const unsigned d_tmem = tmem + lane_sel + d_col0 + (unsigned)e * (unsigned)p.Nacc;
-        const size_t row_off = (size_t)(rho >> 3) * p.group_bytes + (size_t)(rho & 7) * p.d * 8;
+        const unsigned row_bytes = (unsigned)p.d * 8u;
+        const int chunks = p.Nacc >> 4, c_lo = ec == 0 ? 0 : (chunks + 1) >> 1, c_hi = ec == 0 ? (chunks + 1) >> 1 : chunks;
         double *slot = ACCUM ? p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d) : nullptr;
-        for (int64_t i = e; i < my_tiles; i += 2) {
-            const int s = (int)(i % p.NS);
-            const int64_t tile = blockIdx.x + i * gridDim.x;
+        // |c|max^2 in FP32, rounded up; magnitudes FP32 scores cannot carry switch the tensor-core decision off
+        const int cexp = (int)p.cmax2[1];
+        const float cmax2f = (cexp >= -120 && cexp <= 80) ? __double2float_ru(p.cmax2[0]) : INFINITY;
+        // training: the 16 rows this warp feeds to the bulk reductions (TMEM lanes 32 q + 16 ec ..), all in half q >> 1
+        const int Lr = 32 * q + 16 * ec + (lane & 15);
+        const int rr = fast_row_of_lane(Lr);
+        const unsigned red_off = (unsigned)((rr & 63) >> 3) * (unsigned)p.group_bytes + (unsigned)(rr & 7) * row_bytes;
+        int hs = (q >> 1) % p.NS;
+        for (int i = 0; i < my_tiles; i++) {
+            const int e = i & 1;
+            const int64_t tile = blockIdx.x + (int64_t)i * gridDim.x;
             const int64_t row0 = tile * kFastRows;
-            const int rows_valid = (int)min((int64_t)kFastRows, p.n - row0);
+            const int rows_valid = tile == total_tiles - 1 ? last_rows : kFastRows;
             const unsigned ph = (unsigned)((i >> 1) & 1);
+            const unsigned d_tmem = tmem + lane_sel + d_col0 + (unsigned)e * (unsigned)p.Nacc;
             FAST_TRACE(5)
-            mbar_wait(bar(THR_FULL + e), ph);
-            const float thr = thr_s[e * kFastRows + L];
-            mbar_wait(bar(D_FULL + e), ph);
+            float nsq = 0.f;
+            if (ec == 0) {
+                mbar_wait_relaxed(bar(THR_FULL + e), ph);
+                nsq = nsq_s[(e * 2) * kFastRows + L] + nsq_s[(e * 2 + 1) * kFastRows + L];
+            }
+            mbar_wait_relaxed(bar(D_FULL + e), ph);
             tc_fence_after();
             FAST_TRACE(6)
-            float best = -INFINITY, second = -INFINITY;
-            int idx = 0;
-            for (int c0 = 0; c0 < p.Nacc; c0 += 16) {
-                unsigned v[16];
-                tmem_ld16(d_tmem + (unsigned)c0, v);
+            // two independent (best, second, index) chains, merged at the end
+            float b0 = -INFINITY, s0 = -INFINITY, b1 = -INFINITY, s1 = -INFINITY;
+            int i0 = 0, i1 = 0;
+            for (int cc = c_lo; cc < c_hi; cc += 2) {
+                unsigned v[2][16];
+#pragma unroll
+                for (int t = 0; t < 2; t++)
+                    if (cc + t < c_hi) tmem_ld16(d_tmem + (unsigned)(16 * (cc + t)), v[t]);
                 tmem_wait_ld();
-                if (p.dbg_full && rho < rows_valid) {
 #pragma unroll
-                    for (int j = 0; j < 16; j++) p.dbg_full[(size_t)(row0 + rho) * p.Nacc + c0 + j] = __uint_as_float(v[j]);
-                }
+                for (int t = 0; t < 2; t++) {
+                    if (cc + t < c_hi) {
+                        const int g0 = 16 * (cc + t);
+                        if (p.dbg_full && rho < rows_valid) {
 #pragma unroll
-                for (int j = 0; j < 16; j++) {
-                    const float sc = __uint_as_float(v[j]);
-                    const bool gt = sc > best;
-                    second = fmaxf(second, fminf(best, sc));
-                    idx = gt ? c0 + j : idx;
-                    best = fmaxf(best, sc);
+                            for (int j = 0; j < 16; j++) p.dbg_full[(size_t)(row0 + rho) * p.Nacc + g0 + j] = __uint_as_float(v[t][j]);
+                        }
+#pragma unroll
+                        for (int j = 0; j < 16; j += 2) {
+                            const float x0 = __uint_as_float(v[t][j]), x1 = __uint_as_float(v[t][j + 1]);
+                            const int c = g0 + j;
+                            s0 = fmaxf(s0, fminf(b0, x0));
+                            i0 = x0 > b0 ? c : i0;
+                            b0 = fmaxf(b0, x0);
+                            s1 = fmaxf(s1, fminf(b1, x1));
+                            i1 = x1 > b1 ? c + 1 : i1;
+                            b1 = fmaxf(b1, x1);
+                        }
+                    }
                 }
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) {
                 mbar_arrive(bar(D_EMPTY + e));
-                mbar_arrive(bar(THR_EMPTY + e));
+                if (ec == 0) mbar_arrive(bar(THR_EMPTY + e));
             }
             FAST_TRACE(7)
-            const bool valid = rho < rows_valid;
-            const bool decided = (best - second) > thr; // false for NaN, for thr = +inf, for exact ties
-            const bool flagged = valid && !decided;
-            const unsigned word = __ballot_sync(0xffffffffu, flagged);
-            if (lane == 0) p.flag_words[tile * 4 + q] = word;
-            if (p.dbg_scores && valid) {
-                p.dbg_scores[2 * (row0 + rho)] = best;
-                p.dbg_scores[2 * (row0 + rho) + 1] = second;
+            float best = fmaxf(b0, b1);
+            float second = fmaxf(fminf(b0, b1), fmaxf(s0, s1));
+            int idx = b1 > b0 ? i1 : i0;
+            // the two column halves of a row meet in shared memory (named barrier 1 + q: these two warps)
+            if (ec == 1) {
+                mrg_b[L] = best;
+                mrg_s[L] = second;
+                mrg_i[L] = idx;
             }
-            if (p.labels != nullptr && valid) p.labels[row0 + rho] = idx;
+            named_barrier(1 + q, 64);
+            if (ec == 0) {
+                const float ob = mrg_b[L], os = mrg_s[L];
+                const int oi = mrg_i[L];
+                second = fmaxf(fminf(best, ob), fmaxf(second, os));
+                idx = ob > best ? oi : idx;
+                best = fmaxf(best, ob);
+                const bool valid = rho < rows_valid;
+                // decision threshold of this row (see the header)
+                const float thr = p.coef * (nsq * 1.0001f + cmax2f) * 1.001f;
+                const bool decided = (best - second) > thr; // false for NaN, for thr = +inf, for exact ties
+                const bool flagged = valid && !decided;
+                const unsigned word = __ballot_sync(0xffffffffu, flagged);
+                if (lane == 0) {
+                    p.flag_words[tile * 4 + q] = word;
+                    if (word) p.flag_list[atomicAdd(p.flag_count, 1u)] = (uint32_t)(tile * 4 + q);
+                }
+                if (p.dbg_scores && valid) {
+                    p.dbg_scores[2 * (row0 + rho)] = best;
+                    p.dbg_scores[2 * (row0 + rho) + 1] = second;
+                }
+                if (p.labels != nullptr && valid) p.labels[row0 + rho] = idx;
+                if (ACCUM) lab_s[L] = (valid && !flagged) ? idx : -1;
+            }
             if (ACCUM) {
-                // one bulk reduction per decided row: the TMA engine adds the FP64 row, still in its
-                // stage, to sums[label] of this CTA's accumulator; the additions happen in L2
-                if (valid && !flagged) {
-                    bulk_reduce_add_f64(slot + (size_t)idx * p.d,
-                                        (unsigned)__cvta_generic_to_shared(stage0 + (size_t)s * p.stage_bytes + row_off),
-                                        (unsigned)p.d * 8u);
-                    atomicAdd(&counts_s[idx], 1);
+                named_barrier(1 + q, 64); // the labels of this quarter are in lab_s
+                // one bulk reduction per decided row (issued per lane: bulk operations of one thread are performed
+                // one after the other, those of different threads overlap; sixteen lanes of eight warps share a tile)
+                if (lane < 16) {
+                    const int lab = lab_s[Lr];
+                    if (lab >= 0) {
+                        atomicAdd(&counts_s[lab], 1);
+                        bulk_reduce_add_f64(slot + (size_t)lab * p.d,
+                                            (unsigned)__cvta_generic_to_shared(stage0 + (size_t)hs * p.stage_bytes) + red_off, row_bytes);
+                    }
                 }
                 bulk_commit_group();
                 FAST_TRACE(8)
-                bulk_wait_group_read(); // the rows have been read: the stage may be refilled
+                bulk_wait_group_read(); // the rows have been read: the half stage may be refilled
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar(X_EMPTY + s));
+                if (lane == 0) mbar_arrive(bar(X_EMPTY + hs));
+                hs += 2;
+                if (hs >= p.NS) hs -= p.NS;
             }
             FAST_TRACE(9)
         }
         if (ACCUM) bulk_wait_group_all();
-    } else if (warp == kFastLoaderWarp) {
-        // =========================== loader ===========================
-        if (lane == 0) {
+    } else if (warp == kLoaderWarp) {
+        // =========================== loader (warp converged, one elected lane issues) ===========================
+        if (elect_one()) {
             // the centroid terms, once: (KB + 1) + KB boxes of Nacc rows x 32 columns
-            const unsigned bytes_b = (unsigned)((2 * p.KB + 1) * bblk);
-            mbar_arrive_expect_tx(bar(B_FULL), bytes_b);
+            mbar_arrive_expect_tx(bar(B_FULL), (unsigned)((2 * p.KB + 1) * bblk));
             for (int b = 0; b <= p.KB; b++)
                 tma_load_2d((unsigned)__cvta_generic_to_shared(B1 + (size_t)b * bblk), &map1, 32 * b, 0, bar(B_FULL));
             for (int b = 0; b < p.KB; b++)
                 tma_load_2d((unsigned)__cvta_generic_to_shared(B2 + (size_t)b * bblk), &map2, 32 * b, 0, bar(B_FULL));
-            const unsigned row_bytes = (unsigned)p.d * 8u;
-            for (int64_t i = 0; i < my_tiles; i++) {
-                const int s = (int)(i % p.NS);
-                const int64_t row0 = (blockIdx.x + i * gridDim.x) * kFastRows;
-                const int rows_valid = (int)min((int64_t)kFastRows, p.n - row0);
+        }
+        __syncwarp();
+        const unsigned row_bytes = (unsigned)p.d * 8u;
+        const unsigned group_copy = row_bytes * kFastGroupRows;
+        int hs = 0;
+        unsigned ph = 1;
+        for (int i = 0; i < my_tiles; i++) {
+            const int64_t tile = blockIdx.x + (int64_t)i * gridDim.x;
+            const int rows_valid = tile == total_tiles - 1 ? last_rows : kFastRows;
+            for (int h = 0; h < 2; h++) {
+                const int rows_h = max(0, min(kFastHalfRows, rows_valid - h * kFastHalfRows));
+                const double *src = p.x + (tile * kFastRows + h * kFastHalfRows) * p.d;
                 FAST_TRACE(10)
-                mbar_wait(bar(X_EMPTY + s), (unsigned)(((i / p.NS) & 1) ^ 1));
+                mbar_wait_relaxed(bar(X_EMPTY + hs), ph);
                 FAST_TRACE(11)
-                mbar_arrive_expect_tx(bar(FULL_X + s), row_bytes * (unsigned)rows_valid);
-                unsigned char *dst = stage0 + (size_t)s * p.stage_bytes;
-                for (int g = 0; g * kFastGroupRows < rows_valid; g++) {
-                    const int nr = min(kFastGroupRows, rows_valid - g * kFastGroupRows);
-                    bulk_copy_g2s((unsigned)__cvta_generic_to_shared(dst + (size_t)g * p.group_bytes),
-                                  p.x + (row0 + (int64_t)g * kFastGroupRows) * p.d, row_bytes * (unsigned)nr, bar(FULL_X + s));
+                const unsigned dst = (unsigned)__cvta_generic_to_shared(stage0 + (size_t)hs * p.stage_bytes);
+                const unsigned fb = bar(FULL_X + hs);
+                if (elect_one()) {
+                    if (rows_h == 0) {
+                        mbar_arrive(fb); // nothing to bring: the readers mask these rows out
+                    } else {
+                        mbar_arrive_expect_tx(fb, row_bytes * (unsigned)rows_h);
+                        if (rows_h == kFastHalfRows) {
+#pragma unroll
+                            for (int g = 0; g < kFastHalfGroups; g++)
+                                bulk_copy_g2s(dst + (unsigned)g * (unsigned)p.group_bytes, src + (size_t)g * kFastGroupRows * p.d,
+                                              group_copy, fb);
+                        } else {
+                            for (int g = 0; g * kFastGroupRows < rows_h; g++) {
+                                const int nr = min(kFastGroupRows, rows_h - g * kFastGroupRows);
+                                bulk_copy_g2s(dst + (unsigned)g * (unsigned)p.group_bytes, src + (size_t)g * kFastGroupRows * p.d,
+                                              row_bytes * (unsigned)nr, fb);
+                            }
+                        }
+                    }
+                }
+                __syncwarp();
+                if (++hs == p.NS) {
+                    hs = 0;
+                    ph ^= 1u;
                 }
             }
         }
-    } else {
-        // =========================== MMA issuer ===========================
-        if (lane == 0) {
-            const unsigned idesc = umma_idesc_tf32(p.Nacc);
-            const unsigned b1 = (unsigned)__cvta_generic_to_shared(B1), b2 = (unsigned)__cvta_generic_to_shared(B2);
-            const int slabs = p.Kd >> 3;
-            mbar_wait(bar(B_FULL), 0);
-            for (int64_t i = 0; i < my_tiles; i++) {
-                const int a = (int)(i % p.nA), e = (int)(i & 1);
-                FAST_TRACE(12)
-                mbar_wait(bar(A_FULL + a), (unsigned)((i / p.nA) & 1));
-                FAST_TRACE(13)
-                mbar_wait(bar(D_EMPTY + e), (unsigned)(((i >> 1) & 1) ^ 1));
-                tc_fence_after();
-                FAST_TRACE(14)
-                const unsigned a_hi = tmem + kFastACol + (unsigned)a * a_cols, a_lo = a_hi + (unsigned)p.Kd;
-                const unsigned dt = tmem + d_col0 + (unsigned)e * (unsigned)p.Nacc;
-                unsigned acc = 0;
-                // small terms first: xh.c2, then xl.c1
+    } else if (warp == kMmaWarp) {
+        // =========================== MMA issuer (warp converged, one elected lane issues) ===========================
+        const unsigned idesc = umma_idesc_tf32(p.Nacc);
+        const unsigned b1 = (unsigned)__cvta_generic_to_shared(B1), b2 = (unsigned)__cvta_generic_to_shared(B2);
+        const int slabs = p.Kd >> 3;
+        const uint64_t desc_hi = ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61) | ((uint64_t)1 << 16);
+        mbar_wait_relaxed(bar(B_FULL), 0);
+        int a = 0;
+        unsigned ph_a = 0;
+        for (int i = 0; i < my_tiles; i++) {
+            const int e = i & 1;
+            FAST_TRACE(12)
+            mbar_wait_relaxed(bar(A_FULL + a), ph_a);
+            FAST_TRACE(13)
+            mbar_wait_relaxed(bar(D_EMPTY + e), (unsigned)(((i >> 1) & 1) ^ 1));
+            tc_fence_after();
+            FAST_TRACE(14)
+            const unsigned a_hi = tmem + kFastACol + (unsigned)a * a_cols, a_lo = a_hi + (unsigned)p.Kd;
+            const unsigned dt = tmem + d_col0 + (unsigned)e * (unsigned)p.Nacc;
+            if (elect_one()) {
+                // small terms first: xh.c2, then xl.c1; then the main term xh.c1 and the constant column times (h1, h2, h3)
                 for (int sl = 0; sl < slabs; sl++) {
-                    tc_mma_tf32_ts(dt, a_hi + 8u * sl, umma_desc_sw128(b2 + (unsigned)(sl >> 2) * bblk + (unsigned)(sl & 3) * 32u), idesc, acc);
-                    acc = 1;
+                    const unsigned off = (unsigned)(sl >> 2) * (unsigned)bblk + (unsigned)(sl & 3) * 32u;
+                    tc_mma_tf32_ts(dt, a_hi + 8u * sl, desc_hi | (uint64_t)(((b2 + off) >> 4) & 0x3fffu), idesc, sl > 0);
                 }
-                for (int sl = 0; sl < slabs; sl++)
-                    tc_mma_tf32_ts(dt, a_lo + 8u * sl, umma_desc_sw128(b1 + (unsigned)(sl >> 2) * bblk + (unsigned)(sl & 3) * 32u), idesc, 1);
-                // the main term xh.c1 and the constant column times (h1, h2, h3)
-                for (int sl = 0; sl < slabs; sl++)
-                    tc_mma_tf32_ts(dt, a_hi + 8u * sl, umma_desc_sw128(b1 + (unsigned)(sl >> 2) * bblk + (unsigned)(sl & 3) * 32u), idesc, 1);
-                tc_mma_tf32_ts(dt, tmem + kFastOnesCol, umma_desc_sw128(b1 + (unsigned)p.KB * bblk), idesc, 1);
+                for (int sl = 0; sl < slabs; sl++) {
+                    const unsigned off = (unsigned)(sl >> 2) * (unsigned)bblk + (unsigned)(sl & 3) * 32u;
+                    tc_mma_tf32_ts(dt, a_lo + 8u * sl, desc_hi | (uint64_t)(((b1 + off) >> 4) & 0x3fffu), idesc, 1);
+                }
+                for (int sl = 0; sl < slabs; sl++) {
+                    const unsigned off = (unsigned)(sl >> 2) * (unsigned)bblk + (unsigned)(sl & 3) * 32u;
+                    tc_mma_tf32_ts(dt, a_hi + 8u * sl, desc_hi | (uint64_t)(((b1 + off) >> 4) & 0x3fffu), idesc, 1);
+                }
+                tc_mma_tf32_ts(dt, tmem + kFastOnesCol, desc_hi | (uint64_t)(((b1 + (unsigned)p.KB * (unsigned)bblk) >> 4) & 0x3fffu),
+                               idesc, 1);
                 tc_commit(bar(A_EMPTY + a)); // the A buffer may be overwritten once these MMAs have read it
                 tc_commit(bar(D_FULL + e));  // and the scores are complete
-                FAST_TRACE(15)
+            }
+            __syncwarp();
+            FAST_TRACE(15)
+            if (++a == p.nA) {
+                a = 0;
+                ph_a ^= 1u;
             }
         }
     }
@@ -488,37 +635,59 @@ __global__ void __launch_bounds__(kFastThreads, 1)
         for (int i = threadIdx.x; i < p.k; i += blockDim.x)
             if (counts_s[i]) atomicAdd(&slot[(size_t)p.k * p.d + i], (double)counts_s[i]);
     }
-    if (warp == kFastMmaWarp) tmem_dealloc(tmem, kFastTmemCols);
+    if (warp == kMmaWarp) tmem_dealloc(tmem, kFastTmemCols);
 }
 
 // ------------------------------------------------------------------------------------------
 // The rows the tensor-core pass did not decide (bit l of word 4 t + q: TMEM lane 32 q + l of tile t),
-// replayed with the reference arithmetic: one warp per flagged row.
-template <bool ACCUM>
+// replayed with the reference arithmetic: one warp per flagged row.  The non-zero bitmap words were
+// listed by the assign kernel, so the warps share them evenly; a flagged row is first brought into shared
+// memory with one coalesced read (the replay walks it element by element), then labelled by
+// exact_find_closest over the transposed centroids -- staged in shared memory once per block when they fit
+// (CT_SMEM: the replay's dependent loads then cost a shared-memory access each instead of an L2 round trip).
+// Dynamic shared memory: (blockDim.x / 32) * d doubles (+ d * ldt doubles with CT_SMEM).
+template <bool ACCUM, bool CT_SMEM>
 __global__ void __launch_bounds__(256) recheck_rows_kernel(const double *x, int64_t n, int d, const uint32_t *flag_words,
-                                                            int64_t n_words, const double *c, const double *cn, int k,
-                                                            int fma_mode, int32_t *labels, double *slot,
+                                                            const uint32_t *flag_list, const uint32_t *flag_count,
+                                                            const double *ct, int ldt, const double *cn, int k, int fma_mode,
+                                                            int32_t *labels, double *partials, int n_partials,
                                                             unsigned long long *recheck_count) {
+    extern __shared__ __align__(16) double recheck_rows[];
     const int lane = threadIdx.x & 31;
-    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    double *buf = recheck_rows + (size_t)(threadIdx.x >> 5) * d;
+    const unsigned warps = (gridDim.x * blockDim.x) >> 5;
+    const unsigned count = *flag_count;
+    if (CT_SMEM) {
+        if (count == 0u) return; // nothing to replay (block-uniform)
+        double *ct_s = recheck_rows + (size_t)(blockDim.x >> 5) * d;
+        for (int i = threadIdx.x; i < d * ldt; i += blockDim.x) ct_s[i] = ct[i];
+        __syncthreads();
+        ct = ct_s;
+    }
+    // the replayed rows are few but their additions must not meet on one accumulator: slot by block
+    double *slot = ACCUM ? partials + (size_t)(blockIdx.x % n_partials) * partial_stride(k, d) : nullptr;
     unsigned long long mine = 0;
-    for (int64_t w = (((int64_t)blockIdx.x * blockDim.x) + threadIdx.x) >> 5; w < n_words; w += warps) {
-        unsigned mask = flag_words[w];
-        const int64_t tile = w >> 2;
-        const int q = (int)(w & 3);
+    for (unsigned i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < count; i += warps) {
+        const uint32_t word = flag_list[i];
+        unsigned mask = flag_words[word];
+        const int64_t tile = word >> 2;
+        const int q = (int)(word & 3u);
         while (mask) { // warp-uniform
             const int l = __ffs(mask) - 1;
             mask &= mask - 1;
             const int64_t row = tile * kFastRows + fast_row_of_lane(32 * q + l);
             if (row >= n) continue;
             const double *xr = x + row * d;
-            const int lab = exact_find_closest(xr, c, cn, k, d, fma_mode);
+            for (int c = lane; c < d; c += 32) buf[c] = xr[c];
+            __syncwarp();
+            const int lab = exact_find_closest_impl(buf, nullptr, ct, (size_t)ldt, cn, k, d, fma_mode);
             mine++;
             if (labels != nullptr && lane == 0) labels[row] = lab;
             if (ACCUM) {
-                for (int col = lane; col < d; col += 32) atomicAdd(&slot[(size_t)lab * d + col], xr[col]);
+                for (int col = lane; col < d; col += 32) atomicAdd(&slot[(size_t)lab * d + col], buf[col]);
                 if (lane == 0) atomicAdd(&slot[(size_t)k * d + lab], 1.0);
             }
+            __syncwarp();
         }
     }
     if (lane == 0 && mine && recheck_count) atomicAdd(recheck_count, mine);

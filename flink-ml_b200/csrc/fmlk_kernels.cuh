@@ -187,6 +187,22 @@ __device__ __forceinline__ double ref_ddot(const double *x, const double *y, int
     return sum;
 }
 
+// Same operations, same order, with y read at a stride (a transposed copy of the centroids: the 32
+// lanes of a warp, one centroid each, then read consecutive addresses).
+__device__ __forceinline__ double ref_ddot_strided(const double *x, const double *y, size_t ys, int d, int fma_mode) {
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int i = 0, n4 = d & ~3;
+    for (; i < n4; i += 4) {
+        s0 = ref_mul_add(x[i + 0], y[(size_t)(i + 0) * ys], s0, fma_mode);
+        s1 = ref_mul_add(x[i + 1], y[(size_t)(i + 1) * ys], s1, fma_mode);
+        s2 = ref_mul_add(x[i + 2], y[(size_t)(i + 2) * ys], s2, fma_mode);
+        s3 = ref_mul_add(x[i + 3], y[(size_t)(i + 3) * ys], s3, fma_mode);
+    }
+    double sum = __dadd_rn(0.0, __dadd_rn(__dadd_rn(__dadd_rn(s0, s1), s2), s3));
+    for (; i < d; i++) sum = ref_mul_add(x[i], y[(size_t)i * ys], sum, fma_mode);
+    return sum;
+}
+
 // netlib JavaBLAS dnrm2 before the square root (CORE/linalg/BLAS.java:124-126).
 __device__ __forceinline__ double ref_sumsq(const double *x, int d, int fma_mode) {
     double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
@@ -216,8 +232,9 @@ __device__ __forceinline__ double ref_dist2(double pn, double cn, double dot) {
 // strict <, first index wins) is then replayed in index order over each group of 32.  A group
 // in which no distance is below the running best cannot change it and is skipped.
 // x: the row (shared or global memory), c/cn: global.  All lanes return the label.
-__device__ __noinline__ int exact_find_closest(const double *x, const double *c, const double *cn, int k, int d,
-                                  int fma_mode) {
+// ct != nullptr: the centroids transposed, ct[i * ldt + j] = c[j * d + i] (same values, coalesced reads).
+__device__ __forceinline__ int exact_find_closest_impl(const double *x, const double *c, const double *ct, size_t ldt,
+                                                       const double *cn, int k, int d, int fma_mode) {
     const int lane = threadIdx.x & 31;
     const double pn = sqrt(ref_sumsq(x, d, fma_mode)); // correctly rounded, as Math.sqrt
     double best = INFINITY;
@@ -229,21 +246,27 @@ __device__ __noinline__ int exact_find_closest(const double *x, const double *c,
             const double cnj = cn[j];
             const double lbs = __dadd_rn(pn, -cnj);
             lb = __dmul_rn(lbs, lbs);
-            dist = ref_dist2(pn, cnj, ref_ddot(x, c + (size_t)j * d, d, fma_mode));
+            const double dot = ct ? ref_ddot_strided(x, ct + j, ldt, d, fma_mode) : ref_ddot(x, c + (size_t)j * d, d, fma_mode);
+            dist = ref_dist2(pn, cnj, dot);
         }
-        if (__ballot_sync(0xffffffffu, dist < best) == 0u) continue;
-        const int cnt = min(32, k - base);
-        for (int t = 0; t < cnt; t++) {
-            const double dt = __shfl_sync(0xffffffffu, dist, t);
-            const double lt = __shfl_sync(0xffffffffu, lb, t);
-            if (lt >= best) continue;
-            if (dt < best) {
-                best = dt;
-                best_idx = base + t;
-            }
+        // The sequential scan over this group (if (lb >= best) continue; if (d < best) take it) only ever
+        // takes an element whose distance AND lower bound are below the running best, and the best only
+        // falls: jump from one such element to the next instead of visiting all 32.
+        int from = 0; // lanes below `from` have been passed
+        for (;;) {
+            const unsigned cand = __ballot_sync(0xffffffffu, lane >= from && dist < best && lb < best);
+            if (cand == 0u) break;
+            const int t = __ffs(cand) - 1;
+            best = __shfl_sync(0xffffffffu, dist, t);
+            best_idx = base + t;
+            from = t + 1;
         }
     }
     return best_idx;
+}
+__device__ __noinline__ int exact_find_closest(const double *x, const double *c, const double *cn, int k, int d,
+                                               int fma_mode) {
+    return exact_find_closest_impl(x, c, nullptr, 0, cn, k, d, fma_mode);
 }
 
 // ------------------------------------------------------------------------------------------

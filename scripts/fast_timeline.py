@@ -9,14 +9,15 @@ NAMES = {(0, 1): "wait rows", (1, 2): "wait A free", (2, 3): "convert+st", (3, 4
          (5, 6): "wait thr+scores", (6, 7): "ld+top2", (7, 8): "flags+reduce issue", (8, 9): "wait reduce read",
          (7, 9): "flags+labels", (9, 5): "loop", (10, 11): "wait stage free", (11, 10): "issue copies",
          (12, 13): "wait A", (13, 14): "wait D free", (14, 15): "issue mma", (15, 12): "loop"}
-ROLE = ["conv"] * 4 + ["epi0"] * 4 + ["epi1"] * 4 + ["load", "mma"]
+ROLE = ["cnv0"] * 4 + ["cnv1"] * 4 + ["epi0"] * 4 + ["epi1"] * 4 + ["load", "mma"]
+NAMES.update({(7, 9): "merge+flags+labels", (7, 8): "merge+flags+reduce issue", (11, 10): "issue copies (half)"})
 ev = np.fromfile(sys.argv[1], dtype=np.uint64).reshape(len(ROLE), -1)
 for w in range(ev.shape[0]):
     e = ev[w][ev[w] != 0]
     if e.size < 8:
         continue
-    t = (e >> np.uint64(4)).astype(np.int64)
-    k = (e & np.uint64(15)).astype(np.int64)
+    t = (e >> np.uint64(5)).astype(np.int64)
+    k = (e & np.uint64(31)).astype(np.int64)
     dur = {}
     for i in range(len(k) - 1):
         dur.setdefault((int(k[i]), int(k[i + 1])), []).append(t[i + 1] - t[i])

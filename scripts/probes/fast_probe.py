@@ -35,7 +35,7 @@ with native.Context(0, flags=native.FLAG_FAST_TF32 | native.FLAG_PROFILE) as ctx
     scale = (x * x).sum(1)[:, None] + (c * c).sum(1).max()
     print("scores: nan %d  max abs err %.3e  max rel-to-bound-base %.3e (2^%.1f)  model coef/2.5 = 2^%.1f"
           % (np.isnan(got).sum(), np.nanmax(err), np.nanmax(err / scale), np.log2(max(np.nanmax(err / scale), 1e-300)),
-             np.log2((((d + 7) // 8) + 6) * 2.0 ** -22)))
+             np.log2(((((d + 7) // 8) * 8) / 16.0 + 5.5) * 2.0 ** -22)))
     if np.nanmax(err / scale) > 1e-4:
         bad_r, bad_c = np.unravel_index(np.nanargmax(err), err.shape)
         print("worst at row %d col %d: got %.6f want %.6f" % (bad_r, bad_c, got[bad_r, bad_c], exact[bad_r, bad_c]))
