@@ -335,8 +335,30 @@ def run_ours(args):
 
     # ---- e2e: the public API with HOST buffers: KMeans.fit(Table) -> model, H2D and D2H inside
     e2e = None
-    cluster = K.Cluster(rank, world, local, flags=main_flags | native.FLAG_PROFILE, host_group=host_group)
-    est = F.KMeans(cluster).set_k(k).set_max_iter(rounds)
+
+    def e2e_fits(flags, table_, steps_):
+        cl = K.Cluster(rank, world, local, flags=flags, host_group=host_group)
+        est_ = F.KMeans(cl).set_k(k).set_max_iter(rounds)
+        est_.fit(table_)  # warm-up (allocations, page tables)
+        barrier()
+        t0_ = time.perf_counter()
+        for _ in range(steps_):
+            model_ = est_.fit(table_)
+        barrier()
+        dt_ = torch.tensor([time.perf_counter() - t0_], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt_, op=dist.ReduceOp.MAX)
+        md_ = F.KMeansModelData.from_table(model_.get_model_data()[0])
+        cl.close()
+        sec = float(dt_.item())
+        return {"value": float(total_rows) * rounds * steps_ / sec, "unit": UNIT,
+                "h2d_bytes_per_step": int(n * d * 8 + k * d * 8), "d2h_bytes_per_step": int(k * d * 8 + (k * d + k) * 8),
+                "steps": steps_, "ms_per_step": sec / steps_ * 1e3,
+                "h2d_gbs_per_rank_if_copy_only": n * d * 8 / 1e9 / (sec / steps_),
+                "api": "flink_ml_b200.KMeans.fit(Table) from pinned host rows; timed on the host clock "
+                       "around the calls (max over ranks)",
+                "model_matches_device_run": bool(np.allclose(md_.centroids, model_c, rtol=1e-9, atol=0, equal_nan=True))}
+
     if not args.no_e2e:
         host = torch.empty((n, d), dtype=torch.float64, pin_memory=True)
         host.copy_(x)
@@ -345,27 +367,13 @@ def run_ours(args):
         torch.cuda.empty_cache()
         table = F.Table({"features": host.numpy()})
         e2e_steps = max(1, min(args.steps, args.e2e_steps))
-        est.fit(table)  # warm-up (allocations, page tables)
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(e2e_steps):
-            model = est.fit(table)
-        barrier()
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        md = F.KMeansModelData.from_table(model.get_model_data()[0])
-        ok = bool(np.allclose(md.centroids, model_c, rtol=1e-9, atol=0, equal_nan=True))
-        e2e = {"value": float(total_rows) * rounds * e2e_steps / float(dt.item()), "unit": UNIT,
-               "h2d_bytes_per_step": int(n * d * 8 + k * d * 8), "d2h_bytes_per_step": int(k * d * 8 + (k * d + k) * 8),
-               "steps": e2e_steps, "ms_per_step": float(dt.item()) / e2e_steps * 1e3,
-               "api": "flink_ml_b200.KMeans.fit(Table) from pinned host rows; timed on the host clock "
-                      "around the calls (max over ranks)", "model_matches_device_run": ok}
+        e2e = e2e_fits(main_flags, table, e2e_steps)
+        if fast_rec is not None:
+            fast_rec["e2e"] = e2e_fits(native.FLAG_FAST_TF32, table, e2e_steps)
         del host, table
     else:
         del x
         torch.cuda.empty_cache()
-    cluster.close()
 
     # ---- the north-star shape (config 4: 1e9 x 64, k = 1000 over 8 GPUs): this GPU's share, a short run
     north = None

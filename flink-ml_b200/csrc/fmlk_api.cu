@@ -130,6 +130,10 @@ struct fmlk_ctx {
     int32_t k = 0;
     std::vector<Chunk> chunks;
     int64_t n_total = 0;
+    // fmlk_clear_points keeps the largest buffer of the cache for the next fit (released by fmlk_destroy):
+    // a task that fits repeatedly does not pay a multi-GB cudaFree + cudaMalloc per fit
+    double *spare = nullptr;
+    size_t spare_bytes = 0;
 
     // model-sized device buffers, (re)allocated in ensure_model()
     int32_t k_cap = 0;
@@ -886,6 +890,14 @@ int grow_points(fmlk_ctx *ctx, int64_t n, double **dst) {
     // bytes: at least 32 MB (or the request), at most 32 GB per chunk, never more than what is free;
     // on failure halve towards the request instead of dropping straight to it.
     const int64_t row_bytes = (int64_t)ctx->d * (int64_t)sizeof(double);
+    if (ctx->spare && (int64_t)(ctx->spare_bytes / row_bytes) >= n) {
+        ctx->chunks.push_back(Chunk{ctx->spare, n, (int64_t)(ctx->spare_bytes / row_bytes), true});
+        ctx->spare = nullptr;
+        ctx->spare_bytes = 0;
+        ctx->n_total += n;
+        *dst = ctx->chunks.back().ptr;
+        return FMLK_OK;
+    }
     const int64_t min_rows = std::max<int64_t>(1, ((int64_t)32 << 20) / row_bytes);
     const int64_t max_rows = std::max<int64_t>(1, ((int64_t)32 << 30) / row_bytes);
     int64_t cap = std::max<int64_t>(n, std::min<int64_t>(std::max<int64_t>(ctx->n_total, min_rows), max_rows));
@@ -1024,6 +1036,7 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     if (ctx->comm) nccl().CommDestroy(ctx->comm);
     for (Chunk &c : ctx->chunks)
         if (c.owned) dev_free(c.ptr);
+    dev_free(ctx->spare);
     dev_free(ctx->centroids);
     dev_free(ctx->c_mma);
     dev_free(ctx->weights);
@@ -1076,6 +1089,13 @@ int32_t fmlk_reserve_points(fmlk_ctx *ctx, int64_t n_rows, int32_t d) {
     if (rc) return rc;
     if ((rc = check_dim(ctx, d))) return rc;
     if (n_rows <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "n_rows must be positive");
+    if (ctx->spare && ctx->spare_bytes >= (size_t)n_rows * d * sizeof(double)) {
+        ctx->d = d;
+        ctx->chunks.push_back(Chunk{ctx->spare, 0, (int64_t)(ctx->spare_bytes / ((size_t)d * sizeof(double))), true});
+        ctx->spare = nullptr;
+        ctx->spare_bytes = 0;
+        return FMLK_OK;
+    }
     double *p = nullptr;
     cudaError_t e = cudaMalloc((void **)&p, (size_t)n_rows * d * sizeof(double));
     if (e != cudaSuccess) {
@@ -1278,8 +1298,17 @@ int32_t fmlk_clear_points(fmlk_ctx *ctx) {
     int rc = use_device(ctx);
     if (rc) return rc;
     CK(ctx, cudaStreamSynchronize(ctx->stream));
-    for (Chunk &c : ctx->chunks)
-        if (c.owned) dev_free(c.ptr);
+    for (Chunk &c : ctx->chunks) {
+        if (!c.owned) continue;
+        const size_t bytes = (size_t)c.cap * ctx->d * sizeof(double);
+        if (bytes > ctx->spare_bytes) { // keep the largest buffer for the next fit
+            dev_free(ctx->spare);
+            ctx->spare = c.ptr;
+            ctx->spare_bytes = bytes;
+        } else {
+            dev_free(c.ptr);
+        }
+    }
     ctx->chunks.clear();
     ctx->n_total = 0;
     ctx->d = 0;

@@ -124,7 +124,9 @@ int32_t fmlk_decode_rows_dev(int32_t device, void *cuda_stream, const uint8_t *r
  * keeps it alive and unchanged until fmlk_clear_points / fmlk_destroy. */
 int32_t fmlk_adopt_points_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d);
 
-/* points.clear() (KMeans.java:305). */
+/* points.clear() (KMeans.java:305).  The largest device buffer of the cache is kept for the next fit
+ * (a job that fits repeatedly does not pay a multi-GB cudaFree + cudaMalloc each time); fmlk_destroy
+ * releases it. */
 int32_t fmlk_clear_points(fmlk_ctx *ctx);
 
 int64_t fmlk_num_points(const fmlk_ctx *ctx);
