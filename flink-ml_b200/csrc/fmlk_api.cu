@@ -164,7 +164,7 @@ struct fmlk_ctx {
 
     // fast mode (FMLK_FLAG_FAST_TF32): the centroids as TF32 terms + their tensor maps, the bitmap of
     // rows left to the exact replay
-    float *bt1 = nullptr, *bt2 = nullptr;
+    float *bt1 = nullptr, *bt2 = nullptr, *h32 = nullptr;
     double *ct = nullptr; // the centroids transposed (d x k_rows) for the exact replay
     size_t bt_cap = 0; // floats in bt1 (bt2 and ct are never larger)
     alignas(64) CUtensorMap map1, map2;
@@ -538,7 +538,7 @@ bool fast_shape(const fmlk_ctx *ctx, int k, int d, bool accum, FastPlan *out) {
     if (kFastACol + f.nA * 2 * f.Kd + 2 * f.Nacc > kFastTmemCols) return false;
     f.group_bytes = kFastGroupRows * d * 8 + 16;
     f.stage_bytes = kFastHalfGroups * f.group_bytes;
-    const size_t fixed = (size_t)(2 * f.KB + 1) * f.Nacc * 128 + 8 * kFastRows * sizeof(float) + (size_t)f.Nacc * sizeof(int) +
+    const size_t fixed = (size_t)(2 * f.KB) * f.Nacc * 128 + 8 * kFastRows * sizeof(float) + (size_t)f.Nacc * 2 * sizeof(int) +
                          40 * 8 + 16 + 1024 /* alignment slack */;
     // training keeps a half stage until its rows have been added: a whole tile in flight beside the one in work
     const int min_stages = accum ? 4 : 2;
@@ -550,31 +550,33 @@ bool fast_shape(const fmlk_ctx *ctx, int k, int d, bool accum, FastPlan *out) {
 }
 
 int ensure_fast(fmlk_ctx *ctx, const FastPlan &f) {
-    const size_t need = (size_t)f.k_rows * (32 * f.KB + 32);
+    const size_t need = (size_t)f.k_rows * (32 * f.KB);
     int rc;
     bool fresh = false;
     if (need > ctx->bt_cap) {
         dev_free(ctx->bt1);
         dev_free(ctx->bt2);
         dev_free(ctx->ct);
-        ctx->bt1 = ctx->bt2 = nullptr;
+        dev_free(ctx->h32);
+        ctx->bt1 = ctx->bt2 = ctx->h32 = nullptr;
         ctx->ct = nullptr;
         ctx->bt_cap = 0;
         if ((rc = dev_alloc(ctx, &ctx->bt1, need))) return rc;
         if ((rc = dev_alloc(ctx, &ctx->bt2, need))) return rc;
         if ((rc = dev_alloc(ctx, &ctx->ct, need))) return rc;
+        if ((rc = dev_alloc(ctx, &ctx->h32, (size_t)256))) return rc;
         ctx->bt_cap = need;
         fresh = true;
     }
     if (fresh || ctx->map_k_rows != f.k_rows || ctx->map_KB != f.KB || ctx->map_nacc != f.Nacc) {
         EncodeTiledFn enc = encode_tiled();
         if (!enc) return fail(ctx, FMLK_ERR_CUDA, "cuTensorMapEncodeTiled is not available from this driver");
-        // bt1: k_rows x (32 KB + 32) floats, bt2: k_rows x 32 KB floats; boxes of Nacc rows x 32 columns
+        // bt1, bt2: k_rows x 32 KB floats; boxes of Nacc rows x 32 columns
         // (128 bytes) land with the 128-byte swizzle, the layout the MMA's shared-memory descriptor names.
         // Both maps cover buffers of this context, i.e. this GPU's own memory.
         const cuuint32_t box[2] = {32u, (cuuint32_t)f.Nacc}, estr[2] = {1u, 1u};
         for (int t = 0; t < 2; t++) {
-            const cuuint64_t ld = (cuuint64_t)(32 * f.KB + (t == 0 ? 32 : 0));
+            const cuuint64_t ld = (cuuint64_t)(32 * f.KB);
             const cuuint64_t dims[2] = {ld, (cuuint64_t)f.k_rows}, strides[1] = {ld * sizeof(float)};
             CUresult r = enc(t == 0 ? &ctx->map1 : &ctx->map2, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2,
                              t == 0 ? (void *)ctx->bt1 : (void *)ctx->bt2, dims, strides, box, estr,
@@ -620,6 +622,7 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
     p.group_bytes = f.group_bytes;
     p.coef = (float)(2.5 * (f.Kd / 16.0 + 5.5) * 0x1.0p-22);
     p.cmax2 = ctx->cmax2;
+    p.h32 = ctx->h32;
     p.c = ctx->centroids;
     p.cn = ctx->cn;
     p.labels = labels;
@@ -688,9 +691,9 @@ int prep_centroids(fmlk_ctx *ctx) {
     if (fast_shape(ctx, ctx->k, ctx->md, false, &f)) {
         int rc = ensure_fast(ctx, f);
         if (rc) return rc;
-        const int total = f.k_rows * (32 * f.KB + 32);
+        const int total = f.k_rows * (32 * f.KB);
         prep_fast_kernel<<<(total + 255) / 256, 256, 0, ctx->stream>>>(ctx->centroids, ctx->c_mma, ctx->h, ctx->k, ctx->md,
-                                                                       f.k_rows, f.KB, ctx->bt1, ctx->bt2, ctx->ct);
+                                                                       f.k_rows, f.KB, ctx->bt1, ctx->bt2, ctx->h32, ctx->ct);
         ctx->total_launches++;
         CK(ctx, cudaGetLastError());
     }
@@ -1055,6 +1058,7 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     dev_free(ctx->bt1);
     dev_free(ctx->bt2);
     dev_free(ctx->ct);
+    dev_free(ctx->h32);
     dev_free(ctx->flag_words);
     dev_free(ctx->ar_probe);
     dev_free(ctx->ar_buf);

@@ -9,16 +9,17 @@
 // kind::tf32, accumulators in TMEM) with every FP64 operand split into TF32 terms:
 //     x = xh + xl (+ e_x),  |xl| <= 2^-11 |x|,  |e_x| <= 1.25 * 2^-22 |x|      (split on the fly, per row tile)
 //     c = c1 + c2 (+ e_c),  |c2| <= 2^-11 |c|,  |e_c| <= 2^-22 |c|              (split once per round)
-//     -|c|^2/2 = h1 + h2 + h3 (to 2^-33), multiplied by a constant column of ones
 // and three passes accumulated into ONE TMEM accumulator, small terms first:
-//     xh.c2 ,  xl.c1 ,  xh.c1 + 1.h
+//     xh.c2 ,  xl.c1 ,  xh.c1
+// The epilogue adds h = -|c|^2/2, rounded to FP32, to every score it reads (one FADD; keeping h out of the
+// B operand leaves room for a fifth half stage of rows at d = 64, k = 100).
 // Error of the score (S' = |x||c| + |c|^2/2 <= |x|^2 + |c|max^2):
 //   - dropped products xl.c2, x.e_c, e_x.c:            <= 3.3 * 2^-22 S'
 //   - FP32 accumulation in the tensor core: each tcgen05.mma step (K = 8) adds eight exact products
 //     to the accumulator and rounds or truncates once to FP32: at most one ulp, 2^-23 relative to the
 //     largest magnitude involved.  The two small passes carry partial sums <= 2^-10 S'; only the
-//     Kd/8 + 1 steps of the last pass see S' itself:   <= (Kd/16 + 0.5 + Kd * 2^-13) * 2^-22 S'
-//   - FP32 work of the epilogue (row norm, subtraction): <= 2^-22 S'
+//     Kd/8 steps of the last pass see S' itself:       <= (Kd/16 + Kd * 2^-13) * 2^-22 S'
+//   - h in FP32 and its addition, the FP32 row norm and subtraction of the epilogue: <= 1.5 * 2^-22 S'
 //   => |v_fast - v_exact| <= E = (Kd/16 + 5.5) * 2^-22 * S'
 // A row is decided by the tensor-core pass when best - second > 2.5 E (2E for the two scores, the
 // rest covers the FP32 subtraction, the FP32 row norm and the FP64 reference's own rounding, all
@@ -64,8 +65,7 @@ constexpr int kFastWarps = kFastMmaWarp + 1;
 constexpr int kFastThreads = kFastWarps * 32;
 constexpr int kFastMaxStages = 8;
 constexpr int kFastTmemCols = 512;
-constexpr int kFastOnesCol = 0;      // 8 columns [1,1,1,0,0,0,0,0] in every lane
-constexpr int kFastACol = 16;        // first A buffer
+constexpr int kFastACol = 0;         // first A buffer
 
 struct FastParams {
     const double *x;
@@ -81,6 +81,7 @@ struct FastParams {
     int32_t group_bytes; // 8 * d * 8 + 16
     float coef;       // 2.5 * (Kd/16 + 5.5) * 2^-22
     const double *cmax2; // [0] max finite |c|^2, [1] ceil(log2) of it
+    const float *h32;    // [Nacc] -|c|^2/2 in FP32; -inf for dead centroids and padding
     const double *c;     // k x d centroids as given (exact replay)
     const double *cn;
     int32_t *labels;     // or null
@@ -214,42 +215,29 @@ __host__ __device__ __forceinline__ int fast_row_of_lane(int L) {
 __device__ __forceinline__ unsigned tf32_rn_bits(float v) { return (__float_as_uint(v) + 0x1000u) & 0xffffe000u; }
 
 // ------------------------------------------------------------------------------------------
-// Per round: the centroids as TF32 terms, row-major with rows of 32-column blocks, for the tensor-map loads.
-//   bt1[j][0 .. 32 KB)       = c1 = tf32(c)          bt1[j][32 KB + 0..2] = h1, h2, h3 (three-term -|c|^2/2)
-//   bt2[j][0 .. 32 KB)       = c2 = tf32(c - c1)
-// rows j >= k and dead centroids: zeros with h1 = -inf (they score -inf and never win).
+// Per round: the centroids as TF32 terms, row-major with rows of 32 KB columns, for the tensor-map loads.
+//   bt1[j][i] = c1 = tf32(c)      bt2[j][i] = c2 = tf32(c - c1)      h32[j] = float(-|c_j|^2 / 2)
+// rows j >= k and dead centroids: zeros with h32 = -inf (they score -inf and never win).
 // ct[i][j] = c[j][i] (the centroids as given, transposed, rows of k_rows doubles): the exact replay reads it.
 __global__ void prep_fast_kernel(const double *c, const double *c_mma, const double *h, int k, int d, int k_rows, int KB,
-                                 float *bt1, float *bt2, double *ct) {
-    const int ld1 = 32 * KB + 32, ld2 = 32 * KB;
-    const int total = k_rows * ld1;
+                                 float *bt1, float *bt2, float *h32, double *ct) {
+    const int ld = 32 * KB;
+    const int total = k_rows * ld;
     for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
-        const int j = idx / ld1, i = idx - j * ld1;
+        const int j = idx / ld, i = idx - j * ld;
         float v1 = 0.f, v2 = 0.f;
         if (i < d && j < k) {
             const double cv = c_mma[(size_t)j * d + i];
             v1 = __uint_as_float(tf32_rn_bits(__double2float_rn(cv)));
             v2 = __uint_as_float(tf32_rn_bits(__double2float_rn(cv - (double)v1)));
-        } else if (i >= 32 * KB && i < 32 * KB + 3) {
-            const double hv = j < k ? h[j] : -INFINITY;
-            const int t = i - 32 * KB;
-            if (!isfinite(hv)) {
-                v1 = t == 0 ? -INFINITY : 0.f;
-            } else {
-                const float a = __uint_as_float(tf32_rn_bits(__double2float_rn(hv)));
-                const double r1 = hv - (double)a;
-                const float b = __uint_as_float(tf32_rn_bits(__double2float_rn(r1)));
-                const float cc = __uint_as_float(tf32_rn_bits(__double2float_rn(r1 - (double)b)));
-                v1 = t == 0 ? a : (t == 1 ? b : cc);
-            }
         }
         bt1[idx] = v1;
-        if (i < ld2) bt2[(size_t)j * ld2 + i] = v2;
+        bt2[idx] = v2;
         if (i < d) ct[(size_t)i * k_rows + j] = j < k ? c[(size_t)j * d + i] : 0.0;
+        if (i == 0) h32[j] = j < k ? __double2float_rn(h[j]) : -INFINITY;
     }
 }
 
-// ------------------------------------------------------------------------------------------
 __device__ __forceinline__ void named_barrier(int id, int nthreads) {
     asm volatile("bar.sync %0, %1;\n" ::"r"(id), "r"(nthreads) : "memory");
 }
@@ -267,8 +255,8 @@ __global__ void __launch_bounds__(kFastThreads, 1)
 #endif
     // carve-up (the B tiles first: the swizzle wants 1024-byte alignment)
     const int bblk = p.Nacc * 128; // bytes of one 32-column block of B
-    unsigned char *B1 = smem_raw;                       // (KB + 1) blocks of bt1
-    unsigned char *B2 = B1 + (size_t)(p.KB + 1) * bblk; // KB blocks of bt2
+    unsigned char *B1 = smem_raw;                 // KB blocks of bt1
+    unsigned char *B2 = B1 + (size_t)p.KB * bblk; // KB blocks of bt2
     unsigned char *stage0 = B2 + (size_t)p.KB * bblk;   // NS half stages
     float *nsq_s = reinterpret_cast<float *>(stage0 + (size_t)p.NS * p.stage_bytes); // [2 tiles][2 column halves][128]
     float *mrg_b = nsq_s + 4 * kFastRows;                                             // [128] second column half: best
@@ -276,7 +264,8 @@ __global__ void __launch_bounds__(kFastThreads, 1)
     int *mrg_i = reinterpret_cast<int *>(mrg_s + kFastRows);                          // [128]                     index
     int *lab_s = mrg_i + kFastRows;                                                   // [128] label by TMEM lane, -1: not decided
     int *counts_s = lab_s + kFastRows;                                                // [Nacc]
-    unsigned long long *bars = reinterpret_cast<unsigned long long *>(counts_s + p.Nacc);
+    float *h_s = reinterpret_cast<float *>(counts_s + p.Nacc);                        // [Nacc] -|c|^2/2
+    unsigned long long *bars = reinterpret_cast<unsigned long long *>(h_s + p.Nacc);
     unsigned *tmem_slot = reinterpret_cast<unsigned *>(bars + 40);
     auto bar = [&](int i) { return (unsigned)__cvta_generic_to_shared(&bars[i]); };
     // barrier indices
@@ -301,7 +290,10 @@ __global__ void __launch_bounds__(kFastThreads, 1)
         mbar_init(bar(B_FULL), 1);
         mbar_fence_init();
     }
-    for (int i = threadIdx.x; i < p.Nacc; i += blockDim.x) counts_s[i] = 0;
+    for (int i = threadIdx.x; i < p.Nacc; i += blockDim.x) {
+        counts_s[i] = 0;
+        h_s[i] = p.h32[i];
+    }
     if (warp == kMmaWarp) tmem_alloc((unsigned)__cvta_generic_to_shared(tmem_slot), kFastTmemCols);
     tc_fence_before();
     __syncthreads();
@@ -321,14 +313,6 @@ __global__ void __launch_bounds__(kFastThreads, 1)
         const int L = 32 * q + lane;
         const int rho = fast_row_of_lane(L);
         const unsigned lane_sel = (unsigned)(32 * q) << 16;
-        if (cs == 0) {
-            // the constant column block [1, 1, 1, 0, ...] that multiplies (h1, h2, h3)
-            unsigned ones[16];
-#pragma unroll
-            for (int i = 0; i < 16; i++) ones[i] = i < 3 ? __float_as_uint(1.0f) : 0u;
-            tmem_st8(tmem + lane_sel + kFastOnesCol, ones);
-            tmem_wait_st();
-        }
         const int steps = (p.Kd + 15) >> 4;
         const int step_lo = cs == 0 ? 0 : (steps + 1) >> 1, step_hi = cs == 0 ? (steps + 1) >> 1 : steps;
         const size_t row_off = (size_t)((rho & 63) >> 3) * p.group_bytes + (size_t)(rho & 7) * p.d * 8;
@@ -448,12 +432,13 @@ __global__ void __launch_bounds__(kFastThreads, 1)
                         const int g0 = 16 * (cc + t);
                         if (p.dbg_full && rho < rows_valid) {
 #pragma unroll
-                            for (int j = 0; j < 16; j++) p.dbg_full[(size_t)(row0 + rho) * p.Nacc + g0 + j] = __uint_as_float(v[t][j]);
+                            for (int j = 0; j < 16; j++)
+                                p.dbg_full[(size_t)(row0 + rho) * p.Nacc + g0 + j] = __uint_as_float(v[t][j]) + h_s[g0 + j];
                         }
 #pragma unroll
                         for (int j = 0; j < 16; j += 2) {
-                            const float x0 = __uint_as_float(v[t][j]), x1 = __uint_as_float(v[t][j + 1]);
                             const int c = g0 + j;
+                            const float x0 = __uint_as_float(v[t][j]) + h_s[c], x1 = __uint_as_float(v[t][j + 1]) + h_s[c + 1];
                             s0 = fmaxf(s0, fminf(b0, x0));
                             i0 = x0 > b0 ? c : i0;
                             b0 = fmaxf(b0, x0);
@@ -530,9 +515,9 @@ __global__ void __launch_bounds__(kFastThreads, 1)
     } else if (warp == kLoaderWarp) {
         // =========================== loader (warp converged, one elected lane issues) ===========================
         if (elect_one()) {
-            // the centroid terms, once: (KB + 1) + KB boxes of Nacc rows x 32 columns
-            mbar_arrive_expect_tx(bar(B_FULL), (unsigned)((2 * p.KB + 1) * bblk));
-            for (int b = 0; b <= p.KB; b++)
+            // the centroid terms, once: KB + KB boxes of Nacc rows x 32 columns
+            mbar_arrive_expect_tx(bar(B_FULL), (unsigned)(2 * p.KB * bblk));
+            for (int b = 0; b < p.KB; b++)
                 tma_load_2d((unsigned)__cvta_generic_to_shared(B1 + (size_t)b * bblk), &map1, 32 * b, 0, bar(B_FULL));
             for (int b = 0; b < p.KB; b++)
                 tma_load_2d((unsigned)__cvta_generic_to_shared(B2 + (size_t)b * bblk), &map2, 32 * b, 0, bar(B_FULL));
@@ -599,7 +584,7 @@ __global__ void __launch_bounds__(kFastThreads, 1)
             const unsigned a_hi = tmem + kFastACol + (unsigned)a * a_cols, a_lo = a_hi + (unsigned)p.Kd;
             const unsigned dt = tmem + d_col0 + (unsigned)e * (unsigned)p.Nacc;
             if (elect_one()) {
-                // small terms first: xh.c2, then xl.c1; then the main term xh.c1 and the constant column times (h1, h2, h3)
+                // small terms first: xh.c2, then xl.c1; then the main term xh.c1
                 for (int sl = 0; sl < slabs; sl++) {
                     const unsigned off = (unsigned)(sl >> 2) * (unsigned)bblk + (unsigned)(sl & 3) * 32u;
                     tc_mma_tf32_ts(dt, a_hi + 8u * sl, desc_hi | (uint64_t)(((b2 + off) >> 4) & 0x3fffu), idesc, sl > 0);
@@ -612,8 +597,6 @@ __global__ void __launch_bounds__(kFastThreads, 1)
                     const unsigned off = (unsigned)(sl >> 2) * (unsigned)bblk + (unsigned)(sl & 3) * 32u;
                     tc_mma_tf32_ts(dt, a_hi + 8u * sl, desc_hi | (uint64_t)(((b1 + off) >> 4) & 0x3fffu), idesc, 1);
                 }
-                tc_mma_tf32_ts(dt, tmem + kFastOnesCol, desc_hi | (uint64_t)(((b1 + (unsigned)p.KB * (unsigned)bblk) >> 4) & 0x3fffu),
-                               idesc, 1);
                 tc_commit(bar(A_EMPTY + a)); // the A buffer may be overwritten once these MMAs have read it
                 tc_commit(bar(D_FULL + e));  // and the scores are complete
             }
