@@ -273,11 +273,14 @@ def run_ours(args):
         if fast:
             # the contraction is on the tcgen05 pipe (three TF32 passes: 6*k*d flop per point-iteration);
             # nothing FP64 is left on the critical path, so the row stream from HBM is what bounds it
-            roof = dict(hbm)
             tf32_peak = peaks.get("bf16_tflops", 0.0) / 2.0
-            roof["tf32_tensor"] = {"achieved": 3.0 * tf, "peak": tf32_peak, "unit": "TFLOP/s",
-                                   "frac": 3.0 * tf / tf32_peak if tf32_peak else None,
-                                   "peak_source": "half of MEASURED_PEAKS.json's burst bf16 figure (TF32 runs at half the bf16 rate)"}
+            tf32 = {"bound": "tensor", "achieved": 3.0 * tf, "peak": tf32_peak, "unit": "TFLOP/s",
+                    "frac": 3.0 * tf / tf32_peak if tf32_peak else 0.0,
+                    "peak_source": "half of MEASURED_PEAKS.json's burst bf16 figure (TF32 runs at half the bf16 rate); "
+                                   "flop = 3 TF32 passes x 2*k*d per point-iteration"}
+            # few centroids: the row stream from HBM bounds it; many: the three TF32 passes on the tcgen05 pipe
+            roof = dict(tf32) if tf32["frac"] > hbm_frac else dict(hbm)
+            roof["tf32_tensor"] = tf32
             kern = "fmlk::assign_fast_kernel<true> (tcgen05 TF32x3 contraction, FP64 exact replay of near-tie rows, sums by bulk reductions)"
         elif tensor_frac >= hbm_frac:
             roof = {"bound": "tensor", "achieved": tf, "peak": dmma_peak, "unit": "TFLOP/s", "frac": tensor_frac,
@@ -390,7 +393,7 @@ def run_ours(args):
                 models[name] = nr["model"]
                 recs[name] = {"value": nr["value"], "unit": UNIT, "ms_per_round": nr["ms_per_round"],
                               "per_gpu_fp64_equivalent_tflops": nr["roofline"]["fp64_tensor"]["achieved"],
-                              "roofline": {kx: nr["roofline"][kx] for kx in ("bound", "achieved", "peak", "unit", "frac", "kernel")},
+                              "roofline": {kx: nr["roofline"][kx] for kx in ("bound", "achieved", "peak", "unit", "frac", "kernel", "launch")},
                               "took_tcgen05_kernel": nr["fast"], "rechecked_rows": nr["prof"]["rechecked_rows"]}
             if "tf32x3+f64-recheck" in recs:
                 recs["tf32x3+f64-recheck"]["weights_bit_exact_vs_f64_mode"] = bool(

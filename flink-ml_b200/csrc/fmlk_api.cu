@@ -504,7 +504,7 @@ void drain_events(fmlk_ctx *ctx) {
 
 // ---- fast mode (fmlk_fast.cuh): geometry, per-round operand preparation, launch -------------------
 struct FastPlan {
-    int Kd, KB, k_rows, Nacc, nA, NS, stage_bytes, group_bytes;
+    int Kd, KB, k_rows, Nacc, P, NB, nA, NS, stage_bytes, group_bytes;
     size_t smem;
 };
 
@@ -523,34 +523,54 @@ EncodeTiledFn encode_tiled() {
     return fn;
 }
 
-// Does the tcgen05 kernel take (k, d)?  First version: centroid terms resident in shared memory
-// (k <= 240 after rounding up to 16), rows of at most 128 columns, at least two 64-row half stages.
+// Does the tcgen05 kernel take (k, d)?  Rows of at most 128 columns (even).  The TF32 terms of the
+// centroids stay resident in shared memory when they fit beside the row stages (one pass, Nacc = k rounded
+// up to 16); otherwise they stream from L2 through a two-stage ring, Nacc centroids per pass.
 bool fast_shape(const fmlk_ctx *ctx, int k, int d, bool accum, FastPlan *out) {
     if (!(ctx->flags & FMLK_FLAG_FAST_TF32)) return false;
     if (d < 2 || (d & 1) || d > 128) return false;
     FastPlan f{};
     f.Kd = (d + 7) & ~7;
     f.KB = (f.Kd + 31) / 32;
-    f.k_rows = (k + 15) & ~15;
-    if (f.k_rows > 256) return false;
-    f.Nacc = f.k_rows;
-    f.nA = (kFastACol + 2 * 2 * f.Kd + 2 * f.Nacc <= kFastTmemCols) ? 2 : 1;
-    if (kFastACol + f.nA * 2 * f.Kd + 2 * f.Nacc > kFastTmemCols) return false;
     f.group_bytes = kFastGroupRows * d * 8 + 16;
     f.stage_bytes = kFastHalfGroups * f.group_bytes;
-    const size_t fixed = (size_t)(2 * f.KB) * f.Nacc * 128 + 8 * kFastRows * sizeof(float) + (size_t)f.Nacc * 2 * sizeof(int) +
-                         40 * 8 + 16 + 1024 /* alignment slack */;
     // training keeps a half stage until its rows have been added: a whole tile in flight beside the one in work
     const int min_stages = accum ? 4 : 2;
-    if (fixed + (size_t)min_stages * f.stage_bytes > ctx->smem_optin) return false;
-    f.NS = (int)std::min<size_t>(kFastMaxStages, (ctx->smem_optin - fixed) / f.stage_bytes);
-    f.smem = fixed + (size_t)f.NS * f.stage_bytes;
+    auto fits = [&](int nacc, int passes, int nb) -> bool {
+        const int na = (kFastACol + 2 * 2 * f.Kd + 2 * nacc <= kFastTmemCols) ? 2 : 1;
+        if (kFastACol + na * 2 * f.Kd + 2 * nacc > kFastTmemCols) return false;
+        const size_t k_rows = (size_t)nacc * passes;
+        const size_t fixed = (size_t)nb * (2 * f.KB) * nacc * 128 + 8 * kFastRows * sizeof(float) + k_rows * 2 * sizeof(int) +
+                             48 * 8 + 16 + 1024 /* alignment slack */;
+        if (fixed + (size_t)min_stages * f.stage_bytes > ctx->smem_optin) return false;
+        f.Nacc = nacc;
+        f.P = passes;
+        f.NB = nb;
+        f.nA = na;
+        f.k_rows = (int)k_rows;
+        f.NS = (int)std::min<size_t>(kFastMaxStages, (ctx->smem_optin - fixed) / f.stage_bytes);
+        f.smem = fixed + (size_t)f.NS * f.stage_bytes;
+        return true;
+    };
+    const int k16 = (k + 15) & ~15;
+    bool ok = k16 <= 256 && fits(k16, 1, 1);
+    if (!ok) {
+        if (k16 > 4096) return false; // (the per-row bookkeeping in shared memory is sized by k)
+        // streamed: the widest pass that leaves room for the row stages, two ring stages
+        static const int widths[] = {128, 112, 96, 80, 64, 48, 32};
+        for (int w : widths) {
+            if (w >= k16) continue;
+            if ((ok = fits(w, (k16 + w - 1) / w, 2))) break;
+        }
+    }
+    if (!ok) return false;
     *out = f;
     return true;
 }
 
 int ensure_fast(fmlk_ctx *ctx, const FastPlan &f) {
     const size_t need = (size_t)f.k_rows * (32 * f.KB);
+    const size_t need_h = (size_t)f.k_rows;
     int rc;
     bool fresh = false;
     if (need > ctx->bt_cap) {
@@ -564,7 +584,7 @@ int ensure_fast(fmlk_ctx *ctx, const FastPlan &f) {
         if ((rc = dev_alloc(ctx, &ctx->bt1, need))) return rc;
         if ((rc = dev_alloc(ctx, &ctx->bt2, need))) return rc;
         if ((rc = dev_alloc(ctx, &ctx->ct, need))) return rc;
-        if ((rc = dev_alloc(ctx, &ctx->h32, (size_t)256))) return rc;
+        if ((rc = dev_alloc(ctx, &ctx->h32, std::max<size_t>(need_h, 4096 + 128)))) return rc;
         ctx->bt_cap = need;
         fresh = true;
     }
@@ -616,6 +636,8 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
     p.KB = f.KB;
     p.k = ctx->k;
     p.Nacc = f.Nacc;
+    p.P = f.P;
+    p.NB = f.NB;
     p.nA = f.nA;
     p.NS = f.NS;
     p.stage_bytes = f.stage_bytes;
@@ -680,7 +702,9 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
     return FMLK_OK;
 }
 
-int prep_centroids(fmlk_ctx *ctx) {
+// accum: the launch that follows accumulates (the fast mode's geometry, and with it the layout of the
+// centroid terms, differs between training and predict)
+int prep_centroids(fmlk_ctx *ctx, bool accum) {
     const int k_pad = (ctx->k + 7) & ~7;
     prep_centroids_kernel<<<1, 256, 0, ctx->stream>>>(ctx->centroids, ctx->k, k_pad, ctx->md,
                                                      (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0, ctx->cn, ctx->h,
@@ -688,7 +712,7 @@ int prep_centroids(fmlk_ctx *ctx) {
     ctx->total_launches++;
     CK(ctx, cudaGetLastError());
     FastPlan f;
-    if (fast_shape(ctx, ctx->k, ctx->md, false, &f)) {
+    if (fast_shape(ctx, ctx->k, ctx->md, accum, &f)) {
         int rc = ensure_fast(ctx, f);
         if (rc) return rc;
         const int total = f.k_rows * (32 * f.KB);
@@ -818,7 +842,7 @@ int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
     }
     const size_t stride = partial_stride(ctx->k, ctx->md); // len rounded up to even
     if ((rc = ensure_partials(ctx, stride * cfg.n_partials))) return rc;
-    if ((rc = prep_centroids(ctx))) return rc;
+    if ((rc = prep_centroids(ctx, true))) return rc;
     CK(ctx, cudaMemsetAsync(ctx->partials, 0, stride * cfg.n_partials * sizeof(double), ctx->stream));
     if (extra_rows) {
         if ((rc = launch_assign(ctx, cfg, extra_rows, extra_n, nullptr, true))) return rc;
@@ -1394,7 +1418,7 @@ static int32_t predict_impl(fmlk_ctx *ctx, const double *rows_dev, int64_t n, in
     PredictPlan pl;
     int rc = plan_predict(ctx, &pl);
     if (rc) return rc;
-    if ((rc = prep_centroids(ctx))) return rc;
+    if ((rc = prep_centroids(ctx, false))) return rc;
     return run_predict(ctx, pl, rows_dev, n, labels_dev);
 }
 
@@ -1422,7 +1446,7 @@ int32_t fmlk_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t 
     if ((rc = ensure_stage(ctx, (size_t)step * d, (size_t)step))) return rc;
     PredictPlan pl;
     if ((rc = plan_predict(ctx, &pl))) return rc;
-    if ((rc = prep_centroids(ctx))) return rc;
+    if ((rc = prep_centroids(ctx, false))) return rc;
     for (int64_t off = 0; off < n; off += step) {
         const int64_t m = std::min(step, n - off);
         CK(ctx, cudaMemcpyAsync(ctx->stage_rows, rows_host + off * d, (size_t)m * d * sizeof(double),
@@ -1447,7 +1471,7 @@ int32_t fmlk_predict_cached(fmlk_ctx *ctx, int32_t *out_labels_host) {
     if ((rc = ensure_stage(ctx, 0, (size_t)ctx->n_total))) return rc;
     PredictPlan pl;
     if ((rc = plan_predict(ctx, &pl))) return rc;
-    if ((rc = prep_centroids(ctx))) return rc;
+    if ((rc = prep_centroids(ctx, false))) return rc;
     int64_t off = 0;
     for (const Chunk &ch : ctx->chunks) {
         if ((rc = run_predict(ctx, pl, ch.ptr, ch.rows, ctx->stage_labels + off))) return rc;
@@ -1764,9 +1788,10 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
         if (accumulate) cudaFuncGetAttributes(&fa, assign_fast_kernel<true>);
         else cudaFuncGetAttributes(&fa, assign_fast_kernel<false>);
         snprintf(out, (size_t)out_len,
-                 "fast=1 regs=%d local=%zu grid=%d block=%d smem=%zu Kd=%d KB=%d Nacc=%d tmem_a_buffers=%d half_stages=%d "
-                 "n_partials=%d wide=0 (rows below 4096 or unaligned rows take the FP64 kernel)",
-                 fa.numRegs, fa.localSizeBytes, ctx->sm_count, kFastThreads, f.smem, f.Kd, f.KB, f.Nacc, f.nA, f.NS, c.n_partials);
+                 "fast=1 regs=%d local=%zu grid=%d block=%d smem=%zu Kd=%d KB=%d Nacc=%d passes=%d centroid_ring=%d "
+                 "tmem_a_buffers=%d half_stages=%d n_partials=%d wide=0 (rows below 4096 or unaligned rows take the FP64 kernel)",
+                 fa.numRegs, fa.localSizeBytes, ctx->sm_count, kFastThreads, f.smem, f.Kd, f.KB, f.Nacc, f.P, f.P > 1 ? f.NB : 0,
+                 f.nA, f.NS, c.n_partials);
         return FMLK_OK;
     }
     cudaFuncAttributes fa{};

@@ -34,8 +34,11 @@
 //                    (16-byte pad between the groups: conflict-free 128-bit reads, one thread per row)
 //   converter warps  one thread per row: FP64 -> (xh, xl) TF32, tcgen05.st into TMEM (the A operand
 //                    never touches shared memory), FP32 row norm -> decision threshold
-//   MMA warp         one thread: tcgen05.mma A(TMEM) x B(shared, 128-byte swizzle, staged once by
-//                    tensor-map TMA loads), tcgen05.commit -> mbarriers
+//   MMA warp         one thread: tcgen05.mma A(TMEM) x B(shared, 128-byte swizzle, staged by tensor-map
+//                    TMA loads), tcgen05.commit -> mbarriers
+//   centroid warp    the TF32 terms of the centroids: once, when they all fit beside the rows (P = 1);
+//                    otherwise P passes of Nacc centroids per row tile stream from L2 through a ring
+//                    (the scores of pass p + 1 are multiplied while the epilogue reads those of pass p)
 //   epilogue warps   eight warps on every tile: one thread per row and column half runs tcgen05.ld and the
 //                    running (best, second, index); the halves meet in shared memory, then the margin
 //                    test and the label.  Training: sixteen lanes of each warp issue one
@@ -59,9 +62,10 @@ constexpr int kFastConvSets = 2;     // warps 0..7   two sets of four (TMEM lane
 constexpr int kFastConvWarps = 4 * kFastConvSets;
 constexpr int kFastEpiWarp0 = kFastConvWarps; // warps 8..15  two sets of four, each half of the score columns
 constexpr int kFastEpiWarps = 8;
-constexpr int kFastLoaderWarp = kFastEpiWarp0 + kFastEpiWarps;
+constexpr int kFastLoaderWarp = kFastEpiWarp0 + kFastEpiWarps; // rows
 constexpr int kFastMmaWarp = kFastLoaderWarp + 1;
-constexpr int kFastWarps = kFastMmaWarp + 1;
+constexpr int kFastBWarp = kFastMmaWarp + 1;                    // centroid terms
+constexpr int kFastWarps = kFastBWarp + 1;
 constexpr int kFastThreads = kFastWarps * 32;
 constexpr int kFastMaxStages = 8;
 constexpr int kFastTmemCols = 512;
@@ -75,6 +79,8 @@ struct FastParams {
     int32_t KB;       // 32-column blocks of B covering Kd
     int32_t k;
     int32_t Nacc;     // accumulator columns = centroids per pass (multiple of 16, <= 256)
+    int32_t P;        // passes over the centroids per row tile (1: all of them resident in shared memory)
+    int32_t NB;       // stages of the centroid ring when P > 1 (each holds the 2 KB blocks of one pass)
     int32_t nA;       // A buffers in TMEM (1 or 2)
     int32_t NS;       // 64-row half stages in shared memory (2 .. 8)
     int32_t stage_bytes; // of one half stage
@@ -255,22 +261,23 @@ __global__ void __launch_bounds__(kFastThreads, 1)
 #endif
     // carve-up (the B tiles first: the swizzle wants 1024-byte alignment)
     const int bblk = p.Nacc * 128; // bytes of one 32-column block of B
-    unsigned char *B1 = smem_raw;                 // KB blocks of bt1
-    unsigned char *B2 = B1 + (size_t)p.KB * bblk; // KB blocks of bt2
-    unsigned char *stage0 = B2 + (size_t)p.KB * bblk;   // NS half stages
+    const int bstage = 2 * p.KB * bblk; // one stage of the centroid ring: KB blocks of bt1, then KB blocks of bt2
+    unsigned char *Bring = smem_raw;
+    unsigned char *stage0 = Bring + (size_t)max(p.NB, 1) * bstage; // NS half stages
     float *nsq_s = reinterpret_cast<float *>(stage0 + (size_t)p.NS * p.stage_bytes); // [2 tiles][2 column halves][128]
     float *mrg_b = nsq_s + 4 * kFastRows;                                             // [128] second column half: best
     float *mrg_s = mrg_b + kFastRows;                                                 // [128]                     second
     int *mrg_i = reinterpret_cast<int *>(mrg_s + kFastRows);                          // [128]                     index
     int *lab_s = mrg_i + kFastRows;                                                   // [128] label by TMEM lane, -1: not decided
-    int *counts_s = lab_s + kFastRows;                                                // [Nacc]
-    float *h_s = reinterpret_cast<float *>(counts_s + p.Nacc);                        // [Nacc] -|c|^2/2
-    unsigned long long *bars = reinterpret_cast<unsigned long long *>(h_s + p.Nacc);
+    const int k_rows = p.P * p.Nacc;
+    int *counts_s = lab_s + kFastRows;                                                // [k_rows]
+    float *h_s = reinterpret_cast<float *>(counts_s + k_rows);                        // [k_rows] -|c|^2/2
+    unsigned long long *bars = reinterpret_cast<unsigned long long *>(h_s + k_rows);
     unsigned *tmem_slot = reinterpret_cast<unsigned *>(bars + 40);
     auto bar = [&](int i) { return (unsigned)__cvta_generic_to_shared(&bars[i]); };
     // barrier indices
     const int FULL_X = 0, X_EMPTY = 8, A_FULL = 16, A_EMPTY = 18, D_FULL = 20, D_EMPTY = 22, THR_FULL = 24, THR_EMPTY = 26,
-              B_FULL = 32;
+              B_FULL = 32, B_EMPTY = 36;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kFastMaxStages; s++) {
@@ -287,10 +294,13 @@ __global__ void __launch_bounds__(kFastThreads, 1)
             mbar_init(bar(THR_FULL + a), kFastConvWarps);
             mbar_init(bar(THR_EMPTY + a), 4);
         }
-        mbar_init(bar(B_FULL), 1);
+        for (int s = 0; s < 4; s++) {
+            mbar_init(bar(B_FULL + s), 1);
+            mbar_init(bar(B_EMPTY + s), 1);
+        }
         mbar_fence_init();
     }
-    for (int i = threadIdx.x; i < p.Nacc; i += blockDim.x) {
+    for (int i = threadIdx.x; i < k_rows; i += blockDim.x) {
         counts_s[i] = 0;
         h_s[i] = p.h32[i];
     }
@@ -401,59 +411,63 @@ __global__ void __launch_bounds__(kFastThreads, 1)
         const int rr = fast_row_of_lane(Lr);
         const unsigned red_off = (unsigned)((rr & 63) >> 3) * (unsigned)p.group_bytes + (unsigned)(rr & 7) * row_bytes;
         int hs = (q >> 1) % p.NS;
+        unsigned gp = 0; // passes done so far: the scores of pass gp are in accumulator gp & 1
         for (int i = 0; i < my_tiles; i++) {
             const int e = i & 1;
             const int64_t tile = blockIdx.x + (int64_t)i * gridDim.x;
             const int64_t row0 = tile * kFastRows;
             const int rows_valid = tile == total_tiles - 1 ? last_rows : kFastRows;
             const unsigned ph = (unsigned)((i >> 1) & 1);
-            const unsigned d_tmem = tmem + lane_sel + d_col0 + (unsigned)e * (unsigned)p.Nacc;
             FAST_TRACE(5)
             float nsq = 0.f;
             if (ec == 0) {
                 mbar_wait_relaxed(bar(THR_FULL + e), ph);
                 nsq = nsq_s[(e * 2) * kFastRows + L] + nsq_s[(e * 2 + 1) * kFastRows + L];
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(THR_EMPTY + e));
             }
-            mbar_wait_relaxed(bar(D_FULL + e), ph);
-            tc_fence_after();
-            FAST_TRACE(6)
-            // two independent (best, second, index) chains, merged at the end
+            // two independent (best, second, index) chains over all passes, merged at the end
             float b0 = -INFINITY, s0 = -INFINITY, b1 = -INFINITY, s1 = -INFINITY;
             int i0 = 0, i1 = 0;
-            for (int cc = c_lo; cc < c_hi; cc += 2) {
-                unsigned v[2][16];
+            for (int ps = 0; ps < p.P; ps++, gp++) {
+                const int db = (int)(gp & 1u);
+                const unsigned d_tmem = tmem + lane_sel + d_col0 + (unsigned)db * (unsigned)p.Nacc;
+                const int cbase = ps * p.Nacc;
+                mbar_wait_relaxed(bar(D_FULL + db), (gp >> 1) & 1u);
+                tc_fence_after();
+                FAST_TRACE(6)
+                for (int cc = c_lo; cc < c_hi; cc += 2) {
+                    unsigned v[2][16];
 #pragma unroll
-                for (int t = 0; t < 2; t++)
-                    if (cc + t < c_hi) tmem_ld16(d_tmem + (unsigned)(16 * (cc + t)), v[t]);
-                tmem_wait_ld();
+                    for (int t = 0; t < 2; t++)
+                        if (cc + t < c_hi) tmem_ld16(d_tmem + (unsigned)(16 * (cc + t)), v[t]);
+                    tmem_wait_ld();
 #pragma unroll
-                for (int t = 0; t < 2; t++) {
-                    if (cc + t < c_hi) {
-                        const int g0 = 16 * (cc + t);
-                        if (p.dbg_full && rho < rows_valid) {
+                    for (int t = 0; t < 2; t++) {
+                        if (cc + t < c_hi) {
+                            const int g0 = cbase + 16 * (cc + t);
+                            if (p.dbg_full && rho < rows_valid) {
 #pragma unroll
-                            for (int j = 0; j < 16; j++)
-                                p.dbg_full[(size_t)(row0 + rho) * p.Nacc + g0 + j] = __uint_as_float(v[t][j]) + h_s[g0 + j];
-                        }
+                                for (int j = 0; j < 16; j++)
+                                    p.dbg_full[(size_t)(row0 + rho) * k_rows + g0 + j] = __uint_as_float(v[t][j]) + h_s[g0 + j];
+                            }
 #pragma unroll
-                        for (int j = 0; j < 16; j += 2) {
-                            const int c = g0 + j;
-                            const float x0 = __uint_as_float(v[t][j]) + h_s[c], x1 = __uint_as_float(v[t][j + 1]) + h_s[c + 1];
-                            s0 = fmaxf(s0, fminf(b0, x0));
-                            i0 = x0 > b0 ? c : i0;
-                            b0 = fmaxf(b0, x0);
-                            s1 = fmaxf(s1, fminf(b1, x1));
-                            i1 = x1 > b1 ? c + 1 : i1;
-                            b1 = fmaxf(b1, x1);
+                            for (int j = 0; j < 16; j += 2) {
+                                const int c = g0 + j;
+                                const float x0 = __uint_as_float(v[t][j]) + h_s[c], x1 = __uint_as_float(v[t][j + 1]) + h_s[c + 1];
+                                s0 = fmaxf(s0, fminf(b0, x0));
+                                i0 = x0 > b0 ? c : i0;
+                                b0 = fmaxf(b0, x0);
+                                s1 = fmaxf(s1, fminf(b1, x1));
+                                i1 = x1 > b1 ? c + 1 : i1;
+                                b1 = fmaxf(b1, x1);
+                            }
                         }
                     }
                 }
-            }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) {
-                mbar_arrive(bar(D_EMPTY + e));
-                if (ec == 0) mbar_arrive(bar(THR_EMPTY + e));
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(D_EMPTY + db));
             }
             FAST_TRACE(7)
             float best = fmaxf(b0, b1);
@@ -514,15 +528,6 @@ __global__ void __launch_bounds__(kFastThreads, 1)
         if (ACCUM) bulk_wait_group_all();
     } else if (warp == kLoaderWarp) {
         // =========================== loader (warp converged, one elected lane issues) ===========================
-        if (elect_one()) {
-            // the centroid terms, once: KB + KB boxes of Nacc rows x 32 columns
-            mbar_arrive_expect_tx(bar(B_FULL), (unsigned)(2 * p.KB * bblk));
-            for (int b = 0; b < p.KB; b++)
-                tma_load_2d((unsigned)__cvta_generic_to_shared(B1 + (size_t)b * bblk), &map1, 32 * b, 0, bar(B_FULL));
-            for (int b = 0; b < p.KB; b++)
-                tma_load_2d((unsigned)__cvta_generic_to_shared(B2 + (size_t)b * bblk), &map2, 32 * b, 0, bar(B_FULL));
-        }
-        __syncwarp();
         const unsigned row_bytes = (unsigned)p.d * 8u;
         const unsigned group_copy = row_bytes * kFastGroupRows;
         int hs = 0;
@@ -567,44 +572,89 @@ __global__ void __launch_bounds__(kFastThreads, 1)
     } else if (warp == kMmaWarp) {
         // =========================== MMA issuer (warp converged, one elected lane issues) ===========================
         const unsigned idesc = umma_idesc_tf32(p.Nacc);
-        const unsigned b1 = (unsigned)__cvta_generic_to_shared(B1), b2 = (unsigned)__cvta_generic_to_shared(B2);
+        const unsigned bring = (unsigned)__cvta_generic_to_shared(Bring);
         const int slabs = p.Kd >> 3;
         const uint64_t desc_hi = ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61) | ((uint64_t)1 << 16);
-        mbar_wait_relaxed(bar(B_FULL), 0);
-        int a = 0;
-        unsigned ph_a = 0;
+        if (p.P == 1) mbar_wait_relaxed(bar(B_FULL), 0); // resident centroids: loaded once
+        int a = 0, bs = 0;
+        unsigned ph_a = 0, ph_b = 0, gp = 0;
         for (int i = 0; i < my_tiles; i++) {
-            const int e = i & 1;
             FAST_TRACE(12)
             mbar_wait_relaxed(bar(A_FULL + a), ph_a);
-            FAST_TRACE(13)
-            mbar_wait_relaxed(bar(D_EMPTY + e), (unsigned)(((i >> 1) & 1) ^ 1));
             tc_fence_after();
-            FAST_TRACE(14)
+            FAST_TRACE(13)
             const unsigned a_hi = tmem + kFastACol + (unsigned)a * a_cols, a_lo = a_hi + (unsigned)p.Kd;
-            const unsigned dt = tmem + d_col0 + (unsigned)e * (unsigned)p.Nacc;
-            if (elect_one()) {
-                // small terms first: xh.c2, then xl.c1; then the main term xh.c1
-                for (int sl = 0; sl < slabs; sl++) {
-                    const unsigned off = (unsigned)(sl >> 2) * (unsigned)bblk + (unsigned)(sl & 3) * 32u;
-                    tc_mma_tf32_ts(dt, a_hi + 8u * sl, desc_hi | (uint64_t)(((b2 + off) >> 4) & 0x3fffu), idesc, sl > 0);
+            for (int ps = 0; ps < p.P; ps++, gp++) {
+                const int db = (int)(gp & 1u);
+                if (p.P > 1) mbar_wait_relaxed(bar(B_FULL + bs), ph_b);
+                mbar_wait_relaxed(bar(D_EMPTY + db), ((gp >> 1) & 1u) ^ 1u);
+                tc_fence_after();
+                FAST_TRACE(14)
+                const unsigned dt = tmem + d_col0 + (unsigned)db * (unsigned)p.Nacc;
+                const unsigned b1 = bring + (unsigned)bs * (unsigned)bstage, b2 = b1 + (unsigned)p.KB * (unsigned)bblk;
+                if (elect_one()) {
+                    // small terms first: xh.c2, then xl.c1; then the main term xh.c1
+                    for (int sl = 0; sl < slabs; sl++) {
+                        const unsigned off = (unsigned)(sl >> 2) * (unsigned)bblk + (unsigned)(sl & 3) * 32u;
+                        tc_mma_tf32_ts(dt, a_hi + 8u * sl, desc_hi | (uint64_t)(((b2 + off) >> 4) & 0x3fffu), idesc, sl > 0);
+                    }
+                    for (int sl = 0; sl < slabs; sl++) {
+                        const unsigned off = (unsigned)(sl >> 2) * (unsigned)bblk + (unsigned)(sl & 3) * 32u;
+                        tc_mma_tf32_ts(dt, a_lo + 8u * sl, desc_hi | (uint64_t)(((b1 + off) >> 4) & 0x3fffu), idesc, 1);
+                    }
+                    for (int sl = 0; sl < slabs; sl++) {
+                        const unsigned off = (unsigned)(sl >> 2) * (unsigned)bblk + (unsigned)(sl & 3) * 32u;
+                        tc_mma_tf32_ts(dt, a_hi + 8u * sl, desc_hi | (uint64_t)(((b1 + off) >> 4) & 0x3fffu), idesc, 1);
+                    }
+                    if (p.P > 1) tc_commit(bar(B_EMPTY + bs)); // this ring stage may be refilled once the MMAs have read it
+                    if (ps == p.P - 1) tc_commit(bar(A_EMPTY + a)); // so may the A buffer after the last pass
+                    tc_commit(bar(D_FULL + db)); // and the scores of this pass are complete
                 }
-                for (int sl = 0; sl < slabs; sl++) {
-                    const unsigned off = (unsigned)(sl >> 2) * (unsigned)bblk + (unsigned)(sl & 3) * 32u;
-                    tc_mma_tf32_ts(dt, a_lo + 8u * sl, desc_hi | (uint64_t)(((b1 + off) >> 4) & 0x3fffu), idesc, 1);
+                __syncwarp();
+                if (p.P > 1 && ++bs == p.NB) {
+                    bs = 0;
+                    ph_b ^= 1u;
                 }
-                for (int sl = 0; sl < slabs; sl++) {
-                    const unsigned off = (unsigned)(sl >> 2) * (unsigned)bblk + (unsigned)(sl & 3) * 32u;
-                    tc_mma_tf32_ts(dt, a_hi + 8u * sl, desc_hi | (uint64_t)(((b1 + off) >> 4) & 0x3fffu), idesc, 1);
-                }
-                tc_commit(bar(A_EMPTY + a)); // the A buffer may be overwritten once these MMAs have read it
-                tc_commit(bar(D_FULL + e));  // and the scores are complete
             }
-            __syncwarp();
             FAST_TRACE(15)
             if (++a == p.nA) {
                 a = 0;
                 ph_a ^= 1u;
+            }
+        }
+    } else if (warp == kFastBWarp) {
+        // =========================== centroid terms (warp converged, one elected lane issues) ===========================
+        // a stage = KB boxes of bt1 then KB boxes of bt2, each Nacc rows x 32 columns, rows [pass * Nacc, ...)
+        if (p.P == 1) {
+            if (elect_one()) {
+                mbar_arrive_expect_tx(bar(B_FULL), (unsigned)bstage);
+                for (int b = 0; b < p.KB; b++) {
+                    tma_load_2d((unsigned)__cvta_generic_to_shared(Bring + (size_t)b * bblk), &map1, 32 * b, 0, bar(B_FULL));
+                    tma_load_2d((unsigned)__cvta_generic_to_shared(Bring + (size_t)(p.KB + b) * bblk), &map2, 32 * b, 0, bar(B_FULL));
+                }
+            }
+        } else {
+            int bs = 0;
+            unsigned ph_b = 1;
+            for (int i = 0; i < my_tiles; i++) {
+                for (int ps = 0; ps < p.P; ps++) {
+                    mbar_wait_relaxed(bar(B_EMPTY + bs), ph_b);
+                    if (elect_one()) {
+                        unsigned char *dst = Bring + (size_t)bs * bstage;
+                        mbar_arrive_expect_tx(bar(B_FULL + bs), (unsigned)bstage);
+                        for (int b = 0; b < p.KB; b++) {
+                            tma_load_2d((unsigned)__cvta_generic_to_shared(dst + (size_t)b * bblk), &map1, 32 * b, ps * p.Nacc,
+                                        bar(B_FULL + bs));
+                            tma_load_2d((unsigned)__cvta_generic_to_shared(dst + (size_t)(p.KB + b) * bblk), &map2, 32 * b,
+                                        ps * p.Nacc, bar(B_FULL + bs));
+                        }
+                    }
+                    __syncwarp();
+                    if (++bs == p.NB) {
+                        bs = 0;
+                        ph_b ^= 1u;
+                    }
+                }
             }
         }
     }

@@ -14,7 +14,9 @@ FAST = native.FLAG_FAST_TF32 | native.FLAG_PROFILE
 # (n, d, k): config-2 shape, the reference's two shipped benchmark shapes, ragged sizes, d not a
 # multiple of 8 / 16 / 32, k = 1 .. 256, a tail tile of one row
 SHAPES = [(20000, 64, 100), (8192, 10, 2), (30011, 100, 10), (16400, 32, 200), (4096 + 77, 8, 16), (10000, 2, 3),
-          (9000, 66, 17), (4097, 64, 1), (12345, 48, 33), (6000, 96, 16)]
+          (9000, 66, 17), (4097, 64, 1), (12345, 48, 33), (6000, 96, 16),
+          # more centroids than stay resident: their TF32 terms stream through the ring, several passes per tile
+          (20000, 64, 1000), (9000, 32, 300), (7000, 48, 257), (5000, 16, 2000)]
 
 
 def _data(n, d, k, seed):
