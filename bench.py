@@ -378,6 +378,109 @@ def run_ours(args):
         del x
         torch.cuda.empty_cache()
 
+    # ---- the other two entry points north_star names, each device-timed and end to end from pinned host rows:
+    # KMeansModel.transform (config 3's shape, a bounded number of rows) and OnlineKMeans mini-batches (config 5)
+    transform_rec = online_rec = None
+    if not args.no_extra and args.workload == "c2":
+        modes = [("f64", 0)] + ([] if args.no_fast else [("tf32x3+f64-recheck", native.FLAG_FAST_TF32)])
+        tn, td, tk = args.transform_rows, 128, 1000
+        cent = torch.empty((tk, td), dtype=torch.float64, device=dev)
+        native.generate_dense_dev(local, stream.cuda_stream, 1, 0, 1, tk, td, cent.data_ptr())  # model data: seed 1
+        xt = generate(tn, td)
+        host_t = torch.empty((tn, td), dtype=torch.float64, pin_memory=True)
+        host_t.copy_(xt)
+        torch.cuda.synchronize()
+        cent_h = cent.cpu().numpy()
+        table_t = F.Table({"features": host_t.numpy()})
+        transform_rec = {"workload": "KMeansModel.transform, config 3's shape: %d x %d FP64 rows per GPU, k=%d" % (tn, td, tk),
+                         "unit": "rows/s", "modes": {}}
+        ref_labels = None
+        for name, fl in modes:
+            cl = K.Cluster(rank, world, local, flags=fl | native.FLAG_PROFILE, host_group=host_group)
+            cx = cl.context()
+            cx.set_stream(stream.cuda_stream)
+            cx.set_centroids(cent_h)
+            lab = torch.empty((tn,), dtype=torch.int32, device=dev)
+            for _ in range(3):
+                cx.predict_dev(xt.data_ptr(), tn, td, lab.data_ptr())
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            e0.record(stream)
+            for _ in range(3):
+                cx.predict_dev(xt.data_ptr(), tn, td, lab.data_ptr())
+            e1.record(stream)
+            barrier()
+            ms = torch.tensor([e0.elapsed_time(e1) / 3], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            dev_ms = float(ms.item())
+            model = F.KMeansModel(cl).set_k(tk).set_model_data(F.KMeansModelData(cent_h, np.zeros(tk)).to_table())
+            model.transform(table_t)  # warm-up
+            barrier()
+            t0 = time.perf_counter()
+            out_t = model.transform(table_t)[0]
+            barrier()
+            dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            labels_h = np.asarray(out_t.column("prediction"))
+            same = bool(np.array_equal(labels_h, lab.cpu().numpy()))
+            if ref_labels is None:
+                ref_labels = labels_h
+            tf_t = 2.0 * tk * td * tn / (dev_ms * 1e-3) * 1e-12
+            transform_rec["modes"][name] = {
+                "value": tn * world / (dev_ms * 1e-3), "ms_per_launch": dev_ms, "fp64_equivalent_tflops": tf_t,
+                "frac_of_fp64_dmma_peak": tf_t / dmma_peak if dmma_peak else None, "launch": cx.describe_launch(tk, td, False),
+                "e2e": {"value": tn * world / float(dt.item()), "unit": "rows/s", "ms": float(dt.item()) * 1e3,
+                        "h2d_bytes_per_step": int(tn * td * 8 + tk * td * 8), "d2h_bytes_per_step": int(tn * 4),
+                        "api": "KMeansModel.transform(Table) from pinned host rows (copy and kernel overlapped on two streams)",
+                        "labels_match_device_run": same},
+                "labels_bit_exact_vs_f64_mode": bool(np.array_equal(labels_h, ref_labels))}
+            cl.close()
+        del xt, host_t, table_t, cent
+        torch.cuda.empty_cache()
+
+        bn, bd, bk, nbatch = 100_000, 128, 256, args.online_batches
+        per_rank = bn // world
+        xb = generate(per_rank * nbatch, bd)
+        host_b = torch.empty((per_rank * nbatch, bd), dtype=torch.float64, pin_memory=True)
+        host_b.copy_(xb)
+        torch.cuda.synchronize()
+        del xb
+        hb = host_b.numpy()
+        c0 = torch.empty((bk, bd), dtype=torch.float64, device=dev)
+        native.generate_dense_dev(local, stream.cuda_stream, 0, 0, 1, bk, bd, c0.data_ptr())
+        c0h = c0.cpu().numpy()
+        online_rec = {"workload": "OnlineKMeans mini-batches, config 5: global batch %d x %d (%d rows per GPU), k=%d, decay 0.5, "
+                                  "%d batches" % (bn, bd, per_rank, bk, nbatch), "unit": "rows/s", "modes": {}}
+        ref_model = None
+        for name, fl in modes:
+            cl = K.Cluster(rank, world, local, flags=fl, host_group=host_group)
+            cx = cl.context()
+            c, w = c0h.copy(), np.zeros(bk)
+            for b in range(3):
+                cx.online_round(hb[b * per_rank:(b + 1) * per_rank], c, w, 0.5)
+            c, w = c0h.copy(), np.zeros(bk)
+            barrier()
+            t0 = time.perf_counter()
+            for b in range(nbatch):
+                c, w = cx.online_round(hb[b * per_rank:(b + 1) * per_rank], c, w, 0.5)
+            barrier()
+            dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+            if ref_model is None:
+                ref_model = (c, w)
+            online_rec["modes"][name] = {
+                "value": bn * nbatch / float(dt.item()), "ms_per_batch": float(dt.item()) / nbatch * 1e3,
+                "h2d_bytes_per_step": int(per_rank * bd * 8 + (bk * bd + bk) * 8), "d2h_bytes_per_step": int((bk * bd + bk) * 8),
+                "api": "fmlk_online_round per batch: host batch and model in, merged model out (what OnlineKMeans.fit calls)",
+                "weights_bit_exact_vs_f64_mode": bool(np.array_equal(w, ref_model[1])),
+                "centroids_within_1e-9_of_f64_mode": bool(np.allclose(c, ref_model[0], rtol=1e-9, atol=0, equal_nan=True))}
+            cl.close()
+        del host_b, hb
+        torch.cuda.empty_cache()
+
     # ---- the north-star shape (config 4: 1e9 x 64, k = 1000 over 8 GPUs): this GPU's share, a short run
     north = None
     if not args.no_north_star and args.workload == "c2":
@@ -424,7 +527,7 @@ def run_ours(args):
             "clocks": clocks, "e2e": e2e, "gpu_launches": prof["total_launches"],
             "roofline": roofline, "cpu_baseline": base, "parity": parity,
             "wall_ms_per_step": wall / args.steps * 1e3, "rechecked_rows": prof["rechecked_rows"],
-            "fast_mode": fast_rec, "north_star": north,
+            "fast_mode": fast_rec, "transform": transform_rec, "online": online_rec, "north_star": north,
         }
         print(json.dumps(out))
     if world > 1:
@@ -448,6 +551,9 @@ def main():
                     help="headline line in the tcgen05 fast mode (FMLK_FLAG_FAST_TF32) instead of the FP64 mode")
     ap.add_argument("--no-fast", action="store_true", help="skip the fast-mode sub-record of the default run")
     ap.add_argument("--no-north-star", action="store_true", help="skip the config-4-share sub-record")
+    ap.add_argument("--no-extra", action="store_true", help="skip the transform (config 3) and online (config 5) sub-records")
+    ap.add_argument("--transform-rows", type=int, default=4_000_000, help="rows per GPU of the transform sub-record")
+    ap.add_argument("--online-batches", type=int, default=40)
     ap.add_argument("--north-rows", type=int, default=125_000_000, help="rows per GPU of the north-star sub-record")
     args = ap.parse_args()
     if args.impl == "ours":

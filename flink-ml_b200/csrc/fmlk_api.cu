@@ -161,6 +161,9 @@ struct fmlk_ctx {
     size_t stage_rows_cap = 0; // doubles
     int32_t *stage_labels = nullptr;
     size_t stage_labels_cap = 0;
+    int32_t *pinned_labels = nullptr; // host, page-locked: labels of two pieces on their way to the caller's buffer
+    size_t pinned_labels_cap = 0;
+    cudaEvent_t ev_labels[2] = {nullptr, nullptr};
 
     // fast mode (FMLK_FLAG_FAST_TF32): the centroids as TF32 terms + their tensor maps, the bitmap of
     // rows left to the exact replay
@@ -1087,7 +1090,9 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     dev_free(ctx->ar_probe);
     dev_free(ctx->ar_buf);
     dev_free(ctx->gather_ptrs);
+    if (ctx->pinned_labels) cudaFreeHost(ctx->pinned_labels);
     for (int b = 0; b < 2; b++) {
+        if (ctx->ev_labels[b]) cudaEventDestroy(ctx->ev_labels[b]);
         if (ctx->ev_copied[b]) cudaEventDestroy(ctx->ev_copied[b]);
         if (ctx->ev_decoded[b]) cudaEventDestroy(ctx->ev_decoded[b]);
     }
@@ -1440,21 +1445,63 @@ int32_t fmlk_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t 
     if (d != ctx->md) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
     if (n < 0 || (n > 0 && (!rows_host || !out_labels_host))) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad rows / labels");
     if (n == 0) return FMLK_OK;
-    // micro-batches through a reusable staging buffer: copy in, label, copy out
-    const int64_t max_rows = std::max<int64_t>(1, ((int64_t)256 << 20) / ((int64_t)d * 8));
+    // micro-batches through two staging buffers: the copy of piece i + 1 (copy stream) runs while piece i
+    // is labelled and its labels go back (the context's stream) -- the micro-batching a record-at-a-time
+    // PredictLabelFunction needs on a GPU, with the host link and the kernel overlapped
+    const int64_t max_rows = std::max<int64_t>(1024, ((int64_t)64 << 20) / ((int64_t)d * 8));
     const int64_t step = std::min(n, max_rows);
-    if ((rc = ensure_stage(ctx, (size_t)step * d, (size_t)step))) return rc;
+    if ((rc = ensure_stage(ctx, (size_t)2 * step * d, (size_t)2 * step))) return rc;
+    if (!ctx->copy_stream) {
+        CK(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        for (int b = 0; b < 2; b++) {
+            CK(ctx, cudaEventCreateWithFlags(&ctx->ev_copied[b], cudaEventDisableTiming));
+            CK(ctx, cudaEventCreateWithFlags(&ctx->ev_decoded[b], cudaEventDisableTiming));
+        }
+    }
+    // the labels come back through page-locked memory of our own: a device-to-host copy into pageable
+    // memory would block this thread until the kernel before it is done, and with it the next piece's copy
+    if ((size_t)2 * step > ctx->pinned_labels_cap) {
+        if (ctx->pinned_labels) cudaFreeHost(ctx->pinned_labels);
+        ctx->pinned_labels = nullptr;
+        ctx->pinned_labels_cap = 0;
+        CK(ctx, cudaMallocHost((void **)&ctx->pinned_labels, (size_t)2 * step * sizeof(int32_t)));
+        ctx->pinned_labels_cap = (size_t)2 * step;
+    }
+    for (int b = 0; b < 2; b++)
+        if (!ctx->ev_labels[b]) CK(ctx, cudaEventCreateWithFlags(&ctx->ev_labels[b], cudaEventDisableTiming));
     PredictPlan pl;
     if ((rc = plan_predict(ctx, &pl))) return rc;
     if ((rc = prep_centroids(ctx, false))) return rc;
-    for (int64_t off = 0; off < n; off += step) {
+    int64_t piece = 0;
+    auto hand_over = [&](int64_t pc) -> cudaError_t { // labels of piece pc: pinned slot -> the caller's buffer
+        const int b = (int)(pc & 1);
+        cudaError_t e = cudaEventSynchronize(ctx->ev_labels[b]);
+        if (e != cudaSuccess) return e;
+        const int64_t off = pc * step, m = std::min(step, n - off);
+        memcpy(out_labels_host + off, ctx->pinned_labels + (size_t)b * step, (size_t)m * sizeof(int32_t));
+        return cudaSuccess;
+    };
+    for (int64_t off = 0; off < n; off += step, piece++) {
         const int64_t m = std::min(step, n - off);
-        CK(ctx, cudaMemcpyAsync(ctx->stage_rows, rows_host + off * d, (size_t)m * d * sizeof(double),
-                                cudaMemcpyHostToDevice, ctx->stream));
-        if ((rc = run_predict(ctx, pl, ctx->stage_rows, m, ctx->stage_labels))) return rc;
-        CK(ctx, cudaMemcpyAsync(out_labels_host + off, ctx->stage_labels, (size_t)m * sizeof(int32_t),
+        const int b = (int)(piece & 1);
+        double *rows = ctx->stage_rows + (size_t)b * step * d;
+        int32_t *labels = ctx->stage_labels + (size_t)b * step;
+        // both buffers of slot b were last used by piece - 2: its labels go to the caller first
+        if (piece >= 2) {
+            CK(ctx, hand_over(piece - 2));
+            CK(ctx, cudaStreamWaitEvent(ctx->copy_stream, ctx->ev_decoded[b], 0));
+        }
+        CK(ctx, cudaMemcpyAsync(rows, rows_host + off * d, (size_t)m * d * sizeof(double), cudaMemcpyHostToDevice,
+                                ctx->copy_stream));
+        CK(ctx, cudaEventRecord(ctx->ev_copied[b], ctx->copy_stream));
+        CK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_copied[b], 0));
+        if ((rc = run_predict(ctx, pl, rows, m, labels))) return rc;
+        CK(ctx, cudaEventRecord(ctx->ev_decoded[b], ctx->stream));
+        CK(ctx, cudaMemcpyAsync(ctx->pinned_labels + (size_t)b * step, labels, (size_t)m * sizeof(int32_t),
                                 cudaMemcpyDeviceToHost, ctx->stream));
+        CK(ctx, cudaEventRecord(ctx->ev_labels[b], ctx->stream));
     }
+    for (int64_t pc = std::max<int64_t>(0, piece - 2); pc < piece; pc++) CK(ctx, hand_over(pc));
     CK(ctx, cudaStreamSynchronize(ctx->stream));
     drain_events(ctx);
     return FMLK_OK;
