@@ -541,6 +541,53 @@ class OnlineKMeansModel(_KMeansModelParams):
             labels = ctx.predict(points)
         return [table.with_column(self.get_prediction_col(), labels)]
 
+    def transform_stream(self, events, micro_batch=4096):
+        """PredictLabelOperator's two-input semantics (OnlineKMeansModel.java:170-195) over an interleaved
+        sequence of events in arrival order: ``("row", vector)`` and ``("model", KMeansModelData)``.
+        A row is labelled with the model that is current when it arrives; rows that arrive before the first
+        model are buffered and labelled by the first model, in arrival order (:172-175, :191-194); every model
+        record increments ``model_data_version`` (:189).  Rows are micro-batched for the GPU, and the pending
+        batch is labelled before a new model replaces the centroids, so batching never changes a label.
+        Returns ``(labels, versions)`` aligned with the rows' arrival order: the label of each row and the
+        model version that produced it.  Rows still buffered at the end (no model ever arrived) get no
+        label: they are left out, as the reference operator emits nothing for them."""
+        self._require_euclidean()
+        ctx = (self._cluster or Cluster.default()).context()
+        labels, versions = [], []
+        buffered, pending = [], []  # rows waiting for the first model / for the next predict call
+        have_model = False
+
+        def flush():
+            if pending:
+                out = ctx.predict(np.asarray(pending, dtype=np.float64))
+                labels.extend(int(v) for v in out)
+                versions.extend([self.model_data_version] * len(pending))
+                pending.clear()
+
+        for kind, payload in events:
+            if kind == "row":
+                row = np.asarray(payload, dtype=np.float64).reshape(-1)
+                if not have_model:
+                    buffered.append(row)
+                    continue
+                pending.append(row)
+                if len(pending) >= micro_batch:
+                    flush()
+            elif kind == "model":
+                md = payload
+                if md.centroids.shape[0] > self.get_k():
+                    raise IllegalArgumentError("modelData.centroids.length <= k")  # OnlineKMeansModel.java:185
+                flush()  # rows that arrived under the previous model are labelled with it
+                ctx.set_centroids(md.centroids)
+                have_model = True
+                self.model_data_version += 1
+                pending.extend(buffered)
+                buffered.clear()
+            else:
+                raise IllegalArgumentError("unknown event kind %r" % (kind,))
+        flush()
+        return np.asarray(labels, dtype=np.int32), np.asarray(versions, dtype=np.int32)
+
     def save(self, path):
         _save_model_data([KMeansModelData.from_table(self._model_data_table, r)
                           for r in range(len(self._model_data_table.column("centroids")))], path)

@@ -17,6 +17,7 @@ typedef uint8_t jboolean;
 class _jobject {};
 typedef _jobject *jobject;
 typedef jobject jclass;
+typedef jobject jstring;
 typedef jobject jarray;
 typedef jarray jbyteArray;
 typedef jarray jintArray;
@@ -26,6 +27,7 @@ typedef jarray jdoubleArray;
 struct JNIEnv {
     jclass FindClass(const char *name);
     jint ThrowNew(jclass cls, const char *msg);
+    jstring NewStringUTF(const char *utf);
     void *GetDirectBufferAddress(jobject buf);
     jsize GetArrayLength(jarray a);
     jbyteArray NewByteArray(jsize n);

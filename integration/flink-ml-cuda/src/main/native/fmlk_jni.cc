@@ -37,6 +37,10 @@ struct Doubles {
 
 extern "C" {
 
+JNIEXPORT jstring JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_version(JNIEnv *env, jclass) {
+    return env->NewStringUTF(fmlk_version());
+}
+
 JNIEXPORT jint JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_deviceCount(JNIEnv *, jclass) {
     return fmlk_device_count();
 }
@@ -67,6 +71,12 @@ JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_destroy(JNIEnv
     fmlk_destroy(ctx_of(h));
 }
 
+// a cudaStream_t the host already owns (as a long), instead of the context's own stream
+JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_setStream(JNIEnv *env, jclass, jlong h, jlong stream) {
+    int rc = fmlk_set_stream(ctx_of(h), reinterpret_cast<void *>(stream));
+    if (rc) throw_for(env, rc, ctx_of(h));
+}
+
 JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_reservePoints(JNIEnv *env, jclass, jlong h,
                                                                                jlong rows, jint d) {
     int rc = fmlk_reserve_points(ctx_of(h), rows, d);
@@ -82,7 +92,7 @@ JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_appendPoints(J
 }
 
 // rows still in the serializer's bytes (a ListStateWithCache memory segment)
-JNIEXPORT jlong JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_appendSerialized(JNIEnv *env, jclass, jlong h,
+JNIEXPORT jlong JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_appendPointsSerialized(JNIEnv *env, jclass, jlong h,
                                                                                    jobject buf, jlong nbytes,
                                                                                    jint format, jint d) {
     const uint8_t *rec = static_cast<const uint8_t *>(env->GetDirectBufferAddress(buf));
@@ -122,6 +132,50 @@ JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_fit(JNIEnv *en
     Doubles pc(env, c), pw(env, w);
     int rc = fmlk_fit(ctx_of(h), maxIter, pc.p, pw.p);
     if (rc) throw_for(env, rc, ctx_of(h));
+}
+
+// the record emitted at KMeans.java:297: this subtask's (sums, counts), before any cross-subtask reduction
+JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_localPartials(JNIEnv *env, jclass, jlong h,
+                                                                               jdoubleArray sums, jlongArray counts) {
+    Doubles ps(env, sums);
+    const jsize k = env->GetArrayLength(counts);
+    std::vector<int64_t> cnt(static_cast<size_t>(k));
+    int rc = fmlk_local_partials(ctx_of(h), ps.p, cnt.data());
+    if (rc) {
+        throw_for(env, rc, ctx_of(h));
+        return;
+    }
+    env->SetLongArrayRegion(counts, 0, k, reinterpret_cast<const jlong *>(cnt.data()));
+}
+
+JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_getModel(JNIEnv *env, jclass, jlong h, jdoubleArray c,
+                                                                          jdoubleArray w) {
+    Doubles pc(env, c), pw(env, w);
+    int rc = fmlk_get_model(ctx_of(h), pc.p, pw.p);
+    if (rc) throw_for(env, rc, ctx_of(h));
+}
+
+// the allocation-free local round: every pointer is a device address out of the host's own memory pool
+JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_localPartialsNoalloc(
+    JNIEnv *env, jclass, jint device, jlong stream, jlong rows, jlong n, jint d, jlong centroids, jint k, jlong out_sums,
+    jlong out_counts) {
+    int rc = fmlk_local_partials_noalloc(device, reinterpret_cast<void *>(stream), reinterpret_cast<const double *>(rows), n, d,
+                                         reinterpret_cast<const double *>(centroids), k, reinterpret_cast<double *>(out_sums),
+                                         reinterpret_cast<double *>(out_counts));
+    if (rc) throw_for(env, rc, nullptr);
+}
+
+// labels of the cached rows, in append order
+JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_predictCached(JNIEnv *env, jclass, jlong h,
+                                                                               jintArray labels) {
+    const jsize n = env->GetArrayLength(labels);
+    std::vector<int32_t> out(static_cast<size_t>(n));
+    int rc = fmlk_predict_cached(ctx_of(h), out.data());
+    if (rc) {
+        throw_for(env, rc, ctx_of(h));
+        return;
+    }
+    env->SetIntArrayRegion(labels, 0, n, reinterpret_cast<const jint *>(out.data()));
 }
 
 // PredictLabelFunction.map (KMeansModel.java:129-144) for a micro-batch

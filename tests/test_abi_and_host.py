@@ -208,22 +208,69 @@ def test_rows_on_task_matches_row_generator():
         assert [native.rows_on_task(n, t, p) for t in range(p)] == [O.rows_on_task(n, t, p) for t in range(p)]
 
 
-def test_jni_shim_type_checks_against_the_header():
-    """integration/flink-ml-cuda/src/main/native/fmlk_jni.cc cannot be built here (no JDK); it must at
-    least parse and type-check against include/fmlk.h with a minimal stand-in for jni.h, and every
-    native method the Java class declares must have its JNI function."""
+# entry points of include/fmlk.h a JVM host has no use for, and why; everything else must have its native
+NOT_BOUND_FROM_THE_JVM = {
+    "fmlk_last_error": "read by the shim itself when it throws",
+    "fmlk_append_points_dev": "device pointers: the harness' way of keeping H2D out of a timing",
+    "fmlk_adopt_points_dev": "device pointers (harness)",
+    "fmlk_predict_dev": "device pointers (harness)",
+    "fmlk_all_reduce_sum_dev": "device pointers (harness)",
+    "fmlk_decode_rows_dev": "device pointers (harness); the JVM calls fmlk_append_points_serialized",
+    "fmlk_generate_dense_dev": "benchmark data generator",
+    "fmlk_get_profile": "measurement helper",
+    "fmlk_reset_profile": "measurement helper",
+    "fmlk_measure_fp64_peaks": "measurement helper",
+    "fmlk_describe_launch": "measurement helper",
+    "fmlk_fast_debug": "test hook",
+    "fmlk_fast_launches": "test hook",
+}
+
+
+def _camel(name):
+    parts = name[len("fmlk_"):].split("_")
+    return parts[0] + "".join(p.capitalize() for p in parts[1:])
+
+
+def test_jni_shim_and_java_natives_cover_the_header():
+    """integration/flink-ml-cuda cannot be built here (no JDK).  The shim must at least parse and type-check
+    against include/fmlk.h with a minimal stand-in for jni.h, and header <-> Java <-> shim must agree: every
+    entry point of the header is either bound (a `native` in KMeansNative.java with its JNI function in the
+    shim) or listed above with the reason a JVM host does not need it."""
     import re
     import shutil
     import subprocess
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     shim = os.path.join(root, "integration", "flink-ml-cuda", "src", "main", "native", "fmlk_jni.cc")
-    java = os.path.join(root, "integration", "flink-ml-cuda", "src", "main", "java", "org", "apache", "flink", "ml",
-                        "cuda", "KMeansNative.java")
+    jdir = os.path.join(root, "integration", "flink-ml-cuda", "src", "main", "java", "org", "apache", "flink", "ml", "cuda")
     gxx = shutil.which("g++")
     assert gxx, "g++ not found"
     out = subprocess.run([gxx, "-std=c++17", "-fsyntax-only", "-Wall", "-Werror", "-I" + os.path.join(root, "integration", "check"),
                           "-I" + os.path.join(root, "include"), shim], capture_output=True, text=True)
     assert out.returncode == 0, out.stderr[-2000:]
-    natives = set(re.findall(r"native\s+[\w\[\]]+\s+(\w+)\s*\(", open(java).read()))
+    natives = set(re.findall(r"native\s+[\w\[\]]+\s+(\w+)\s*\(", open(os.path.join(jdir, "KMeansNative.java")).read()))
     exported = set(re.findall(r"Java_org_apache_flink_ml_cuda_KMeansNative_(\w+)\s*\(", open(shim).read()))
     assert natives and natives == exported, (natives ^ exported)
+    header = set(re.findall(r"\b(fmlk_\w+)\s*\(", open(os.path.join(root, "include", "fmlk.h")).read()))
+    assert header == set(native.SIGNATURES)  # the ctypes table covers the header too
+    assert set(NOT_BOUND_FROM_THE_JVM) <= header
+    bound = {_camel(f) for f in header - set(NOT_BOUND_FROM_THE_JVM)}
+    assert bound == natives, (bound ^ natives)
+    # every fmlk_* call the shim makes exists in the header
+    assert set(re.findall(r"\b(fmlk_\w+)\s*\(", open(shim).read())) <= header
+
+
+def test_java_operator_sources_are_present_and_name_their_reference_bodies():
+    """The three operator bodies SURVEY 8(b) names, as files (they cannot be compiled here): each cites the
+    reference operator it stands in for and drives the GPU only through KMeansNative."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    jdir = os.path.join(root, "integration", "flink-ml-cuda", "src", "main", "java", "org", "apache", "flink", "ml", "cuda")
+    want = {"GpuCentroidsUpdateAccumulator.java": ("KMeans.java:214-308", "TwoInputStreamOperator", "IterationListener"),
+            "GpuPredictLabelOperator.java": ("KMeansModel.java:105-145", "OneInputStreamOperator", "prepareSnapshotPreBarrier"),
+            "GpuOnlinePredictLabelOperator.java": ("OnlineKMeansModel.java:108-196", "modelDataVersion", "bufferedPoints"),
+            "GpuModelDataLocalUpdater.java": ("OnlineKMeans.java:227-326", "TwoInputStreamOperator", "onlineRound")}
+    for name, needles in want.items():
+        text = open(os.path.join(jdir, name)).read()
+        assert "package org.apache.flink.ml.cuda;" in text and "KMeansNative" in text
+        for s in needles:
+            assert s in text, (name, s)
+        assert text.count("{") == text.count("}") and text.count("(") == text.count(")")

@@ -444,3 +444,48 @@ def test_deterministic_context_step_parity(n, d, k):
         assert np.array_equal(a[1], b[1])
         if "sums_in_smem=1" in c.describe_launch(k, d, True):
             assert np.array_equal(a[0], b[0])
+
+
+def test_online_model_labels_rows_with_the_model_current_at_arrival():
+    """OnlineKMeansModel.PredictLabelOperator (OnlineKMeansModel.java:170-195): rows before the first model are
+    buffered and labelled by it, later rows by whichever model is current when they arrive, and the version
+    gauge counts model records.  Checked event by event against the oracle."""
+    import flink_ml_b200 as F
+    rng = np.random.default_rng(11)
+    d, k = 6, 5
+    models = [F.KMeansModelData(rng.random((k, d)) * s, np.zeros(k)) for s in (1.0, 3.0, 0.2)]
+    events, rows = [], []
+    plan = [("row", 7), ("model", 0), ("row", 300), ("model", 1), ("row", 1), ("model", 2), ("row", 50)]
+    for kind, arg in plan:
+        if kind == "model":
+            events.append(("model", models[arg]))
+        else:
+            for _ in range(arg):
+                r = rng.random(d) * 3.0
+                rows.append(r)
+                events.append(("row", r))
+    model = F.OnlineKMeansModel().set_k(k)
+    labels, versions = model.transform_stream(events, micro_batch=64)
+    # the oracle, one event at a time
+    want_l, want_v, cur, ver, held = [], [], None, 0, []
+    for kind, payload in events:
+        if kind == "model":
+            cur, ver = payload.centroids, ver + 1
+            for r in held:
+                want_l.append(int(O.predict(r.reshape(1, -1), cur)[0]))
+                want_v.append(ver)
+            held = []
+        elif cur is None:
+            held.append(payload)
+        else:
+            want_l.append(int(O.predict(payload.reshape(1, -1), cur)[0]))
+            want_v.append(ver)
+    assert model.model_data_version == 3
+    assert np.array_equal(labels, np.asarray(want_l, dtype=np.int32))
+    assert np.array_equal(versions, np.asarray(want_v, dtype=np.int32))
+    # no model ever arrives: nothing is emitted
+    lonely = F.OnlineKMeansModel().set_k(k)
+    l2, v2 = lonely.transform_stream([("row", r) for r in rows[:5]])
+    assert l2.size == 0 and v2.size == 0 and lonely.model_data_version == 0
+    with pytest.raises(native.IllegalArgumentError):
+        F.OnlineKMeansModel().set_k(2).transform_stream([("model", models[0])])
