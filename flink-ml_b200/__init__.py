@@ -10,7 +10,8 @@ from flink_ml_b200.table import Table  # noqa: F401
 from flink_ml_b200.kmeans import (  # noqa: F401
     KMeans, KMeansModel, KMeansModelData, OnlineKMeans, OnlineKMeansModel,
 )
+from flink_ml_b200.knn import Knn, KnnModel, KnnModelData  # noqa: F401
 from flink_ml_b200 import native  # noqa: F401
 
 __all__ = ["DenseVector", "SparseVector", "Vectors", "Table", "KMeans", "KMeansModel", "KMeansModelData",
-           "OnlineKMeans", "OnlineKMeansModel", "native"]
+           "OnlineKMeans", "OnlineKMeansModel", "Knn", "KnnModel", "KnnModelData", "native"]

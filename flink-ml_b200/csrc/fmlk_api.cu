@@ -6,6 +6,7 @@
 #include "../../include/fmlk.h"
 #include "fmlk_kernels.cuh"
 #include "fmlk_fast.cuh"
+#include "fmlk_knn.cuh"
 
 #include <dlfcn.h>
 #include <algorithm>
@@ -185,6 +186,14 @@ struct fmlk_ctx {
     // fmlk_get_points: device table of row addresses + gathered rows
     const double **gather_ptrs = nullptr;
     size_t gather_ptrs_cap = 0;
+
+    // KnnModelData on the device (fmlk_knn_set_model): m x d points, their norm squares and labels
+    double *knn_feat = nullptr, *knn_nsq = nullptr, *knn_labels = nullptr;
+    size_t knn_feat_cap = 0, knn_m_cap = 0;
+    int32_t knn_m = 0, knn_d = 0;
+    double *knn_out = nullptr; // predictions of the rows of a call
+    size_t knn_out_cap = 0;
+    int32_t *knn_status = nullptr;
 
     // profile
     std::vector<cudaEvent_t> ev_pool;
@@ -1090,6 +1099,11 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     dev_free(ctx->ar_probe);
     dev_free(ctx->ar_buf);
     dev_free(ctx->gather_ptrs);
+    dev_free(ctx->knn_feat);
+    dev_free(ctx->knn_nsq);
+    dev_free(ctx->knn_labels);
+    dev_free(ctx->knn_out);
+    dev_free(ctx->knn_status);
     if (ctx->pinned_labels) cudaFreeHost(ctx->pinned_labels);
     for (int b = 0; b < 2; b++) {
         if (ctx->ev_labels[b]) cudaEventDestroy(ctx->ev_labels[b]);
@@ -1600,6 +1614,162 @@ struct JRandom {
     }
 };
 } // namespace
+
+// ---- Knn: KnnModelData on the device, KnnModel.PredictLabelFunction (fmlk_knn.cuh) ------------------
+namespace {
+int knn_launch(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t k, double *out_dev) {
+    const size_t smem = fmlk::knn_smem_bytes(k);
+    if (smem > ctx->smem_optin) return fail(ctx, FMLK_ERR_INVALID_ARG, "k too large for the neighbour heaps");
+    static std::mutex attr_mutex;
+    static size_t attr_set[64] = {0};
+    {
+        std::lock_guard<std::mutex> lock(attr_mutex);
+        if (ctx->device < 64 && attr_set[ctx->device] < smem) {
+            CK(ctx, cudaFuncSetAttribute(fmlk::knn_predict_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr_set[ctx->device] = smem;
+        }
+    }
+    fmlk::KnnParams p{};
+    p.x = rows_dev;
+    p.n = n;
+    p.d = ctx->knn_d;
+    p.feat = ctx->knn_feat;
+    p.nsq = ctx->knn_nsq;
+    p.labels = ctx->knn_labels;
+    p.m = ctx->knn_m;
+    p.k = k;
+    p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
+    p.out = out_dev;
+    p.status = ctx->knn_status;
+    const int64_t blocks = (n + fmlk::kKnnRows - 1) / fmlk::kKnnRows;
+    fmlk::knn_predict_kernel<<<(unsigned)blocks, 256, smem, ctx->stream>>>(p);
+    CK(ctx, cudaGetLastError());
+    ctx->total_launches++;
+    return FMLK_OK;
+}
+
+int knn_check(fmlk_ctx *ctx, int64_t n, int32_t d, int32_t k, const void *rows, const void *out) {
+    if (!ctx->knn_feat && ctx->knn_m == 0 && ctx->knn_d == 0)
+        return fail(ctx, FMLK_ERR_STATE, "no Knn model data: call fmlk_knn_set_model first");
+    if (d != ctx->knn_d) return fail(ctx, FMLK_ERR_DIM, "Matrix and vector size mismatched."); // BLAS.gemv's check
+    if (k < 1 || k > fmlk::kKnnMaxK) return fail(ctx, FMLK_ERR_INVALID_ARG, "k must be in 1..128");
+    if (n < 0 || (n > 0 && (!rows || !out))) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad rows / predictions");
+    if (n > (int64_t)0x7fffffff * fmlk::kKnnRows) return fail(ctx, FMLK_ERR_INVALID_ARG, "too many rows for one call");
+    return FMLK_OK;
+}
+
+int knn_status_check(fmlk_ctx *ctx) { // after the stream has been synchronised
+    int32_t st = 0;
+    CK(ctx, cudaMemcpy(&st, ctx->knn_status, sizeof(st), cudaMemcpyDeviceToHost));
+    if (st) {
+        CK(ctx, cudaMemsetAsync(ctx->knn_status, 0, sizeof(int32_t), ctx->stream));
+        return fail(ctx, FMLK_ERR_INVALID_ARG,
+                    "a row's k neighbours hold more than 8 labels with one HashMap slot: vote order not replayed");
+    }
+    return FMLK_OK;
+}
+} // namespace
+
+int32_t fmlk_knn_set_model(fmlk_ctx *ctx, const double *features_host, const double *labels_host,
+                           const double *norm_squares_host_or_null, int32_t m, int32_t d) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if (m < 0 || d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad m / d");
+    if (m > 0 && (!features_host || !labels_host)) return fail(ctx, FMLK_ERR_INVALID_ARG, "model data is null");
+    const size_t md = (size_t)m * d;
+    if (md > ctx->knn_feat_cap || !ctx->knn_feat) {
+        dev_free(ctx->knn_feat);
+        ctx->knn_feat = nullptr;
+        ctx->knn_feat_cap = 0;
+        if ((rc = dev_alloc(ctx, &ctx->knn_feat, std::max<size_t>(md, 1)))) return rc;
+        ctx->knn_feat_cap = std::max<size_t>(md, 1);
+    }
+    if ((size_t)m > ctx->knn_m_cap || !ctx->knn_nsq) {
+        dev_free(ctx->knn_nsq);
+        dev_free(ctx->knn_labels);
+        ctx->knn_nsq = ctx->knn_labels = nullptr;
+        ctx->knn_m_cap = 0;
+        if ((rc = dev_alloc(ctx, &ctx->knn_nsq, std::max<size_t>(m, 1)))) return rc;
+        if ((rc = dev_alloc(ctx, &ctx->knn_labels, std::max<size_t>(m, 1)))) return rc;
+        ctx->knn_m_cap = std::max<size_t>(m, 1);
+    }
+    if (!ctx->knn_status) {
+        if ((rc = dev_alloc(ctx, &ctx->knn_status, 1))) return rc;
+        CK(ctx, cudaMemsetAsync(ctx->knn_status, 0, sizeof(int32_t), ctx->stream));
+    }
+    ctx->knn_m = m;
+    ctx->knn_d = d;
+    if (m > 0) {
+        CK(ctx, cudaMemcpyAsync(ctx->knn_feat, features_host, md * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        CK(ctx, cudaMemcpyAsync(ctx->knn_labels, labels_host, (size_t)m * sizeof(double), cudaMemcpyHostToDevice,
+                                ctx->stream));
+        if (norm_squares_host_or_null) {
+            CK(ctx, cudaMemcpyAsync(ctx->knn_nsq, norm_squares_host_or_null, (size_t)m * sizeof(double),
+                                    cudaMemcpyHostToDevice, ctx->stream));
+        } else {
+            fmlk::knn_norm_squares_kernel<<<(m + 127) / 128, 128, 0, ctx->stream>>>(
+                ctx->knn_feat, m, d, (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0, ctx->knn_nsq);
+            CK(ctx, cudaGetLastError());
+            ctx->total_launches++;
+        }
+    }
+    CK(ctx, cudaStreamSynchronize(ctx->stream)); // the host buffers are the caller's again
+    return FMLK_OK;
+}
+
+int32_t fmlk_knn_get_norm_squares(fmlk_ctx *ctx, double *out_norm_squares) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if (!ctx->knn_nsq) return fail(ctx, FMLK_ERR_STATE, "no Knn model data: call fmlk_knn_set_model first");
+    if (ctx->knn_m == 0) return FMLK_OK;
+    if (!out_norm_squares) return fail(ctx, FMLK_ERR_INVALID_ARG, "out is null");
+    CK(ctx, cudaMemcpyAsync(out_norm_squares, ctx->knn_nsq, (size_t)ctx->knn_m * sizeof(double), cudaMemcpyDeviceToHost,
+                            ctx->stream));
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    return FMLK_OK;
+}
+
+int32_t fmlk_knn_predict_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d, int32_t k,
+                             double *out_predictions_dev) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = knn_check(ctx, n, d, k, rows_dev, out_predictions_dev))) return rc;
+    if (n == 0) return FMLK_OK;
+    if ((rc = knn_launch(ctx, rows_dev, n, k, out_predictions_dev))) return rc;
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    return knn_status_check(ctx);
+}
+
+int32_t fmlk_knn_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t d, int32_t k,
+                         double *out_predictions_host) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = knn_check(ctx, n, d, k, rows_host, out_predictions_host))) return rc;
+    if (n == 0) return FMLK_OK;
+    const int64_t step = std::min<int64_t>(n, std::max<int64_t>(1024, ((int64_t)64 << 20) / ((int64_t)d * 8)));
+    if ((rc = ensure_stage(ctx, (size_t)step * d, 0))) return rc;
+    if ((size_t)step > ctx->knn_out_cap) {
+        dev_free(ctx->knn_out);
+        ctx->knn_out = nullptr;
+        ctx->knn_out_cap = 0;
+        if ((rc = dev_alloc(ctx, &ctx->knn_out, (size_t)step))) return rc;
+        ctx->knn_out_cap = (size_t)step;
+    }
+    for (int64_t off = 0; off < n; off += step) {
+        const int64_t rows = std::min(step, n - off);
+        CK(ctx, cudaMemcpyAsync(ctx->stage_rows, rows_host + off * d, (size_t)rows * d * sizeof(double),
+                                cudaMemcpyHostToDevice, ctx->stream));
+        if ((rc = knn_launch(ctx, ctx->stage_rows, rows, k, ctx->knn_out))) return rc;
+        CK(ctx, cudaMemcpyAsync(out_predictions_host + off, ctx->knn_out, (size_t)rows * sizeof(double),
+                                cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    return knn_status_check(ctx);
+}
 
 int32_t fmlk_all_reduce_sum_dev(fmlk_ctx *ctx, double *values_dev_inout, int64_t len) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;

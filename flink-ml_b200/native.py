@@ -77,6 +77,10 @@ SIGNATURES = {
     "fmlk_describe_launch": (_i32, [_vp, _i32, _i32, _i32, C.c_char_p, _i32]),
     "fmlk_fast_debug": (_i32, [_vp, _vp, _vp]),
     "fmlk_fast_launches": (_i64, [_vp]),
+    "fmlk_knn_set_model": (_i32, [_vp, _vp, _vp, _vp, _i32, _i32]),
+    "fmlk_knn_get_norm_squares": (_i32, [_vp, _vp]),
+    "fmlk_knn_predict": (_i32, [_vp, _vp, _i64, _i32, _i32, _vp]),
+    "fmlk_knn_predict_dev": (_i32, [_vp, _vp, _i64, _i32, _i32, _vp]),
 }
 
 _lib = None
@@ -330,6 +334,43 @@ class Context:
                                          float(decay), c.ctypes.data, w.ctypes.data))
         self.k, self.md = k, d
         return c, w
+
+    # -- Knn
+    def knn_set_model(self, features, labels, norm_squares=None):
+        """KnnModelData to the device: m x d points, m labels, m featureNormSquares (None: computed there)."""
+        f = np.ascontiguousarray(features, dtype=np.float64)
+        if f.ndim != 2 or f.shape[1] == 0:
+            raise IllegalArgumentError("features must be m x d with d > 0")
+        m, d = f.shape
+        lab = np.ascontiguousarray(labels, dtype=np.float64).reshape(-1)
+        if lab.size != m:
+            raise IllegalArgumentError("one label per model point")
+        ns = None
+        if norm_squares is not None:
+            ns = np.ascontiguousarray(norm_squares, dtype=np.float64).reshape(-1)
+            if ns.size != m:
+                raise IllegalArgumentError("one norm square per model point")
+        self._ck(lib().fmlk_knn_set_model(self._h, f.ctypes.data if m else None, lab.ctypes.data if m else None,
+                                          ns.ctypes.data if (ns is not None and m) else None, m, d))
+        self._knn_m = m
+
+    def knn_norm_squares(self):
+        out = np.empty(getattr(self, "_knn_m", 0), dtype=np.float64)
+        self._ck(lib().fmlk_knn_get_norm_squares(self._h, out.ctypes.data if out.size else None))
+        return out
+
+    def knn_predict(self, rows, k):
+        rows = np.ascontiguousarray(rows, dtype=np.float64)
+        if rows.ndim != 2:
+            raise IllegalArgumentError("rows must be n x d")
+        n, d = rows.shape
+        out = np.empty(n, dtype=np.float64)
+        self._ck(lib().fmlk_knn_predict(self._h, rows.ctypes.data if n else None, n, d, int(k),
+                                        out.ctypes.data if n else None))
+        return out
+
+    def knn_predict_dev(self, dev_ptr, n, d, k, out_dev_ptr):
+        self._ck(lib().fmlk_knn_predict_dev(self._h, dev_ptr, int(n), int(d), int(k), out_dev_ptr))
 
     # -- DataStreamUtils.allReduceSum
     def all_reduce_sum(self, values):

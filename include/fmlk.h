@@ -206,6 +206,33 @@ int32_t fmlk_predict_cached(fmlk_ctx *ctx, int32_t *out_labels_host);
 int32_t fmlk_online_round(fmlk_ctx *ctx, const double *local_batch_host, int64_t n_local, int32_t d,
                           int32_t k, double decay, double *centroids_inout, double *weights_inout);
 
+/* ---- Knn: the caller next to KMeans on the same rows
+ *      Knn.fit / computeNormSquare       LIB/classification/knn/Knn.java:74-101,145-156
+ *      KnnModelData                      LIB/classification/knn/KnnModelData.java:52-66
+ *      KnnModel.PredictLabelFunction     LIB/classification/knn/KnnModel.java:141-192 ---- */
+
+/* The broadcast KnnModelData as the operator's open() receives it: m training points of dimension d
+ * (features_host: m x d, one point after the other -- exactly the column-major d x m DenseMatrix
+ * `packedFeatures`), their labels (m doubles) and featureNormSquares (m doubles; NULL: computed on the
+ * device as Knn.computeNormSquare does, Math.pow(BLAS.norm2(feature), 2), and readable back with
+ * fmlk_knn_get_norm_squares -- which is Knn.fit's whole computation).  Copied to HBM, where it stays. */
+int32_t fmlk_knn_set_model(fmlk_ctx *ctx, const double *features_host, const double *labels_host,
+                           const double *norm_squares_host_or_null, int32_t m, int32_t d);
+int32_t fmlk_knn_get_norm_squares(fmlk_ctx *ctx, double *out_norm_squares);
+
+/* PredictLabelFunction.predictLabel (KnnModel.java:151-192) for n rows: distances to all m points in the
+ * reference's own floating-point order (bit-identical), the k nearest through java.util.PriorityQueue's
+ * sift order, the vote in java.util.HashMap<Double, Double>'s iteration order, first strict maximum wins
+ * (-1.0 for an empty model).  1 <= k <= 128.  d != the model's: FMLK_ERR_DIM "Matrix and vector size
+ * mismatched." (BLAS.gemv, CORE/linalg/BLAS.java:186-190).  A row whose k neighbours carry 8 or more distinct
+ * labels that fall into one slot of a HashMap of 64 or more slots would need the JDK's tree bins to
+ * reproduce the iteration order: FMLK_ERR_INVALID_ARG (that row's prediction is NaN); label sets as
+ * classifiers have them (small integers) never get there. */
+int32_t fmlk_knn_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t d, int32_t k,
+                         double *out_predictions_host);
+int32_t fmlk_knn_predict_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d, int32_t k,
+                             double *out_predictions_dev);
+
 /* ---- DataStreamUtils.allReduceSum (CORE/common/datastream/DataStreamUtils.java:102-104,
  *      AllReduceImpl.java:71-302) ---- */
 

@@ -59,6 +59,12 @@ final class KMeansNative implements AutoCloseable {
     private static native void allReduceSum(long h, double[] valuesInOut);            // fmlk_all_reduce_sum
     private static native void getPoints(long h, long[] rowIds, double[] outRows);    // fmlk_get_points
     static native int reservoir(long n, int k, long seed, long[] outIds);             // fmlk_reservoir
+    // Knn (KnnModel.java:141-192, Knn.java:145-156): model data m x d (= DenseMatrix packedFeatures.values as it is)
+    private static native void knnSetModel(long h, double[] packedFeatures, double[] labels, double[] normSquaresOrNull,
+                                           int m, int d);                             // fmlk_knn_set_model
+    private static native void knnGetNormSquares(long h, double[] outNormSquares);    // fmlk_knn_get_norm_squares
+    private static native void knnPredict(long h, ByteBuffer rowsDirectLE, long n, int d, int k,
+                                          double[] outPredictions);                   // fmlk_knn_predict
     /**
      * fmlk_local_partials_noalloc: for a task manager whose GPU memory belongs to its own pool.  All arguments but
      * the shape are device addresses the caller obtained from that pool; nothing is allocated or freed.
@@ -87,6 +93,13 @@ final class KMeansNative implements AutoCloseable {
     }
     void allReduceSum(double[] valuesInOut) { allReduceSum(handle, valuesInOut); }
     void getPoints(long[] rowIds, double[] outRows) { getPoints(handle, rowIds, outRows); }
+    void knnSetModel(double[] packedFeatures, double[] labels, double[] normSquaresOrNull, int m, int d) {
+        knnSetModel(handle, packedFeatures, labels, normSquaresOrNull, m, d);
+    }
+    void knnGetNormSquares(double[] outNormSquares) { knnGetNormSquares(handle, outNormSquares); }
+    void knnPredict(ByteBuffer rowsDirectLE, long n, int d, int k, double[] outPredictions) {
+        knnPredict(handle, rowsDirectLE, n, d, k, outPredictions);
+    }
 
     @Override
     public void close() {

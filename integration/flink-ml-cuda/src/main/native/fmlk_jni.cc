@@ -219,6 +219,31 @@ JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_getPoints(JNIE
     if (rc) throw_for(env, rc, ctx_of(h));
 }
 
+// KnnModelData to the device (KnnModelData.java:52-66); normSquares == null: Knn.computeNormSquare on the device
+JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_knnSetModel(JNIEnv *env, jclass, jlong h,
+                                                                             jdoubleArray feats, jdoubleArray labels,
+                                                                             jdoubleArray norm_squares, jint m, jint d) {
+    Doubles pf(env, feats), pl(env, labels), pn(env, norm_squares);
+    int rc = fmlk_knn_set_model(ctx_of(h), pf.p, pl.p, pn.p, m, d);
+    if (rc) throw_for(env, rc, ctx_of(h));
+}
+
+JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_knnGetNormSquares(JNIEnv *env, jclass, jlong h,
+                                                                                   jdoubleArray out) {
+    Doubles po(env, out);
+    int rc = fmlk_knn_get_norm_squares(ctx_of(h), po.p);
+    if (rc) throw_for(env, rc, ctx_of(h));
+}
+
+// KnnModel.PredictLabelFunction.predictLabel (KnnModel.java:151-192) for a micro-batch of rows
+JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_knnPredict(JNIEnv *env, jclass, jlong h, jobject buf,
+                                                                            jlong n, jint d, jint k, jdoubleArray out) {
+    const double *rows = static_cast<const double *>(env->GetDirectBufferAddress(buf));
+    Doubles po(env, out);
+    int rc = fmlk_knn_predict(ctx_of(h), rows, n, d, k, po.p);
+    if (rc) throw_for(env, rc, ctx_of(h));
+}
+
 // SamplingOperator (DataStreamUtils.java:633-704)
 JNIEXPORT jint JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_reservoir(JNIEnv *env, jclass, jlong n, jint k,
                                                                            jlong seed, jlongArray out) {

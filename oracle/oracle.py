@@ -21,8 +21,8 @@ _u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
 
 def build(force=False):
     """Compile the oracle with its Makefile (gcc only; a few seconds)."""
-    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < os.path.getmtime(
-            os.path.join(_HERE, "kmeans_oracle.c")):
+    srcs = [os.path.join(_HERE, f) for f in ("kmeans_oracle.c", "knn_oracle.c", "Makefile")]
+    if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-s", "-C", _HERE])
     return _SO
 
@@ -75,6 +75,9 @@ def lib():
         "orc_decode_rows": (C.c_int64, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p]),
         "orc_train_round_mt": (None, [C.c_int64, C.c_int32, _f64p, C.c_int32, _f64p, _f64p, _i32p, C.c_int32]),
         "orc_max_threads": (C.c_int32, []),
+        "orc_knn_norm_square": (C.c_double, [C.c_int32, _f64p]),
+        "orc_knn_predict": (None, [C.c_int64, C.c_int32, _f64p, C.c_int32, _f64p, _f64p, _f64p, C.c_int32, _f64p]),
+        "orc_knn_distances": (None, [C.c_int32, _f64p, C.c_int32, _f64p, _f64p, _f64p]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -357,3 +360,29 @@ def train_round_mt(points, centroids, threads):
 
 def max_threads():
     return int(lib().orc_max_threads())
+
+
+# ---------------------------------------------------------------- Knn (oracle/knn_oracle.c)
+
+def knn_norm_squares(features):
+    """Knn.computeNormSquare (Knn.java:145-156): Math.pow(BLAS.norm2(feature), 2) per row."""
+    f = _rows(features)
+    return np.array([lib().orc_knn_norm_square(f.shape[1], np.ascontiguousarray(r)) for r in f], dtype=np.float64)
+
+
+def knn_predict(rows, features, labels, k, norm_squares=None):
+    """KnnModel.PredictLabelFunction.predictLabel (KnnModel.java:151-192) for every row."""
+    x, f = _rows(rows), _rows(features)
+    lab = np.ascontiguousarray(labels, dtype=np.float64).reshape(-1)
+    ns = knn_norm_squares(f) if norm_squares is None else np.ascontiguousarray(norm_squares, dtype=np.float64)
+    out = np.empty(x.shape[0], dtype=np.float64)
+    lib().orc_knn_predict(x.shape[0], x.shape[1], x.reshape(-1), f.shape[0], f.reshape(-1), ns, lab, int(k), out)
+    return out
+
+
+def knn_distances(row, features, norm_squares=None):
+    f = _rows(features)
+    ns = knn_norm_squares(f) if norm_squares is None else np.ascontiguousarray(norm_squares, dtype=np.float64)
+    out = np.empty(f.shape[0], dtype=np.float64)
+    lib().orc_knn_distances(f.shape[1], np.ascontiguousarray(row, dtype=np.float64).reshape(-1), f.shape[0], f.reshape(-1), ns, out)
+    return out

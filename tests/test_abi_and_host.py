@@ -214,6 +214,7 @@ NOT_BOUND_FROM_THE_JVM = {
     "fmlk_append_points_dev": "device pointers: the harness' way of keeping H2D out of a timing",
     "fmlk_adopt_points_dev": "device pointers (harness)",
     "fmlk_predict_dev": "device pointers (harness)",
+    "fmlk_knn_predict_dev": "device pointers (harness)",
     "fmlk_all_reduce_sum_dev": "device pointers (harness)",
     "fmlk_decode_rows_dev": "device pointers (harness); the JVM calls fmlk_append_points_serialized",
     "fmlk_generate_dense_dev": "benchmark data generator",
@@ -267,7 +268,8 @@ def test_java_operator_sources_are_present_and_name_their_reference_bodies():
     want = {"GpuCentroidsUpdateAccumulator.java": ("KMeans.java:214-308", "TwoInputStreamOperator", "IterationListener"),
             "GpuPredictLabelOperator.java": ("KMeansModel.java:105-145", "OneInputStreamOperator", "prepareSnapshotPreBarrier"),
             "GpuOnlinePredictLabelOperator.java": ("OnlineKMeansModel.java:108-196", "modelDataVersion", "bufferedPoints"),
-            "GpuModelDataLocalUpdater.java": ("OnlineKMeans.java:227-326", "TwoInputStreamOperator", "onlineRound")}
+            "GpuModelDataLocalUpdater.java": ("OnlineKMeans.java:227-326", "TwoInputStreamOperator", "onlineRound"),
+            "GpuKnnPredictOperator.java": ("KnnModel.java:141-192", "OneInputStreamOperator", "knnPredict")}
     for name, needles in want.items():
         text = open(os.path.join(jdir, name)).read()
         assert "package org.apache.flink.ml.cuda;" in text and "KMeansNative" in text
