@@ -1620,13 +1620,15 @@ namespace {
 int knn_launch(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t k, double *out_dev) {
     const size_t smem = fmlk::knn_smem_bytes(k);
     if (smem > ctx->smem_optin) return fail(ctx, FMLK_ERR_INVALID_ARG, "k too large for the neighbour heaps");
+    const bool fma = (ctx->flags & FMLK_FLAG_BLAS_FMA) != 0;
     static std::mutex attr_mutex;
-    static size_t attr_set[64] = {0};
+    static size_t attr_set[64][2] = {{0}};
     {
         std::lock_guard<std::mutex> lock(attr_mutex);
-        if (ctx->device < 64 && attr_set[ctx->device] < smem) {
-            CK(ctx, cudaFuncSetAttribute(fmlk::knn_predict_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            attr_set[ctx->device] = smem;
+        if (ctx->device < 64 && attr_set[ctx->device][fma] < smem) {
+            CK(ctx, cudaFuncSetAttribute(fma ? fmlk::knn_predict_kernel<true> : fmlk::knn_predict_kernel<false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr_set[ctx->device][fma] = smem;
         }
     }
     fmlk::KnnParams p{};
@@ -1638,11 +1640,12 @@ int knn_launch(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t k, doub
     p.labels = ctx->knn_labels;
     p.m = ctx->knn_m;
     p.k = k;
-    p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
+    p.fma_mode = fma ? 1 : 0;
     p.out = out_dev;
     p.status = ctx->knn_status;
     const int64_t blocks = (n + fmlk::kKnnRows - 1) / fmlk::kKnnRows;
-    fmlk::knn_predict_kernel<<<(unsigned)blocks, 256, smem, ctx->stream>>>(p);
+    if (fma) fmlk::knn_predict_kernel<true><<<(unsigned)blocks, 256, smem, ctx->stream>>>(p);
+    else fmlk::knn_predict_kernel<false><<<(unsigned)blocks, 256, smem, ctx->stream>>>(p);
     CK(ctx, cudaGetLastError());
     ctx->total_launches++;
     return FMLK_OK;

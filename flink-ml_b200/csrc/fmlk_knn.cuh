@@ -180,13 +180,16 @@ __device__ __forceinline__ void knn_vote_add(KnnVote &v, double label) {
 constexpr size_t kKnnVoteBytes = (size_t)kKnnMaxK * (8 + 8 + 4 + 4) + (size_t)kKnnVoteTable * 4;
 static_assert(8 * kKnnVoteBytes <= (size_t)kKnnRows * kKnnPts * 8, "the eight warps' vote scratch lives in the distance tile");
 
-// dynamic shared memory: tiles | distances | heaps (64 rows x k x 2 doubles) | heap sizes | row norm squares
+// dynamic shared memory: tiles | distances | heaps (64 rows x k x 2 doubles) | row norm squares | the tile's
+// model norm squares and labels | heap sizes
 __host__ __device__ inline size_t knn_smem_bytes(int k) {
-    return (size_t)2 * kKnnDk * kKnnLd * 8 + (size_t)kKnnRows * kKnnPts * 8 + (size_t)kKnnRows * k * 16 + kKnnRows * 4 +
-           kKnnRows * 8;
+    return (size_t)2 * kKnnDk * kKnnLd * 8 + (size_t)kKnnRows * kKnnPts * 8 + (size_t)kKnnRows * k * 16 + kKnnRows * 8 +
+           2 * kKnnPts * 8 + kKnnRows * 4;
 }
 
-__global__ void __launch_bounds__(256) knn_predict_kernel(const KnnParams p) {
+// FMA: netlib's JDK >= 11 variant (a compile-time switch: a run-time one costs a select per product)
+template <bool FMA>
+__global__ void __launch_bounds__(256, 4) knn_predict_kernel(const KnnParams p) {
     extern __shared__ __align__(16) unsigned char knn_smem[];
     double *Xt = reinterpret_cast<double *>(knn_smem);       // [kKnnDk][kKnnLd]: Xt[kk][row]
     double *Pt = Xt + kKnnDk * kKnnLd;                        // [kKnnDk][kKnnLd]: Pt[kk][point]
@@ -194,9 +197,13 @@ __global__ void __launch_bounds__(256) knn_predict_kernel(const KnnParams p) {
     double *hd = Ds + kKnnRows * kKnnPts;                     // [rows][k] heap: distances
     double *hl = hd + (size_t)kKnnRows * p.k;                 // [rows][k] heap: labels
     double *xn = hl + (size_t)kKnnRows * p.k;                 // [rows] Math.pow(norm2(x), 2)
-    int *hsize = reinterpret_cast<int *>(xn + kKnnRows);      // [rows]
+    double *tn = xn + kKnnRows;                               // [points] featureNormSquares of the current tile
+    double *tl = tn + kKnnPts;                                // [points] labels of the current tile
+    int *hsize = reinterpret_cast<int *>(tl + kKnnPts);       // [rows]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int ty = tid >> 4, tx = tid & 15; // this thread's sums: rows 4 ty .. 4 ty + 3, points 4 tx .. 4 tx + 3
+    // this thread's 4 x 4 sums: rows 2 ty, 2 ty + 1, 32 + 2 ty, 33 + 2 ty x points 2 tx, 2 tx + 1, 32 + 2 tx, 33 + 2 tx
+    // (a half warp then reads 16 x 16 contiguous bytes of a tile row: no bank conflicts)
+    const int ty = tid >> 4, tx = tid & 15;
     const int64_t row0 = (int64_t)blockIdx.x * kKnnRows;
     const int rows = (int)min((int64_t)kKnnRows, p.n - row0);
     if (tid < kKnnRows) {
@@ -211,6 +218,8 @@ __global__ void __launch_bounds__(256) knn_predict_kernel(const KnnParams p) {
         for (int i = 0; i < 4; i++)
 #pragma unroll
             for (int j = 0; j < 4; j++) acc[i][j] = 0.0;
+        if (tid < kKnnPts) tn[tid] = tid < pts ? p.nsq[t0 + tid] : 0.0;
+        else if (tid < 2 * kKnnPts) tl[tid - kKnnPts] = tid - kKnnPts < pts ? p.labels[t0 + tid - kKnnPts] : 0.0;
         for (int k0 = 0; k0 < p.d; k0 += kKnnDk) {
             // both tiles, transposed: element (r, kk) of the rows and of the model points (zero past the ends)
             for (int e = tid; e < kKnnRows * kKnnDk; e += 256) {
@@ -221,16 +230,23 @@ __global__ void __launch_bounds__(256) knn_predict_kernel(const KnnParams p) {
             }
             __syncthreads();
             const int kmax = min(kKnnDk, p.d - k0);
-            for (int kk = 0; kk < kmax; kk++) {
-                const double2 xa = *reinterpret_cast<const double2 *>(Xt + kk * kKnnLd + 4 * ty);
-                const double2 xb = *reinterpret_cast<const double2 *>(Xt + kk * kKnnLd + 4 * ty + 2);
-                const double2 pa = *reinterpret_cast<const double2 *>(Pt + kk * kKnnLd + 4 * tx);
-                const double2 pb = *reinterpret_cast<const double2 *>(Pt + kk * kKnnLd + 4 * tx + 2);
+            auto step = [&](int kk) {
+                const double2 xa = *reinterpret_cast<const double2 *>(Xt + kk * kKnnLd + 2 * ty);
+                const double2 xb = *reinterpret_cast<const double2 *>(Xt + kk * kKnnLd + 32 + 2 * ty);
+                const double2 pa = *reinterpret_cast<const double2 *>(Pt + kk * kKnnLd + 2 * tx);
+                const double2 pb = *reinterpret_cast<const double2 *>(Pt + kk * kKnnLd + 32 + 2 * tx);
                 const double xv[4] = {xa.x, xa.y, xb.x, xb.y}, pv[4] = {pa.x, pa.y, pb.x, pb.y};
 #pragma unroll
                 for (int i = 0; i < 4; i++)
 #pragma unroll
-                    for (int j = 0; j < 4; j++) acc[i][j] = ref_mul_add(xv[i], pv[j], acc[i][j], p.fma_mode);
+                    for (int j = 0; j < 4; j++)
+                        acc[i][j] = FMA ? fma(xv[i], pv[j], acc[i][j]) : __dadd_rn(acc[i][j], __dmul_rn(xv[i], pv[j]));
+            };
+            if (kmax == kKnnDk) {
+#pragma unroll
+                for (int kk = 0; kk < kKnnDk; kk++) step(kk);
+            } else {
+                for (int kk = 0; kk < kmax; kk++) step(kk);
             }
             __syncthreads();
         }
@@ -238,14 +254,12 @@ __global__ void __launch_bounds__(256) knn_predict_kernel(const KnnParams p) {
 #pragma unroll
         for (int i = 0; i < 4; i++)
 #pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const int r = 4 * ty + i, c = 4 * tx + j;
-                double dist = 0.0;
-                if (c < pts) {
-                    const double y = __dmul_rn(-2.0, acc[i][j]);
-                    dist = sqrt(fabs(__dadd_rn(__dadd_rn(y, xn[r]), p.nsq[t0 + c])));
-                }
-                Ds[r * kKnnPts + c] = dist;
+            for (int jp = 0; jp < 2; jp++) {
+                const int r = (i & 1) + 2 * ty + 32 * (i >> 1), c = 2 * tx + 32 * jp;
+                double2 dist = make_double2(0.0, 0.0);
+                if (c < pts) dist.x = sqrt(fabs(__dadd_rn(__dadd_rn(__dmul_rn(-2.0, acc[i][2 * jp]), xn[r]), tn[c])));
+                if (c + 1 < pts) dist.y = sqrt(fabs(__dadd_rn(__dadd_rn(__dmul_rn(-2.0, acc[i][2 * jp + 1]), xn[r]), tn[c + 1])));
+                *reinterpret_cast<double2 *>(Ds + r * kKnnPts + c) = dist;
             }
         __syncthreads();
         // the heaps: warp w, rows 8 w .. 8 w + 7, candidates in index order
@@ -253,11 +267,18 @@ __global__ void __launch_bounds__(256) knn_predict_kernel(const KnnParams p) {
             const int r = 8 * warp + rr;
             if (r >= rows) break;
             double *rd = hd + (size_t)r * p.k, *rl = hl + (size_t)r * p.k;
-            for (int c0 = 0; c0 < pts; c0 += 32) {
-                const int c = c0 + lane;
-                const bool valid = c < pts;
-                const double dist = valid ? Ds[r * kKnnPts + c] : 0.0;
-                const double lab = valid ? p.labels[t0 + c] : 0.0;
+            // lane l looks at candidates l and l + 32; nearly always neither beats the head and the row is done
+            const double d0 = Ds[r * kKnnPts + lane], d1 = Ds[r * kKnnPts + 32 + lane];
+            const bool v0 = lane < pts, v1 = lane + 32 < pts;
+            {
+                const int size = hsize[r];
+                const double head = rd[0];
+                if (size >= p.k && !__any_sync(0xffffffffu, (v0 && head > d0) || (v1 && head > d1))) continue;
+            }
+#pragma unroll
+            for (int half = 0; half < 2; half++) {
+                const bool valid = half ? v1 : v0;
+                const double dist = half ? d1 : d0;
                 int from = 0;
                 for (;;) {
                     const int size = hsize[r];
@@ -269,7 +290,7 @@ __global__ void __launch_bounds__(256) knn_predict_kernel(const KnnParams p) {
                     if (lane == t) {
                         int s = size;
                         if (s >= p.k) knn_poll(rd, rl, s); // the farthest neighbour leaves
-                        knn_sift_up(rd, rl, s, dist, lab);
+                        knn_sift_up(rd, rl, s, dist, tl[32 * half + lane]);
                         hsize[r] = s + 1;
                     }
                     __syncwarp();
