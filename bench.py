@@ -399,7 +399,7 @@ def run_ours(args):
 
     # ---- the other two entry points north_star names, each device-timed and end to end from pinned host rows:
     # KMeansModel.transform (config 3's shape, a bounded number of rows) and OnlineKMeans mini-batches (config 5)
-    transform_rec = online_rec = None
+    transform_rec = online_rec = knn_rec = None
     if not args.no_extra and args.workload == "c2":
         modes = [("f64", 0)] + ([] if args.no_fast else [("tf32x3+f64-recheck", native.FLAG_FAST_TF32)])
         tn, td, tk = args.transform_rows, 128, 1000
@@ -500,6 +500,60 @@ def run_ours(args):
         del host_b, hb
         torch.cuda.empty_cache()
 
+        # KnnModel.transform: every row against every training point, exact FP64, reference order
+        qn, qm, qd, qk = args.knn_rows, 10_000, 64, 5
+        feats = generate(qm, qd)
+        rows_q = generate(qn, qd)
+        feats_h = feats.cpu().numpy()
+        host_q = torch.empty((qn, qd), dtype=torch.float64, pin_memory=True)
+        host_q.copy_(rows_q)
+        torch.cuda.synchronize()
+        labels_h = (np.arange(qm) % 10).astype(np.float64)
+        cl = K.Cluster(rank, world, local, flags=0, host_group=host_group)
+        cx = cl.context()
+        cx.set_stream(stream.cuda_stream)
+        cx.knn_set_model(feats_h, labels_h)
+        pred = torch.empty((qn,), dtype=torch.float64, device=dev)
+        for _ in range(2):
+            cx.knn_predict_dev(rows_q.data_ptr(), qn, qd, qk, pred.data_ptr())
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record(stream)
+        for _ in range(3):
+            cx.knn_predict_dev(rows_q.data_ptr(), qn, qd, qk, pred.data_ptr())
+        e1.record(stream)
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1) / 3], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        knn_ms = float(ms.item())
+        from flink_ml_b200.knn import KnnModel, KnnModelData
+        kmodel = KnnModel(cl).set_k(qk).set_model_data(KnnModelData(feats_h, cx.knn_norm_squares(), labels_h).to_table())
+        table_q = F.Table({"features": host_q.numpy()})
+        kmodel.transform(table_q)
+        barrier()
+        t0 = time.perf_counter()
+        out_q = kmodel.transform(table_q)[0]
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        knn_tf = 2.0 * qn * qm * qd / (knn_ms * 1e-3) * 1e-12
+        knn_rec = {"workload": "KnnModel.transform: %d x %d FP64 rows per GPU against %d training points, k=%d" % (qn, qd, qm, qk),
+                   "unit": "rows/s", "value": qn * world / (knn_ms * 1e-3), "ms_per_launch": knn_ms,
+                   "roofline": {"bound": "fp64 pipe (multiply and add kept apart, as the reference rounds them)",
+                                "achieved": knn_tf, "peak": dfma_peak / 2.0, "unit": "TFLOP/s",
+                                "frac": knn_tf / (dfma_peak / 2.0) if dfma_peak else None,
+                                "peak_is": "half the measured DFMA rate: one DMUL + one DADD per 2 flop"},
+                   "e2e": {"value": qn * world / float(dt.item()), "unit": "rows/s", "ms": float(dt.item()) * 1e3,
+                           "h2d_bytes_per_step": int(qn * qd * 8 + qm * qd * 8 + qm * 16), "d2h_bytes_per_step": int(qn * 8),
+                           "api": "KnnModel.transform(Table) from pinned host rows (model data re-sent per call)",
+                           "predictions_match_device_run": bool(np.array_equal(np.asarray(out_q.column("prediction")),
+                                                                                pred.cpu().numpy()))}}
+        cl.close()
+        del feats, rows_q, host_q, table_q
+        torch.cuda.empty_cache()
+
     # ---- the north-star shape (config 4: 1e9 x 64, k = 1000 over 8 GPUs): this GPU's share, a short run
     north = None
     if not args.no_north_star and args.workload == "c2":
@@ -546,7 +600,7 @@ def run_ours(args):
             "clocks": clocks, "e2e": e2e, "gpu_launches": prof["total_launches"],
             "roofline": roofline, "cpu_baseline": base, "parity": parity,
             "wall_ms_per_step": wall / args.steps * 1e3, "rechecked_rows": prof["rechecked_rows"],
-            "fast_mode": fast_rec, "transform": transform_rec, "online": online_rec, "north_star": north,
+            "fast_mode": fast_rec, "transform": transform_rec, "online": online_rec, "knn": knn_rec, "north_star": north,
         }
         print(json.dumps(out))
     if world > 1:
@@ -570,6 +624,7 @@ def main():
                     help="headline line in the tcgen05 fast mode (FMLK_FLAG_FAST_TF32) instead of the FP64 mode")
     ap.add_argument("--no-fast", action="store_true", help="skip the fast-mode sub-record of the default run")
     ap.add_argument("--no-north-star", action="store_true", help="skip the config-4-share sub-record")
+    ap.add_argument("--knn-rows", type=int, default=1 << 17, help="rows per GPU of the KnnModel.transform sub-record")
     ap.add_argument("--no-extra", action="store_true", help="skip the transform (config 3) and online (config 5) sub-records")
     ap.add_argument("--transform-rows", type=int, default=4_000_000, help="rows per GPU of the transform sub-record")
     ap.add_argument("--online-batches", type=int, default=40)
