@@ -151,6 +151,7 @@ struct fmlk_ctx {
     double *partials = nullptr;    // n_partials_cap * (k*d + k)
     size_t partials_cap = 0;       // in doubles
     unsigned long long *recheck = nullptr;
+    unsigned *tail_counter = nullptr; // round_tail_kernel's arrival counter (zero between launches)
 
     // staging for predict / online batches
     uint8_t *ingest_buf = nullptr; // staging for serialized records
@@ -716,13 +717,16 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
 
 // accum: the launch that follows accumulates (the fast mode's geometry, and with it the layout of the
 // centroid terms, differs between training and predict)
-int prep_centroids(fmlk_ctx *ctx, bool accum) {
+// base_done: the round before ended in round_tail_kernel, which has already done prep_centroids_kernel's work
+int prep_centroids(fmlk_ctx *ctx, bool accum, bool base_done = false) {
     const int k_pad = (ctx->k + 7) & ~7;
-    prep_centroids_kernel<<<1, 256, 0, ctx->stream>>>(ctx->centroids, ctx->k, k_pad, ctx->md,
-                                                     (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0, ctx->cn, ctx->h,
-                                                     ctx->cmax2, ctx->c_mma);
-    ctx->total_launches++;
-    CK(ctx, cudaGetLastError());
+    if (!base_done) {
+        prep_centroids_kernel<<<1, 256, 0, ctx->stream>>>(ctx->centroids, ctx->k, k_pad, ctx->md,
+                                                         (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0, ctx->cn, ctx->h,
+                                                         ctx->cmax2, ctx->c_mma);
+        ctx->total_launches++;
+        CK(ctx, cudaGetLastError());
+    }
     FastPlan f;
     if (fast_shape(ctx, ctx->k, ctx->md, accum, &f)) {
         int rc = ensure_fast(ctx, f);
@@ -835,7 +839,14 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
 }
 
 // [sums | counts] of this subtask's cached points for the current centroids -> ctx->red.
-int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
+// One GPU's tail of a round in one launch is worth it (and one CTA can prepare the model) for models up to this size
+constexpr size_t kFusedTailMaxModel = (size_t)1 << 18;
+
+// fused_tail: reduce + finalize + prep run as round_tail_kernel (world == 1, fmlk_fit / fmlk_train_round);
+// tail_ran_before: the previous round of this fit ended in that kernel -- the model is prepared and the
+// accumulators are clear
+int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n, bool fused_tail = false,
+                bool tail_ran_before = false) {
     if (!extra_rows && ctx->n_total > 0 && ctx->d != ctx->md) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
     LaunchCfg cfg;
     ctx->rows_aligned16 = extra_rows ? (reinterpret_cast<uintptr_t>(extra_rows) & 15) == 0 : true;
@@ -852,10 +863,19 @@ int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
         const int64_t ctas = (most + (int64_t)kWideWarps * kWarpRows - 1) / ((int64_t)kWideWarps * kWarpRows);
         cfg.n_partials = (int)std::max<int64_t>(1, std::min<int64_t>(cfg.n_partials, ctas));
     }
+    if (!cfg.wide) {
+        // never more accumulators than the largest launch has CTAs (a small problem: less to clear and to add up)
+        int64_t most = extra_rows ? extra_n : 0;
+        if (!extra_rows)
+            for (const Chunk &ch : ctx->chunks) most = std::max(most, ch.rows);
+        const int64_t tiles = (most + kWarpRows - 1) / kWarpRows;
+        cfg.n_partials = (int)std::max<int64_t>(1, std::min<int64_t>(cfg.n_partials, (tiles + cfg.warps - 1) / cfg.warps));
+    }
     const size_t stride = partial_stride(ctx->k, ctx->md); // len rounded up to even
     if ((rc = ensure_partials(ctx, stride * cfg.n_partials))) return rc;
-    if ((rc = prep_centroids(ctx, true))) return rc;
-    CK(ctx, cudaMemsetAsync(ctx->partials, 0, stride * cfg.n_partials * sizeof(double), ctx->stream));
+    if ((rc = prep_centroids(ctx, true, tail_ran_before))) return rc;
+    if (!tail_ran_before)
+        CK(ctx, cudaMemsetAsync(ctx->partials, 0, stride * cfg.n_partials * sizeof(double), ctx->stream));
     if (extra_rows) {
         if ((rc = launch_assign(ctx, cfg, extra_rows, extra_n, nullptr, true))) return rc;
     } else {
@@ -863,8 +883,19 @@ int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n) {
             if ((rc = launch_assign(ctx, cfg, ch.ptr, ch.rows, nullptr, true))) return rc;
     }
     const int threads = 256;
-    reduce_partials_kernel<<<(unsigned)((len + threads - 1) / threads), threads, 0, ctx->stream>>>(
-        ctx->partials, cfg.n_partials, (int)len, stride, ctx->red);
+    if (fused_tail) {
+        if (!ctx->tail_counter) {
+            if ((rc = dev_alloc(ctx, &ctx->tail_counter, 1))) return rc;
+            CK(ctx, cudaMemsetAsync(ctx->tail_counter, 0, sizeof(unsigned), ctx->stream));
+        }
+        round_tail_kernel<<<(unsigned)((len + 31) / 32), threads, 0, ctx->stream>>>(
+            ctx->partials, cfg.n_partials, (int)len, stride, ctx->red, ctx->k, ctx->md, (ctx->k + 7) & ~7,
+            (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0, ctx->centroids, ctx->weights, ctx->cn, ctx->h, ctx->cmax2, ctx->c_mma,
+            ctx->tail_counter);
+    } else {
+        reduce_partials_kernel<<<(unsigned)((len + threads - 1) / threads), threads, 0, ctx->stream>>>(
+            ctx->partials, cfg.n_partials, (int)len, stride, ctx->red);
+    }
     ctx->total_launches++;
     CK(ctx, cudaGetLastError());
     return FMLK_OK;
@@ -881,10 +912,17 @@ int run_predict(fmlk_ctx *ctx, const PredictPlan &pl, const double *x, int64_t n
     return launch_assign(ctx, pl.cfg, x, n, labels, false);
 }
 
-int one_train_round(fmlk_ctx *ctx) {
+// *tail_ran (in: the previous round of the same fit ended in round_tail_kernel; out: this one did)
+int one_train_round(fmlk_ctx *ctx, bool *tail_ran = nullptr) {
+    const size_t len = (size_t)ctx->k * ctx->md + ctx->k;
+    if (ctx->world == 1 && len <= kFusedTailMaxModel) {
+        const bool before = tail_ran && *tail_ran;
+        int rc = local_round(ctx, nullptr, 0, true, before);
+        if (tail_ran) *tail_ran = rc == FMLK_OK;
+        return rc;
+    }
     int rc = local_round(ctx, nullptr, 0);
     if (rc) return rc;
-    const size_t len = (size_t)ctx->k * ctx->md + ctx->k;
     if (ctx->world > 1)
         CKN(ctx, nccl().AllReduce(ctx->red, ctx->red, len, ncclFloat64, ncclSum, ctx->comm, ctx->stream));
     const int threads = 256;
@@ -1087,6 +1125,7 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     dev_free(ctx->gathered);
     dev_free(ctx->partials);
     dev_free(ctx->recheck);
+    dev_free(ctx->tail_counter);
     dev_free(ctx->stage_rows);
     dev_free(ctx->stage_labels);
     dev_free(ctx->ingest_buf);
@@ -1402,8 +1441,9 @@ int32_t fmlk_fit(fmlk_ctx *ctx, int32_t max_iter, double *out_centroids, double 
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
     if (max_iter <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "maxIter must be > 0");
+    bool tail_ran = false;
     for (int it = 0; it < max_iter; it++)
-        if ((rc = one_train_round(ctx))) return rc;
+        if ((rc = one_train_round(ctx, &tail_ran))) return rc;
     return copy_model_out(ctx, out_centroids, out_weights);
 }
 

@@ -1455,6 +1455,86 @@ __global__ void finalize_centroids_kernel(const double *red, int k, int d, doubl
     if (i < k) weights[i] = red[(size_t)k * d + i];
 }
 
+// The end of a round on one GPU in ONE launch (the three kernels above, same arithmetic, same order): every
+// block adds up its slice of the per-CTA accumulators (in a fixed order), writes it to `red` and clears the slots
+// for the next round; the block that finishes last turns `red` into the new model (ModelDataGenerator) and prepares
+// it for the next round's assign kernel (prep_centroids_kernel).  A small problem's round is then two launches
+// (assign + this) instead of five.  counter: one zeroed unsigned, left at zero again.
+__global__ void __launch_bounds__(256) round_tail_kernel(double *partials, int n_partials, int len, size_t stride, double *red,
+                                                         int k, int d, int k_pad, int fma_mode, double *centroids,
+                                                         double *weights, double *cn, double *h, double *cmax2,
+                                                         double *c_mma, unsigned *counter) {
+    __shared__ double mxs[256];
+    __shared__ bool last;
+    // a block owns 32 elements; warp g adds the slots g, g + 8, g + 16, ... of each (coalesced rows of the slot),
+    // then the eight partial sums are added in warp order: a fixed order, so the result is reproducible
+    const int e = threadIdx.x & 31, g = threadIdx.x >> 5;
+    const int i = blockIdx.x * 32 + e;
+    double s = 0.0;
+    if (i < len) {
+        int b = g;
+        for (; b + 24 < n_partials; b += 32) {
+            double v[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) v[u] = __ldcg(partials + (size_t)(b + 8 * u) * stride + i);
+#pragma unroll
+            for (int u = 0; u < 4; u++) s = __dadd_rn(s, v[u]);
+#pragma unroll
+            for (int u = 0; u < 4; u++) partials[(size_t)(b + 8 * u) * stride + i] = 0.0;
+        }
+        for (; b < n_partials; b += 8) {
+            s = __dadd_rn(s, __ldcg(partials + (size_t)b * stride + i));
+            partials[(size_t)b * stride + i] = 0.0;
+        }
+    }
+    mxs[threadIdx.x] = s;
+    __syncthreads();
+    if (g == 0 && i < len) {
+#pragma unroll
+        for (int u = 1; u < 8; u++) s = __dadd_rn(s, mxs[32 * u + e]);
+        red[i] = s;
+    }
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        last = atomicAdd(counter, 1u) == gridDim.x - 1;
+        if (last) *counter = 0u;
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    const int kd = k * d;
+    for (int e = threadIdx.x; e < kd; e += blockDim.x) {
+        const double cnt = __ldcg(red + kd + e / d);
+        centroids[e] = __dmul_rn(__ldcg(red + e), __ddiv_rn(1.0, cnt));
+    }
+    for (int j = threadIdx.x; j < k; j += blockDim.x) weights[j] = __ldcg(red + kd + j);
+    __syncthreads();
+    double mx = 0.0;
+    for (int j = threadIdx.x; j < k_pad; j += blockDim.x) {
+        if (j < k) {
+            const double ss = ref_sumsq(centroids + (size_t)j * d, d, fma_mode);
+            cn[j] = sqrt(ss);
+            const bool live = isfinite(ss);
+            h[j] = live ? -0.5 * ss : -INFINITY;
+            if (live && ss > mx) mx = ss;
+            for (int e = 0; e < d; e++) c_mma[(size_t)j * d + e] = live ? centroids[(size_t)j * d + e] : 0.0;
+        } else {
+            h[j] = -INFINITY;
+        }
+    }
+    mxs[threadIdx.x] = mx;
+    __syncthreads();
+    for (int s = blockDim.x >> 1; s > 0; s >>= 1) {
+        if (threadIdx.x < s) mxs[threadIdx.x] = fmax(mxs[threadIdx.x], mxs[threadIdx.x + s]);
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        cmax2[0] = mxs[0];
+        cmax2[1] = mxs[0] > 0.0 ? (double)(ilogb(mxs[0]) + 1) : -1100.0;
+    }
+}
+
 // ModelDataLocalUpdater (OnlineKMeans.java:309-322) on [k*d sums | k counts]:
 //   weights *= decay / parallelism; for counts > 0: w += n; lambda = n / w;
 //   c = c * (1 - lambda); c += (lambda / n) * sums.
