@@ -95,6 +95,7 @@ struct Chunk {
 struct LaunchCfg {
     int warps, acc_warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid, private_sums;
     int spin_ns, stagger_ns;
+    int warp_slots; // MODE 3: one accumulator per warp
     int red_sums; // MMA warps add to a global accumulator per CTA (no accumulator warps)
     int wide; // rows too long for the shared-memory tiling: assign_wide_kernel
     size_t smem;
@@ -151,6 +152,8 @@ struct fmlk_ctx {
     double *partials = nullptr;    // n_partials_cap * (k*d + k)
     size_t partials_cap = 0;       // in doubles
     unsigned long long *recheck = nullptr;
+    double *warp_scratch = nullptr; // per-warp accumulators of assign_kernel<3> with few centroids (zero between launches)
+    size_t warp_scratch_cap = 0;    // doubles
     unsigned *tail_counter = nullptr; // round_tail_kernel's arrival counter (zero between launches)
 
     // staging for predict / online batches
@@ -323,6 +326,8 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
                 c.n_ctiles = 1;
                 c.sums_in_smem = 0;
                 c.red_sums = 1;
+                c.warp_slots = env_int("FMLK_TUNE_WSLOT", c.k_pad <= 16 ? 1 : 0); // measured: k = 2, d = 64 1.9 -> 3.2 TB/s, k = 10, d = 100 2.7 -> 4.0; k >= 24: none
+                if (ctx->max_partial_slots > 0) c.warp_slots = 0; // borrowed scratch (the allocation-free entry point)
                 c.n_partials = (int)std::max<size_t>(1, std::min<size_t>((size_t)c.grid, ((size_t)64 << 20) / (((size_t)k * d + k) * sizeof(double))));
                 if (ctx->max_partial_slots > 0) c.n_partials = std::min(c.n_partials, ctx->max_partial_slots);
                 c.smem = need;
@@ -783,6 +788,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.spin_ns = cfg.spin_ns;
     p.stagger_ns = cfg.stagger_ns;
     p.acc_dmma = env_int("FMLK_TUNE_ACC_DMMA", 1);
+    p.warp_scratch = (accum && cfg.warp_slots && cfg.red_sums && !cfg.wide) ? ctx->warp_scratch : nullptr;
     // few centroids (HBM-bound): one bulk copy per row tile; otherwise one per row
     p.row_copies = env_int("FMLK_TUNE_ROW_COPIES", cfg.k_pad <= 32 ? 0 : 1);
     p.no_bulk_red = env_int("FMLK_TUNE_NO_BULK_RED", 0);
@@ -873,6 +879,17 @@ int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n, bool f
     }
     const size_t stride = partial_stride(ctx->k, ctx->md); // len rounded up to even
     if ((rc = ensure_partials(ctx, stride * cfg.n_partials))) return rc;
+    if (cfg.warp_slots && cfg.red_sums && !cfg.wide) {
+        const size_t need = stride * (size_t)cfg.grid * cfg.warps;
+        if (need > ctx->warp_scratch_cap) {
+            dev_free(ctx->warp_scratch);
+            ctx->warp_scratch = nullptr;
+            ctx->warp_scratch_cap = 0;
+            if ((rc = dev_alloc(ctx, &ctx->warp_scratch, need))) return rc;
+            ctx->warp_scratch_cap = need;
+            CK(ctx, cudaMemsetAsync(ctx->warp_scratch, 0, need * sizeof(double), ctx->stream)); // the kernel keeps it zero
+        }
+    }
     if ((rc = prep_centroids(ctx, true, tail_ran_before))) return rc;
     if (!tail_ran_before)
         CK(ctx, cudaMemsetAsync(ctx->partials, 0, stride * cfg.n_partials * sizeof(double), ctx->stream));
@@ -1126,6 +1143,7 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     dev_free(ctx->partials);
     dev_free(ctx->recheck);
     dev_free(ctx->tail_counter);
+    dev_free(ctx->warp_scratch);
     dev_free(ctx->stage_rows);
     dev_free(ctx->stage_labels);
     dev_free(ctx->ingest_buf);

@@ -66,6 +66,9 @@ struct AssignParams {
 #ifdef FMLK_TRACE
     unsigned long long *trace; // [warps of CTA 0][kTraceEvents] (clock << 4 | event), debugging builds only
 #endif
+    double *warp_scratch; // MODE 3, few centroids: [gridDim.x * mma_warps][k*d + k] all zero between launches; each warp adds
+                          // into its own accumulator (the L2 additions of a CTA's warps then never queue on the same cells)
+                          // and the CTA folds them into its slot of `partials` at the end
     int32_t acc_dmma; // 1: accumulator warps add on the FP64 tensor pipe (d = 32 x column groups, finite rows)
     int32_t row_copies; // 1 = one bulk copy per row, 0 = one per tile (chosen by the host: see assign_kernel)
     int32_t no_bulk_red; // tuning: 1 = per-lane L2 atomics instead of bulk reductions
@@ -885,13 +888,18 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                 // with fire-and-forget L2 atomics (the additions happen in L2, nothing queues on the
                 // FP64 pipe); sums then depend on arrival order in their last bits
                 __syncwarp();
-                double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d);
+                // (few centroids: a slot per warp, so that the L2 additions of one CTA's warps do not queue on the same cells)
+                double *slot = p.warp_scratch ? p.warp_scratch + ((size_t)blockIdx.x * W + warp) * partial_stride(p.k, p.d)
+                                              : p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d);
                 const int my_lab = lane < rows_valid ? lab_s[lane] : 0;
                 if (red_bulk) {
                     // one bulk reduction per row, issued by the lane of that row: the TMA engine reads the
-                    // row out of this warp's tile and adds it to sums[label] in L2
+                    // row out of this warp's tile and adds it to sums[label] in L2.  (Tried: folding the rows of a
+                    // tile that share a label into one before sending -- half the L2 additions at k = 10; faster only
+                    // at d = 100 and k <= 4, 4-19 % slower elsewhere: the FP64 adds cost the warp more than L2 saves.)
+                    const bool send = lane < rows_valid;
                     fence_proxy_async_smem();
-                    if (lane < rows_valid)
+                    if (send)
                         bulk_reduce_add_f64(slot + (size_t)my_lab * p.d,
                                             (unsigned)__cvta_generic_to_shared(Xt + (size_t)lane * S), row_bytes);
                     bulk_commit_group();
@@ -1117,6 +1125,27 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
         }
     }
 
+    if (red && p.warp_scratch) {
+        // every reduction of this CTA has been performed (bulk_wait_group_all above): fold the warps' accumulators, in
+        // warp order, into the CTA's slot and leave them zero for the next launch
+        __syncthreads();
+        const size_t stride = partial_stride(p.k, p.d);
+        const int len = p.k * p.d + p.k;
+        double *mine = p.warp_scratch + (size_t)blockIdx.x * W * stride;
+        double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * stride;
+        for (int i = threadIdx.x; i < len; i += blockDim.x) {
+            double acc = 0.0;
+            for (int w0 = 0; w0 < W; w0 += 4) {
+                double v[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) v[u] = w0 + u < W ? __ldcg(mine + (size_t)(w0 + u) * stride + i) : 0.0;
+#pragma unroll
+                for (int u = 0; u < 4; u++) acc += v[u];
+            }
+            for (int w = 0; w < W; w++) mine[(size_t)w * stride + i] = 0.0;
+            atomicAdd(slot + i, acc); // (a slot can be shared by several CTAs when the model is large)
+        }
+    }
     if (priv) {
         // the warps' private sums, combined in warp order, added to this CTA's slot
         __syncthreads();
