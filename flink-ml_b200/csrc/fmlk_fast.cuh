@@ -93,6 +93,8 @@ struct FastParams {
     int32_t *labels;     // or null
     double *partials;    // or null (predict)
     int32_t n_partials;
+    double *warp_scratch; // [gridDim.x * scratch_slots][k*d + k], zero between launches: accumulators of the epilogue warps
+    int32_t scratch_slots; // (warp e adds into slot e % scratch_slots; folded into the CTA's slot of `partials` at the end)
     uint32_t *flag_words; // [ceil(n / 128) * 4]
     uint32_t *flag_list;  // indices of the non-zero words, in arrival order ...
     uint32_t *flag_count; // ... and how many (zeroed before the launch)
@@ -402,7 +404,10 @@ __global__ void __launch_bounds__(kFastThreads, 1)
         const unsigned lane_sel = (unsigned)(32 * q) << 16;
         const unsigned row_bytes = (unsigned)p.d * 8u;
         const int chunks = p.Nacc >> 4, c_lo = ec == 0 ? 0 : (chunks + 1) >> 1, c_hi = ec == 0 ? (chunks + 1) >> 1 : chunks;
-        double *slot = ACCUM ? p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d) : nullptr;
+        double *slot = !ACCUM ? nullptr
+                       : p.warp_scratch ? p.warp_scratch + ((size_t)blockIdx.x * p.scratch_slots + (warp - kFastEpiWarp0) % p.scratch_slots) *
+                                                               partial_stride(p.k, p.d)
+                                        : p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d);
         // |c|max^2 in FP32, rounded up; magnitudes FP32 scores cannot carry switch the tensor-core decision off
         const int cexp = (int)p.cmax2[1];
         const float cmax2f = (cexp >= -120 && cexp <= 80) ? __double2float_ru(p.cmax2[0]) : INFINITY;
@@ -663,6 +668,22 @@ __global__ void __launch_bounds__(kFastThreads, 1)
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    if (ACCUM && p.warp_scratch) {
+        // every bulk reduction of this CTA has been performed (the epilogue lanes waited for theirs): fold the warps'
+        // accumulators into the CTA's slot, in slot order, and leave them zero for the next launch
+        const size_t stride = partial_stride(p.k, p.d);
+        const int kd = p.k * p.d;
+        double *mine = p.warp_scratch + (size_t)blockIdx.x * p.scratch_slots * stride;
+        double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * stride;
+        for (int i = threadIdx.x; i < kd; i += blockDim.x) {
+            double acc = 0.0;
+            for (int s = 0; s < p.scratch_slots; s++) {
+                acc += __ldcg(mine + (size_t)s * stride + i);
+                mine[(size_t)s * stride + i] = 0.0;
+            }
+            atomicAdd(slot + i, acc);
+        }
+    }
     if (ACCUM) {
         double *slot = p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d);
         for (int i = threadIdx.x; i < p.k; i += blockDim.x)
