@@ -137,3 +137,26 @@ def test_score_error_within_model():
         assert np.array_equal(lab.cpu().numpy(), O.predict(x, c))
     # measured error must sit well inside the modelled bound
     assert worst < 0.5, "tensor-core score error reaches %.2f of the modelled bound" % worst
+
+
+def test_fast_context_through_changing_shapes_keeps_its_scratch_clean():
+    """Same as the FP64 test of that name: the accumulators of the epilogue warps (few centroids: four per CTA) are
+    cleared by the kernel that used them; shapes that do and do not take the tcgen05 kernel alternate."""
+    steps = [(30000, 100, 10, "fit"), (30000, 100, 10, "partials"), (8192, 10, 2, "fit"), (20000, 64, 100, "fit"),
+             (30000, 100, 10, "fit"), (12000, 16, 12, "partials"), (3000, 16, 12, "fit"), (9000, 128, 40, "fit")]
+    with native.Context(0, flags=FAST) as ctx:
+        for i, (n, d, k, what) in enumerate(steps):
+            x, init = _data(n, d, k, 100 + i)
+            ctx.clear_points()
+            ctx.append_points(x)
+            ctx.set_centroids(init)
+            if what == "partials":
+                sums, counts = ctx.local_partials()
+                o_sums, o_counts = O.train_local(x, init)
+                assert np.array_equal(counts, o_counts.astype(np.int64)), (i, n, d, k)
+                assert np.allclose(sums, o_sums, rtol=1e-12, atol=0), (i, n, d, k)
+            else:
+                c, w = ctx.fit(3)
+                oc, ow = O.fit([x], init, 3, threads=O.max_threads())
+                assert np.array_equal(w, ow), (i, n, d, k)
+                assert np.allclose(c, oc, rtol=1e-9, atol=0, equal_nan=True), (i, n, d, k)

@@ -269,6 +269,32 @@ def test_train_round_equals_fit(ctx):
     assert np.array_equal(cm, c2) and np.array_equal(wm, w2)
 
 
+def test_one_context_through_changing_shapes_keeps_its_scratch_clean(ctx):
+    """The per-warp accumulators (few centroids) and the per-CTA slots are cleared by the kernels that used them,
+    not by a memset per round: a context that goes through fits, single rounds, local partials and predictions
+    of different shapes, in any order, must give the oracle's answer every time."""
+    steps = [(30000, 100, 10, "fit"), (30000, 100, 10, "partials"), (5000, 10, 2, "fit"), (20000, 64, 100, "round"),
+             (30000, 100, 10, "fit"), (12000, 16, 12, "partials"), (12000, 16, 12, "fit"), (9000, 128, 40, "fit"),
+             (5000, 10, 2, "partials")]
+    for i, (n, d, k, what) in enumerate(steps):
+        x = O.generate_dense(7 + (n % 5), 0, 1, n, d)
+        init = x[:k].copy()
+        ctx.clear_points()
+        ctx.append_points(x)
+        ctx.set_centroids(init)
+        if what == "partials":
+            sums, counts = ctx.local_partials()
+            o_sums, o_counts = O.train_local(x, init)
+            assert np.array_equal(counts, o_counts.astype(np.int64)), (i, n, d, k)
+            assert np.allclose(sums, o_sums, rtol=SUM_RTOL, atol=0), (i, n, d, k)
+        else:
+            iters = 3 if what == "fit" else 1
+            c, w = ctx.fit(iters) if what == "fit" else ctx.train_round()
+            oc, ow = O.fit([x], init, iters, threads=O.max_threads())
+            assert np.array_equal(w, ow), (i, n, d, k)
+            assert np.allclose(c, oc, rtol=CENTROID_RTOL, atol=0, equal_nan=True), (i, n, d, k)
+
+
 # ---------------------------------------------------------------- online
 TRAIN1 = np.array([[10.0, 0.0], [10.0, 0.3], [10.3, 0.0], [-10.0, 0.0], [-10.0, 0.6], [-10.6, 0.0]])
 TRAIN2 = np.array([[10.0, 100.0], [10.0, 100.3], [10.3, 100.0], [-10.0, -100.0], [-10.0, -100.6],
