@@ -558,7 +558,7 @@ bool fast_shape(const fmlk_ctx *ctx, int k, int d, bool accum, FastPlan *out) {
         const int na = (kFastACol + 2 * 2 * f.Kd + 2 * nacc <= kFastTmemCols) ? 2 : 1;
         if (kFastACol + na * 2 * f.Kd + 2 * nacc > kFastTmemCols) return false;
         const size_t k_rows = (size_t)nacc * passes;
-        const size_t fixed = (size_t)nb * (2 * f.KB) * nacc * 128 + 8 * kFastRows * sizeof(float) + k_rows * 2 * sizeof(int) +
+        const size_t fixed = (size_t)nb * (2 * f.KB) * nacc * 128 + 9 * kFastRows * sizeof(float) + k_rows * 2 * sizeof(int) +
                              48 * 8 + 16 + 1024 /* alignment slack */;
         if (fixed + (size_t)min_stages * f.stage_bytes > ctx->smem_optin) return false;
         f.Nacc = nacc;
@@ -671,6 +671,11 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
     // few centroids: the epilogue warps' L2 additions queue on the same cells of one accumulator; four accumulators
     // per CTA (k = 10, d = 100: 1.69 -> 0.94 ms); from k = 100 on the extra fold only costs (1.84 -> 2.0 ms)
     p.scratch_slots = accum ? env_int("FMLK_TUNE_FSLOTS", f.Nacc <= 16 ? 4 : 1) : 1;
+    // who issues the bulk reductions: with streamed centroid terms (several passes per tile) the epilogue warps are
+    // the busiest of the CTA and the converter warps take all of them over (k = 1000, d = 64: 4.81 -> 4.60 ms);
+    // with resident terms the rows' time in shared memory is what bounds training, and the converters send a tile
+    // late (config 2: 1.81 -> 1.89 ms), so the epilogue keeps them
+    p.epi_send = accum ? std::min(16, std::max(0, env_int("FMLK_TUNE_EPI_SEND", f.P > 1 ? 0 : 16))) : 0;
     p.warp_scratch = nullptr;
     if (p.scratch_slots > 1) {
         const size_t need = partial_stride(ctx->k, ctx->md) * (size_t)ctx->sm_count * p.scratch_slots;

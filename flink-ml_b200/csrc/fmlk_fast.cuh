@@ -93,6 +93,7 @@ struct FastParams {
     int32_t *labels;     // or null
     double *partials;    // or null (predict)
     int32_t n_partials;
+    int32_t epi_send; // training: of the 16 rows a warp pair (epilogue, converter) shares, the epilogue warp sends this many
     double *warp_scratch; // [gridDim.x * scratch_slots][k*d + k], zero between launches: accumulators of the epilogue warps
     int32_t scratch_slots; // (warp e adds into slot e % scratch_slots; folded into the CTA's slot of `partials` at the end)
     uint32_t *flag_words; // [ceil(n / 128) * 4]
@@ -270,23 +271,23 @@ __global__ void __launch_bounds__(kFastThreads, 1)
     float *mrg_b = nsq_s + 4 * kFastRows;                                             // [128] second column half: best
     float *mrg_s = mrg_b + kFastRows;                                                 // [128]                     second
     int *mrg_i = reinterpret_cast<int *>(mrg_s + kFastRows);                          // [128]                     index
-    int *lab_s = mrg_i + kFastRows;                                                   // [128] label by TMEM lane, -1: not decided
+    int *lab_s = mrg_i + kFastRows;                                                   // [2 tiles][128] label by TMEM lane, -1: not decided
     const int k_rows = p.P * p.Nacc;
-    int *counts_s = lab_s + kFastRows;                                                // [k_rows]
+    int *counts_s = lab_s + 2 * kFastRows;                                                // [k_rows]
     float *h_s = reinterpret_cast<float *>(counts_s + k_rows);                        // [k_rows] -|c|^2/2
     unsigned long long *bars = reinterpret_cast<unsigned long long *>(h_s + k_rows);
     unsigned *tmem_slot = reinterpret_cast<unsigned *>(bars + 40);
     auto bar = [&](int i) { return (unsigned)__cvta_generic_to_shared(&bars[i]); };
     // barrier indices
     const int FULL_X = 0, X_EMPTY = 8, A_FULL = 16, A_EMPTY = 18, D_FULL = 20, D_EMPTY = 22, THR_FULL = 24, THR_EMPTY = 26,
-              B_FULL = 32, B_EMPTY = 36;
+              B_FULL = 32, B_EMPTY = 36, LAB_FULL = 28, LAB_EMPTY = 30;
 
     if (threadIdx.x == 0) {
         for (int s = 0; s < kFastMaxStages; s++) {
             mbar_init(bar(FULL_X + s), 1);
             // the last readers of a half stage: training, the four epilogue warps whose rows it holds (they feed
             // the bulk reductions from it); predict, the two converter warps of each column set
-            mbar_init(bar(X_EMPTY + s), 4);
+            mbar_init(bar(X_EMPTY + s), (ACCUM && p.epi_send > 0 && p.epi_send < 16) ? 8 : 4);
         }
         for (int a = 0; a < 2; a++) {
             mbar_init(bar(A_FULL + a), kFastConvWarps);
@@ -295,6 +296,8 @@ __global__ void __launch_bounds__(kFastThreads, 1)
             mbar_init(bar(D_EMPTY + a), kFastEpiWarps);
             mbar_init(bar(THR_FULL + a), kFastConvWarps);
             mbar_init(bar(THR_EMPTY + a), 4);
+            mbar_init(bar(LAB_FULL + a), 4);                // the four epilogue warps that hold the rows' labels
+            mbar_init(bar(LAB_EMPTY + a), kFastConvWarps);  // the converter warps, once they have read them
         }
         for (int s = 0; s < 4; s++) {
             mbar_init(bar(B_FULL + s), 1);
@@ -330,6 +333,37 @@ __global__ void __launch_bounds__(kFastThreads, 1)
         const size_t row_off = (size_t)((rho & 63) >> 3) * p.group_bytes + (size_t)(rho & 7) * p.d * 8;
         int hs = (q >> 1) % p.NS, a = 0; // this warp's rows are in half (q >> 1) of every tile
         unsigned ph_x = ((q >> 1) / p.NS) & 1, ph_a = 1; // FULL_X: phase of this use; A_EMPTY: the phase before
+        // Training: the bulk reductions of a tile are issued from here, not by the epilogue warps -- an issue costs
+        // the issuing warp ~125 cycles per row (2 k cycles for its 16 rows), the epilogue warps are the busiest of the
+        // CTA and these wait for rows two thirds of the time.  Warp (cs, q) sends rows 16 cs .. 16 cs + 15 of quarter q
+        // (the epilogue warp (cs, q) keeps the first epi_send of them), one tile behind its own conversion.
+        const int Lr = 32 * q + 16 * cs + (lane & 15);
+        const int rr = fast_row_of_lane(Lr);
+        const unsigned row_bytes_c = (unsigned)p.d * 8u;
+        const unsigned red_off = (unsigned)((rr & 63) >> 3) * (unsigned)p.group_bytes + (unsigned)(rr & 7) * row_bytes_c;
+        double *slot = !ACCUM ? nullptr
+                       : p.warp_scratch ? p.warp_scratch + ((size_t)blockIdx.x * p.scratch_slots + warp % p.scratch_slots) *
+                                                               partial_stride(p.k, p.d)
+                                        : p.partials + (size_t)(blockIdx.x % p.n_partials) * partial_stride(p.k, p.d);
+        int hs_red = (q >> 1) % p.NS;
+        auto send_tile = [&](int j) {
+            const int ej = j & 1;
+            mbar_wait_relaxed(bar(LAB_FULL + ej), (unsigned)((j >> 1) & 1));
+            const int lab = (lane < 16 && lane >= p.epi_send) ? lab_s[ej * kFastRows + Lr] : -1;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(LAB_EMPTY + ej));
+            if (p.epi_send < 16) {
+                if (lab >= 0)
+                    bulk_reduce_add_f64(slot + (size_t)lab * p.d,
+                                        (unsigned)__cvta_generic_to_shared(stage0 + (size_t)hs_red * p.stage_bytes) + red_off, row_bytes_c);
+                bulk_commit_group();
+                bulk_wait_group_read(); // the rows have been read: the half stage may be refilled
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar(X_EMPTY + hs_red));
+            }
+            hs_red += 2;
+            if (hs_red >= p.NS) hs_red -= p.NS;
+        };
         for (int i = 0; i < my_tiles; i++) {
             const int e = i & 1;
             FAST_TRACE(0)
@@ -394,6 +428,11 @@ __global__ void __launch_bounds__(kFastThreads, 1)
                 a = 0;
                 ph_a ^= 1u;
             }
+            if (ACCUM && i >= 1) send_tile(i - 1);
+        }
+        if (ACCUM) {
+            if (my_tiles >= 1) send_tile(my_tiles - 1);
+            bulk_wait_group_all();
         }
     } else if (warp < kFastLoaderWarp) {
         // =========================== epilogue: scores -> label (+ accumulate) ===========================
@@ -506,25 +545,33 @@ __global__ void __launch_bounds__(kFastThreads, 1)
                     p.dbg_scores[2 * (row0 + rho) + 1] = second;
                 }
                 if (p.labels != nullptr && valid) p.labels[row0 + rho] = idx;
-                if (ACCUM) lab_s[L] = (valid && !flagged) ? idx : -1;
+                if (ACCUM) {
+                    // hand the labels to the converter warps (their buffer of two tiles ago has been read)
+                    const int lab = (valid && !flagged) ? idx : -1;
+                    mbar_wait_relaxed(bar(LAB_EMPTY + e), ph ^ 1u);
+                    lab_s[e * kFastRows + L] = lab;
+                    if (lab >= 0) atomicAdd(&counts_s[lab], 1);
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar(LAB_FULL + e));
+                }
             }
-            if (ACCUM) {
+            if (ACCUM && p.epi_send > 0) {
                 named_barrier(1 + q, 64); // the labels of this quarter are in lab_s
-                // one bulk reduction per decided row (issued per lane: bulk operations of one thread are performed
-                // one after the other, those of different threads overlap; sixteen lanes of eight warps share a tile)
-                if (lane < 16) {
-                    const int lab = lab_s[Lr];
-                    if (lab >= 0) {
-                        atomicAdd(&counts_s[lab], 1);
+                // this warp's share of the bulk reductions (issued per lane: bulk operations of one thread are performed
+                // one after the other, those of different threads overlap)
+                if (lane < p.epi_send) {
+                    const int lab = lab_s[e * kFastRows + Lr];
+                    if (lab >= 0)
                         bulk_reduce_add_f64(slot + (size_t)lab * p.d,
                                             (unsigned)__cvta_generic_to_shared(stage0 + (size_t)hs * p.stage_bytes) + red_off, row_bytes);
-                    }
                 }
                 bulk_commit_group();
                 FAST_TRACE(8)
                 bulk_wait_group_read(); // the rows have been read: the half stage may be refilled
                 __syncwarp();
                 if (lane == 0) mbar_arrive(bar(X_EMPTY + hs));
+            }
+            if (ACCUM) {
                 hs += 2;
                 if (hs >= p.NS) hs -= p.NS;
             }
