@@ -7,6 +7,7 @@
 #include "fmlk_kernels.cuh"
 #include "fmlk_fast.cuh"
 #include "fmlk_knn.cuh"
+#include "fmlk_ring.cuh"
 
 #include <dlfcn.h>
 #include <algorithm>
@@ -152,6 +153,8 @@ struct fmlk_ctx {
     double *partials = nullptr;    // n_partials_cap * (k*d + k)
     size_t partials_cap = 0;       // in doubles
     unsigned long long *recheck = nullptr;
+    double *c_blk = nullptr; // the centroids block by block in assign_ring_kernel's shared-memory layout
+    size_t c_blk_cap = 0;    // doubles
     double *warp_scratch = nullptr; // per-warp accumulators of assign_kernel<3> with few centroids (zero between launches)
     size_t warp_scratch_cap = 0;    // doubles
     unsigned *tail_counter = nullptr; // round_tail_kernel's arrival counter (zero between launches)
@@ -681,6 +684,7 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
         const size_t need = partial_stride(ctx->k, ctx->md) * (size_t)ctx->sm_count * p.scratch_slots;
         if (need > ctx->warp_scratch_cap) {
             dev_free(ctx->warp_scratch);
+    dev_free(ctx->c_blk);
             ctx->warp_scratch = nullptr;
             ctx->warp_scratch_cap = 0;
             int rc = dev_alloc(ctx, &ctx->warp_scratch, need);
@@ -744,6 +748,15 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
 
 // accum: the launch that follows accumulates (the fast mode's geometry, and with it the layout of the
 // centroid terms, differs between training and predict)
+int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out);
+
+// The d-blocked kernel with rows of at most 64 columns runs as assign_ring_kernel (no CTA-wide barrier per block)
+// when its bulk copies can be used: even d; the rows' alignment is checked per launch.
+bool ring_shape(fmlk_ctx *ctx, const LaunchCfg &cfg, int d) {
+    return cfg.wide && d <= 2 * kWideDk && (d & 1) == 0 && ctx->max_partial_slots == 0 && kRingSmem <= ctx->smem_optin &&
+           env_int("FMLK_TUNE_RING", 1);
+}
+
 // base_done: the round before ended in round_tail_kernel, which has already done prep_centroids_kernel's work
 int prep_centroids(fmlk_ctx *ctx, bool accum, bool base_done = false) {
     const int k_pad = (ctx->k + 7) & ~7;
@@ -753,6 +766,26 @@ int prep_centroids(fmlk_ctx *ctx, bool accum, bool base_done = false) {
                                                          ctx->cmax2, ctx->c_mma);
         ctx->total_launches++;
         CK(ctx, cudaGetLastError());
+    }
+    {
+        LaunchCfg cfg;
+        int rc = choose_cfg(ctx, ctx->k, ctx->md, accum, &cfg);
+        if (rc) return rc;
+        if (ring_shape(ctx, cfg, ctx->md)) {
+            const int nkb = (ctx->md + kWideDk - 1) / kWideDk, nchunks = (cfg.k_pad + 8 * kChunkTiles - 1) / (8 * kChunkTiles);
+            const size_t need = (size_t)nchunks * nkb * kRingBlockElems;
+            if (need > ctx->c_blk_cap) {
+                dev_free(ctx->c_blk);
+                ctx->c_blk = nullptr;
+                ctx->c_blk_cap = 0;
+                if ((rc = dev_alloc(ctx, &ctx->c_blk, need))) return rc;
+                ctx->c_blk_cap = need;
+            }
+            prep_ring_kernel<<<(unsigned)std::min<size_t>((need + 255) / 256, (size_t)ctx->sm_count * 8), 256, 0, ctx->stream>>>(
+                ctx->c_mma, ctx->k, ctx->md, nchunks, nkb, ctx->c_blk);
+            ctx->total_launches++;
+            CK(ctx, cudaGetLastError());
+        }
     }
     FastPlan f;
     if (fast_shape(ctx, ctx->k, ctx->md, accum, &f)) {
@@ -836,7 +869,11 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
         cudaMemsetAsync(p.trace, 0, trace_len * 8, ctx->stream);
     }
 #endif
-    if (cfg.wide) {
+    if (ring_shape(ctx, cfg, ctx->md) && ctx->c_blk && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+        const int rgrid = (int)std::min<int64_t>(cfg.grid, (n + kRingRows - 1) / kRingRows); // one CTA of 16 warps per SM
+        if (accum) assign_ring_kernel<true><<<rgrid, kRingWarps * 32, kRingSmem, ctx->stream>>>(p, ctx->c_blk);
+        else assign_ring_kernel<false><<<rgrid, kRingWarps * 32, kRingSmem, ctx->stream>>>(p, ctx->c_blk);
+    } else if (cfg.wide) {
         const int wgrid = (int)std::min<int64_t>(cfg.grid * 2, (tiles + kWideWarps - 1) / kWideWarps); // two CTAs per SM
         const bool xres = ctx->md <= 2 * kWideDk; // rows of up to 64 columns stay resident per CTA tile
         if (accum && xres) assign_wide_kernel<true, true><<<wgrid, kWideWarps * 32, cfg.smem, ctx->stream>>>(p);
@@ -1103,6 +1140,10 @@ int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *
             e = cudaFuncSetAttribute(assign_wide_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(assign_wide_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_ring_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_ring_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(assign_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
