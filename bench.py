@@ -289,7 +289,9 @@ def run_ours(args):
         else:
             roof = dict(hbm)
         if not fast:
-            kern = ("fmlk::assign_wide_kernel<true> (d-blocked assign + accumulate)" if "wide=1" in desc_ else
+            kern = ("fmlk::assign_ring_kernel<true> (d-blocked assign + accumulate, centroid blocks through a 4-stage ring)"
+                    if "ring=1" in desc_ else
+                    "fmlk::assign_wide_kernel<true> (d-blocked assign + accumulate)" if "wide=1" in desc_ else
                     "fmlk::assign_kernel<2> (assign + warp-private sums)" if "private_sums=1" in desc_ else
                     "fmlk::assign_kernel<3> (assign + sums by bulk reductions into one accumulator per CTA)"
                     if "red_sums=1" in desc_ else "fmlk::assign_kernel<1> (assign + accumulate)")

@@ -750,11 +750,15 @@ int launch_fast(fmlk_ctx *ctx, const FastPlan &f, const double *x, int64_t n, in
 // centroid terms, differs between training and predict)
 int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out);
 
-// The d-blocked kernel with rows of at most 64 columns runs as assign_ring_kernel (no CTA-wide barrier per block)
-// when its bulk copies can be used: even d; the rows' alignment is checked per launch.
+// The d-blocked kernel with rows of at most 128 columns runs as assign_ring_kernel (no CTA-wide barrier per block)
+// when its 16-byte copies can be used: even d; the rows' alignment is checked per launch.
 bool ring_shape(fmlk_ctx *ctx, const LaunchCfg &cfg, int d) {
-    return cfg.wide && d <= 2 * kWideDk && (d & 1) == 0 && ctx->max_partial_slots == 0 && kRingSmem <= ctx->smem_optin &&
-           env_int("FMLK_TUNE_RING", 1);
+    // rows of 66..128 columns (warp pairs split every chunk of 64 centroids): only with enough whole chunks -- at
+    // k = 100 the second chunk leaves one warp of each pair nearly idle (d = 128 predict: 23.0 against 25.4 TFLOP/s
+    // for assign_wide_kernel; k = 256: 28.5 against 27.7, k = 1000: 28.6 against 27.6)
+    if (d > 2 * kWideDk && cfg.k_pad < 192) return false;
+    return cfg.wide && d <= 4 * kWideDk && (d & 1) == 0 && ctx->max_partial_slots == 0 &&
+           std::max(RingShape<1>::kSmem, RingShape<2>::kSmem) <= ctx->smem_optin && env_int("FMLK_TUNE_RING", 1);
 }
 
 // base_done: the round before ended in round_tail_kernel, which has already done prep_centroids_kernel's work
@@ -870,9 +874,14 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     }
 #endif
     if (ring_shape(ctx, cfg, ctx->md) && ctx->c_blk && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
-        const int rgrid = (int)std::min<int64_t>(cfg.grid, (n + kRingRows - 1) / kRingRows); // one CTA of 16 warps per SM
-        if (accum) assign_ring_kernel<true><<<rgrid, kRingWarps * 32, kRingSmem, ctx->stream>>>(p, ctx->c_blk);
-        else assign_ring_kernel<false><<<rgrid, kRingWarps * 32, kRingSmem, ctx->stream>>>(p, ctx->c_blk);
+        // one CTA of 16 warps per SM; rows of up to 64 columns: 256 per CTA tile, up to 128: 128 (warp pairs share rows)
+        const bool one = ctx->md <= 2 * kWideDk;
+        const int tile_rows = one ? RingShape<1>::kRows : RingShape<2>::kRows;
+        const int rgrid = (int)std::min<int64_t>(cfg.grid, (n + tile_rows - 1) / tile_rows);
+        if (one && accum) assign_ring_kernel<true, 1><<<rgrid, kRingWarps * 32, RingShape<1>::kSmem, ctx->stream>>>(p, ctx->c_blk);
+        else if (one) assign_ring_kernel<false, 1><<<rgrid, kRingWarps * 32, RingShape<1>::kSmem, ctx->stream>>>(p, ctx->c_blk);
+        else if (accum) assign_ring_kernel<true, 2><<<rgrid, kRingWarps * 32, RingShape<2>::kSmem, ctx->stream>>>(p, ctx->c_blk);
+        else assign_ring_kernel<false, 2><<<rgrid, kRingWarps * 32, RingShape<2>::kSmem, ctx->stream>>>(p, ctx->c_blk);
     } else if (cfg.wide) {
         const int wgrid = (int)std::min<int64_t>(cfg.grid * 2, (tiles + kWideWarps - 1) / kWideWarps); // two CTAs per SM
         const bool xres = ctx->md <= 2 * kWideDk; // rows of up to 64 columns stay resident per CTA tile
@@ -1141,9 +1150,13 @@ int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(assign_wide_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(assign_ring_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            e = cudaFuncSetAttribute(assign_ring_kernel<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(assign_ring_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            e = cudaFuncSetAttribute(assign_ring_kernel<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_ring_kernel<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(assign_ring_kernel<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(assign_fast_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e == cudaSuccess)
@@ -2133,6 +2146,21 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
                  "tmem_a_buffers=%d half_stages=%d n_partials=%d wide=0 (rows below 4096 or unaligned rows take the FP64 kernel)",
                  fa.numRegs, fa.localSizeBytes, ctx->sm_count, kFastThreads, f.smem, f.Kd, f.KB, f.Nacc, f.P, f.P > 1 ? f.NB : 0,
                  f.nA, f.NS, c.n_partials);
+        return FMLK_OK;
+    }
+    if (ring_shape(ctx, c, d)) {
+        const bool one = d <= 2 * kWideDk;
+        cudaFuncAttributes fr{};
+        if (one && accumulate) cudaFuncGetAttributes(&fr, assign_ring_kernel<true, 1>);
+        else if (one) cudaFuncGetAttributes(&fr, assign_ring_kernel<false, 1>);
+        else if (accumulate) cudaFuncGetAttributes(&fr, assign_ring_kernel<true, 2>);
+        else cudaFuncGetAttributes(&fr, assign_ring_kernel<false, 2>);
+        snprintf(out, (size_t)out_len,
+                 "ring=1 regs=%d local=%zu grid=%d block=%d smem=%zu rows_per_cta=%d warps=%d centroid_split=%d ring_stages=%d "
+                 "block_bytes=%d k_pad=%d n_partials=%d (rows not 16-byte aligned take assign_wide_kernel)",
+                 fr.numRegs, fr.localSizeBytes, c.grid, kRingWarps * 32, one ? RingShape<1>::kSmem : RingShape<2>::kSmem,
+                 one ? RingShape<1>::kRows : RingShape<2>::kRows, kRingWarps, one ? 1 : 2, kRingStages, kRingBlockElems * 8, c.k_pad,
+                 c.n_partials);
         return FMLK_OK;
     }
     cudaFuncAttributes fa{};

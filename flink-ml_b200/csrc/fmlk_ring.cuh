@@ -1,16 +1,17 @@
-// fmlk_ring.cuh -- assign_ring_kernel: the d-blocked FP64 kernel (assign_wide_kernel, XRES case) without its
-// CTA-wide barrier per column block.
+// fmlk_ring.cuh -- assign_ring_kernel: the d-blocked FP64 kernel (assign_wide_kernel) for rows of at most 128
+// columns, without its CTA-wide barrier per column block.
 //
-// Same arithmetic as assign_wide_kernel<ACCUM, true> (rows of at most 64 columns, centroids streamed in chunks of
-// 64 x 32 columns, DMMA.8x8x4 scores with the integer margin test and the exact replay of near ties; reference:
-// KMeans.java:269-300 / KMeansModel.java:129-144 as for every assign kernel).  What differs is the hand-off:
-//   - one CTA of 16 warps per SM holds 256 rows resident (139 KB);
+// Same arithmetic as assign_wide_kernel (centroids streamed in chunks of 64 x 32 columns, DMMA.8x8x4 scores with
+// the integer margin test and the exact replay of near ties; reference: KMeans.java:269-300 /
+// KMeansModel.java:129-144 as for every assign kernel).  What differs is the hand-off:
+//   - one CTA of 16 warps per SM keeps its row tile resident (256 rows of <= 64 columns, or 128 rows of <= 128);
 //   - the centroid blocks arrive from a copy of the model laid out block by block in the shared-memory layout
 //     (prep_ring_kernel, once per round), so a block is ONE bulk copy (UBLKCP) completing on an mbarrier;
 //   - four ring stages; a warp that has finished a block counts itself on the stage (shared-memory atomic) and the
 //     sixteenth to do so refills the stage with the block four steps ahead -- no producer warp (the register file
 //     has none to spare at 16 x 32 x 128) and no __syncthreads: warps drift up to three blocks apart, so the
-//     tensor pipe no longer idles while the slowest warp of a block arrives (76 % -> see DESIGN.md).
+//     tensor pipe no longer idles while the slowest warp of a block arrives (config 4's shape: 76 % -> 84 % of
+//     the DMMA peak).
 // The ring keeps running across the CTA's row tiles: the first blocks of the next tile are in flight while the
 // labels of this one are written and its rows are reduced into the sums.
 #pragma once
@@ -19,10 +20,19 @@
 namespace fmlk {
 
 constexpr int kRingWarps = 16;
-constexpr int kRingRows = kRingWarps * kWarpRows;       // 256 rows per CTA tile
 constexpr int kRingStages = 4;
 constexpr int kRingBlockElems = 8 * kChunkTiles * kWideS; // 64 centroids x 36 doubles
-constexpr size_t kRingSmem = (size_t)kRingRows * kWideXresS * 8 + (size_t)kRingStages * kRingBlockElems * 8 + 2 * kRingStages * 8 + 16;
+// SPLIT = 1 (d <= 64): 256 rows per CTA tile, warp w owns rows 16 w .. 16 w + 15 and all 64 centroids of a chunk.
+// SPLIT = 2 (d <= 128): 128 rows per CTA tile (as many as fit beside the ring); warps w and w + 8 share rows
+//   16 w .. 16 w + 15 and take centroids 0..31 and 32..63 of every chunk, so the SM still runs 16 warps; the pair's
+//   two (best, second, index) meet in shared memory at the end of the tile and warp w finishes the rows.
+template <int SPLIT>
+struct RingShape {
+    static constexpr int kRows = kRingWarps * kWarpRows / SPLIT;
+    static constexpr int kStride = 2 * kWideDk * SPLIT + 4; // doubles per resident row (== 8 words mod 32: conflict-free fragments)
+    static constexpr size_t kSmem = (size_t)kRows * kStride * 8 + (size_t)kRingStages * kRingBlockElems * 8 + 2 * kRingStages * 8 + 16 +
+                                    (SPLIT == 2 ? (size_t)(kRingWarps / 2) * kWarpRows * 3 * 4 : 0);
+};
 
 // c_blk[(chunk * nkb + kb)][j][q] = c_mma[(64 chunk + j) * d + 32 kb + q] (zero outside the model, and in the four
 // padding columns): the blocks in the order the kernel consumes them, each in its shared-memory layout.
@@ -38,14 +48,19 @@ __global__ void prep_ring_kernel(const double *c_mma, int k, int d, int nchunks,
     }
 }
 
-template <bool ACCUM>
+template <bool ACCUM, int SPLIT>
 __global__ void __launch_bounds__(kRingWarps * 32, 1) assign_ring_kernel(const AssignParams p, const double *c_blk) {
+    constexpr int kRingRows = RingShape<SPLIT>::kRows, kXS = RingShape<SPLIT>::kStride;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    double *Xs = reinterpret_cast<double *>(smem_raw);                       // [256][kWideXresS]
-    double *ring = Xs + (size_t)kRingRows * kWideXresS;                      // [kRingStages][64][kWideS]
+    double *Xs = reinterpret_cast<double *>(smem_raw);                       // [kRingRows][kXS]
+    double *ring = Xs + (size_t)kRingRows * kXS;                             // [kRingStages][64][kWideS]
     unsigned long long *full = reinterpret_cast<unsigned long long *>(ring + (size_t)kRingStages * kRingBlockElems);
     int *done = reinterpret_cast<int *>(full + kRingStages);                 // [kRingStages] arrivals, ever increasing
+    int *mrg = done + kRingStages;                                           // SPLIT 2: [8 pairs][16 rows][best, second, idx]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int rw = SPLIT == 1 ? warp : (warp & 7);   // which 16 rows of the CTA tile
+    const int half = SPLIT == 1 ? 0 : (warp >> 3);   // which 32 centroids of every chunk
+    constexpr int kMyTiles = kChunkTiles / SPLIT;    // n8 tiles of a chunk this warp multiplies
     const int frow = lane >> 2, fk = lane & 3;
     const int cmax2_exp = (int)p.cmax2[1];
     const int dpad_exp = 32 - __clz(4 * p.ksteps);
@@ -78,22 +93,22 @@ __global__ void __launch_bounds__(kRingWarps * 32, 1) assign_ring_kernel(const A
         const int64_t ctile = blockIdx.x + (int64_t)ti * gridDim.x;
         const int64_t crow0 = ctile * kRingRows;
         const int crows = (int)min((int64_t)kRingRows, p.n - crow0);
-        const int64_t row0 = crow0 + warp * kWarpRows;
-        const int rows_valid = max(0, min(kWarpRows, crows - warp * kWarpRows));
+        const int64_t row0 = crow0 + rw * kWarpRows;
+        const int rows_valid = max(0, min(kWarpRows, crows - rw * kWarpRows));
         if (ACCUM) bulk_wait_group_read(); // the reductions have read the previous tile's rows
         __syncthreads();                   // (also: the barriers are initialised before anyone waits on them)
-        // the CTA's rows, two column halves, zero past the ends (16-byte cp.async: the launcher requires even d
-        // and 16-byte aligned rows)
+        // the CTA's rows, one 32-column block after the other, zero past the ends (16-byte cp.async: the launcher
+        // requires even d and 16-byte aligned rows)
         {
             constexpr int cpr = kWideDk / 2, step = kRingWarps * 32 / cpr;
-            for (int half = 0; half < 2; half++) {
+            for (int cb = 0; cb < 2 * SPLIT; cb++) {
                 const int q = 2 * (threadIdx.x % cpr);
-                const int cols = p.d - half * kWideDk;
+                const int cols = p.d - cb * kWideDk;
                 const int have_c = max(0, min(2, cols - q)) * 8;
-                const double *src0 = p.x + crow0 * p.d + half * kWideDk;
+                const double *src0 = p.x + crow0 * p.d + cb * kWideDk;
                 for (int r = threadIdx.x / cpr; r < kRingRows; r += step) {
                     const int have = r < crows ? have_c : 0;
-                    cp_async16_zfill(Xs + (size_t)r * kWideXresS + half * kWideDk + q, have ? src0 + (int64_t)r * p.d + q : p.x, have);
+                    cp_async16_zfill(Xs + (size_t)r * kXS + cb * kWideDk + q, have ? src0 + (int64_t)r * p.d + q : p.x, have);
                 }
             }
             cp_async_commit();
@@ -102,15 +117,16 @@ __global__ void __launch_bounds__(kRingWarps * 32, 1) assign_ring_kernel(const A
         __syncthreads();
         Top2 t0 = top2_init(), t1 = top2_init();
         int mx0 = 0, mx1 = 0;
-        double acc0[kChunkTiles][2], acc1[kChunkTiles][2];
+        double acc0[kChunkTiles][2], acc1[kChunkTiles][2]; // (SPLIT 2 uses the first four)
         for (int s = 0; s < steps; s++, g++) {
             const int ch = s / nkb, kbi = s - ch * nkb;
             const int ch0 = ch * 8 * kChunkTiles;
-            const int cnt = min(kChunkTiles, (p.k_pad - ch0) >> 3);
-            const int col0 = ch0 + fk * 2;
+            const int cnt_all = min(kChunkTiles, (p.k_pad - ch0) >> 3);
+            const int cnt = SPLIT == 1 ? cnt_all : (half == 0 ? min(cnt_all, kMyTiles) : max(cnt_all - kMyTiles, 0));
+            const int col0 = ch0 + half * kMyTiles * 8 + fk * 2;
             if (kbi == 0) {
 #pragma unroll
-                for (int j = 0; j < kChunkTiles; j++) {
+                for (int j = 0; j < kMyTiles; j++) {
                     const double h0 = j < cnt ? p.h[col0 + j * 8] : -INFINITY;
                     const double h1 = j < cnt ? p.h[col0 + j * 8 + 1] : -INFINITY;
                     acc0[j][0] = acc1[j][0] = h0;
@@ -120,18 +136,19 @@ __global__ void __launch_bounds__(kRingWarps * 32, 1) assign_ring_kernel(const A
             const int st = (int)(g % kRingStages);
             mbar_wait(full_bar(st), (unsigned)((g / kRingStages) & 1));
             {
-                const double *Xb = Xs + (size_t)warp * kWarpRows * kWideXresS + kbi * kWideDk;
-                const double *Cb = ring + (size_t)st * kRingBlockElems;
+                const double *Xb = Xs + (size_t)rw * kWarpRows * kXS + kbi * kWideDk;
+                const double *Cb = ring + (size_t)st * kRingBlockElems + (size_t)half * kMyTiles * 8 * kWideS;
                 const bool nsq = ch == 0; // the |x| bound rides along with the first chunk
                 switch (cnt) {
-                    case 8: wide_block<8>(Xb, kWideXresS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 7: wide_block<7>(Xb, kWideXresS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 6: wide_block<6>(Xb, kWideXresS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 5: wide_block<5>(Xb, kWideXresS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 4: wide_block<4>(Xb, kWideXresS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 3: wide_block<3>(Xb, kWideXresS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    case 2: wide_block<2>(Xb, kWideXresS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
-                    default: wide_block<1>(Xb, kWideXresS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 8: if (SPLIT == 1) wide_block<8>(Xb, kXS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 7: if (SPLIT == 1) wide_block<7>(Xb, kXS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 6: if (SPLIT == 1) wide_block<6>(Xb, kXS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 5: if (SPLIT == 1) wide_block<5>(Xb, kXS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 4: wide_block<4>(Xb, kXS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 3: wide_block<3>(Xb, kXS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 2: wide_block<2>(Xb, kXS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    case 1: wide_block<1>(Xb, kXS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;
+                    default: break; // (SPLIT 2: the chunk has no centroids for this half)
                 }
             }
             // this warp is done with the block; the last of the sixteen refills the stage
@@ -146,12 +163,23 @@ __global__ void __launch_bounds__(kRingWarps * 32, 1) assign_ring_kernel(const A
                 }
             }
             if (kbi == nkb - 1) {
-                int3 r0 = select_chunk_row(t0.best, t0.second, t0.idx, col0, acc0[0][0], acc0[0][1], acc0[1][0], acc0[1][1],
-                                           acc0[2][0], acc0[2][1], acc0[3][0], acc0[3][1], acc0[4][0], acc0[4][1], acc0[5][0],
-                                           acc0[5][1], acc0[6][0], acc0[6][1], acc0[7][0], acc0[7][1]);
-                int3 r1 = select_chunk_row(t1.best, t1.second, t1.idx, col0, acc1[0][0], acc1[0][1], acc1[1][0], acc1[1][1],
-                                           acc1[2][0], acc1[2][1], acc1[3][0], acc1[3][1], acc1[4][0], acc1[4][1], acc1[5][0],
-                                           acc1[5][1], acc1[6][0], acc1[6][1], acc1[7][0], acc1[7][1]);
+                constexpr double NI = -INFINITY;
+                int3 r0, r1;
+                if (SPLIT == 1) {
+                    r0 = select_chunk_row(t0.best, t0.second, t0.idx, col0, acc0[0][0], acc0[0][1], acc0[1][0], acc0[1][1], acc0[2][0],
+                                          acc0[2][1], acc0[3][0], acc0[3][1], acc0[4 % kMyTiles][0], acc0[4 % kMyTiles][1],
+                                          acc0[5 % kMyTiles][0], acc0[5 % kMyTiles][1], acc0[6 % kMyTiles][0], acc0[6 % kMyTiles][1],
+                                          acc0[7 % kMyTiles][0], acc0[7 % kMyTiles][1]);
+                    r1 = select_chunk_row(t1.best, t1.second, t1.idx, col0, acc1[0][0], acc1[0][1], acc1[1][0], acc1[1][1], acc1[2][0],
+                                          acc1[2][1], acc1[3][0], acc1[3][1], acc1[4 % kMyTiles][0], acc1[4 % kMyTiles][1],
+                                          acc1[5 % kMyTiles][0], acc1[5 % kMyTiles][1], acc1[6 % kMyTiles][0], acc1[6 % kMyTiles][1],
+                                          acc1[7 % kMyTiles][0], acc1[7 % kMyTiles][1]);
+                } else {
+                    r0 = select_chunk_row(t0.best, t0.second, t0.idx, col0, acc0[0][0], acc0[0][1], acc0[1][0], acc0[1][1], acc0[2][0],
+                                          acc0[2][1], acc0[3][0], acc0[3][1], NI, NI, NI, NI, NI, NI, NI, NI);
+                    r1 = select_chunk_row(t1.best, t1.second, t1.idx, col0, acc1[0][0], acc1[0][1], acc1[1][0], acc1[1][1], acc1[2][0],
+                                          acc1[2][1], acc1[3][0], acc1[3][1], NI, NI, NI, NI, NI, NI, NI, NI);
+                }
                 t0.best = r0.x, t0.second = r0.y, t0.idx = r0.z;
                 t1.best = r1.x, t1.second = r1.y, t1.idx = r1.z;
             }
@@ -164,6 +192,27 @@ __global__ void __launch_bounds__(kRingWarps * 32, 1) assign_ring_kernel(const A
         mx0 = max(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
         mx1 = max(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
         mx1 = max(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        if (SPLIT == 2) {
+            // the two warps of a pair meet: warp w + 8 leaves its (best, second, index) of the 16 rows, warp w merges
+            // them into its own (same rule as between the lanes of a quad) and finishes the rows
+            int *m = mrg + (size_t)rw * kWarpRows * 3;
+            if (half == 1 && fk == 0) {
+                m[frow * 3 + 0] = t0.best, m[frow * 3 + 1] = t0.second, m[frow * 3 + 2] = t0.idx;
+                m[(frow + 8) * 3 + 0] = t1.best, m[(frow + 8) * 3 + 1] = t1.second, m[(frow + 8) * 3 + 2] = t1.idx;
+            }
+            asm volatile("bar.sync %0, 64;\n" ::"r"(1 + rw) : "memory");
+            if (half == 1) continue;
+            auto merge = [](Top2 &t, int ob, int os, int oi) {
+                const int loser = ob > t.best ? t.best : ob;
+                if (ob > t.best || (ob == t.best && oi < t.idx)) {
+                    t.best = ob;
+                    t.idx = oi;
+                }
+                t.second = max(max(t.second, os), loser);
+            };
+            merge(t0, m[frow * 3 + 0], m[frow * 3 + 1], m[frow * 3 + 2]);
+            merge(t1, m[(frow + 8) * 3 + 0], m[(frow + 8) * 3 + 1], m[(frow + 8) * 3 + 2]);
+        }
         // the margin test of assign_kernel (see there)
         auto row_ok = [&](const Top2 &t, int mx) -> bool {
             if (mx >= 0x7ff00000) return false;
@@ -202,7 +251,7 @@ __global__ void __launch_bounds__(kRingWarps * 32, 1) assign_ring_kernel(const A
             fence_proxy_async_smem();
             if (lane < rows_valid)
                 bulk_reduce_add_f64(slot + (size_t)lab * p.d,
-                                    (unsigned)__cvta_generic_to_shared(Xs + (size_t)(warp * kWarpRows + lane) * kWideXresS),
+                                    (unsigned)__cvta_generic_to_shared(Xs + (size_t)(rw * kWarpRows + lane) * kXS),
                                     (unsigned)p.d * 8u);
             bulk_commit_group();
             if (lane < rows_valid) atomicAdd(&slot[(size_t)p.k * p.d + lab], 1.0);

@@ -125,6 +125,9 @@ SHAPES = [
     (6000, 64, 1000),    # config 4 shape
     (3000, 128, 1000),   # config 3 shape
     (2000, 128, 257),    # config 5's d with a ragged last centroid tile
+    (9000, 96, 600),     # ring kernel, warp pairs split each chunk, three column blocks, ragged row tile
+    (7001, 32, 700),     # ring kernel, one column block, last chunk of 60
+    (5000, 128, 192),    # ring kernel, exactly three chunks
     # extremes of the tiling
     (1500, 1000, 7),     # long rows: few MMA warps fit, several columns per accumulator lane
     (600, 1531, 3),      # odd d close to the shared-memory limit of one row tile + centroids
