@@ -48,7 +48,7 @@ int main() {
     cudaMalloc(&acc, cap);
     cudaMemset(acc, 0, cap);
     cudaFuncSetAttribute(red_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    const int shapes[][2] = {{2, 64}, {10, 100}, {10, 64}, {100, 64}, {1000, 64}, {256, 128}};
+    const int shapes[][2] = {{2, 64}, {10, 100}, {10, 64}, {100, 64}, {1000, 64}, {256, 96}};
     for (auto &s : shapes) {
         const int k = s[0], d = s[1];
         for (int per_warp = 0; per_warp < 2; per_warp++)

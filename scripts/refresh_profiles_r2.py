@@ -14,7 +14,8 @@ from collections import defaultdict
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 G, P = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles")
-for f in ("r2_bench_n1.json", "r2_bench_reference_n1.json", "r2_bench_fast_n1.json", "r2_launches_bench.csv"):
+for f in ("r2_bench_n1.json", "r2_bench_reference_n1.json", "r2_bench_fast_n1.json", "r2_launches_bench.csv", "r2_configs_n1.jsonl",
+          "r2_l2_add_bench.txt"):
     if os.path.exists(os.path.join(G, f)):
         shutil.copy(os.path.join(G, f), os.path.join(P, f))
 
@@ -48,9 +49,11 @@ names = {"c2_train_f64": "assign_kernel<3>, config 2 (10M x 64, k=100), training
          "c2_predict_fast": "assign_fast_kernel<false>, config 2 shape, predict, fast mode",
          "c1b_train_f64": "assign_kernel<3>, kmeans-benchmark.json shape (1M x 100, k=10), training, FP64 mode",
          "c1b_predict_f64": "assign_kernel<0>, kmeans-benchmark.json shape, predict, FP64 mode",
-         "c4shape_train_f64": "assign_wide_kernel<true,true>, config 4's shape (10M x 64, k=1000), training, FP64 mode",
+         "c4shape_train_f64": "assign_ring_kernel<true,1>, config 4's shape (10M x 64, k=1000), training, FP64 mode",
          "c4shape_train_fast": "assign_fast_kernel<true>, config 4's shape, training, fast mode (streamed centroid terms)",
-         "c3shape_predict_f64": "assign_wide_kernel<false,false>, config 3's shape (4M x 128, k=1000), predict, FP64 mode"}
+         "c3shape_predict_f64": "assign_ring_kernel<false,2>, config 3's shape (4M x 128, k=1000), predict, FP64 mode",
+         "c5shape_train_f64": "assign_ring_kernel<true,2>, config 5's shape (4M x 128, k=256), training, FP64 mode",
+         "knn": "knn_predict_kernel<false>, KnnModel.transform: 65536 rows x 64 against 10000 training points, k=5"}
 traffic = {}
 for key, title in names.items():
     rep = os.path.join(G, "r2_%s.ncu-rep" % key)
