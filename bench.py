@@ -634,10 +634,17 @@ def main():
     args = ap.parse_args()
     if args.impl == "ours":
         args.warmup = max(args.warmup, 3)  # timing rule: at least 3 warm-up steps
+    # exactly one line on stdout: libraries that talk on fd 1 (NCCL prints its version there on some boxes) are
+    # sent to stderr for the duration of the run; the JSON line goes to the real stdout
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    sys.stdout = os.fdopen(real_stdout, "w", buffering=1)
     if args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)
+    sys.stdout.flush()
 
 
 if __name__ == "__main__":
