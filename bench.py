@@ -156,7 +156,33 @@ def run_reference(args):
     }))
 
 
+def bind_near_gpu(gpu_index):
+    """Pins this process to the CPUs NVML lists as local to the GPU (its NUMA node / PCIe root), so the pinned host
+    buffers allocated afterwards sit on that node.  Returns what was done, for the e2e record."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(gpu_index)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = {64 * w + b for w, m in enumerate(mask) for b in range(64) if (m >> b) & 1}
+        allowed = os.sched_getaffinity(0)
+        cpus &= allowed
+        if not cpus:
+            return "NVML affinity set is empty; left at %d CPUs" % len(allowed)
+        if cpus != allowed:
+            os.sched_setaffinity(0, cpus)
+        return "%d CPUs local to GPU %d (%d..%d) of %d" % (len(cpus), gpu_index, min(cpus), max(cpus), len(allowed))
+    except Exception as e:  # no NVML, no permission: the run goes on unbound
+        return "not bound: %s" % e
+
+
 def run_ours(args):
+    rank = int(os.environ.get("RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    local = int(os.environ.get("LOCAL_RANK", 0))
+    affinity = bind_near_gpu(local)  # before anything allocates pinned memory
+
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -164,9 +190,6 @@ def run_ours(args):
     from flink_ml_b200 import kmeans as K
     from flink_ml_b200 import native
 
-    rank = int(os.environ.get("RANK", 0))
-    world = int(os.environ.get("WORLD_SIZE", 1))
-    local = int(os.environ.get("LOCAL_RANK", 0))
     if world != args.gpus:
         if world == 1 and args.gpus > 1:
             raise SystemExit("--gpus %d needs torchrun with --nproc-per-node %d" % (args.gpus, args.gpus))
@@ -390,7 +413,8 @@ def run_ours(args):
             dist.all_reduce(tot, op=dist.ReduceOp.SUM)
         e2e["host_link"] = {"h2d_gbs_per_rank_min": float(lo.item()), "h2d_gbs_all_ranks": float(tot.item()),
                             "how": "3 x %d MiB pinned host-to-device copies per rank, all ranks at once" % (probe_bytes >> 20),
-                            "copy_only_ms_per_step": n * d * 8 / 1e9 / float(lo.item()) * 1e3}
+                            "copy_only_ms_per_step": n * d * 8 / 1e9 / float(lo.item()) * 1e3,
+                            "cpu_affinity_rank0": affinity}
         del sink
         if fast_rec is not None:
             fast_rec["e2e"] = e2e_fits(native.FLAG_FAST_TF32, table, e2e_steps)
