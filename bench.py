@@ -581,7 +581,7 @@ def run_ours(args):
         torch.cuda.empty_cache()
 
     # ---- the north-star shape (config 4: 1e9 x 64, k = 1000 over 8 GPUs): this GPU's share, a short run
-    north = None
+    north = strong = None
     if not args.no_north_star and args.workload == "c2":
         nn, nd, nk, nrounds = args.north_rows, 64, 1000, 3
         free_b, _ = torch.cuda.mem_get_info(local)
@@ -607,6 +607,25 @@ def run_ours(args):
                      "scaling": "weak", "modes": recs}
             del xs
             torch.cuda.empty_cache()
+            # the same shape with the TOTAL fixed (strong scaling): north_rows rows over all ranks.  At one GPU that is
+            # the record above; at N GPUs each rank holds its RowGenerator slice of them
+            if world == 1:
+                strong = {"workload": "%d x %d FP64 rows in all, k=%d (at one GPU: the north_star record)" % (nn, nd, nk),
+                          "scaling": "strong", "rows_total": nn,
+                          "modes": {m: {"value": v["value"], "unit": UNIT, "ms_per_round": v["ms_per_round"]} for m, v in recs.items()}}
+            else:
+                per = nn // world
+                xs = generate(per, nd)
+                srecs = {}
+                for name, fl in (("f64", 0), ("tf32x3+f64-recheck", native.FLAG_FAST_TF32)):
+                    if name != "f64" and args.no_fast:
+                        continue
+                    nr = timed_fits(fl, xs, nk, nrounds, 1, 1)
+                    srecs[name] = {"value": nr["value"], "unit": UNIT, "ms_per_round": nr["ms_per_round"]}
+                strong = {"workload": "%d x %d FP64 rows in all (%d per GPU), k=%d, %d rounds, device-resident" % (
+                              per * world, nd, per, nk, nrounds), "scaling": "strong", "rows_total": per * world, "modes": srecs}
+                del xs
+                torch.cuda.empty_cache()
 
     base = None
     if rank == 0 and world == 1 and not args.no_cpu:
@@ -626,7 +645,7 @@ def run_ours(args):
             "clocks": clocks, "e2e": e2e, "gpu_launches": prof["total_launches"],
             "roofline": roofline, "cpu_baseline": base, "parity": parity,
             "wall_ms_per_step": wall / args.steps * 1e3, "rechecked_rows": prof["rechecked_rows"],
-            "fast_mode": fast_rec, "transform": transform_rec, "online": online_rec, "knn": knn_rec, "north_star": north,
+            "fast_mode": fast_rec, "transform": transform_rec, "online": online_rec, "knn": knn_rec, "north_star": north, "strong_scaling": strong,
         }
         print(json.dumps(out))
     if world > 1:
