@@ -752,11 +752,13 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out);
 
 // The d-blocked kernel with rows of at most 128 columns runs as assign_ring_kernel (no CTA-wide barrier per block)
 // when its 16-byte copies can be used: even d; the rows' alignment is checked per launch.
-bool ring_shape(fmlk_ctx *ctx, const LaunchCfg &cfg, int d) {
-    // rows of 66..128 columns (warp pairs split every chunk of 64 centroids): only with enough whole chunks -- at
-    // k = 100 the second chunk leaves one warp of each pair nearly idle (d = 128 predict: 23.0 against 25.4 TFLOP/s
-    // for assign_wide_kernel; k = 256: 28.5 against 27.7, k = 1000: 28.6 against 27.6)
-    if (d > 2 * kWideDk && cfg.k_pad < 192) return false;
+bool ring_shape(fmlk_ctx *ctx, const LaunchCfg &cfg, int d, bool accum) {
+    // rows of 66..128 columns (128-row tiles, warp pairs split every chunk of 64 centroids).  Training: always --
+    // the sums go out as bulk reductions from the resident rows instead of per-lane atomics on re-read rows
+    // (d = 128: k = 64 21.1 against 19.7 TFLOP/s, k = 100 21.8 against 20.5, k = 256 26.7 against 24.8).  Predict:
+    // from three chunks on (k = 256 28.7 against 27.5, k = 1000 28.6 against 27.7); below that assign_wide_kernel's
+    // two CTAs per SM cover each other's tile boundaries better (k = 100 25.2 against 24.2, k = 64 27.0 against 23.7)
+    if (d > 2 * kWideDk && !accum && cfg.k_pad < env_int("FMLK_TUNE_RING_MINK", 192)) return false;
     return cfg.wide && d <= 4 * kWideDk && (d & 1) == 0 && ctx->max_partial_slots == 0 &&
            std::max(RingShape<1>::kSmem, RingShape<2>::kSmem) <= ctx->smem_optin && env_int("FMLK_TUNE_RING", 1);
 }
@@ -775,7 +777,7 @@ int prep_centroids(fmlk_ctx *ctx, bool accum, bool base_done = false) {
         LaunchCfg cfg;
         int rc = choose_cfg(ctx, ctx->k, ctx->md, accum, &cfg);
         if (rc) return rc;
-        if (ring_shape(ctx, cfg, ctx->md)) {
+        if (ring_shape(ctx, cfg, ctx->md, accum)) {
             const int nkb = (ctx->md + kWideDk - 1) / kWideDk, nchunks = (cfg.k_pad + 8 * kChunkTiles - 1) / (8 * kChunkTiles);
             const size_t need = (size_t)nchunks * nkb * kRingBlockElems;
             if (need > ctx->c_blk_cap) {
@@ -873,7 +875,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
         cudaMemsetAsync(p.trace, 0, trace_len * 8, ctx->stream);
     }
 #endif
-    if (ring_shape(ctx, cfg, ctx->md) && ctx->c_blk && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    if (ring_shape(ctx, cfg, ctx->md, accum) && ctx->c_blk && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
         // one CTA of 16 warps per SM; rows of up to 64 columns: 256 per CTA tile, up to 128: 128 (warp pairs share rows)
         const bool one = ctx->md <= 2 * kWideDk;
         const int tile_rows = one ? RingShape<1>::kRows : RingShape<2>::kRows;
@@ -2148,7 +2150,7 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
                  f.nA, f.NS, c.n_partials);
         return FMLK_OK;
     }
-    if (ring_shape(ctx, c, d)) {
+    if (ring_shape(ctx, c, d, accumulate != 0)) {
         const bool one = d <= 2 * kWideDk;
         cudaFuncAttributes fr{};
         if (one && accumulate) cudaFuncGetAttributes(&fr, assign_ring_kernel<true, 1>);

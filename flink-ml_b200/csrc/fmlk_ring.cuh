@@ -87,34 +87,39 @@ __global__ void __launch_bounds__(kRingWarps * 32, 1) assign_ring_kernel(const A
         for (int st = 0; st < kRingStages; st++)
             if (st < total_steps) refill(st, st);
     }
+    __syncthreads(); // the barriers are initialised before anyone waits on them
     unsigned long long local_rechecks = 0;
-    long long g = 0; // this CTA's block counter: stage g % kRingStages, use g / kRingStages
+    long long g = 0; // this warp's block counter: stage g % kRingStages, use g / kRingStages
     for (int ti = 0; ti < my_tiles; ti++) {
         const int64_t ctile = blockIdx.x + (int64_t)ti * gridDim.x;
         const int64_t crow0 = ctile * kRingRows;
         const int crows = (int)min((int64_t)kRingRows, p.n - crow0);
         const int64_t row0 = crow0 + rw * kWarpRows;
         const int rows_valid = max(0, min(kWarpRows, crows - rw * kWarpRows));
-        if (ACCUM) bulk_wait_group_read(); // the reductions have read the previous tile's rows
-        __syncthreads();                   // (also: the barriers are initialised before anyone waits on them)
-        // the CTA's rows, one 32-column block after the other, zero past the ends (16-byte cp.async: the launcher
-        // requires even d and 16-byte aligned rows)
+        // The rows of a warp (SPLIT 2: of a pair of warps) are nobody else's, so the tile boundary needs no CTA-wide
+        // barrier: a warp reloads its sixteen rows while the others multiply (the ring bounds how far they drift).
+        if (ACCUM) bulk_wait_group_read(); // this thread's reductions have read the previous tile's rows
+        if (SPLIT == 2) asm volatile("bar.sync %0, 64;\n" ::"r"(1 + rw) : "memory");
+        else __syncwarp();
         {
-            constexpr int cpr = kWideDk / 2, step = kRingWarps * 32 / cpr;
+            // 16 rows x d by 16-byte cp.async, zero past the ends (the launcher requires even d and 16-byte aligned rows)
+            constexpr int cpr = kWideDk / 2, loaders = 32 * SPLIT, row_step = loaders / cpr;
+            const int t = SPLIT == 1 ? lane : half * 32 + lane;
+            const int q = 2 * (t % cpr);
             for (int cb = 0; cb < 2 * SPLIT; cb++) {
-                const int q = 2 * (threadIdx.x % cpr);
                 const int cols = p.d - cb * kWideDk;
                 const int have_c = max(0, min(2, cols - q)) * 8;
-                const double *src0 = p.x + crow0 * p.d + cb * kWideDk;
-                for (int r = threadIdx.x / cpr; r < kRingRows; r += step) {
-                    const int have = r < crows ? have_c : 0;
-                    cp_async16_zfill(Xs + (size_t)r * kXS + cb * kWideDk + q, have ? src0 + (int64_t)r * p.d + q : p.x, have);
+                for (int r = t / cpr; r < kWarpRows; r += row_step) {
+                    const int have = r < rows_valid ? have_c : 0;
+                    cp_async16_zfill(Xs + (size_t)(rw * kWarpRows + r) * kXS + cb * kWideDk + q,
+                                     have ? p.x + (row0 + r) * p.d + cb * kWideDk + q : p.x, have);
                 }
             }
             cp_async_commit();
             cp_async_wait<0>();
         }
-        __syncthreads();
+        if (SPLIT == 2) asm volatile("bar.sync %0, 64;\n" ::"r"(1 + rw) : "memory");
+        else __syncwarp();
         Top2 t0 = top2_init(), t1 = top2_init();
         int mx0 = 0, mx1 = 0;
         double acc0[kChunkTiles][2], acc1[kChunkTiles][2]; // (SPLIT 2 uses the first four)
