@@ -97,6 +97,7 @@ struct LaunchCfg {
     int warps, acc_warps, xs, S, ksteps, k_pad, nc_tile, n_ctiles, sums_in_smem, n_partials, grid, private_sums;
     int spin_ns, stagger_ns;
     int warp_slots; // MODE 3: one accumulator per warp
+    int ordered;    // MODE 3 + warp_slots: additions in a fixed order (FMLK_FLAG_DETERMINISTIC)
     int red_sums; // MMA warps add to a global accumulator per CTA (no accumulator warps)
     int wide; // rows too long for the shared-memory tiling: assign_wide_kernel
     size_t smem;
@@ -307,6 +308,13 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     const int(*cand)[2] = accum ? (small ? small_acc : large_acc) : (small ? small_pred : large_pred);
     const int ncand = 6; // down to two MMA warps: long rows leave room for little else
     const bool det = (ctx->flags & FMLK_FLAG_DETERMINISTIC) != 0;
+    // FMLK_FLAG_DETERMINISTIC: the same kernel with one accumulator per warp and ordered additions (see the kernel)
+    // when the rows can go out as bulk reductions (even d, aligned), every CTA has a slot of its own and the per-warp
+    // accumulators stay under 256 MB; otherwise the accumulator warps / warp-private sums below
+    const size_t model_bytes = ((size_t)k * d + k + 1) * sizeof(double);
+    const bool ordered_ok = det && accum && (d & 1) == 0 && ctx->rows_aligned16 && ctx->max_partial_slots == 0 &&
+                            model_bytes * c.grid <= ((size_t)64 << 20) && model_bytes * c.grid * 16 <= ((size_t)256 << 20) &&
+                            env_int("FMLK_TUNE_ORDERED", 1);
     auto try_red = [&]() -> bool {
         if (!accum || !env_int("FMLK_TUNE_RED_SUMS", 1)) return false;
 
@@ -331,6 +339,11 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
                 c.red_sums = 1;
                 c.warp_slots = env_int("FMLK_TUNE_WSLOT", c.k_pad <= 16 ? 1 : 0); // measured: k = 2, d = 64 1.9 -> 3.2 TB/s, k = 10, d = 100 2.7 -> 4.0; k >= 24: none
                 if (ctx->max_partial_slots > 0) c.warp_slots = 0; // borrowed scratch (the allocation-free entry point)
+                c.ordered = 0;
+                if (ordered_ok) {
+                    c.warp_slots = 1;
+                    c.ordered = 1;
+                }
                 c.n_partials = (int)std::max<size_t>(1, std::min<size_t>((size_t)c.grid, ((size_t)64 << 20) / (((size_t)k * d + k) * sizeof(double))));
                 if (ctx->max_partial_slots > 0) c.n_partials = std::min(c.n_partials, ctx->max_partial_slots);
                 c.smem = need;
@@ -343,6 +356,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     // few centroids: with rows the TMA engine can reduce from (even d, 16-byte aligned) the sums go out as
     // bulk reductions too -- measured at k = 10, d = 100 against warp-private sums in shared memory, whose
     // 64 FP64 adds per tile each wait ~100 cycles next to the other warps' DMMAs; otherwise private sums
+    if (ordered_ok && try_red()) return FMLK_OK;
     if (accum && small && !det && (d & 1) == 0 && ctx->rows_aligned16 && env_int("FMLK_TUNE_SMALL_RED", 1) && try_red())
         return FMLK_OK;
     if (accum && small) {
@@ -850,6 +864,7 @@ int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t 
     p.stagger_ns = cfg.stagger_ns;
     p.acc_dmma = env_int("FMLK_TUNE_ACC_DMMA", 1);
     p.warp_scratch = (accum && cfg.warp_slots && cfg.red_sums && !cfg.wide) ? ctx->warp_scratch : nullptr;
+    p.ordered = (p.warp_scratch && cfg.ordered) ? 1 : 0;
     // few centroids (HBM-bound): one bulk copy per row tile; otherwise one per row
     p.row_copies = env_int("FMLK_TUNE_ROW_COPIES", cfg.k_pad <= 32 ? 0 : 1);
     p.no_bulk_red = env_int("FMLK_TUNE_NO_BULK_RED", 0);
@@ -2174,11 +2189,11 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
     else cudaFuncGetAttributes(&fa, assign_kernel<0>);
     snprintf(out, (size_t)out_len,
              "regs=%d max_threads=%d local=%zu grid=%d block=%d smem=%zu mma_warps=%d acc_warps=%d xs=%d S=%d ksteps=%d k_pad=%d nc_tile=%d n_ctiles=%d "
-             "sums_in_smem=%d n_partials=%d private_sums=%d red_sums=%d wide=%d",
+             "sums_in_smem=%d n_partials=%d private_sums=%d red_sums=%d warp_slots=%d ordered=%d wide=%d",
              fa.numRegs, fa.maxThreadsPerBlock, fa.localSizeBytes, c.grid, (c.warps + c.acc_warps) * 32, c.smem, c.warps,
              c.acc_warps, c.xs, c.S, c.ksteps, c.k_pad,
              c.nc_tile, c.n_ctiles,
-             c.sums_in_smem, c.n_partials, c.private_sums, c.red_sums, c.wide);
+             c.sums_in_smem, c.n_partials, c.private_sums, c.red_sums, c.warp_slots, c.ordered, c.wide);
     return FMLK_OK;
 }
 

@@ -66,6 +66,7 @@ struct AssignParams {
 #ifdef FMLK_TRACE
     unsigned long long *trace; // [warps of CTA 0][kTraceEvents] (clock << 4 | event), debugging builds only
 #endif
+    int32_t ordered; // MODE 3 with warp_scratch: additions in a fixed order (FMLK_FLAG_DETERMINISTIC)
     double *warp_scratch; // MODE 3, few centroids: [gridDim.x * mma_warps][k*d + k] all zero between launches; each warp adds
                           // into its own accumulator (the L2 additions of a CTA's warps then never queue on the same cells)
                           // and the CTA folds them into its slot of `partials` at the end
@@ -897,7 +898,27 @@ __global__ void __launch_bounds__(512, 1) assign_kernel(const AssignParams p) {
                     // row out of this warp's tile and adds it to sums[label] in L2.  (Tried: folding the rows of a
                     // tile that share a label into one before sending -- half the L2 additions at k = 10; faster only
                     // at d = 100 and k <= 4, 4-19 % slower elsewhere: the FP64 adds cost the warp more than L2 saves.)
-                    const bool send = lane < rows_valid;
+                    bool send = lane < rows_valid;
+                    if (p.ordered) {
+                        // FMLK_FLAG_DETERMINISTIC: this warp adds into an accumulator of its own, so the order of the
+                        // additions into a cell is the order of this warp's reductions -- fixed once (a) rows of the
+                        // tile that share a label are added up here first, in row order (two reductions in flight to
+                        // one address have no order), and (b) a tile's reductions are complete before the next
+                        // tile's are issued (they have had the whole multiply phase of this tile for it)
+                        const unsigned same = __match_any_sync(0xffffffffu, send ? my_lab : -1 - lane);
+                        const int firstrow = __ffs(same) - 1;
+                        const bool is_dup = send && firstrow != lane;
+                        unsigned dupmask = __ballot_sync(0xffffffffu, is_dup);
+                        while (dupmask) { // warp-uniform
+                            const int r = __ffs(dupmask) - 1;
+                            dupmask &= dupmask - 1;
+                            const int f = __shfl_sync(0xffffffffu, firstrow, r);
+                            for (int c = lane; c < p.d; c += 32) Xt[(size_t)f * S + c] += Xt[(size_t)r * S + c];
+                        }
+                        __syncwarp();
+                        send = send && !is_dup;
+                        bulk_wait_group_all();
+                    }
                     fence_proxy_async_smem();
                     if (send)
                         bulk_reduce_add_f64(slot + (size_t)my_lab * p.d,

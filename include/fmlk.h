@@ -42,9 +42,11 @@ typedef enum fmlk_status {
 /* fmlk_create flags */
 #define FMLK_FLAG_PROFILE 0x1  /* time every assign-kernel launch with CUDA events (fmlk_get_profile) */
 #define FMLK_FLAG_BLAS_FMA 0x2 /* exact paths follow netlib's JDK>=11 (Math.fma) variant instead of JDK 8 */
-#define FMLK_FLAG_DETERMINISTIC 0x4 /* per-cluster sums added in a fixed order (bit-identical from run to run)
-                                       wherever they fit in shared memory, at a few percent of throughput;
-                                       default: additions performed in L2 (bulk reductions), last bits depend on arrival order.  Labels,
+#define FMLK_FLAG_DETERMINISTIC 0x4 /* per-cluster sums added in a fixed order (bit-identical from run to run) when the
+                                       centroids stay resident in shared memory: one accumulator per warp with ordered
+                                       bulk reductions (even d, models up to 256 MB / (16 x SMs)), else accumulator
+                                       warps or warp-private sums in shared memory; a few percent of throughput.
+                                       Default: additions performed in L2 in arrival order (last bits vary).  Labels,
                                        counts and weights are bit-exact either way. */
 
 #define FMLK_FLAG_FAST_TF32 0x8 /* north_star's fast mode: the contraction x.c - |c|^2/2 runs on the tcgen05 tensor cores

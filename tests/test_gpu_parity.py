@@ -435,9 +435,10 @@ def test_rows_far_beyond_the_shared_memory_tiling(ctx):
 
 
 def test_deterministic_flag_gives_bit_identical_sums():
-    """FMLK_FLAG_DETERMINISTIC: per-cluster sums are added in a fixed order (accumulator warps, sums in
-    shared memory): two rounds over the same rows give the same bits; the default (L2 atomics) agrees
-    with both to summation order, and labels / counts are bit-exact in either mode."""
+    """FMLK_FLAG_DETERMINISTIC: per-cluster sums are added in a fixed order (one accumulator per warp with ordered
+    bulk reductions, or accumulator warps with the sums in shared memory): rounds over the same rows give the same
+    bits, also through a whole fit; the default (unordered L2 additions) agrees with them to summation order, and
+    labels / counts are bit-exact in either mode."""
     n, d, k = 300_000, 64, 100
     x = O.generate_dense(2, 0, 1, n, d)
     cent = x[:k].copy()
@@ -448,11 +449,19 @@ def test_deterministic_flag_gives_bit_identical_sums():
             c.set_centroids(cent)
             a = c.local_partials()
             b = c.local_partials()
-            results[name] = (a, b, c.describe_launch(k, d, True))
-    (a, b, desc) = results["det"]
-    assert "sums_in_smem=1" in desc and "red_sums=0" in desc
+            more = [c.local_partials() for _ in range(3)]
+            fits = []
+            for _ in range(2):
+                c.set_centroids(cent)
+                fits.append(c.fit(4))
+            results[name] = (a, b, c.describe_launch(k, d, True), more, fits)
+    (a, b, desc, more, fits) = results["det"]
+    assert "ordered=1" in desc or ("sums_in_smem=1" in desc and "red_sums=0" in desc)
     assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1])
-    (fa, fb, fdesc) = results["fast"]
+    for m in more:
+        assert np.array_equal(m[0], a[0]) and np.array_equal(m[1], a[1])
+    assert np.array_equal(fits[0][0], fits[1][0], equal_nan=True) and np.array_equal(fits[0][1], fits[1][1])
+    (fa, fb, fdesc) = results["fast"][:3]
     assert "red_sums=1" in fdesc
     assert np.array_equal(fa[1], a[1]) and np.array_equal(fb[1], a[1])
     assert np.allclose(fa[0], a[0], rtol=SUM_RTOL, atol=0) and np.allclose(fb[0], a[0], rtol=SUM_RTOL, atol=0)
