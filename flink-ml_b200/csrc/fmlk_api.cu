@@ -241,6 +241,21 @@ int use_device(fmlk_ctx *ctx) {
     return FMLK_OK;
 }
 
+// An entry point leaves the calling thread's current device as it found it (a JVM operator thread, or a
+// framework with its own idea of the current device, must not see it change under its feet).
+struct DeviceScope {
+    int prev = -1;
+    DeviceScope() {
+        if (cudaGetDevice(&prev) != cudaSuccess) {
+            prev = -1;
+            cudaGetLastError();
+        }
+    }
+    ~DeviceScope() {
+        if (prev >= 0) cudaSetDevice(prev);
+    }
+};
+
 int stride_for(int d) {
     int d4 = (d + 3) & ~3;
     return (d4 % 8 == 4) ? d4 : d4 + 4;
@@ -1143,6 +1158,7 @@ int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *
     ctx->rank = rank;
     ctx->world = world;
     ctx->flags = flags;
+    DeviceScope device_scope;
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
     int smem = 0, sms = 0, major = 0;
@@ -1218,6 +1234,7 @@ int32_t fmlk_create(int32_t device, int32_t rank, int32_t world, const uint8_t *
 
 void fmlk_destroy(fmlk_ctx *ctx) {
     if (!ctx) return;
+    DeviceScope device_scope;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
     if (ctx->comm) nccl().CommDestroy(ctx->comm);
@@ -1271,6 +1288,7 @@ const char *fmlk_last_error(const fmlk_ctx *ctx) { return ctx ? ctx->err.c_str()
 
 int32_t fmlk_set_stream(fmlk_ctx *ctx, void *cuda_stream) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     CK(ctx, cudaStreamSynchronize(ctx->stream));
@@ -1282,6 +1300,7 @@ int32_t fmlk_set_stream(fmlk_ctx *ctx, void *cuda_stream) {
 
 int32_t fmlk_reserve_points(fmlk_ctx *ctx, int64_t n_rows, int32_t d) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = check_dim(ctx, d))) return rc;
@@ -1306,6 +1325,7 @@ int32_t fmlk_reserve_points(fmlk_ctx *ctx, int64_t n_rows, int32_t d) {
 
 static int32_t append_impl(fmlk_ctx *ctx, const double *rows, int64_t n, int32_t d, cudaMemcpyKind kind) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if (n < 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "n must be >= 0");
@@ -1370,6 +1390,7 @@ static int decode_status(fmlk_ctx *ctx, int bad) {
 int32_t fmlk_append_points_serialized(fmlk_ctx *ctx, const uint8_t *records_host, int64_t nbytes, int32_t format,
                                       int32_t d, int64_t *out_rows) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     int hdr = 0;
@@ -1468,6 +1489,7 @@ int32_t fmlk_decode_rows_dev(int32_t device, void *cuda_stream, const uint8_t *r
     if ((reinterpret_cast<uintptr_t>(records_dev) & 7) != 0)
         return fail(nullptr, FMLK_ERR_INVALID_ARG, "records_dev must be 8-byte aligned");
     if (n == 0) return FMLK_OK;
+    DeviceScope device_scope;
     cudaError_t e = cudaSetDevice(device);
     if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, cudaGetErrorString(e));
     int sms = 0;
@@ -1492,6 +1514,7 @@ int32_t fmlk_adopt_points_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, 
 
 int32_t fmlk_clear_points(fmlk_ctx *ctx) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     CK(ctx, cudaStreamSynchronize(ctx->stream));
@@ -1516,6 +1539,7 @@ int64_t fmlk_num_points(const fmlk_ctx *ctx) { return ctx ? ctx->n_total : 0; }
 
 int32_t fmlk_set_centroids(fmlk_ctx *ctx, const double *centroids_host, int32_t k, int32_t d) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if (k < 1) return fail(ctx, FMLK_ERR_INVALID_ARG, "k must be >= 1");
@@ -1539,6 +1563,7 @@ static int need_model(fmlk_ctx *ctx) {
 
 int32_t fmlk_train_round(fmlk_ctx *ctx, double *out_centroids, double *out_weights) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
@@ -1548,6 +1573,7 @@ int32_t fmlk_train_round(fmlk_ctx *ctx, double *out_centroids, double *out_weigh
 
 int32_t fmlk_fit(fmlk_ctx *ctx, int32_t max_iter, double *out_centroids, double *out_weights) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
@@ -1560,6 +1586,7 @@ int32_t fmlk_fit(fmlk_ctx *ctx, int32_t max_iter, double *out_centroids, double 
 
 int32_t fmlk_local_partials(fmlk_ctx *ctx, double *out_sums, int64_t *out_counts) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
@@ -1578,6 +1605,7 @@ int32_t fmlk_local_partials(fmlk_ctx *ctx, double *out_sums, int64_t *out_counts
 
 int32_t fmlk_get_model(fmlk_ctx *ctx, double *out_centroids, double *out_weights) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
@@ -1594,6 +1622,7 @@ static int32_t predict_impl(fmlk_ctx *ctx, const double *rows_dev, int64_t n, in
 
 int32_t fmlk_predict_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d, int32_t *out_labels_dev) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
@@ -1604,6 +1633,7 @@ int32_t fmlk_predict_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32
 
 int32_t fmlk_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t d, int32_t *out_labels_host) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
@@ -1674,6 +1704,7 @@ int32_t fmlk_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t 
 
 int32_t fmlk_predict_cached(fmlk_ctx *ctx, int32_t *out_labels_host) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = need_model(ctx))) return rc;
@@ -1699,6 +1730,7 @@ int32_t fmlk_predict_cached(fmlk_ctx *ctx, int32_t *out_labels_host) {
 int32_t fmlk_online_round(fmlk_ctx *ctx, const double *local_batch_host, int64_t n_local, int32_t d, int32_t k,
                           double decay, double *centroids_inout, double *weights_inout) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if (k < 1 || d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad k / d");
@@ -1827,6 +1859,7 @@ int knn_status_check(fmlk_ctx *ctx) { // after the stream has been synchronised
 int32_t fmlk_knn_set_model(fmlk_ctx *ctx, const double *features_host, const double *labels_host,
                            const double *norm_squares_host_or_null, int32_t m, int32_t d) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if (m < 0 || d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad m / d");
@@ -1874,6 +1907,7 @@ int32_t fmlk_knn_set_model(fmlk_ctx *ctx, const double *features_host, const dou
 
 int32_t fmlk_knn_get_norm_squares(fmlk_ctx *ctx, double *out_norm_squares) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if (!ctx->knn_nsq) return fail(ctx, FMLK_ERR_STATE, "no Knn model data: call fmlk_knn_set_model first");
@@ -1888,6 +1922,7 @@ int32_t fmlk_knn_get_norm_squares(fmlk_ctx *ctx, double *out_norm_squares) {
 int32_t fmlk_knn_predict_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d, int32_t k,
                              double *out_predictions_dev) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = knn_check(ctx, n, d, k, rows_dev, out_predictions_dev))) return rc;
@@ -1900,6 +1935,7 @@ int32_t fmlk_knn_predict_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, i
 int32_t fmlk_knn_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t d, int32_t k,
                          double *out_predictions_host) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if ((rc = knn_check(ctx, n, d, k, rows_host, out_predictions_host))) return rc;
@@ -1927,6 +1963,7 @@ int32_t fmlk_knn_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int3
 
 int32_t fmlk_all_reduce_sum_dev(fmlk_ctx *ctx, double *values_dev_inout, int64_t len) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if (len < 0 || (len > 0 && !values_dev_inout)) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad values / len");
@@ -1938,6 +1975,7 @@ int32_t fmlk_all_reduce_sum_dev(fmlk_ctx *ctx, double *values_dev_inout, int64_t
 
 int32_t fmlk_all_reduce_sum(fmlk_ctx *ctx, double *values_host_inout, int64_t len) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if (len < 0 || (len > 0 && !values_host_inout)) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad values / len");
@@ -1995,6 +2033,7 @@ int32_t fmlk_reservoir(int64_t n, int32_t k, int64_t seed, int64_t *out_ids) {
 
 int32_t fmlk_get_points(fmlk_ctx *ctx, const int64_t *row_ids, int32_t m, double *out_rows_host) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     if (m < 0 || (m > 0 && (!row_ids || !out_rows_host))) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad row ids");
@@ -2035,6 +2074,7 @@ int32_t fmlk_generate_dense_dev(int32_t device, void *cuda_stream, int64_t seed,
                                 int64_t num_values, int32_t d, double *out_dev) {
     if (num_tasks < 1 || task < 0 || task >= num_tasks || d <= 0 || num_values < 0 || !out_dev)
         return fail(nullptr, FMLK_ERR_INVALID_ARG, "bad generator arguments");
+    DeviceScope device_scope;
     cudaError_t e = cudaSetDevice(device);
     if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, cudaGetErrorString(e));
     const int64_t dv = num_values / num_tasks, md = num_values % num_tasks;
@@ -2068,6 +2108,7 @@ int32_t fmlk_generate_dense_dev(int32_t device, void *cuda_stream, int64_t seed,
 int32_t fmlk_get_profile(fmlk_ctx *ctx, double *assign_ms, int64_t *assign_launches, int64_t *total_launches,
                          int64_t *rechecked_rows) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     CK(ctx, cudaStreamSynchronize(ctx->stream));
@@ -2085,6 +2126,7 @@ int32_t fmlk_get_profile(fmlk_ctx *ctx, double *assign_ms, int64_t *assign_launc
 
 int32_t fmlk_reset_profile(fmlk_ctx *ctx) {
     if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
     CK(ctx, cudaStreamSynchronize(ctx->stream));
@@ -2096,6 +2138,7 @@ int32_t fmlk_reset_profile(fmlk_ctx *ctx) {
 }
 
 int32_t fmlk_measure_fp64_peaks(int32_t device, double ms, double *dmma_tflops, double *dfma_tflops) {
+    DeviceScope device_scope;
     cudaError_t e = cudaSetDevice(device);
     if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, cudaGetErrorString(e));
     int sms = 0;
@@ -2293,6 +2336,7 @@ extern "C" int32_t fmlk_local_partials_noalloc(int32_t device, void *cuda_stream
                     "use fmlk_local_partials on a context instead");
     if (!centroids_dev || !out_sums_dev || !out_counts_dev || (n > 0 && !rows_dev))
         return fail(nullptr, FMLK_ERR_INVALID_ARG, "null device pointer");
+    DeviceScope device_scope;
     cudaError_t e = cudaSetDevice(device);
     if (e != cudaSuccess) return fail(nullptr, FMLK_ERR_CUDA, cudaGetErrorString(e));
     int rc = noalloc_setup(device);
