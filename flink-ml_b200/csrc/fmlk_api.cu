@@ -330,6 +330,12 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     const bool ordered_ok = det && accum && (d & 1) == 0 && ctx->rows_aligned16 && ctx->max_partial_slots == 0 &&
                             model_bytes * c.grid <= ((size_t)64 << 20) && model_bytes * c.grid * 16 <= ((size_t)256 << 20) &&
                             env_int("FMLK_TUNE_ORDERED", 1);
+    // Resident centroids are only worth it with enough MMA warps beside them: where the ring kernel can take the
+    // shape (even d <= 128, aligned rows) a resident geometry with fewer than 12 warps loses to it (d = 64:
+    // k = 256, 8 warps, 28.2 against 30.3 TFLOP/s; k = 320 19.8 against 30.5; d = 48, k = 512 10.0 against 23.4)
+    const int min_w = (!det && !small && (d & 1) == 0 && d <= 4 * kWideDk && ctx->rows_aligned16 && ctx->max_partial_slots == 0)
+                          ? env_int("FMLK_TUNE_MINW", 12)
+                          : 0;
     auto try_red = [&]() -> bool {
         if (!accum || !env_int("FMLK_TUNE_RED_SUMS", 1)) return false;
 
@@ -343,6 +349,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
         for (int i = 0; i < 5; i++) {
             if (red_cand[i][1] == 2 && !small) continue;
             const int cw = force_w ? force_w : red_cand[i][0], cx = force_xs ? force_xs : red_cand[i][1];
+            if (cw < min_w) continue;
             size_t need = smem_bytes(cw, 0, cx, c.S, k, d, c.k_pad, c.k_pad, 1, false);
             if (need <= budget) {
                 c.warps = cw;
@@ -404,6 +411,7 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
             const int cw = force_w ? force_w : cand[i][0], cx = force_xs ? force_xs : cand[i][1];
             size_t need = smem_bytes(cw, c.acc_warps, cx, c.S, k, d, c.k_pad, c.k_pad, 1, sums);
             if ((cw + c.acc_warps) * 32 > 512) continue;
+            if (cw < min_w) continue;
             // fixed-order sums are only worth their accumulator warps with enough MMA warps beside them
             if (sums && cw < 8 && env_int("FMLK_TUNE_RED_SUMS", 1)) continue;
             if (need <= budget) {
@@ -424,6 +432,11 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     //   d = 64, k = 1000: 26.7 / 28.2 against 26.0 / 28.5     d = 64, k = 500: 25.6 / 27.9 against 23.3 / 26.8
     //   d = 32, k = 1000: 24.5 / 25.6 against 22.5 / 25.8     d = 96, k = 300: 23.7 / 26.5 against 20.4 / 24.8
     // with padding waste (d = 100, k = 1000: 21.0 against 24.8) this kernel's lock-step tiles win.
+    // No resident geometry with enough warps.  The ring kernel pads rows to 32-column blocks: it is the better streamer
+    // while that wastes at most a fifth (d = 112, k = 128: 22.1 / 23.6 against 14.6 / 19.7 TFLOP/s training / predict for
+    // the lock-step tiles below; d = 80, k = 300: 22.9 / 23.5 against 19.6 / 24.9), beyond that the tiles below are
+    // (d = 100, k = 1000: 24.4 / 26.2 against 22.0 / 22.7; d = 48, k = 512: 22.2 / 26.6 against 23.3 / 23.6)
+    if (force_wide < 0 && min_w > 0 && 5 * d >= 4 * kWideDk * ((d + kWideDk - 1) / kWideDk)) return take_wide();
     if (force_wide < 0 && d >= 32 && d % 32 == 0) return take_wide();
     // streaming: one row stage per MMA warp, the rest of shared memory split into two centroid tiles.
     // More MMA warps keep the tensor pipe fed but leave less room for the centroid tiles (shorter
