@@ -330,11 +330,14 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     const bool ordered_ok = det && accum && (d & 1) == 0 && ctx->rows_aligned16 && ctx->max_partial_slots == 0 &&
                             model_bytes * c.grid <= ((size_t)64 << 20) && model_bytes * c.grid * 16 <= ((size_t)256 << 20) &&
                             env_int("FMLK_TUNE_ORDERED", 1);
-    // Resident centroids are only worth it with enough MMA warps beside them: where the ring kernel can take the
-    // shape (even d <= 128, aligned rows) a resident geometry with fewer than 12 warps loses to it (d = 64:
-    // k = 256, 8 warps, 28.2 against 30.3 TFLOP/s; k = 320 19.8 against 30.5; d = 48, k = 512 10.0 against 23.4)
+    // Resident centroids are only worth it with enough MMA warps beside them.  Where a streamer can take the shape
+    // (even d <= 128, aligned rows) a resident geometry needs 8 MMA warps -- with 4 or 2 it falls off a cliff (d = 64,
+    // k = 320: 19.8 TFLOP/s against 30.4 streamed; d = 96, k = 160: 18.3 against 23.9; d = 112, k = 256: 17.9 against
+    // 23.5) -- and 12 when d is 32 or 64, which the ring kernel streams without padding and with 256-row tiles
+    // (d = 64, k = 256: 8 resident warps 28.1, ring 30.3; but d = 96, k = 100: 24.2 against 21.0).  Eight warps are fine otherwise (d = 100, k = 100: 25.8
+    // against 18.0 for the ring; d = 48, k = 400: 26.4 against 23.3).
     const int min_w = (!det && !small && (d & 1) == 0 && d <= 4 * kWideDk && ctx->rows_aligned16 && ctx->max_partial_slots == 0)
-                          ? env_int("FMLK_TUNE_MINW", 12)
+                          ? env_int("FMLK_TUNE_MINW", (d % kWideDk == 0 && d <= 2 * kWideDk) ? 12 : 8)
                           : 0;
     auto try_red = [&]() -> bool {
         if (!accum || !env_int("FMLK_TUNE_RED_SUMS", 1)) return false;
@@ -432,11 +435,11 @@ int choose_cfg(fmlk_ctx *ctx, int k, int d, bool accum, LaunchCfg *out) {
     //   d = 64, k = 1000: 26.7 / 28.2 against 26.0 / 28.5     d = 64, k = 500: 25.6 / 27.9 against 23.3 / 26.8
     //   d = 32, k = 1000: 24.5 / 25.6 against 22.5 / 25.8     d = 96, k = 300: 23.7 / 26.5 against 20.4 / 24.8
     // with padding waste (d = 100, k = 1000: 21.0 against 24.8) this kernel's lock-step tiles win.
-    // No resident geometry with enough warps.  The ring kernel pads rows to 32-column blocks: it is the better streamer
-    // while that wastes at most a fifth (d = 112, k = 128: 22.1 / 23.6 against 14.6 / 19.7 TFLOP/s training / predict for
-    // the lock-step tiles below; d = 80, k = 300: 22.9 / 23.5 against 19.6 / 24.9), beyond that the tiles below are
-    // (d = 100, k = 1000: 24.4 / 26.2 against 22.0 / 22.7; d = 48, k = 512: 22.2 / 26.6 against 23.3 / 23.6)
-    if (force_wide < 0 && min_w > 0 && 5 * d >= 4 * kWideDk * ((d + kWideDk - 1) / kWideDk)) return take_wide();
+    // No resident geometry with enough warps.  The ring kernel pads rows to 32-column blocks; with more than about an
+    // eighth of padding the lock-step streamed tiles below are the better streamer (d = 80, k = 1000: 25.2 / 27.8
+    // TFLOP/s training / predict against 22.4 / 22.7 for the ring; d = 100: 24.1 / 25.8 against 21.8 / 22.0; d = 48:
+    // 24.6 / 27.3 against 23.2 / 23.5), with less the ring (d = 112, k = 1000: 23.9 / 24.8 against 20.7 / 22.1)
+    if (force_wide < 0 && min_w > 0 && 20 * d >= 17 * kWideDk * ((d + kWideDk - 1) / kWideDk)) return take_wide();
     if (force_wide < 0 && d >= 32 && d % 32 == 0) return take_wide();
     // streaming: one row stage per MMA warp, the rest of shared memory split into two centroid tiles.
     // More MMA warps keep the tensor pipe fed but leave less room for the centroid tiles (shorter
