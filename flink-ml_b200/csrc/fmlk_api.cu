@@ -8,6 +8,7 @@
 #include "fmlk_fast.cuh"
 #include "fmlk_knn.cuh"
 #include "fmlk_ring.cuh"
+#include "fmlk_small.cuh"
 
 #include <dlfcn.h>
 #include <algorithm>
@@ -852,8 +853,75 @@ int prep_centroids(fmlk_ctx *ctx, bool accum, bool base_done = false) {
 }
 
 // Launches the assign kernel over one block of rows.  partials != null: accumulate.
+// Short rows against few centroids run the reference loop as written, one row per thread (fmlk_small.cuh).  Exact by
+// construction, so it serves the fast mode too.  Measured against the tensor-core kernel (8 M rows, training /
+// predict ms): d = 10, k = 2 0.34 / 0.21 against 0.91 / 0.76; d = 4, k = 8 0.62 / 0.46 against 1.53 / 1.22; d = 8, k = 16
+// 0.66 / 0.52 against 0.91 / 0.76; d = 16, k = 4 0.80 / 0.65 against 0.92 / 0.77 -- but d = 16, k = 8 1.04 / 0.79 against
+// 0.92 / 0.77, d = 32, k = 2 0.95 / 0.56 against 0.50 / 0.42, d = 4, k = 30 1.74 / 1.37 against 1.62 / 1.26: the FP64 pipe
+// runs this loop at about a third of its rate (compares and selects between the multiply-adds), so the window is small.
+bool small_shape(const fmlk_ctx *ctx, int k, int d) {
+    (void)ctx;
+    if (!env_int("FMLK_TUNE_SMALL", 1)) return false;
+    const int64_t cost = (int64_t)k * (2 * d + 8);
+    if (cost <= env_int("FMLK_TUNE_SMALL_COST", 0) && d <= 32) return true; // (tuning builds: force)
+    return (d <= 12 && cost <= 400) || (d <= 16 && k <= 4);
+}
+
+template <int DPAD>
+int launch_small_t(fmlk_ctx *ctx, const SmallParams &p, bool accum, bool fma) {
+    const size_t smem = small_smem_bytes<DPAD>(p.k, p.d, accum);
+    const int64_t tiles = (p.n + 31) / 32;
+    const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, ctx->smem_optin / std::max<size_t>(smem, 1)));
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->sm_count * per_sm, (tiles + kSmallWarps - 1) / kSmallWarps));
+#define FMLK_SMALL(F, A)                                                                                              \
+    do {                                                                                                              \
+        static bool attr_done[64] = {false};                                                                          \
+        if (ctx->device < 64 && !attr_done[ctx->device]) {                                                            \
+            CK(ctx, cudaFuncSetAttribute(assign_small_kernel<DPAD, F, A>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                         (int)ctx->smem_optin));                                                      \
+            attr_done[ctx->device] = true;                                                                            \
+        }                                                                                                             \
+        assign_small_kernel<DPAD, F, A><<<grid, kSmallWarps * 32, smem, ctx->stream>>>(p);                            \
+    } while (0)
+    if (fma && accum) FMLK_SMALL(true, true);
+    else if (fma) FMLK_SMALL(true, false);
+    else if (accum) FMLK_SMALL(false, true);
+    else FMLK_SMALL(false, false);
+#undef FMLK_SMALL
+    CK(ctx, cudaGetLastError());
+    return FMLK_OK;
+}
+
+int launch_small(fmlk_ctx *ctx, const double *x, int64_t n, int32_t *labels, bool accum, int n_partials) {
+    SmallParams p{};
+    p.x = x;
+    p.n = n;
+    p.d = ctx->md;
+    p.k = ctx->k;
+    p.c = ctx->centroids;
+    p.cn = ctx->cn;
+    p.labels = labels;
+    p.partials = accum ? ctx->partials : nullptr;
+    p.n_partials = n_partials;
+    const bool fma = (ctx->flags & FMLK_FLAG_BLAS_FMA) != 0;
+    if (ctx->md <= 8) return launch_small_t<8>(ctx, p, accum, fma);
+    if (ctx->md <= 16) return launch_small_t<16>(ctx, p, accum, fma);
+    if (ctx->md <= 24) return launch_small_t<24>(ctx, p, accum, fma);
+    return launch_small_t<32>(ctx, p, accum, fma);
+}
+
 int launch_assign(fmlk_ctx *ctx, const LaunchCfg &cfg, const double *x, int64_t n, int32_t *labels, bool accum) {
     if (n <= 0) return FMLK_OK;
+    if (small_shape(ctx, ctx->k, ctx->md)) {
+        const bool prof = (ctx->flags & FMLK_FLAG_PROFILE) != 0;
+        cudaEvent_t e0 = prof ? next_event(ctx) : nullptr, e1 = prof ? next_event(ctx) : nullptr;
+        if (e0 && e1) cudaEventRecord(e0, ctx->stream);
+        int rc = launch_small(ctx, x, n, labels, accum, cfg.n_partials);
+        if (e0 && e1) cudaEventRecord(e1, ctx->stream);
+        ctx->assign_launches++;
+        ctx->total_launches++;
+        return rc;
+    }
     {
         FastPlan f;
         if (fast_rows_ok(x, n) && fast_shape(ctx, ctx->k, ctx->md, accum, &f)) {
@@ -2212,6 +2280,13 @@ int32_t fmlk_describe_launch(fmlk_ctx *ctx, int32_t k, int32_t d, int32_t accumu
     LaunchCfg c;
     int rc = choose_cfg(ctx, k, d, accumulate != 0, &c);
     if (rc) return rc;
+    if (small_shape(ctx, k, d)) {
+        snprintf(out, (size_t)out_len,
+                 "small=1 one row per thread, reference arithmetic (no screening pass): block=%d warps=%d rows_per_warp_tile=32 "
+                 "cost_per_row=%d FP64 instructions n_partials=%d",
+                 kSmallWarps * 32, kSmallWarps, k * (2 * d + 8), c.n_partials);
+        return FMLK_OK;
+    }
     FastPlan f;
     if (fast_shape(ctx, k, d, accumulate != 0, &f)) {
         cudaFuncAttributes fa{};

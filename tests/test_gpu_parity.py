@@ -37,7 +37,8 @@ def _step_parity(ctx, x, cent, expect_rechecks=None):
     assert np.array_equal(counts, o_counts.astype(np.int64))
     assert np.allclose(sums, o_sums, rtol=SUM_RTOL, atol=1e-300, equal_nan=True)
     assert ctx.predict(x).tolist() == o_labels.tolist()  # host-buffer entry point, same answer
-    if expect_rechecks is not None:
+    if expect_rechecks is not None and "small=1" not in ctx.describe_launch(cent.shape[0], x.shape[1], True):
+        # (short rows against few centroids run the reference loop itself: nothing is screened, nothing replayed)
         assert ctx.profile()["rechecked_rows"] >= expect_rechecks
     return labels
 
@@ -79,7 +80,16 @@ def test_g3_fewer_distinct_points_than_clusters(ctx):
     oc, ow = O.fit([data], data[:2], 20)
     assert np.array_equal(c, oc, equal_nan=True) and np.isnan(c[1]).all() and w.tolist() == [3.0, 0.0]
     assert ctx.predict(data).tolist() == [0, 0, 0]
-    assert ctx.profile()["rechecked_rows"] >= 3  # round 1 went through the exact replay
+    # the same fixture with 38 zero columns appended runs on the tensor-core kernel: round 1 goes through the exact replay
+    wide = np.concatenate([data, np.zeros((3, 38))], axis=1)
+    ctx.clear_points()
+    ctx.reset_profile()
+    ctx.append_points(wide)
+    ctx.set_centroids(wide[:2])
+    c, w = ctx.fit(20)
+    oc, ow = O.fit([wide], wide[:2], 20)
+    assert np.array_equal(c, oc, equal_nan=True) and np.isnan(c[1]).all() and w.tolist() == [3.0, 0.0]
+    assert ctx.profile()["rechecked_rows"] >= 3
 
 
 def test_host_mirror_fit_and_predict():
@@ -133,7 +143,8 @@ SHAPES = [
     (600, 1531, 3),      # odd d close to the shared-memory limit of one row tile + centroids
     (3000, 2, 3000),     # many more centroids than dimensions
     (2500, 513, 33),     # odd d: 8-byte cp.async row loads, streamed centroids
-    (4000, 10, 2),       # config 1 shape
+    (4000, 10, 2),       # config 1 shape (one row per thread: assign_small_kernel)
+    (5003, 2, 3), (4099, 7, 5), (3000, 12, 16), (2500, 16, 4), (1000, 1, 2), (2001, 3, 1), (70, 8, 9),  # same kernel
     (4000, 100, 10),     # kmeans-benchmark.json shape
 ]
 
@@ -156,9 +167,10 @@ def test_step_parity_model_generator_centroids(ctx):
     _step_parity(ctx, x, cent)
 
 
-def test_ties_duplicates_and_nan_go_through_exact_replay(ctx):
+@pytest.mark.parametrize("d", [16, 40])  # 16: one row per thread, reference arithmetic; 40: tensor cores + exact replay
+def test_ties_duplicates_and_nan_go_through_exact_replay(ctx, d):
     rng = np.random.default_rng(5)
-    d, k = 16, 24
+    k = 24
     cent = rng.standard_normal((k, d))
     cent[7] = cent[3]            # duplicate centroids: exact ties, lower index must win
     cent[20] = cent[3]
@@ -173,6 +185,36 @@ def test_ties_duplicates_and_nan_go_through_exact_replay(ctx):
     assert (labels[:500] == 3).all() and labels[600] == 0
     # all-identical centroids: every row replayed, every label 0
     _step_parity(ctx, x[:1000], np.repeat(cent[:1], 9, axis=0), expect_rechecks=1000)
+
+
+def test_small_kernel_ties_duplicates_and_non_finite(ctx):
+    """assign_small_kernel (short rows, few centroids) runs the reference loop itself: the same edge cases as above
+    must come out as the oracle's, including the pruning branch's (pn - |c|)^2 >= best skip on NaN / Inf."""
+    rng = np.random.default_rng(8)
+    d, k = 8, 9
+    assert "small=1" in ctx.describe_launch(k, d, True)
+    cent = rng.standard_normal((k, d))
+    cent[5] = cent[2]
+    cent[7] = cent[2]
+    cent[4] = np.nan
+    x = rng.standard_normal((5000, d))
+    x[:300] = cent[2]
+    x[300:400] = 0.5 * (cent[0] + cent[1])
+    x[400] = np.nan
+    x[401] = np.inf
+    x[402] = -np.inf
+    x[403] = 1e200
+    x[404] = 1e-200
+    x[405] = 0.0
+    x[406, 3] = np.nan
+    labels = _step_parity(ctx, x, cent)
+    assert (labels[:300] == 2).all() and labels[400] == 0
+    # centroids with norms spread over many orders of magnitude (the pruning branch), an Inf centroid, all equal
+    cent2 = rng.standard_normal((k, d)) * np.logspace(-6, 6, k)[:, None]
+    _step_parity(ctx, x, cent2)
+    cent2[3] = np.inf
+    _step_parity(ctx, x, cent2)
+    _step_parity(ctx, x[:1000], np.repeat(cent[:1], 4, axis=0))
 
 
 def test_pruning_branch_cases(ctx):
