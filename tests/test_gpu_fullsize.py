@@ -37,13 +37,16 @@ def rows():
     torch.cuda.empty_cache()
 
 
-@pytest.mark.parametrize("k", [100, 1000])
-def test_full_size_round_properties(rows, k):
+@pytest.mark.parametrize("k,flags", [(100, 0), (1000, 0), (100, native.FLAG_FAST_TF32), (1000, native.FLAG_FAST_TF32),
+                                     (100, native.FLAG_DETERMINISTIC)])
+def test_full_size_round_properties(rows, k, flags):
+    """FP64 mode (k = 100: assign_kernel, k = 1000: assign_ring_kernel), the tcgen05 fast mode (resident and streamed
+    centroid terms) and the ordered sums of FMLK_FLAG_DETERMINISTIC."""
     import torch
     n, d = rows.shape
     ids = native.reservoir(n, k, O.KMEANS_DEFAULT_SEED)
     cent = rows[torch.as_tensor(ids, device=rows.device)].cpu().numpy()
-    with native.Context(0) as ctx:
+    with native.Context(0, flags=flags) as ctx:
         ctx.adopt_points_dev(rows.data_ptr(), n, d, keep=rows)
         ctx.set_centroids(cent)
         sums, counts = ctx.local_partials()
@@ -53,7 +56,8 @@ def test_full_size_round_properties(rows, k):
         ctx.profile()  # synchronises the context's stream
         # P5
         assert np.array_equal(counts, counts2)
-        if "sums_in_smem=1" in ctx.describe_launch(k, d, True):
+        desc = ctx.describe_launch(k, d, True)
+        if "sums_in_smem=1" in desc or "ordered=1" in desc:
             assert np.array_equal(sums, sums2)
         else:
             assert np.allclose(sums, sums2, rtol=1e-12, atol=1e-300)
