@@ -607,23 +607,32 @@ def run_ours(args):
                      "scaling": "weak", "modes": recs}
             del xs
             torch.cuda.empty_cache()
-            # the same shape with the TOTAL fixed (strong scaling): north_rows rows over all ranks.  At one GPU that is
-            # the record above; at N GPUs each rank holds its RowGenerator slice of them
-            if world == 1:
+            # the same shape with the TOTAL fixed (strong scaling, SURVEY 8d: 2.5e8 rows = 128 GB over 1/2/4/8 GPUs): each
+            # rank holds its RowGenerator slice.  (A total that does not fit this GPU's free memory falls back to
+            # north_rows, which at one GPU is the record above.)
+            total = args.strong_rows - args.strong_rows % world
+            per = total // world
+            free_b, _ = torch.cuda.mem_get_info(local)
+            fits = torch.tensor([1 if free_b > per * nd * 8 + (8 << 30) else 0], dtype=torch.int64, device=dev)
+            if world > 1:
+                dist.all_reduce(fits, op=dist.ReduceOp.MIN)
+            if not int(fits.item()):
+                total = nn - nn % world
+                per = total // world
+            if world == 1 and per == nn:
                 strong = {"workload": "%d x %d FP64 rows in all, k=%d (at one GPU: the north_star record)" % (nn, nd, nk),
                           "scaling": "strong", "rows_total": nn,
                           "modes": {m: {"value": v["value"], "unit": UNIT, "ms_per_round": v["ms_per_round"]} for m, v in recs.items()}}
             else:
-                per = nn // world
                 xs = generate(per, nd)
                 srecs = {}
                 for name, fl in (("f64", 0), ("tf32x3+f64-recheck", native.FLAG_FAST_TF32)):
                     if name != "f64" and args.no_fast:
                         continue
-                    nr = timed_fits(fl, xs, nk, nrounds, 1, 1)
+                    nr = timed_fits(fl, xs, nk, 2, 1, 1)
                     srecs[name] = {"value": nr["value"], "unit": UNIT, "ms_per_round": nr["ms_per_round"]}
-                strong = {"workload": "%d x %d FP64 rows in all (%d per GPU), k=%d, %d rounds, device-resident" % (
-                              per * world, nd, per, nk, nrounds), "scaling": "strong", "rows_total": per * world, "modes": srecs}
+                strong = {"workload": "%d x %d FP64 rows in all (%d per GPU), k=%d, 2 rounds, device-resident" % (
+                              total, nd, per, nk), "scaling": "strong", "rows_total": total, "modes": srecs}
                 del xs
                 torch.cuda.empty_cache()
 
@@ -674,6 +683,7 @@ def main():
     ap.add_argument("--transform-rows", type=int, default=4_000_000, help="rows per GPU of the transform sub-record")
     ap.add_argument("--online-batches", type=int, default=40)
     ap.add_argument("--north-rows", type=int, default=125_000_000, help="rows per GPU of the north-star sub-record")
+    ap.add_argument("--strong-rows", type=int, default=250_000_000, help="total rows of the strong-scaling sub-record")
     args = ap.parse_args()
     if args.impl == "ours":
         args.warmup = max(args.warmup, 3)  # timing rule: at least 3 warm-up steps
