@@ -360,6 +360,14 @@ def run_ours(args):
             "centroids_within_1e-9_of_f64_mode": bool(np.allclose(fc, model_c, rtol=1e-9, atol=0, equal_nan=True)),
             "gpu_launches": fr["prof"]["total_launches"],
         }
+        fast_traffic = os.path.join(ROOT, "profiles", "traffic_%s_fast.json" % args.workload)
+        if fr["fast"] and os.path.exists(fast_traffic):
+            try:
+                fast_rec["roofline"]["traffic"] = json.load(open(fast_traffic)).get("dram_bytes_per_launch")
+                fast_rec["roofline"]["traffic_source"] = "ncu --set full capture of this kernel on this workload, committed as " + \
+                                                         os.path.relpath(fast_traffic, ROOT)
+            except Exception:
+                pass
 
     # ---- e2e: the public API with HOST buffers: KMeans.fit(Table) -> model, H2D and D2H inside
     e2e = None
