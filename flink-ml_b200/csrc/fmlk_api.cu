@@ -872,7 +872,10 @@ int launch_small_t(fmlk_ctx *ctx, const SmallParams &p, bool accum, bool fma) {
     const size_t smem = small_smem_bytes<DPAD>(p.k, p.d, accum);
     const int64_t tiles = (p.n + 31) / 32;
     const int per_sm = (int)std::max<size_t>(1, std::min<size_t>(8, ctx->smem_optin / std::max<size_t>(smem, 1)));
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->sm_count * per_sm, (tiles + kSmallWarps - 1) / kSmallWarps));
+    int grid = (int)std::max<int64_t>(1, std::min<int64_t>((int64_t)ctx->sm_count * per_sm, (tiles + kSmallWarps - 1) / kSmallWarps));
+    // FMLK_FLAG_DETERMINISTIC: one CTA per accumulator slot (two CTAs adding into one slot would do so in arrival order);
+    // inside a CTA the order is fixed by construction
+    if (accum && (ctx->flags & FMLK_FLAG_DETERMINISTIC)) grid = std::max(1, std::min(grid, p.n_partials));
 #define FMLK_SMALL(F, A)                                                                                              \
     do {                                                                                                              \
         static bool attr_done[64] = {false};                                                                          \

@@ -511,6 +511,23 @@ def test_deterministic_flag_gives_bit_identical_sums():
     assert np.array_equal(a[1], o_counts.astype(np.int64)) and np.allclose(a[0], o_sums, rtol=SUM_RTOL, atol=0)
 
 
+@pytest.mark.parametrize("n,d,k", [(400_000, 8, 5), (300_000, 100, 10), (200_000, 10, 2)])
+def test_deterministic_flag_small_and_few_centroid_shapes_repeat_bit_for_bit(n, d, k):
+    """The one-row-per-thread kernel (one CTA per slot in this mode) and the few-centroids geometry (ordered bulk
+    reductions): ten rounds over the same rows, identical bits."""
+    x = O.generate_dense(2, 0, 1, n, d)
+    cent = x[:k].copy()
+    with native.Context(0, flags=native.FLAG_DETERMINISTIC) as c:
+        c.append_points(x)
+        c.set_centroids(cent)
+        first = c.local_partials()
+        for _ in range(10):
+            again = c.local_partials()
+            assert np.array_equal(again[0], first[0]) and np.array_equal(again[1], first[1])
+    o_sums, o_counts = O.train_local(x, cent)
+    assert np.array_equal(first[1], o_counts.astype(np.int64)) and np.allclose(first[0], o_sums, rtol=SUM_RTOL, atol=0)
+
+
 @pytest.mark.parametrize("n,d,k", [(50_000, 100, 10), (30_000, 10, 2), (40_000, 64, 100), (20_000, 64, 250)])
 def test_deterministic_context_step_parity(n, d, k):
     """The fixed-order paths (warp-private sums for few centroids, accumulator warps otherwise) against
