@@ -157,6 +157,9 @@ struct fmlk_ctx {
     unsigned long long *recheck = nullptr;
     double *c_blk = nullptr; // the centroids block by block in assign_ring_kernel's shared-memory layout
     size_t c_blk_cap = 0;    // doubles
+    cudaEvent_t ev_piece[4] = {nullptr, nullptr, nullptr, nullptr}; // online batches arrive in pieces (copy stream)
+    int extra_pieces = 0;            // local_round: extra_rows is this many equal pieces, piece i ready at ev_piece[i]
+    int64_t extra_piece_rows = 0;
     double *warp_scratch = nullptr; // per-warp accumulators of assign_kernel<3> with few centroids (zero between launches)
     size_t warp_scratch_cap = 0;    // doubles
     unsigned *tail_counter = nullptr; // round_tail_kernel's arrival counter (zero between launches)
@@ -1080,7 +1083,15 @@ int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n, bool f
     if ((rc = prep_centroids(ctx, true, tail_ran_before))) return rc;
     if (!tail_ran_before)
         CK(ctx, cudaMemsetAsync(ctx->partials, 0, stride * cfg.n_partials * sizeof(double), ctx->stream));
-    if (extra_rows) {
+    if (extra_rows && ctx->extra_pieces > 1) {
+        // the batch is still arriving, piece by piece, on the copy stream: each piece is labelled as soon as it is there
+        for (int i = 0; i < ctx->extra_pieces; i++) {
+            const int64_t off = (int64_t)i * ctx->extra_piece_rows, m = std::min(ctx->extra_piece_rows, extra_n - off);
+            if (m <= 0) break;
+            CK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_piece[i], 0));
+            if ((rc = launch_assign(ctx, cfg, extra_rows + off * ctx->md, m, nullptr, true))) return rc;
+        }
+    } else if (extra_rows) {
         if ((rc = launch_assign(ctx, cfg, extra_rows, extra_n, nullptr, true))) return rc;
     } else {
         for (const Chunk &ch : ctx->chunks)
@@ -1364,6 +1375,8 @@ void fmlk_destroy(fmlk_ctx *ctx) {
         if (ctx->ev_copied[b]) cudaEventDestroy(ctx->ev_copied[b]);
         if (ctx->ev_decoded[b]) cudaEventDestroy(ctx->ev_decoded[b]);
     }
+    for (int b = 0; b < 4; b++)
+        if (ctx->ev_piece[b]) cudaEventDestroy(ctx->ev_piece[b]);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     for (cudaEvent_t e : ctx->ev_pool) cudaEventDestroy(e);
     if (ctx->own_stream && ctx->stream) cudaStreamDestroy(ctx->stream);
@@ -1831,11 +1844,29 @@ int32_t fmlk_online_round(fmlk_ctx *ctx, const double *local_batch_host, int64_t
     CK(ctx, cudaMemcpyAsync(ctx->centroids, centroids_inout, kd * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     CK(ctx, cudaMemcpyAsync(ctx->weights, weights_inout, (size_t)k * sizeof(double), cudaMemcpyHostToDevice,
                             ctx->stream));
-    if (n_local > 0)
+    ctx->extra_pieces = 0;
+    if (n_local >= 32768) {
+        // four pieces on the copy stream: the assign launches of piece i run while piece i + 1 is on the host link
+        if (!ctx->copy_stream) CK(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        for (int b = 0; b < 4; b++)
+            if (!ctx->ev_piece[b]) CK(ctx, cudaEventCreateWithFlags(&ctx->ev_piece[b], cudaEventDisableTiming));
+        const int64_t piece = ((n_local + 3) / 4 + 1) & ~(int64_t)1; // even: every piece starts 16-byte aligned
+        ctx->extra_pieces = (int)((n_local + piece - 1) / piece);
+        ctx->extra_piece_rows = piece;
+        for (int i = 0; i < ctx->extra_pieces; i++) {
+            const int64_t off = (int64_t)i * piece, m = std::min(piece, n_local - off);
+            CK(ctx, cudaMemcpyAsync(ctx->stage_rows + off * d, local_batch_host + off * d, (size_t)m * d * sizeof(double),
+                                    cudaMemcpyHostToDevice, ctx->copy_stream));
+            CK(ctx, cudaEventRecord(ctx->ev_piece[i], ctx->copy_stream));
+        }
+    } else if (n_local > 0) {
         CK(ctx, cudaMemcpyAsync(ctx->stage_rows, local_batch_host, (size_t)n_local * d * sizeof(double),
                                 cudaMemcpyHostToDevice, ctx->stream));
+    }
     if (n_local > 0) {
-        if ((rc = local_round(ctx, ctx->stage_rows, n_local))) return rc;
+        rc = local_round(ctx, ctx->stage_rows, n_local);
+        ctx->extra_pieces = 0;
+        if (rc) return rc;
     } else {
         CK(ctx, cudaMemsetAsync(ctx->red, 0, len * sizeof(double), ctx->stream));
     }

@@ -363,7 +363,8 @@ def test_g4_g5_online_golden(ctx):
 
 
 @pytest.mark.parametrize("n,d,k,decay", [(1000, 16, 8, 0.5), (20000, 128, 256, 0.5), (500, 8, 40, 0.0),
-                                         (64, 4, 3, 1.0)])
+                                         (64, 4, 3, 1.0),
+                                         (40001, 64, 100, 0.5), (33000, 7, 5, 0.25)])  # batches that arrive in four pieces
 def test_online_round_parity(ctx, n, d, k, decay):
     c, w = O.random_model_data(k, d, 0.0, 0)
     oc, ow = c.copy(), w.copy()
