@@ -428,6 +428,34 @@ def test_predict_dev_and_adopt(ctx):
     ctx.clear_points()
 
 
+@pytest.mark.parametrize("d,k,flags", [(64, 1000, 0), (128, 256, 0), (64, 100, 0), (100, 10, 0), (8, 5, 0),
+                                       (64, 100, native.FLAG_FAST_TF32), (64, 100, native.FLAG_DETERMINISTIC)])
+def test_rows_that_are_only_8_byte_aligned(d, k, flags):
+    """Caller-owned device rows that start 8 bytes off a 16-byte boundary: the kernels that need 16-byte copies (ring,
+    bulk copies and reductions, tcgen05 staging) hand over to the ones that do not; the answer is the oracle's."""
+    import torch
+    n = 30001
+    buf = torch.empty(n * d + 1, dtype=torch.float64, device="cuda:0")
+    native.generate_dense_dev(0, torch.cuda.current_stream().cuda_stream, 2, 0, 1, n * d + 1, 1, buf.data_ptr())
+    torch.cuda.synchronize()
+    view = buf[1:].view(n, d)
+    assert view.data_ptr() % 16 == 8
+    x = view.cpu().numpy()
+    cent = x[:k].copy()
+    with native.Context(0, flags=flags) as c:
+        c.adopt_points_dev(view.data_ptr(), n, d, keep=buf)
+        c.set_centroids(cent)
+        labels = c.predict_cached()
+        sums, counts = c.local_partials()
+        lab = torch.empty(n, dtype=torch.int32, device="cuda:0")
+        c.predict_dev(view.data_ptr(), n, d, lab.data_ptr())
+        c.profile()
+    o_sums, o_counts, o_labels = O.train_local(x, cent, want_labels=True)
+    assert np.array_equal(labels, o_labels) and np.array_equal(lab.cpu().numpy(), o_labels)
+    assert np.array_equal(counts, o_counts.astype(np.int64))
+    assert np.allclose(sums, o_sums, rtol=SUM_RTOL, atol=0)
+
+
 def test_fp64_peaks_are_plausible():
     dmma, dfma = native.measure_fp64_peaks(0, 50.0)
     assert 5.0 < dmma < 100.0 and 5.0 < dfma < 100.0
