@@ -2,7 +2,7 @@
 # Round-2 evidence in one gpurun call: the bench lines, the launch list of the bench, and one
 # `ncu --set full` capture per kernel family at the shapes DESIGN.md quotes.  Everything lands under
 # gpurun_out/; scripts/refresh_profiles_r2.py turns it into the tracked summaries under profiles/.
-# usage: gpu_evidence_r2.sh 1|2   (two calls: gpurun merges at most 64 MiB of gpurun_out/ per call)
+# usage: gpu_evidence_r2.sh 1|2|3   (separate calls: gpurun merges at most 64 MiB of gpurun_out/ per call)
 PART=${1:-1}
 mkdir -p gpurun_out
 if [ "$PART" = 1 ]; then
@@ -20,7 +20,10 @@ cap() { # name, kernel regex, env, args...
   env $envs ncu --set full --clock-control none --import-source on -k regex:$regex -s 1 -c 1 -f -o gpurun_out/r2_$name python scripts/run_assign.py "$@" > gpurun_out/ncu_$name.log 2>&1
   echo "$name rc=$? $(tail -1 gpurun_out/plain_$name.log | cut -c1-80)"
 }
-if [ "$PART" = 1 ]; then
+if [ "$PART" = 3 ]; then
+cap c1shape_train_small assign_small FMLK_FAST=0 8000000 10 2 3
+cap c2_train_ordered assign_kernel FMLK_DET=1 10000000 64 100 3
+elif [ "$PART" = 1 ]; then
 cap c2_train_f64 assign_kernel FMLK_FAST=0 10000000 64 100 3
 cap c2_train_fast assign_fast FMLK_FAST=1 10000000 64 100 3
 cap c2_predict_fast assign_fast FMLK_FAST=1 10000000 64 100 3 predict

@@ -53,6 +53,8 @@ names = {"c2_train_f64": "assign_kernel<3>, config 2 (10M x 64, k=100), training
          "c4shape_train_fast": "assign_fast_kernel<true>, config 4's shape, training, fast mode (streamed centroid terms)",
          "c3shape_predict_f64": "assign_ring_kernel<false,2>, config 3's shape (4M x 128, k=1000), predict, FP64 mode",
          "c5shape_train_f64": "assign_ring_kernel<true,2>, config 5's shape (4M x 128, k=256), training, FP64 mode",
+         "c1shape_train_small": "assign_small_kernel<16,false,true>, config 1's shape with 8M rows (d=10, k=2), training: one row per thread",
+         "c2_train_ordered": "assign_kernel<3> with FMLK_FLAG_DETERMINISTIC (ordered bulk reductions, one accumulator per warp), config 2, training",
          "knn": "knn_predict_kernel<false>, KnnModel.transform: 65536 rows x 64 against 10000 training points, k=5"}
 traffic = {}
 for key, title in names.items():
