@@ -157,6 +157,18 @@ struct fmlk_ctx {
     unsigned long long *recheck = nullptr;
     double *c_blk = nullptr; // the centroids block by block in assign_ring_kernel's shared-memory layout
     size_t c_blk_cap = 0;    // doubles
+    // fmlk_append_points_async: rows of the last append that are still on the host link (copy stream).  The first
+    // training round labels them piece by piece as they arrive; every other consumer makes the stream wait for the
+    // last piece first.
+    struct PendingPiece {
+        double *ptr;
+        int64_t rows;
+        cudaEvent_t ev;
+    };
+    std::vector<PendingPiece> pending;
+    int pending_chunk = -1;     // index into chunks
+    int64_t pending_row0 = 0;   // first row of that chunk the pieces cover
+    std::vector<cudaEvent_t> pending_events; // pool
     cudaEvent_t ev_piece[4] = {nullptr, nullptr, nullptr, nullptr}; // online batches arrive in pieces (copy stream)
     int extra_pieces = 0;            // local_round: extra_rows is this many equal pieces, piece i ready at ev_piece[i]
     int64_t extra_piece_rows = 0;
@@ -1094,8 +1106,21 @@ int local_round(fmlk_ctx *ctx, const double *extra_rows, int64_t extra_n, bool f
     } else if (extra_rows) {
         if ((rc = launch_assign(ctx, cfg, extra_rows, extra_n, nullptr, true))) return rc;
     } else {
-        for (const Chunk &ch : ctx->chunks)
-            if ((rc = launch_assign(ctx, cfg, ch.ptr, ch.rows, nullptr, true))) return rc;
+        for (size_t ci = 0; ci < ctx->chunks.size(); ci++) {
+            const Chunk &ch = ctx->chunks[ci];
+            if (!ctx->pending.empty() && (int)ci == ctx->pending_chunk) {
+                // rows still arriving (fmlk_append_points_async): each piece is labelled as soon as it is there
+                if (ctx->pending_row0 > 0 && (rc = launch_assign(ctx, cfg, ch.ptr, ctx->pending_row0, nullptr, true))) return rc;
+                for (const fmlk_ctx::PendingPiece &pc : ctx->pending) {
+                    CK(ctx, cudaStreamWaitEvent(ctx->stream, pc.ev, 0));
+                    if ((rc = launch_assign(ctx, cfg, pc.ptr, pc.rows, nullptr, true))) return rc;
+                }
+            } else if ((rc = launch_assign(ctx, cfg, ch.ptr, ch.rows, nullptr, true))) {
+                return rc;
+            }
+        }
+        ctx->pending.clear(); // (the stream has waited for every piece)
+        ctx->pending_chunk = -1;
     }
     const int threads = 256;
     if (fused_tail) {
@@ -1168,6 +1193,16 @@ int check_dim(fmlk_ctx *ctx, int32_t d) {
 }
 
 // Destination for n more rows: the tail of the last owned chunk, or a new chunk.
+// Rows of an asynchronous append may still be on their way: whatever is enqueued on the context's stream from now on
+// runs after the last of them (copies on the copy stream complete in order).
+int settle_pending(fmlk_ctx *ctx) {
+    if (ctx->pending.empty()) return FMLK_OK;
+    CK(ctx, cudaStreamWaitEvent(ctx->stream, ctx->pending.back().ev, 0));
+    ctx->pending.clear();
+    ctx->pending_chunk = -1;
+    return FMLK_OK;
+}
+
 int grow_points(fmlk_ctx *ctx, int64_t n, double **dst) {
     if (!ctx->chunks.empty()) {
         Chunk &last = ctx->chunks.back();
@@ -1375,6 +1410,8 @@ void fmlk_destroy(fmlk_ctx *ctx) {
         if (ctx->ev_copied[b]) cudaEventDestroy(ctx->ev_copied[b]);
         if (ctx->ev_decoded[b]) cudaEventDestroy(ctx->ev_decoded[b]);
     }
+    if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
+    for (cudaEvent_t e : ctx->pending_events) cudaEventDestroy(e);
     for (int b = 0; b < 4; b++)
         if (ctx->ev_piece[b]) cudaEventDestroy(ctx->ev_piece[b]);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
@@ -1433,11 +1470,48 @@ static int32_t append_impl(fmlk_ctx *ctx, const double *rows, int64_t n, int32_t
     if (n == 0) return FMLK_OK;
     if (!rows) return fail(ctx, FMLK_ERR_INVALID_ARG, "rows is null");
     ctx->d = d;
+    if ((rc = settle_pending(ctx))) return rc;
     double *dst = nullptr;
     if ((rc = grow_points(ctx, n, &dst))) return rc;
     CK(ctx, cudaMemcpyAsync(dst, rows, (size_t)n * d * sizeof(double), kind, ctx->stream));
     // the caller may reuse its buffer as soon as we return (Flink object reuse)
     CK(ctx, cudaStreamSynchronize(ctx->stream));
+    return FMLK_OK;
+}
+
+int32_t fmlk_append_points_async(fmlk_ctx *ctx, const double *rows_host_pinned, int64_t n, int32_t d) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    // only page-locked memory can be copied behind the caller's back; anything else takes the synchronous path
+    cudaPointerAttributes attr{};
+    const bool pinned = rows_host_pinned && cudaPointerGetAttributes(&attr, rows_host_pinned) == cudaSuccess &&
+                        attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    if (!pinned || n <= 0) return append_impl(ctx, rows_host_pinned, n, d, cudaMemcpyHostToDevice);
+    if ((rc = check_dim(ctx, d))) return rc;
+    ctx->d = d;
+    if ((rc = settle_pending(ctx))) return rc;
+    double *dst = nullptr;
+    if ((rc = grow_points(ctx, n, &dst))) return rc;
+    if (!ctx->copy_stream) CK(ctx, cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    const int64_t piece = std::max<int64_t>(2, (((int64_t)64 << 20) / ((int64_t)d * 8)) & ~(int64_t)1); // 64 MB, even rows
+    const size_t pieces = (size_t)((n + piece - 1) / piece);
+    while (ctx->pending_events.size() < pieces) {
+        cudaEvent_t e;
+        CK(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        ctx->pending_events.push_back(e);
+    }
+    ctx->pending_chunk = (int)ctx->chunks.size() - 1;
+    ctx->pending_row0 = ctx->chunks.back().rows - n;
+    for (size_t i = 0; i < pieces; i++) {
+        const int64_t off = (int64_t)i * piece, m = std::min(piece, n - off);
+        CK(ctx, cudaMemcpyAsync(dst + off * d, rows_host_pinned + off * d, (size_t)m * d * sizeof(double), cudaMemcpyHostToDevice,
+                                ctx->copy_stream));
+        CK(ctx, cudaEventRecord(ctx->pending_events[i], ctx->copy_stream));
+        ctx->pending.push_back(fmlk_ctx::PendingPiece{dst + off * d, m, ctx->pending_events[i]});
+    }
     return FMLK_OK;
 }
 
@@ -1493,6 +1567,7 @@ int32_t fmlk_append_points_serialized(fmlk_ctx *ctx, const uint8_t *records_host
     DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
+    if ((rc = settle_pending(ctx))) return rc;
     int hdr = 0;
     int64_t rec = 0;
     if ((rc = record_layout(ctx, format, d, &hdr, &rec))) return rc;
@@ -1617,6 +1692,7 @@ int32_t fmlk_clear_points(fmlk_ctx *ctx) {
     DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
+    if ((rc = settle_pending(ctx))) return rc;
     CK(ctx, cudaStreamSynchronize(ctx->stream));
     for (Chunk &c : ctx->chunks) {
         if (!c.owned) continue;
@@ -1807,6 +1883,7 @@ int32_t fmlk_predict_cached(fmlk_ctx *ctx, int32_t *out_labels_host) {
     DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
+    if ((rc = settle_pending(ctx))) return rc;
     if ((rc = need_model(ctx))) return rc;
     if (ctx->n_total == 0) return FMLK_OK;
     if (ctx->d != ctx->md) return fail(ctx, FMLK_ERR_DIM, "Vector size mismatched.");
@@ -2154,6 +2231,7 @@ int32_t fmlk_get_points(fmlk_ctx *ctx, const int64_t *row_ids, int32_t m, double
     DeviceScope device_scope;
     int rc = use_device(ctx);
     if (rc) return rc;
+    if ((rc = settle_pending(ctx))) return rc;
     if (m < 0 || (m > 0 && (!row_ids || !out_rows_host))) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad row ids");
     if (m == 0) return FMLK_OK;
     // resolve every id to its device address on the host, gather on the device, one copy back

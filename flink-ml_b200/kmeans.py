@@ -403,7 +403,7 @@ class KMeansModel(_KMeansModelParams):
 # ------------------------------------------------------------------------------------------
 # KMeans
 
-def select_random_centroids(ctx, cluster, k, seed, ids=None):
+def select_random_centroids(ctx, cluster, k, seed, ids=None, host_rows=None):
     """KMeans.selectRandomCentroids (KMeans.java:310-327) = DataStreamUtils.sample
     (DataStreamUtils.java:212-227) over the points already in the contexts' caches: a reservoir
     per subtask from Random(seed), then one reservoir from a fresh Random(seed) over the
@@ -411,7 +411,11 @@ def select_random_centroids(ctx, cluster, k, seed, ids=None):
     caller has computed them already (they depend only on the row count)."""
     if ids is None:
         ids = native.reservoir(ctx.num_points(), k, seed)
-    mine = ctx.get_points(ids) if ids.size else np.empty((0, max(ctx.d, 0)))
+    if host_rows is not None:
+        # the subtask's rows are still at hand on the host (and may still be on their way to the device): pick there
+        mine = np.ascontiguousarray(host_rows[ids]) if ids.size else np.empty((0, host_rows.shape[1]))
+    else:
+        mine = ctx.get_points(ids) if ids.size else np.empty((0, max(ctx.d, 0)))
     if cluster.world == 1:
         return mine  # the second stage sees <= k elements and passes them through
     stage1 = [p for p in cluster.all_gather_object(mine) if p.shape[0]]
@@ -460,17 +464,18 @@ class KMeans(_KMeansModelParams, _HasSeed):
         # run it while the rows are copied to the device
         with ThreadPoolExecutor(max_workers=1) as pool:
             ids_future = pool.submit(native.reservoir, points.shape[0], self.get_k(), self.get_seed())
-            ctx.append_points(points)
+            # page-locked rows are copied behind the call and the first round overlaps the copy (pageable ones: as before)
+            ctx.append_points_async(points)
             ids = ids_future.result()
-        md = self._fit_cached(ctx, cluster, ids)
+        md = self._fit_cached(ctx, cluster, ids, host_rows=points)
         ctx.clear_points()  # onIterationTerminated, KMeans.java:302-307
         model = KMeansModel(cluster).set_model_data(md.to_table())
         self._copy_params_to(model)
         return model
 
-    def _fit_cached(self, ctx, cluster, ids=None):
+    def _fit_cached(self, ctx, cluster, ids=None, host_rows=None):
         """The part of fit() after ingestion: initial centroids, maxIter rounds, model data."""
-        init = select_random_centroids(ctx, cluster, self.get_k(), self.get_seed(), ids)
+        init = select_random_centroids(ctx, cluster, self.get_k(), self.get_seed(), ids, host_rows)
         if init.shape[0] == 0:
             raise IllegalStateError("no input points")
         ctx.set_centroids(init)

@@ -51,6 +51,7 @@ SIGNATURES = {
     "fmlk_reserve_points": (_i32, [_vp, _i64, _i32]),
     "fmlk_append_points": (_i32, [_vp, _vp, _i64, _i32]),
     "fmlk_append_points_dev": (_i32, [_vp, _vp, _i64, _i32]),
+    "fmlk_append_points_async": (_i32, [_vp, _vp, _i64, _i32]),
     "fmlk_append_points_serialized": (_i32, [_vp, _vp, _i64, _i32, _i32, C.POINTER(_i64)]),
     "fmlk_decode_rows_dev": (_i32, [_i32, _vp, _vp, _i64, _i32, _i32, _vp, _vp]),
     "fmlk_all_reduce_sum": (_i32, [_vp, _vp, _i64]),
@@ -220,6 +221,17 @@ class Context:
         if n:
             self.d = d
 
+    def append_points_async(self, rows):
+        """Page-locked host rows (e.g. the numpy view of a pinned torch tensor): the copy runs behind the call and the
+        first training round overlaps it; pageable memory is copied synchronously.  The array is kept alive here until
+        the cache is cleared."""
+        rows = _f64_matrix(rows)
+        n, d = rows.shape
+        self._ck(lib().fmlk_append_points_async(self._h, rows.ctypes.data, n, d))
+        if n:
+            self.d = d
+            self._async_keep = getattr(self, "_async_keep", []) + [rows]
+
     def append_points_ptr(self, host_ptr, n, d):
         """Host rows given as a raw address (e.g. a pinned torch tensor's data_ptr())."""
         self._ck(lib().fmlk_append_points(self._h, host_ptr, int(n), int(d)))
@@ -254,6 +266,7 @@ class Context:
     def clear_points(self):
         self._ck(lib().fmlk_clear_points(self._h))
         self._keep = []
+        self._async_keep = []
         self.d = 0
 
     def num_points(self):

@@ -92,6 +92,14 @@ int32_t fmlk_reserve_points(fmlk_ctx *ctx, int64_t n_rows, int32_t d);
  * into HBM, where they stay for every round.  d must match earlier appends (FMLK_ERR_DIM). */
 int32_t fmlk_append_points(fmlk_ctx *ctx, const double *rows_host, int64_t n, int32_t d);
 
+/* The same append for PAGE-LOCKED host rows, without waiting for the copy: it runs on a second stream in 64 MB
+ * pieces, and the first training round that follows labels each piece as it arrives (the host link and round 1
+ * overlap); every other use of the cache waits for the last piece on the device.  The caller keeps rows_host_pinned
+ * alive and unchanged until a call on this context that returns results (fmlk_fit, fmlk_train_round,
+ * fmlk_local_partials, fmlk_predict_cached, fmlk_get_points, fmlk_clear_points) has returned.  Memory that is not
+ * page-locked (cudaHostAlloc / cudaHostRegister) takes the synchronous path of fmlk_append_points. */
+int32_t fmlk_append_points_async(fmlk_ctx *ctx, const double *rows_host_pinned, int64_t n, int32_t d);
+
 /* Same with the rows already on this context's device (device-to-device copy). */
 int32_t fmlk_append_points_dev(fmlk_ctx *ctx, const double *rows_dev, int64_t n, int32_t d);
 

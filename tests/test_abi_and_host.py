@@ -212,6 +212,7 @@ def test_rows_on_task_matches_row_generator():
 NOT_BOUND_FROM_THE_JVM = {
     "fmlk_last_error": "read by the shim itself when it throws",
     "fmlk_append_points_dev": "device pointers: the harness' way of keeping H2D out of a timing",
+    "fmlk_append_points_async": "needs page-locked host memory that stays put: a JVM operator copies rows out of reused objects",
     "fmlk_adopt_points_dev": "device pointers (harness)",
     "fmlk_predict_dev": "device pointers (harness)",
     "fmlk_knn_predict_dev": "device pointers (harness)",

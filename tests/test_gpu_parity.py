@@ -456,6 +456,59 @@ def test_rows_that_are_only_8_byte_aligned(d, k, flags):
     assert np.allclose(sums, o_sums, rtol=SUM_RTOL, atol=0)
 
 
+def test_async_append_of_page_locked_rows():
+    """fmlk_append_points_async: the copy runs behind the call, the first training round labels the pieces as they
+    arrive, every other consumer of the cache waits for the last piece; pageable memory takes the synchronous path."""
+    import torch
+    n, d, k = 3_000_001, 64, 50   # 1.5 GB: 23 pieces of 64 MB
+    host = torch.empty((n, d), dtype=torch.float64, pin_memory=True)
+    dev = torch.empty((n, d), dtype=torch.float64, device="cuda:0")
+    native.generate_dense_dev(0, torch.cuda.current_stream().cuda_stream, 2, 0, 1, n, d, dev.data_ptr())
+    host.copy_(dev)
+    torch.cuda.synchronize()
+    del dev
+    x = host.numpy()
+    cent = x[:k].copy()
+    o_sums, o_counts, o_labels = O.train_local(x[:200_000], cent, want_labels=True)
+    with native.Context(0) as c:
+        # (1) training straight behind the copy
+        c.append_points_async(x)
+        c.set_centroids(cent)
+        sums, counts = c.local_partials()
+        assert int(counts.sum()) == n
+        labels = c.predict_cached()
+        assert np.array_equal(np.bincount(labels, minlength=k), counts)
+        assert np.array_equal(labels[:200_000], o_labels)
+        fit_c, fit_w = c.fit(3)
+        c.clear_points()
+        # (2) a consumer that is not a training round right after the call: it must see every row
+        c.set_centroids(cent)
+        c.append_points_async(x)
+        assert np.array_equal(c.predict_cached(), labels)
+        ids = np.array([0, n - 1, n // 2], dtype=np.int64)
+        assert np.array_equal(c.get_points(ids), x[ids])
+        c.clear_points()
+        # (3) two asynchronous appends and a synchronous one in between; then a whole fit
+        half = n // 2 + 1
+        c.append_points_async(x[:half])
+        c.append_points(x[half:half + 1000])
+        c.append_points_async(x[half + 1000:])
+        c.set_centroids(cent)
+        s3, c3 = c.local_partials()
+        assert np.array_equal(c3, counts) and np.allclose(s3, sums, rtol=SUM_RTOL, atol=0)
+        c.set_centroids(cent)
+        fit_c3, fit_w3 = c.fit(3)
+        assert np.array_equal(fit_w3, fit_w) and np.allclose(fit_c3, fit_c, rtol=CENTROID_RTOL, atol=0)
+        c.clear_points()
+        # (4) pageable memory: same answer through the synchronous path
+        small = np.array(x[:50_000], copy=True)
+        c.append_points_async(small)
+        c.set_centroids(cent)
+        s4, c4 = c.local_partials()
+        o4_sums, o4_counts = O.train_local(small, cent)
+        assert np.array_equal(c4, o4_counts.astype(np.int64)) and np.allclose(s4, o4_sums, rtol=SUM_RTOL, atol=0)
+
+
 def test_fp64_peaks_are_plausible():
     dmma, dfma = native.measure_fp64_peaks(0, 50.0)
     assert 5.0 < dmma < 100.0 and 5.0 < dfma < 100.0
