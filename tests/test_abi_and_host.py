@@ -42,6 +42,35 @@ def test_library_has_no_oracle_or_torch_dependency():
     assert "oracle" not in out and "torch" not in out and "nccl" not in out  # NCCL is dlopen'ed when world > 1
 
 
+def test_nccl_loader_is_safe_to_race():
+    """Sibling subtasks of one task manager call fmlk_nccl_unique_id / fmlk_create(world > 1) together at open(): the
+    lazy loader of libnccl must give every thread the same, complete answer (it is a function-local static)."""
+    import ctypes as C
+    import threading
+    L = native.lib()
+    results = [None] * 16
+    start = threading.Barrier(16)
+
+    def worker(i):
+        buf = (C.c_uint8 * native.NCCL_ID_BYTES)()
+        start.wait()
+        rc = L.fmlk_nccl_unique_id(buf)
+        msg = L.fmlk_last_error(None)
+        results[i] = (rc, (msg or b"").decode())
+
+    threads = [threading.Thread(target=worker, args=(i,)) for i in range(16)]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    codes = {rc for rc, _ in results}
+    assert len(codes) == 1, results
+    rc = codes.pop()
+    if rc != 0:  # no usable NCCL / no GPU here: every thread must say why
+        assert rc in (native.ERR_NCCL, native.ERR_CUDA)
+        assert all(msg for _, msg in results), results
+
+
 def test_no_cpu_fallback_without_gpu():
     import torch
     if torch.cuda.is_available():
