@@ -44,7 +44,12 @@
 //                    test and the label.  Training: sixteen lanes of each warp issue one
 //                    cp.reduce.async.bulk add.f64 per decided row -- the TMA engine adds the FP64 row,
 //                    still in its half stage, to sums[label] of the CTA's accumulator in global memory
-//                    (the additions happen in L2) -- and the half stage is refilled once they have been read
+//                    (the additions happen in L2) -- and the half stage is refilled once they have been read.
+//                    With streamed centroid terms (P > 1) the epilogue is the busiest role and the converter
+//                    warps issue the reductions instead: the labels go to them through a double-buffered
+//                    array and two mbarriers (LAB_FULL / LAB_EMPTY).  With few centroids (Nacc <= 16) the
+//                    warps add into four accumulators per CTA (folded at the end), not one: additions of
+//                    eight warps into the same ten rows queue in L2
 // (Keeping the sums in shared memory and re-reading the decided rows from L2 was built and measured: rows
 // that arrived by bulk copy are not in L2 afterwards -- 6 % hit rate, DRAM traffic x 1.9, with or without an
 // evict-last hint or an explicit L2 prefetch -- so the rows have to be added while they are in shared memory.)
