@@ -6,12 +6,15 @@
 //                      LIB/clustering/kmeans/KMeans.java:291-295 with
 //                      CORE/common/distance/EuclideanDistanceMeasure.java:41-73;
 //                      also PredictLabelFunction.map, LIB/clustering/kmeans/KMeansModel.java:129-144
-//   assign_wide_kernel the same, blocked along d (d >= 128, streamed centroids with d % 32 == 0, any d
-//                      the whole-row tiles cannot hold)
+//   assign_wide_kernel the same, blocked along d (any d the whole-row tiles cannot hold; d > 128)
+//                      (fmlk_ring.cuh: its barrier-free variant for d <= 128, the north-star shapes;
+//                       fmlk_small.cuh: short rows against few centroids, one row per thread;
+//                       fmlk_fast.cuh: the tcgen05 fast mode)
 //   decode_records_*   DenseVectorSerializer / VectorWithNormSerializer.deserialize on the ingest path
 //   prep_centroids     new VectorWithNorm(centroid), KMeans.java:279-282
 //   reduce_partials    CentroidsUpdateReducer, KMeans.java:185-198 (within one GPU)
 //   finalize_centroids ModelDataGenerator, KMeans.java:200-212
+//   round_tail         the three above in one launch (one GPU): reduce, finalise, prepare the next round
 //   online_update      ModelDataLocalUpdater, LIB/clustering/kmeans/OnlineKMeans.java:309-322
 //   online_merge       ModelDataGlobalReducer, OnlineKMeans.java:188-211
 //   generate_dense     DenseVectorGenerator / java.util.Random (benchmark data)
