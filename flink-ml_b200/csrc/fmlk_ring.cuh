@@ -24,7 +24,7 @@ constexpr int kRingStages = 4;
 constexpr int kRingBlockElems = 8 * kChunkTiles * kWideS; // 64 centroids x 36 doubles
 // SPLIT = 1 (d <= 64): 256 rows per CTA tile, warp w owns rows 16 w .. 16 w + 15 and all 64 centroids of a chunk.
 // SPLIT = 2 (d <= 128): 128 rows per CTA tile (as many as fit beside the ring); warps w and w + 8 share rows
-//   16 w .. 16 w + 15 and take centroids 0..31 and 32..63 of every chunk, so the SM still runs 16 warps; the pair's
+//   16 w .. 16 w + 15 and take one half each of the n8 tiles of every chunk, so the SM still runs 16 warps; the pair's
 //   two (best, second, index) meet in shared memory at the end of the tile and warp w finishes the rows.
 template <int SPLIT>
 struct RingShape {
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(kRingWarps * 32, 1) assign_ring_kernel(const A
     int *mrg = done + kRingStages;                                           // SPLIT 2: [8 pairs][16 rows][best, second, idx]
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int rw = SPLIT == 1 ? warp : (warp & 7);   // which 16 rows of the CTA tile
-    const int half = SPLIT == 1 ? 0 : (warp >> 3);   // which 32 centroids of every chunk
+    const int half = SPLIT == 1 ? 0 : (warp >> 3);   // which half of every chunk's n8 tiles
     constexpr int kMyTiles = kChunkTiles / SPLIT;    // n8 tiles of a chunk this warp multiplies
     const int frow = lane >> 2, fk = lane & 3;
     const int cmax2_exp = (int)p.cmax2[1];
@@ -127,8 +127,12 @@ __global__ void __launch_bounds__(kRingWarps * 32, 1) assign_ring_kernel(const A
             const int ch = s / nkb, kbi = s - ch * nkb;
             const int ch0 = ch * 8 * kChunkTiles;
             const int cnt_all = min(kChunkTiles, (p.k_pad - ch0) >> 3);
-            const int cnt = SPLIT == 1 ? cnt_all : (half == 0 ? min(cnt_all, kMyTiles) : max(cnt_all - kMyTiles, 0));
-            const int col0 = ch0 + half * kMyTiles * 8 + fk * 2;
+            // SPLIT 2: the pair shares the chunk's tiles evenly, the odd one to warp w + 8 (warp w also finishes the rows);
+            // a short last chunk then costs the pair half of what is there, not the first warp all of it
+            const int cnt_lo = (ch == 0 && cnt_all == 1) ? 1 : cnt_all >> 1; // (warp w needs a block of chunk 0 for its |x| bound)
+            const int cnt = SPLIT == 1 ? cnt_all : (half == 0 ? cnt_lo : cnt_all - cnt_lo);
+            const int tile0 = SPLIT == 1 ? 0 : half * cnt_lo; // first n8 tile of the chunk this warp multiplies
+            const int col0 = ch0 + tile0 * 8 + fk * 2;
             if (kbi == 0) {
 #pragma unroll
                 for (int j = 0; j < kMyTiles; j++) {
@@ -142,7 +146,7 @@ __global__ void __launch_bounds__(kRingWarps * 32, 1) assign_ring_kernel(const A
             mbar_wait(full_bar(st), (unsigned)((g / kRingStages) & 1));
             {
                 const double *Xb = Xs + (size_t)rw * kWarpRows * kXS + kbi * kWideDk;
-                const double *Cb = ring + (size_t)st * kRingBlockElems + (size_t)half * kMyTiles * 8 * kWideS;
+                const double *Cb = ring + (size_t)st * kRingBlockElems + (size_t)tile0 * 8 * kWideS;
                 const bool nsq = ch == 0; // the |x| bound rides along with the first chunk
                 switch (cnt) {
                     case 8: if (SPLIT == 1) wide_block<8>(Xb, kXS, Cb, frow, fk, acc0, acc1, mx0, mx1, nsq); break;

@@ -138,6 +138,8 @@ SHAPES = [
     (9000, 96, 600),     # ring kernel, warp pairs split each chunk, three column blocks, ragged row tile
     (7001, 32, 700),     # ring kernel, one column block, last chunk of 60
     (5000, 128, 192),    # ring kernel, exactly three chunks
+    (4000, 128, 100),    # ring kernel, warp pairs: a last chunk of five n8 tiles shared two / three
+    (3000, 128, 72),     # ring kernel, warp pairs: a last chunk of one n8 tile (the second warp's alone)
     # extremes of the tiling
     (1500, 1000, 7),     # long rows: few MMA warps fit, several columns per accumulator lane
     (600, 1531, 3),      # odd d close to the shared-memory limit of one row tile + centroids
