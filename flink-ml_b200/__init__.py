@@ -11,7 +11,11 @@ from flink_ml_b200.kmeans import (  # noqa: F401
     KMeans, KMeansModel, KMeansModelData, OnlineKMeans, OnlineKMeansModel,
 )
 from flink_ml_b200.knn import Knn, KnnModel, KnnModelData  # noqa: F401
+from flink_ml_b200.linear import (  # noqa: F401
+    LinearRegression, LinearRegressionModel, LinearSVC, LinearSVCModel, LogisticRegression, LogisticRegressionModel,
+)
 from flink_ml_b200 import native  # noqa: F401
 
 __all__ = ["DenseVector", "SparseVector", "Vectors", "Table", "KMeans", "KMeansModel", "KMeansModelData",
-           "OnlineKMeans", "OnlineKMeansModel", "Knn", "KnnModel", "KnnModelData", "native"]
+           "OnlineKMeans", "OnlineKMeansModel", "Knn", "KnnModel", "KnnModelData", "LogisticRegression", "LogisticRegressionModel", "LinearSVC",
+           "LinearSVCModel", "LinearRegression", "LinearRegressionModel", "native"]

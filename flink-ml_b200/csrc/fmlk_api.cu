@@ -9,6 +9,7 @@
 #include "fmlk_knn.cuh"
 #include "fmlk_ring.cuh"
 #include "fmlk_small.cuh"
+#include "fmlk_sgd.cuh"
 
 #include <dlfcn.h>
 #include <algorithm>
@@ -218,6 +219,18 @@ struct fmlk_ctx {
     double *knn_out = nullptr; // predictions of the rows of a call
     size_t knn_out_cap = 0;
     int32_t *knn_status = nullptr;
+
+    // SGD (fmlk_sgd_set_data): the subtask's training cache, and the optimizer's buffers
+    double *sgd_x = nullptr, *sgd_y = nullptr, *sgd_w = nullptr; // sgd_w null: every weight 1.0
+    bool sgd_owned = false, sgd_set = false;
+    int64_t sgd_n = 0;
+    int32_t sgd_d = 0;
+    double *sgd_coef = nullptr, *sgd_feedback = nullptr, *sgd_partials = nullptr;
+    size_t sgd_coef_cap = 0, sgd_feedback_cap = 0, sgd_partials_cap = 0;
+    fmlk::SgdState *sgd_state = nullptr;
+    // fmlk_linear_predict: staged rows, coefficient and outputs
+    double *lin_rows = nullptr, *lin_coef = nullptr, *lin_out = nullptr;
+    size_t lin_rows_cap = 0, lin_coef_cap = 0, lin_out_cap = 0;
 
     // profile
     std::vector<cudaEvent_t> ev_pool;
@@ -1404,6 +1417,18 @@ void fmlk_destroy(fmlk_ctx *ctx) {
     dev_free(ctx->knn_labels);
     dev_free(ctx->knn_out);
     dev_free(ctx->knn_status);
+    if (ctx->sgd_owned) {
+        dev_free(ctx->sgd_x);
+        dev_free(ctx->sgd_y);
+        dev_free(ctx->sgd_w);
+    }
+    dev_free(ctx->sgd_coef);
+    dev_free(ctx->sgd_feedback);
+    dev_free(ctx->sgd_partials);
+    dev_free(ctx->sgd_state);
+    dev_free(ctx->lin_rows);
+    dev_free(ctx->lin_coef);
+    dev_free(ctx->lin_out);
     if (ctx->pinned_labels) cudaFreeHost(ctx->pinned_labels);
     for (int b = 0; b < 2; b++) {
         if (ctx->ev_labels[b]) cudaEventDestroy(ctx->ev_labels[b]);
@@ -2154,6 +2179,245 @@ int32_t fmlk_knn_predict(fmlk_ctx *ctx, const double *rows_host, int64_t n, int3
     }
     CK(ctx, cudaStreamSynchronize(ctx->stream));
     return knn_status_check(ctx);
+}
+
+// ------------------------------------------------------------------------------------------------
+// SGD and the linear models (fmlk_sgd.cuh)
+
+namespace {
+
+void sgd_drop_data(fmlk_ctx *ctx) {
+    if (ctx->sgd_owned) {
+        dev_free(ctx->sgd_x);
+        dev_free(ctx->sgd_y);
+        dev_free(ctx->sgd_w);
+    }
+    ctx->sgd_x = ctx->sgd_y = ctx->sgd_w = nullptr;
+    ctx->sgd_owned = ctx->sgd_set = false;
+    ctx->sgd_n = 0;
+    ctx->sgd_d = 0;
+}
+
+// MMA-free kernels of fmlk_sgd.cuh: as many warps per CTA (8, 4, 2, 1) as shared memory allows for this d
+int sgd_warps_for(const fmlk_ctx *ctx, int d, bool with_grad) {
+    for (int w = fmlk::kSgdMaxWarps; w >= 1; w >>= 1)
+        if (fmlk::sgd_smem_bytes(d, w, with_grad) <= ctx->smem_optin) return w;
+    return 0;
+}
+
+int grow(fmlk_ctx *ctx, double **p, size_t *cap, size_t need) { // a device buffer of at least `need` doubles
+    if (*p && *cap >= need) return FMLK_OK;
+    dev_free(*p);
+    *p = nullptr;
+    *cap = 0;
+    int rc = dev_alloc(ctx, p, std::max<size_t>(need, 1));
+    if (rc) return rc;
+    *cap = std::max<size_t>(need, 1);
+    return FMLK_OK;
+}
+
+int linear_launch(fmlk_ctx *ctx, int kind, const double *rows_dev, int64_t n, int d, const double *coef_dev, double threshold,
+                  double *pred_dev, double *raw_dev) {
+    const int warps = sgd_warps_for(ctx, d, false);
+    if (warps == 0) return fail(ctx, FMLK_ERR_DIM, "d too large for the linear-model kernels");
+    const size_t smem = fmlk::sgd_smem_bytes(d, warps, false);
+    const int64_t groups = (n + 31) / 32;
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((groups + warps - 1) / warps, (int64_t)ctx->sm_count * 4));
+    const int fma = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
+#define FMLK_LINEAR(K)                                                                                                       \
+    {                                                                                                                        \
+        CK(ctx, cudaFuncSetAttribute(fmlk::linear_predict_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        fmlk::linear_predict_kernel<K><<<grid, warps * 32, smem, ctx->stream>>>(rows_dev, n, d, coef_dev, threshold, fma,    \
+                                                                                pred_dev, raw_dev);                          \
+    }
+    if (kind == FMLK_LOSS_LOGISTIC) FMLK_LINEAR(0)
+    else if (kind == FMLK_LOSS_HINGE) FMLK_LINEAR(1)
+    else FMLK_LINEAR(2)
+#undef FMLK_LINEAR
+    CK(ctx, cudaGetLastError());
+    ctx->total_launches++;
+    return FMLK_OK;
+}
+
+int linear_check(fmlk_ctx *ctx, int kind, const void *rows, int64_t n, int d, const double *coef, const void *pred) {
+    if (kind < FMLK_LOSS_LOGISTIC || kind > FMLK_LOSS_LEAST_SQUARE) return fail(ctx, FMLK_ERR_INVALID_ARG, "unknown model kind");
+    if (n < 0 || d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad n / d");
+    if (!coef) return fail(ctx, FMLK_ERR_INVALID_ARG, "coefficient is null");
+    if (n > 0 && (!rows || !pred)) return fail(ctx, FMLK_ERR_INVALID_ARG, "rows / out is null");
+    return FMLK_OK;
+}
+
+} // namespace
+
+int32_t fmlk_sgd_set_data(fmlk_ctx *ctx, const double *features_host, const double *labels_host,
+                          const double *weights_host_or_null, int64_t n, int32_t d) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if (n < 0 || d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad n / d");
+    if (n > 0 && (!features_host || !labels_host)) return fail(ctx, FMLK_ERR_INVALID_ARG, "training data is null");
+    sgd_drop_data(ctx);
+    ctx->sgd_owned = true;
+    const size_t nd = (size_t)n * d;
+    if ((rc = dev_alloc(ctx, &ctx->sgd_x, std::max<size_t>(nd, 1))) || (rc = dev_alloc(ctx, &ctx->sgd_y, std::max<size_t>(n, 1)))) {
+        sgd_drop_data(ctx);
+        return rc;
+    }
+    if (weights_host_or_null && (rc = dev_alloc(ctx, &ctx->sgd_w, std::max<size_t>(n, 1)))) {
+        sgd_drop_data(ctx);
+        return rc;
+    }
+    if (n > 0) {
+        CK(ctx, cudaMemcpyAsync(ctx->sgd_x, features_host, nd * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        CK(ctx, cudaMemcpyAsync(ctx->sgd_y, labels_host, (size_t)n * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+        if (weights_host_or_null)
+            CK(ctx, cudaMemcpyAsync(ctx->sgd_w, weights_host_or_null, (size_t)n * sizeof(double), cudaMemcpyHostToDevice,
+                                    ctx->stream));
+        CK(ctx, cudaStreamSynchronize(ctx->stream)); // the host buffers are the caller's again
+    }
+    ctx->sgd_n = n;
+    ctx->sgd_d = d;
+    ctx->sgd_set = true;
+    return FMLK_OK;
+}
+
+int32_t fmlk_sgd_set_data_dev(fmlk_ctx *ctx, const double *features_dev, const double *labels_dev,
+                              const double *weights_dev_or_null, int64_t n, int32_t d) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if (n < 0 || d <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "bad n / d");
+    if (n > 0 && (!features_dev || !labels_dev)) return fail(ctx, FMLK_ERR_INVALID_ARG, "training data is null");
+    sgd_drop_data(ctx);
+    ctx->sgd_x = const_cast<double *>(features_dev);
+    ctx->sgd_y = const_cast<double *>(labels_dev);
+    ctx->sgd_w = const_cast<double *>(weights_dev_or_null);
+    ctx->sgd_n = n;
+    ctx->sgd_d = d;
+    ctx->sgd_set = true;
+    return FMLK_OK;
+}
+
+int32_t fmlk_sgd_fit(fmlk_ctx *ctx, int32_t loss, int32_t max_iter, double learning_rate, int32_t global_batch_size,
+                     double tol, double reg, double elastic_net, double *out_coefficient_host, int32_t *out_epochs,
+                     double *out_last_loss) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    // everything that can fail locally is checked before the first collective is enqueued (symmetric across ranks)
+    if (!ctx->sgd_set) return fail(ctx, FMLK_ERR_STATE, "no training data: call fmlk_sgd_set_data first");
+    if (loss < FMLK_LOSS_LOGISTIC || loss > FMLK_LOSS_LEAST_SQUARE) return fail(ctx, FMLK_ERR_INVALID_ARG, "unknown loss");
+    if (max_iter <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "maxIter must be > 0");
+    if (global_batch_size <= 0) return fail(ctx, FMLK_ERR_INVALID_ARG, "globalBatchSize must be > 0");
+    if (!(learning_rate > 0)) return fail(ctx, FMLK_ERR_INVALID_ARG, "learningRate must be > 0");
+    if (!(tol >= 0) || !(reg >= 0) || !(elastic_net >= 0 && elastic_net <= 1))
+        return fail(ctx, FMLK_ERR_INVALID_ARG, "tol >= 0, reg >= 0 and 0 <= elasticNet <= 1 are required");
+    if (!out_coefficient_host) return fail(ctx, FMLK_ERR_INVALID_ARG, "out_coefficient_host is null");
+    const int d = ctx->sgd_d;
+    const int64_t n = ctx->sgd_n;
+    const int warps = sgd_warps_for(ctx, d, true);
+    if (warps == 0) return fail(ctx, FMLK_ERR_DIM, "d too large for the SGD kernel's shared-memory gradient");
+    const size_t smem = fmlk::sgd_smem_bytes(d, warps, true);
+    const int64_t local_batch = global_batch_size / ctx->world + (global_batch_size % ctx->world > ctx->rank ? 1 : 0);
+    const int64_t groups_max = (std::min<int64_t>(local_batch, n) + 31) / 32;
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((groups_max + warps - 1) / warps, (int64_t)ctx->sm_count * 2));
+    if ((rc = grow(ctx, &ctx->sgd_coef, &ctx->sgd_coef_cap, (size_t)d))) return rc;
+    if ((rc = grow(ctx, &ctx->sgd_feedback, &ctx->sgd_feedback_cap, (size_t)d + 2))) return rc;
+    if ((rc = grow(ctx, &ctx->sgd_partials, &ctx->sgd_partials_cap, (size_t)grid * (d + 2)))) return rc;
+    if (!ctx->sgd_state && (rc = dev_alloc(ctx, &ctx->sgd_state, 1))) return rc;
+    CK(ctx, cudaMemsetAsync(ctx->sgd_coef, 0, (size_t)d * sizeof(double), ctx->stream)); // new DenseVector(dim)
+    CK(ctx, cudaMemsetAsync(ctx->sgd_state, 0, sizeof(fmlk::SgdState), ctx->stream));
+    if (loss == FMLK_LOSS_LOGISTIC)
+        CK(ctx, cudaFuncSetAttribute(fmlk::sgd_batch_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else if (loss == FMLK_LOSS_HINGE)
+        CK(ctx, cudaFuncSetAttribute(fmlk::sgd_batch_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else
+        CK(ctx, cudaFuncSetAttribute(fmlk::sgd_batch_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    fmlk::SgdBatchParams p{};
+    p.x = ctx->sgd_x;
+    p.labels = ctx->sgd_y;
+    p.weights = ctx->sgd_w;
+    p.d = d;
+    p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
+    p.coef = ctx->sgd_coef;
+    p.partials = ctx->sgd_partials;
+    p.feedback = ctx->sgd_feedback;
+    p.state = ctx->sgd_state;
+    int64_t offset = 0; // nextBatchOffset (SGD.java:181)
+    for (int epoch = 0; epoch < max_iter; epoch++) {
+        p.begin = offset;
+        p.end = std::min<int64_t>(offset + local_batch, n);
+        offset += local_batch;
+        if (offset >= n) offset = 0;
+        if (loss == FMLK_LOSS_LOGISTIC) fmlk::sgd_batch_kernel<0><<<grid, warps * 32, smem, ctx->stream>>>(p);
+        else if (loss == FMLK_LOSS_HINGE) fmlk::sgd_batch_kernel<1><<<grid, warps * 32, smem, ctx->stream>>>(p);
+        else fmlk::sgd_batch_kernel<2><<<grid, warps * 32, smem, ctx->stream>>>(p);
+        CK(ctx, cudaGetLastError());
+        if (ctx->world > 1)
+            CKN(ctx, nccl().AllReduce(ctx->sgd_feedback, ctx->sgd_feedback, (size_t)d + 2, ncclFloat64, ncclSum, ctx->comm, ctx->stream));
+        fmlk::sgd_update_kernel<<<1, 256, 0, ctx->stream>>>(ctx->sgd_coef, ctx->sgd_feedback, d, learning_rate, reg, elastic_net, max_iter,
+                                                           tol, p.fma_mode, ctx->sgd_state);
+        CK(ctx, cudaGetLastError());
+        ctx->total_launches += 2;
+    }
+    fmlk::SgdState st{};
+    CK(ctx, cudaMemcpyAsync(out_coefficient_host, ctx->sgd_coef, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(ctx, cudaMemcpyAsync(&st, ctx->sgd_state, sizeof(st), cudaMemcpyDeviceToHost, ctx->stream));
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    if (out_epochs) *out_epochs = st.epochs;
+    if (out_last_loss) *out_last_loss = st.last_loss;
+    return FMLK_OK;
+}
+
+int32_t fmlk_linear_predict_dev(fmlk_ctx *ctx, int32_t kind, const double *rows_dev, int64_t n, int32_t d,
+                                const double *coefficient_host, double threshold, double *out_prediction_dev,
+                                double *out_raw_dev_or_null) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = linear_check(ctx, kind, rows_dev, n, d, coefficient_host, out_prediction_dev))) return rc;
+    if (n == 0) return FMLK_OK;
+    if ((rc = grow(ctx, &ctx->lin_coef, &ctx->lin_coef_cap, (size_t)d))) return rc;
+    CK(ctx, cudaMemcpyAsync(ctx->lin_coef, coefficient_host, (size_t)d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    if ((rc = linear_launch(ctx, kind, rows_dev, n, d, ctx->lin_coef, threshold, out_prediction_dev, out_raw_dev_or_null))) return rc;
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    return FMLK_OK;
+}
+
+int32_t fmlk_linear_predict(fmlk_ctx *ctx, int32_t kind, const double *rows_host, int64_t n, int32_t d,
+                            const double *coefficient_host, double threshold, double *out_prediction_host,
+                            double *out_raw_host_or_null) {
+    if (!ctx) return FMLK_ERR_INVALID_ARG;
+    DeviceScope device_scope;
+    int rc = use_device(ctx);
+    if (rc) return rc;
+    if ((rc = linear_check(ctx, kind, rows_host, n, d, coefficient_host, out_prediction_host))) return rc;
+    if (n == 0) return FMLK_OK;
+    const bool want_raw = out_raw_host_or_null && kind != FMLK_LOSS_LEAST_SQUARE;
+    // in pieces of at most 64 MB of rows, so that the staging buffers stay small for any n
+    const int64_t piece = std::max<int64_t>(1, ((int64_t)64 << 20) / ((int64_t)d * 8));
+    if ((rc = grow(ctx, &ctx->lin_coef, &ctx->lin_coef_cap, (size_t)d))) return rc;
+    if ((rc = grow(ctx, &ctx->lin_rows, &ctx->lin_rows_cap, (size_t)std::min(piece, n) * d))) return rc;
+    if ((rc = grow(ctx, &ctx->lin_out, &ctx->lin_out_cap, (size_t)std::min(piece, n) * 3))) return rc;
+    CK(ctx, cudaMemcpyAsync(ctx->lin_coef, coefficient_host, (size_t)d * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    for (int64_t off = 0; off < n; off += piece) {
+        const int64_t rows = std::min(piece, n - off);
+        CK(ctx, cudaMemcpyAsync(ctx->lin_rows, rows_host + off * d, (size_t)rows * d * sizeof(double), cudaMemcpyHostToDevice,
+                                ctx->stream));
+        double *raw_dev = want_raw ? ctx->lin_out + rows : nullptr;
+        if ((rc = linear_launch(ctx, kind, ctx->lin_rows, rows, d, ctx->lin_coef, threshold, ctx->lin_out, raw_dev))) return rc;
+        CK(ctx, cudaMemcpyAsync(out_prediction_host + off, ctx->lin_out, (size_t)rows * sizeof(double), cudaMemcpyDeviceToHost,
+                                ctx->stream));
+        if (want_raw)
+            CK(ctx, cudaMemcpyAsync(out_raw_host_or_null + 2 * off, raw_dev, (size_t)rows * 2 * sizeof(double), cudaMemcpyDeviceToHost,
+                                    ctx->stream));
+    }
+    CK(ctx, cudaStreamSynchronize(ctx->stream));
+    return FMLK_OK;
 }
 
 int32_t fmlk_all_reduce_sum_dev(fmlk_ctx *ctx, double *values_dev_inout, int64_t len) {

@@ -20,6 +20,8 @@ FLAG_DETERMINISTIC = 0x4
 FLAG_FAST_TF32 = 0x8
 # record formats of the reference's serializers (include/fmlk.h)
 FMT_DENSE_VECTOR, FMT_VECTOR, FMT_VECTOR_WITH_NORM = 0, 1, 2
+# loss functions of the SGD optimizer = kinds of linear model (include/fmlk.h)
+LOSS_LOGISTIC, LOSS_HINGE, LOSS_LEAST_SQUARE = 0, 1, 2
 NCCL_ID_BYTES = 128
 
 
@@ -82,6 +84,11 @@ SIGNATURES = {
     "fmlk_knn_get_norm_squares": (_i32, [_vp, _vp]),
     "fmlk_knn_predict": (_i32, [_vp, _vp, _i64, _i32, _i32, _vp]),
     "fmlk_knn_predict_dev": (_i32, [_vp, _vp, _i64, _i32, _i32, _vp]),
+    "fmlk_sgd_set_data": (_i32, [_vp, _vp, _vp, _vp, _i64, _i32]),
+    "fmlk_sgd_set_data_dev": (_i32, [_vp, _vp, _vp, _vp, _i64, _i32]),
+    "fmlk_sgd_fit": (_i32, [_vp, _i32, _i32, _f64, _i32, _f64, _f64, _f64, _vp, _vp, _vp]),
+    "fmlk_linear_predict": (_i32, [_vp, _i32, _vp, _i64, _i32, _vp, _f64, _vp, _vp]),
+    "fmlk_linear_predict_dev": (_i32, [_vp, _i32, _vp, _i64, _i32, _vp, _f64, _vp, _vp]),
 }
 
 _lib = None
@@ -384,6 +391,59 @@ class Context:
 
     def knn_predict_dev(self, dev_ptr, n, d, k, out_dev_ptr):
         self._ck(lib().fmlk_knn_predict_dev(self._h, dev_ptr, int(n), int(d), int(k), out_dev_ptr))
+
+    # -- SGD and the linear models (LogisticRegression / LinearSVC / LinearRegression)
+    def sgd_set_data(self, features, labels, weights=None):
+        """The subtask's training cache to the device: n x d features, n labels, n weights (None: all 1.0)."""
+        f = np.ascontiguousarray(features, dtype=np.float64)
+        if f.ndim != 2 or f.shape[1] == 0:
+            raise IllegalArgumentError("features must be n x d with d > 0")
+        n, d = f.shape
+        lab = np.ascontiguousarray(labels, dtype=np.float64).reshape(-1)
+        if lab.size != n:
+            raise IllegalArgumentError("one label per row")
+        w = None
+        if weights is not None:
+            w = np.ascontiguousarray(weights, dtype=np.float64).reshape(-1)
+            if w.size != n:
+                raise IllegalArgumentError("one weight per row")
+        self._ck(lib().fmlk_sgd_set_data(self._h, f.ctypes.data if n else None, lab.ctypes.data if n else None,
+                                         w.ctypes.data if (w is not None and n) else None, n, d))
+        self._sgd_d = d
+
+    def sgd_set_data_dev(self, features_ptr, labels_ptr, weights_ptr, n, d, keep=None):
+        self._ck(lib().fmlk_sgd_set_data_dev(self._h, features_ptr, labels_ptr, weights_ptr, int(n), int(d)))
+        self._sgd_d = int(d)
+        self._sgd_keep = keep
+
+    def sgd_fit(self, loss, max_iter=20, learning_rate=0.1, global_batch_size=32, tol=1e-6, reg=0.0, elastic_net=0.0):
+        """SGD.optimize from the zero vector; returns (coefficient, epochs run, totalLoss / totalWeight of the last epoch)."""
+        coef = np.empty(max(getattr(self, "_sgd_d", 0), 1), dtype=np.float64)[:getattr(self, "_sgd_d", 0)]
+        epochs = C.c_int32(0)
+        last = C.c_double(0.0)
+        self._ck(lib().fmlk_sgd_fit(self._h, int(loss), int(max_iter), float(learning_rate), int(global_batch_size), float(tol),
+                                    float(reg), float(elastic_net), coef.ctypes.data, C.addressof(epochs), C.addressof(last)))
+        return coef, int(epochs.value), float(last.value)
+
+    def linear_predict(self, kind, rows, coefficient, threshold=0.0):
+        """predictOneDataPoint of the model `kind` for every row: (prediction, raw n x 2 or None)."""
+        rows = np.ascontiguousarray(rows, dtype=np.float64)
+        if rows.ndim != 2:
+            raise IllegalArgumentError("rows must be n x d")
+        n, d = rows.shape
+        coef = np.ascontiguousarray(coefficient, dtype=np.float64).reshape(-1)
+        if coef.size != d:
+            raise IllegalArgumentError("Vector size mismatched.")
+        pred = np.empty(n, dtype=np.float64)
+        raw = np.empty((n, 2), dtype=np.float64) if kind != LOSS_LEAST_SQUARE else None
+        self._ck(lib().fmlk_linear_predict(self._h, int(kind), rows.ctypes.data if n else None, n, d, coef.ctypes.data, float(threshold),
+                                           pred.ctypes.data if n else None, raw.ctypes.data if (raw is not None and n) else None))
+        return pred, raw
+
+    def linear_predict_dev(self, kind, rows_ptr, n, d, coefficient, threshold, pred_ptr, raw_ptr=None):
+        coef = np.ascontiguousarray(coefficient, dtype=np.float64).reshape(-1)
+        self._ck(lib().fmlk_linear_predict_dev(self._h, int(kind), rows_ptr, int(n), int(d), coef.ctypes.data, float(threshold),
+                                               pred_ptr, raw_ptr))
 
     # -- DataStreamUtils.allReduceSum
     def all_reduce_sum(self, values):

@@ -258,6 +258,54 @@ int32_t fmlk_all_reduce_sum(fmlk_ctx *ctx, double *values_host_inout, int64_t le
  * equal lengths on all ranks (no check, no host synchronisation). */
 int32_t fmlk_all_reduce_sum_dev(fmlk_ctx *ctx, double *values_dev_inout, int64_t len);
 
+/* ---- SGD: allReduceSum's other caller -- the optimizer behind LogisticRegression, LinearSVC and
+ *      LinearRegression, on the same boundary: rows resident in HBM, one all-reduce per epoch
+ *      SGD.optimize / CacheDataAndDoTrain     LIB/common/optimizer/SGD.java:84-160,164-300
+ *      RegularizationUtils.regularize         LIB/common/optimizer/RegularizationUtils.java:49-91
+ *      BinaryLogisticLoss, HingeLoss, LeastSquareLoss     LIB/common/lossfunc/ (one file each)
+ *      TerminateOnMaxIterOrTol                CORE/common/iteration/TerminateOnMaxIterOrTol.java:62-67 ---- */
+#define FMLK_LOSS_LOGISTIC 0     /* BinaryLogisticLoss: labels 0 / 1 */
+#define FMLK_LOSS_HINGE 1        /* HingeLoss: labels 0 / 1 */
+#define FMLK_LOSS_LEAST_SQUARE 2 /* LeastSquareLoss */
+
+/* The subtask's training cache (CacheDataAndDoTrain.trainData, SGD.java:176,289-291): n LabeledPointWithWeight of
+ * dimension d -- features (n x d), labels (n), weights (n; NULL: every weight 1.0, LogisticRegression.java:72-76) --
+ * copied to HBM, where it stays until the next call or fmlk_destroy.  Replaces an earlier cache. */
+int32_t fmlk_sgd_set_data(fmlk_ctx *ctx, const double *features_host, const double *labels_host,
+                          const double *weights_host_or_null, int64_t n, int32_t d);
+/* Same for arrays already on the context's device, adopted without a copy (the caller keeps them alive). */
+int32_t fmlk_sgd_set_data_dev(fmlk_ctx *ctx, const double *features_dev, const double *labels_dev,
+                              const double *weights_dev_or_null, int64_t n, int32_t d);
+
+/* SGD.optimize from the zero vector (LogisticRegression.java:101-112): every epoch this subtask's next mini-batch
+ * -- rows [offset, min(offset + localBatch, n)) of its cache, offset advancing by localBatch and returning to 0 once
+ * >= n; localBatch = globalBatchSize / world, one more on the first globalBatchSize % world ranks (SGD.java:205-211)
+ * -- gives [gradient | totalWeight | totalLoss] against the current coefficient, the subtasks' arrays are summed
+ * (ncclAllReduce where the reference calls allReduceSum, SGD.java:130), and every rank applies updateModel
+ * (SGD.java:223-235: coefficient += -learningRate / totalWeight * gradient, then RegularizationUtils.regularize).
+ * The loop ends after max_iter epochs or once totalLoss / totalWeight <= tol; the test runs on the device and the
+ * remaining epochs' launches return at once, so the host enqueues max_iter epochs and synchronises once.
+ * Each row's BLAS.dot is in the reference's order; the sums over a batch are taken in a fixed order of this
+ * library's own (bit-identical from run to run), so coefficients agree with the reference to rounding, not to the
+ * bit.  out_coefficient_host: d doubles; out_epochs: epochs run; out_last_loss: totalLoss / totalWeight of the last
+ * epoch (either may be NULL).  Collective: every rank of the context's world calls it with the same arguments. */
+int32_t fmlk_sgd_fit(fmlk_ctx *ctx, int32_t loss, int32_t max_iter, double learning_rate, int32_t global_batch_size,
+                     double tol, double reg, double elastic_net, double *out_coefficient_host, int32_t *out_epochs,
+                     double *out_last_loss);
+
+/* predictOneDataPoint of the three models for n rows (kind = the FMLK_LOSS_* the model was trained with):
+ *   LOGISTIC      prediction = dot >= 0 ? 1 : 0, raw = [1 - prob, prob], prob = 1 - 1 / (1 + exp(dot))
+ *                 (LogisticRegressionModel.java:164-168)
+ *   HINGE         prediction = dot >= threshold ? 1 : 0, raw = [dot, -dot]   (LinearSVCModel.java:170-174)
+ *   LEAST_SQUARE  prediction = dot, no raw (NULL)                            (LinearRegressionModel.java:158-160)
+ * dot = BLAS.dot(features, coefficient) in the reference's order: predictions are bit-identical. */
+int32_t fmlk_linear_predict(fmlk_ctx *ctx, int32_t kind, const double *rows_host, int64_t n, int32_t d,
+                            const double *coefficient_host, double threshold, double *out_prediction_host,
+                            double *out_raw_host_or_null);
+int32_t fmlk_linear_predict_dev(fmlk_ctx *ctx, int32_t kind, const double *rows_dev, int64_t n, int32_t d,
+                                const double *coefficient_host, double threshold, double *out_prediction_dev,
+                                double *out_raw_dev_or_null);
+
 /* ---- initial centroids: KMeans.selectRandomCentroids (KMeans.java:310-327) ---- */
 
 /* One SamplingOperator (CORE/common/datastream/DataStreamUtils.java:633-704) over a stream of

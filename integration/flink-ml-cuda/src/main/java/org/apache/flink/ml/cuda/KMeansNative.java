@@ -65,6 +65,15 @@ final class KMeansNative implements AutoCloseable {
     private static native void knnGetNormSquares(long h, double[] outNormSquares);    // fmlk_knn_get_norm_squares
     private static native void knnPredict(long h, ByteBuffer rowsDirectLE, long n, int d, int k,
                                           double[] outPredictions);                   // fmlk_knn_predict
+    // SGD (SGD.java:164-300) and the linear models: loss / kind 0 = logistic, 1 = hinge, 2 = least square
+    private static native void sgdSetData(long h, ByteBuffer featuresDirectLE, double[] labels, double[] weightsOrNull,
+                                          long n, int d);                             // fmlk_sgd_set_data
+    private static native int sgdFit(long h, int loss, int maxIter, double learningRate, int globalBatchSize, double tol,
+                                     double reg, double elasticNet, double[] outCoefficient,
+                                     double[] outLastLoss);                           // fmlk_sgd_fit; returns the epochs run
+    private static native void linearPredict(long h, int kind, ByteBuffer rowsDirectLE, long n, int d, double[] coefficient,
+                                             double threshold, double[] outPrediction,
+                                             double[] outRawOrNull);                  // fmlk_linear_predict
     /**
      * fmlk_local_partials_noalloc: for a task manager whose GPU memory belongs to its own pool.  All arguments but
      * the shape are device addresses the caller obtained from that pool; nothing is allocated or freed.
@@ -97,6 +106,17 @@ final class KMeansNative implements AutoCloseable {
         knnSetModel(handle, packedFeatures, labels, normSquaresOrNull, m, d);
     }
     void knnGetNormSquares(double[] outNormSquares) { knnGetNormSquares(handle, outNormSquares); }
+    void sgdSetData(ByteBuffer featuresDirectLE, double[] labels, double[] weightsOrNull, long n, int d) {
+        sgdSetData(handle, featuresDirectLE, labels, weightsOrNull, n, d);
+    }
+    int sgdFit(int loss, int maxIter, double learningRate, int globalBatchSize, double tol, double reg, double elasticNet,
+               double[] outCoefficient, double[] outLastLoss) {
+        return sgdFit(handle, loss, maxIter, learningRate, globalBatchSize, tol, reg, elasticNet, outCoefficient, outLastLoss);
+    }
+    void linearPredict(int kind, ByteBuffer rowsDirectLE, long n, int d, double[] coefficient, double threshold,
+                       double[] outPrediction, double[] outRawOrNull) {
+        linearPredict(handle, kind, rowsDirectLE, n, d, coefficient, threshold, outPrediction, outRawOrNull);
+    }
     void knnPredict(ByteBuffer rowsDirectLE, long n, int d, int k, double[] outPredictions) {
         knnPredict(handle, rowsDirectLE, n, d, k, outPredictions);
     }

@@ -244,6 +244,39 @@ JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_knnPredict(JNI
     if (rc) throw_for(env, rc, ctx_of(h));
 }
 
+// CacheDataAndDoTrain's cache (SGD.java:176,289-291): the subtask's LabeledPointWithWeight rows, once
+JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_sgdSetData(JNIEnv *env, jclass, jlong h, jobject buf,
+                                                                            jdoubleArray labels, jdoubleArray weights, jlong n,
+                                                                            jint d) {
+    const double *feats = static_cast<const double *>(env->GetDirectBufferAddress(buf));
+    Doubles pl(env, labels), pw(env, weights);
+    int rc = fmlk_sgd_set_data(ctx_of(h), feats, pl.p, pw.p, n, d);
+    if (rc) throw_for(env, rc, ctx_of(h));
+}
+
+// SGD.optimize (SGD.java:84-160): every epoch of the iteration body, the all-reduce and the termination test included
+JNIEXPORT jint JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_sgdFit(JNIEnv *env, jclass, jlong h, jint loss, jint max_iter,
+                                                                        jdouble learning_rate, jint global_batch_size,
+                                                                        jdouble tol, jdouble reg, jdouble elastic_net,
+                                                                        jdoubleArray out_coef, jdoubleArray out_last_loss) {
+    Doubles pc(env, out_coef), pl(env, out_last_loss);
+    int32_t epochs = 0;
+    int rc = fmlk_sgd_fit(ctx_of(h), loss, max_iter, learning_rate, global_batch_size, tol, reg, elastic_net, pc.p, &epochs, pl.p);
+    if (rc) throw_for(env, rc, ctx_of(h));
+    return epochs;
+}
+
+// predictOneDataPoint of LogisticRegressionModel / LinearSVCModel / LinearRegressionModel for a micro-batch of rows
+JNIEXPORT void JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_linearPredict(JNIEnv *env, jclass, jlong h, jint kind,
+                                                                               jobject buf, jlong n, jint d, jdoubleArray coef,
+                                                                               jdouble threshold, jdoubleArray out_pred,
+                                                                               jdoubleArray out_raw) {
+    const double *rows = static_cast<const double *>(env->GetDirectBufferAddress(buf));
+    Doubles pc(env, coef), pp(env, out_pred), pr(env, out_raw);
+    int rc = fmlk_linear_predict(ctx_of(h), kind, rows, n, d, pc.p, threshold, pp.p, pr.p);
+    if (rc) throw_for(env, rc, ctx_of(h));
+}
+
 // SamplingOperator (DataStreamUtils.java:633-704)
 JNIEXPORT jint JNICALL Java_org_apache_flink_ml_cuda_KMeansNative_reservoir(JNIEnv *env, jclass, jlong n, jint k,
                                                                            jlong seed, jlongArray out) {

@@ -21,7 +21,7 @@ _u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
 
 def build(force=False):
     """Compile the oracle with its Makefile (gcc only; a few seconds)."""
-    srcs = [os.path.join(_HERE, f) for f in ("kmeans_oracle.c", "knn_oracle.c", "Makefile")]
+    srcs = [os.path.join(_HERE, f) for f in ("kmeans_oracle.c", "knn_oracle.c", "sgd_oracle.c", "Makefile")]
     if force or not os.path.exists(_SO) or os.path.getmtime(_SO) < max(os.path.getmtime(f) for f in srcs):
         subprocess.check_call(["make", "-s", "-C", _HERE])
     return _SO
@@ -76,6 +76,9 @@ def lib():
         "orc_train_round_mt": (None, [C.c_int64, C.c_int32, _f64p, C.c_int32, _f64p, _f64p, _i32p, C.c_int32]),
         "orc_max_threads": (C.c_int32, []),
         "orc_knn_norm_square": (C.c_double, [C.c_int32, _f64p]),
+        "orc_sgd_batch": (None, [C.c_int32, C.c_int32, _f64p, _f64p, C.c_void_p, C.c_int64, C.c_int64, _f64p, _f64p]),
+        "orc_sgd_update": (None, [C.c_int32, _f64p, _f64p, C.c_double, C.c_double, C.c_double]),
+        "orc_linear_predict": (None, [C.c_int32, C.c_int64, C.c_int32, _f64p, _f64p, C.c_double, _f64p, _f64p]),
         "orc_knn_predict": (None, [C.c_int64, C.c_int32, _f64p, C.c_int32, _f64p, _f64p, _f64p, C.c_int32, _f64p]),
         "orc_knn_distances": (None, [C.c_int32, _f64p, C.c_int32, _f64p, _f64p, _f64p]),
     }
@@ -386,3 +389,72 @@ def knn_distances(row, features, norm_squares=None):
     out = np.empty(f.shape[0], dtype=np.float64)
     lib().orc_knn_distances(f.shape[1], np.ascontiguousarray(row, dtype=np.float64).reshape(-1), f.shape[0], f.reshape(-1), ns, out)
     return out
+
+
+# ---------------------------------------------------------------- SGD and the linear models (oracle/sgd_oracle.c)
+LOSS_LOGISTIC, LOSS_HINGE, LOSS_LEAST_SQUARE = 0, 1, 2
+
+
+def sgd_local_batch_sizes(global_batch_size, parallelism):
+    """SGD.java:205-211: globalBatchSize / numTasks, one more on the first globalBatchSize % numTasks subtasks."""
+    return [global_batch_size // parallelism + (1 if global_batch_size % parallelism > t else 0) for t in range(parallelism)]
+
+
+def sgd_batch(loss, x, labels, weights, begin, end, coef):
+    """One subtask's mini-batch (SGD.java:243-268): [gradient | totalWeight | totalLoss]."""
+    x = _rows(x)
+    lab = np.ascontiguousarray(labels, dtype=np.float64).reshape(-1)
+    w = None if weights is None else np.ascontiguousarray(weights, dtype=np.float64).reshape(-1)
+    out = np.empty(x.shape[1] + 2, dtype=np.float64)
+    lib().orc_sgd_batch(int(loss), x.shape[1], x.reshape(-1), lab, None if w is None else w.ctypes.data, int(begin), int(end),
+                        np.ascontiguousarray(coef, dtype=np.float64), out)
+    return out
+
+
+def sgd_update(coef, feedback, learning_rate, reg, elastic_net):
+    """SGD.updateModel (SGD.java:223-235) in place on a copy; returns the new coefficient."""
+    c = np.array(coef, dtype=np.float64)
+    lib().orc_sgd_update(c.shape[0], c, np.ascontiguousarray(feedback, dtype=np.float64), float(learning_rate), float(reg),
+                         float(elastic_net))
+    return c
+
+
+def sgd_fit(shards, loss, max_iter=20, learning_rate=0.1, global_batch_size=32, tol=1e-6, reg=0.0, elastic_net=0.0):
+    """SGD.optimize (SGD.java:84-160) over `shards` = [(x, labels, weights or None), ...], one per subtask: every epoch each
+    subtask emits its mini-batch's feedback, the feedbacks are summed in subtask order (allReduceSum), every subtask applies
+    the same update; the loop ends after maxIter epochs or once totalLoss / totalWeight <= tol
+    (TerminateOnMaxIterOrTol.java:62-67).  Returns (coefficient, epochs run, [loss per epoch])."""
+    p = len(shards)
+    d = _rows(shards[0][0]).shape[1]
+    local = sgd_local_batch_sizes(int(global_batch_size), p)
+    offsets = [0] * p
+    coef = np.zeros(d, dtype=np.float64)
+    losses = []
+    epoch = 0
+    while True:
+        total = np.zeros(d + 2, dtype=np.float64)
+        for t, (x, lab, w) in enumerate(shards):
+            n = _rows(x).shape[0]
+            if n == 0:
+                continue  # (a subtask without data emits nothing, SGD.java:249)
+            total += sgd_batch(loss, x, lab, w, offsets[t], min(offsets[t] + local[t], n), coef)
+            offsets[t] += local[t]
+            if offsets[t] >= n:
+                offsets[t] = 0
+        coef = sgd_update(coef, total, learning_rate, reg, elastic_net)
+        with np.errstate(invalid="ignore", divide="ignore"):
+            cur = float(total[d + 1] / total[d])
+        losses.append(cur)
+        epoch += 1
+        if not (epoch < max_iter and cur > tol):
+            return coef, epoch, losses
+
+
+def linear_predict(kind, x, coef, threshold=0.0):
+    """predictOneDataPoint of the three models; returns (prediction, raw or None)."""
+    x = _rows(x)
+    pred = np.empty(x.shape[0], dtype=np.float64)
+    raw = np.empty((x.shape[0], 2), dtype=np.float64)
+    lib().orc_linear_predict(int(kind), x.shape[0], x.shape[1], x.reshape(-1), np.ascontiguousarray(coef, dtype=np.float64),
+                             float(threshold), pred, raw.reshape(-1))
+    return pred, (raw if kind != LOSS_LEAST_SQUARE else None)

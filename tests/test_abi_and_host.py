@@ -245,6 +245,8 @@ NOT_BOUND_FROM_THE_JVM = {
     "fmlk_adopt_points_dev": "device pointers (harness)",
     "fmlk_predict_dev": "device pointers (harness)",
     "fmlk_knn_predict_dev": "device pointers (harness)",
+    "fmlk_sgd_set_data_dev": "device pointers (harness)",
+    "fmlk_linear_predict_dev": "device pointers (harness)",
     "fmlk_all_reduce_sum_dev": "device pointers (harness)",
     "fmlk_decode_rows_dev": "device pointers (harness); the JVM calls fmlk_append_points_serialized",
     "fmlk_generate_dense_dev": "benchmark data generator",
