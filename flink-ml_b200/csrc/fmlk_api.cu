@@ -2198,11 +2198,25 @@ void sgd_drop_data(fmlk_ctx *ctx) {
     ctx->sgd_d = 0;
 }
 
-// MMA-free kernels of fmlk_sgd.cuh: as many warps per CTA (8, 4, 2, 1) as shared memory allows for this d
-int sgd_warps_for(const fmlk_ctx *ctx, int d, bool with_grad) {
-    for (int w = fmlk::kSgdMaxWarps; w >= 1; w >>= 1)
-        if (fmlk::sgd_smem_bytes(d, w, with_grad) <= ctx->smem_optin) return w;
-    return 0;
+// Geometry of the kernels of fmlk_sgd.cuh: rows a warp stages at a time (32 where they fit, then 16, 8, ... for long rows)
+// and warps per CTA (8, 4, 2, 1); few warps with full groups before many warps with short ones.
+struct SgdGeom {
+    int warps = 0, rows = 0;
+    size_t smem = 0;
+};
+SgdGeom sgd_geom(const fmlk_ctx *ctx, int d, bool with_grad) {
+    SgdGeom g;
+    for (int rows = env_int("FMLK_TUNE_SGD_ROWS", 32); rows >= 1; rows >>= 1)
+        for (int w = fmlk::kSgdMaxWarps; w >= (rows == 32 ? 4 : 1); w >>= 1) {
+            const size_t need = fmlk::sgd_smem_bytes(d, w, rows, with_grad);
+            if (need <= ctx->smem_optin) {
+                g.warps = w;
+                g.rows = rows;
+                g.smem = need;
+                return g;
+            }
+        }
+    return g;
 }
 
 int grow(fmlk_ctx *ctx, double **p, size_t *cap, size_t need) { // a device buffer of at least `need` doubles
@@ -2218,21 +2232,23 @@ int grow(fmlk_ctx *ctx, double **p, size_t *cap, size_t need) { // a device buff
 
 int linear_launch(fmlk_ctx *ctx, int kind, const double *rows_dev, int64_t n, int d, const double *coef_dev, double threshold,
                   double *pred_dev, double *raw_dev) {
-    const int warps = sgd_warps_for(ctx, d, false);
-    if (warps == 0) return fail(ctx, FMLK_ERR_DIM, "d too large for the linear-model kernels");
-    const size_t smem = fmlk::sgd_smem_bytes(d, warps, false);
-    const int64_t groups = (n + 31) / 32;
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((groups + warps - 1) / warps, (int64_t)ctx->sm_count * 4));
+    const SgdGeom geo = sgd_geom(ctx, d, false);
+    if (geo.warps == 0) return fail(ctx, FMLK_ERR_DIM, "d too large for the linear-model kernels");
+    const int warps = geo.warps;
+    const size_t smem = geo.smem;
+    const int64_t groups = (n + geo.rows - 1) / geo.rows;
+    const int64_t ctas_per_sm = std::max<int64_t>(1, std::min<int64_t>(4, (int64_t)(ctx->smem_optin / smem)));
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((groups + warps - 1) / warps, (int64_t)ctx->sm_count * ctas_per_sm));
     const int fma = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
-#define FMLK_LINEAR(K)                                                                                                       \
-    {                                                                                                                        \
-        CK(ctx, cudaFuncSetAttribute(fmlk::linear_predict_kernel<K>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-        fmlk::linear_predict_kernel<K><<<grid, warps * 32, smem, ctx->stream>>>(rows_dev, n, d, coef_dev, threshold, fma,    \
-                                                                                pred_dev, raw_dev);                          \
+#define FMLK_LINEAR(K, F)                                                                                                       \
+    {                                                                                                                           \
+        CK(ctx, cudaFuncSetAttribute(fmlk::linear_predict_kernel<K, F>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+        fmlk::linear_predict_kernel<K, F><<<grid, warps * 32, smem, ctx->stream>>>(rows_dev, n, d, geo.rows, coef_dev, threshold, \
+                                                                                   pred_dev, raw_dev);                          \
     }
-    if (kind == FMLK_LOSS_LOGISTIC) FMLK_LINEAR(0)
-    else if (kind == FMLK_LOSS_HINGE) FMLK_LINEAR(1)
-    else FMLK_LINEAR(2)
+    if (kind == FMLK_LOSS_LOGISTIC) { if (fma) FMLK_LINEAR(0, true) else FMLK_LINEAR(0, false) }
+    else if (kind == FMLK_LOSS_HINGE) { if (fma) FMLK_LINEAR(1, true) else FMLK_LINEAR(1, false) }
+    else { if (fma) FMLK_LINEAR(2, true) else FMLK_LINEAR(2, false) }
 #undef FMLK_LINEAR
     CK(ctx, cudaGetLastError());
     ctx->total_launches++;
@@ -2318,30 +2334,33 @@ int32_t fmlk_sgd_fit(fmlk_ctx *ctx, int32_t loss, int32_t max_iter, double learn
     if (!out_coefficient_host) return fail(ctx, FMLK_ERR_INVALID_ARG, "out_coefficient_host is null");
     const int d = ctx->sgd_d;
     const int64_t n = ctx->sgd_n;
-    const int warps = sgd_warps_for(ctx, d, true);
-    if (warps == 0) return fail(ctx, FMLK_ERR_DIM, "d too large for the SGD kernel's shared-memory gradient");
-    const size_t smem = fmlk::sgd_smem_bytes(d, warps, true);
+    const SgdGeom geo = sgd_geom(ctx, d, true);
+    if (geo.warps == 0) return fail(ctx, FMLK_ERR_DIM, "d too large for the SGD kernel's shared-memory staging");
+    const int warps = geo.warps;
+    const size_t smem = geo.smem;
     const int64_t local_batch = global_batch_size / ctx->world + (global_batch_size % ctx->world > ctx->rank ? 1 : 0);
-    const int64_t groups_max = (std::min<int64_t>(local_batch, n) + 31) / 32;
-    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((groups_max + warps - 1) / warps, (int64_t)ctx->sm_count * 2));
+    const int64_t groups_max = (std::min<int64_t>(local_batch, n) + geo.rows - 1) / geo.rows;
+    // as many CTAs as the SMs hold at once, so that a small mini-batch is one group per warp
+    const int64_t ctas_per_sm = std::max<int64_t>(1, std::min<int64_t>(4, (int64_t)(ctx->smem_optin / smem)));
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>((groups_max + warps - 1) / warps, (int64_t)ctx->sm_count * ctas_per_sm));
     if ((rc = grow(ctx, &ctx->sgd_coef, &ctx->sgd_coef_cap, (size_t)d))) return rc;
     if ((rc = grow(ctx, &ctx->sgd_feedback, &ctx->sgd_feedback_cap, (size_t)d + 2))) return rc;
     if ((rc = grow(ctx, &ctx->sgd_partials, &ctx->sgd_partials_cap, (size_t)grid * (d + 2)))) return rc;
     if (!ctx->sgd_state && (rc = dev_alloc(ctx, &ctx->sgd_state, 1))) return rc;
     CK(ctx, cudaMemsetAsync(ctx->sgd_coef, 0, (size_t)d * sizeof(double), ctx->stream)); // new DenseVector(dim)
     CK(ctx, cudaMemsetAsync(ctx->sgd_state, 0, sizeof(fmlk::SgdState), ctx->stream));
-    if (loss == FMLK_LOSS_LOGISTIC)
-        CK(ctx, cudaFuncSetAttribute(fmlk::sgd_batch_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    else if (loss == FMLK_LOSS_HINGE)
-        CK(ctx, cudaFuncSetAttribute(fmlk::sgd_batch_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    else
-        CK(ctx, cudaFuncSetAttribute(fmlk::sgd_batch_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const bool fma = (ctx->flags & FMLK_FLAG_BLAS_FMA) != 0;
+    void (*batch_kernel)(fmlk::SgdBatchParams) =
+        loss == FMLK_LOSS_LOGISTIC ? (fma ? fmlk::sgd_batch_kernel<0, true> : fmlk::sgd_batch_kernel<0, false>)
+        : loss == FMLK_LOSS_HINGE  ? (fma ? fmlk::sgd_batch_kernel<1, true> : fmlk::sgd_batch_kernel<1, false>)
+                                   : (fma ? fmlk::sgd_batch_kernel<2, true> : fmlk::sgd_batch_kernel<2, false>);
+    CK(ctx, cudaFuncSetAttribute(batch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     fmlk::SgdBatchParams p{};
     p.x = ctx->sgd_x;
     p.labels = ctx->sgd_y;
     p.weights = ctx->sgd_w;
     p.d = d;
-    p.fma_mode = (ctx->flags & FMLK_FLAG_BLAS_FMA) ? 1 : 0;
+    p.group_rows = geo.rows;
     p.coef = ctx->sgd_coef;
     p.partials = ctx->sgd_partials;
     p.feedback = ctx->sgd_feedback;
@@ -2352,14 +2371,12 @@ int32_t fmlk_sgd_fit(fmlk_ctx *ctx, int32_t loss, int32_t max_iter, double learn
         p.end = std::min<int64_t>(offset + local_batch, n);
         offset += local_batch;
         if (offset >= n) offset = 0;
-        if (loss == FMLK_LOSS_LOGISTIC) fmlk::sgd_batch_kernel<0><<<grid, warps * 32, smem, ctx->stream>>>(p);
-        else if (loss == FMLK_LOSS_HINGE) fmlk::sgd_batch_kernel<1><<<grid, warps * 32, smem, ctx->stream>>>(p);
-        else fmlk::sgd_batch_kernel<2><<<grid, warps * 32, smem, ctx->stream>>>(p);
+        batch_kernel<<<grid, warps * 32, smem, ctx->stream>>>(p);
         CK(ctx, cudaGetLastError());
         if (ctx->world > 1)
             CKN(ctx, nccl().AllReduce(ctx->sgd_feedback, ctx->sgd_feedback, (size_t)d + 2, ncclFloat64, ncclSum, ctx->comm, ctx->stream));
         fmlk::sgd_update_kernel<<<1, 256, 0, ctx->stream>>>(ctx->sgd_coef, ctx->sgd_feedback, d, learning_rate, reg, elastic_net, max_iter,
-                                                           tol, p.fma_mode, ctx->sgd_state);
+                                                           tol, fma ? 1 : 0, ctx->sgd_state);
         CK(ctx, cudaGetLastError());
         ctx->total_launches += 2;
     }

@@ -8,17 +8,23 @@
 // with BinaryLogisticLoss.java:35-50, HingeLoss.java:39-57, LeastSquareLoss.java:35-49 and
 // RegularizationUtils.java:49-91.
 //
-// HBM-bound (8 d bytes and ~4 d flops per row) and launch-bound at the reference's batch sizes, so the work is laid
-// out for coalesced rows and a fixed summation order, not for the tensor cores:
-//   - a warp takes 32 rows at a time, one row per lane.  Pass 1 walks the rows in 32-column chunks through a
-//     32 x 33 shared-memory tile (coalesced loads, conflict-free reads down a lane's own row) and each lane adds up its
-//     row's BLAS.dot in netlib's order (four interleaved sums, then the tail: ref_ddot's arithmetic), so the dot --
-//     and with it every prediction's comparison -- is the reference's to the bit;
-//   - the lane then has its row's loss term and gradient multiplier; pass 2 walks the same chunks again (from L1/L2)
-//     with one column per lane and adds multiplier[r] * x[r][c] for r = 0..31 in row order into the warp's own
-//     gradient in shared memory: plain loads and stores, no atomics;
+// HBM-bound by its algorithmic work (8 d bytes and ~4 d flops per row) but, at the reference's batch sizes (a mini-batch
+// is a few dozen row groups per SM), bound by instruction issue and latency: ncu shows 0.9 instructions per cycle and SM
+// with eight resident warps.  So the work is laid out for one trip to HBM per row, few instructions per row and a fixed
+// summation order:
+//   - a warp takes a group of R consecutive rows (R = 32 where shared memory allows).  They are contiguous in the cache
+//     and arrive in the warp's own staging buffer by 8-byte cp.async (LDGSTS: coalesced, no registers, the whole group
+//     in flight at once), each row at an ODD stride of doubles, so that pass 1's lanes sit on different banks;
+//   - pass 1, one row per lane: BLAS.dot(features, coefficient) in netlib's order (four interleaved sums, then the
+//     tail), so the dot -- and with it every prediction's comparison -- is the reference's to the bit; the lane then has
+//     its row's loss term and gradient multiplier;
+//   - pass 2, from the same staging buffer (no second read of the rows): gradient += multiplier . X on the FP64 tensor
+//     cores, as row 0 of D = A B + C (DMMA.8x8x4, A's other rows zero), into the warp's own gradient in shared memory;
+//     a group with a non-finite element (0 x Inf would be NaN where the reference skips a zero multiplier) and the
+//     short last group take a scalar loop, one column per lane, rows in order.  No atomics either way;
 //   - the CTA adds its warps in warp order, the last CTA to finish adds the CTAs in CTA order: the feedback is
 //     bit-identical from run to run (it differs from the reference's row-by-row order in the last bits only).
+// Measured (scripts/measure_sgd.py, logisticregression-benchmark.json's shape): see DESIGN.md.
 // sgd_update_kernel applies updateModel and the termination test on the device; once the test says stop, the
 // remaining epochs' kernels return at their first instruction, so the host never waits inside the loop.
 #pragma once
@@ -27,84 +33,103 @@
 namespace fmlk {
 
 constexpr int kSgdMaxWarps = 8;
-constexpr int kSgdTile = 32 * 33; // doubles per warp tile
 
-// device-side state of one fit: [0] stop flag, [1] epochs run; loss of the last epoch in `last_loss`
+// device-side state of one fit
 struct SgdState {
-    int32_t stop;
-    int32_t epochs;
+    int32_t stop;       // the termination test has fired
+    int32_t epochs;     // epochs run
     uint32_t ctas_done; // last-CTA election of sgd_batch_kernel (returns to 0 by itself)
     int32_t pad;
-    double last_loss;
+    double last_loss;   // totalLoss / totalWeight of the last epoch
 };
 
-__host__ __device__ inline size_t sgd_smem_bytes(int d, int warps, bool with_grad) {
-    return ((size_t)d + (size_t)warps * (kSgdTile + (with_grad ? d : 0)) + 2 * (size_t)warps) * sizeof(double);
+// shared memory: coefficient (d) | per warp: staging (R rows at stride S = d | 1) | gradients [warps][d] | [warps][2] weight, loss
+__host__ __device__ inline int sgd_stride(int d) { return d | 1; }
+__host__ __device__ inline size_t sgd_stage_elems(int d, int rows) { return (size_t)rows * sgd_stride(d); }
+__host__ __device__ inline size_t sgd_smem_bytes(int d, int warps, int rows, bool with_grad) {
+    return ((size_t)d + (size_t)warps * sgd_stage_elems(d, rows) + (with_grad ? (size_t)warps * d + 2 * (size_t)warps : 0)) * sizeof(double);
 }
 
-// BLAS.dot(features, coefficient) of rows row0 + lane (lane < rows) in netlib's order; x: row-major, d columns;
-// tile: this warp's 32 x 33 doubles; coef_s: the coefficient in shared memory.
-__device__ __forceinline__ double sgd_rows_dot(const double *x, int64_t row0, int rows, int d, double *tile, const double *coef_s,
-                                               int lane, int fma_mode) {
-    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0, sum = 0.0;
-    const int n4 = d & ~3;
-    for (int c0 = 0; c0 < d; c0 += 32) {
-        const int cols = min(32, d - c0);
-        __syncwarp();
-        for (int r = 0; r < rows; r++)
-            if (lane < cols) tile[r * 33 + lane] = __ldg(x + (row0 + r) * d + c0 + lane);
-        __syncwarp();
-        const double *mine = tile + lane * 33;
-        int j = 0;
-        for (; c0 + j + 3 < n4 && j + 3 < cols; j += 4) {
-            s0 = ref_mul_add(mine[j + 0], coef_s[c0 + j + 0], s0, fma_mode);
-            s1 = ref_mul_add(mine[j + 1], coef_s[c0 + j + 1], s1, fma_mode);
-            s2 = ref_mul_add(mine[j + 2], coef_s[c0 + j + 2], s2, fma_mode);
-            s3 = ref_mul_add(mine[j + 3], coef_s[c0 + j + 3], s3, fma_mode);
-        }
-        if (c0 + cols == d) { // last chunk: fold the four sums, then the tail in order
-            sum = __dadd_rn(0.0, __dadd_rn(__dadd_rn(__dadd_rn(s0, s1), s2), s3));
-            for (; j < cols; j++) sum = ref_mul_add(mine[j], coef_s[c0 + j], sum, fma_mode);
-        }
+// rows x d doubles from src (global, contiguous) into this warp's staging buffer, row r at r * S.  All lanes return with
+// the data visible.
+__device__ __forceinline__ void sgd_load_group(double *stage, const double *src, int rows, int d, int lane) {
+    const int S = sgd_stride(d);
+    __syncwarp(); // every lane is done with the previous group
+    for (int r = 0; r < rows; r++) {
+        const double *s = src + (size_t)r * d;
+        double *t = stage + (size_t)r * S;
+        for (int c = lane; c < d; c += 32) cp_async8(t + c, s + c);
     }
+    cp_async_commit();
+    cp_async_wait<0>();
+    __syncwarp();
+}
+
+// BLAS.dot in netlib's order (ref_ddot's arithmetic with the multiply-add variant fixed at compile time: the run-time
+// choice doubles the FP64 instructions of a kernel that is bound by instruction issue)
+template <bool FMA>
+__device__ __forceinline__ double sgd_mul_add(double a, double b, double acc) {
+    return FMA ? fma(a, b, acc) : __dadd_rn(acc, __dmul_rn(a, b));
+}
+template <bool FMA>
+__device__ __forceinline__ double sgd_ddot(const double *x, const double *y, int d) {
+    double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+    int i = 0;
+    const int n4 = d & ~3;
+#pragma unroll 2
+    for (; i < n4; i += 4) {
+        s0 = sgd_mul_add<FMA>(x[i + 0], y[i + 0], s0);
+        s1 = sgd_mul_add<FMA>(x[i + 1], y[i + 1], s1);
+        s2 = sgd_mul_add<FMA>(x[i + 2], y[i + 2], s2);
+        s3 = sgd_mul_add<FMA>(x[i + 3], y[i + 3], s3);
+    }
+    double sum = __dadd_rn(0.0, __dadd_rn(__dadd_rn(__dadd_rn(s0, s1), s2), s3));
+    for (; i < d; i++) sum = sgd_mul_add<FMA>(x[i], y[i], sum);
     return sum;
 }
 
 struct SgdBatchParams {
     const double *x, *labels, *weights; // weights may be null (1.0)
     int64_t begin, end;                 // rows of the cache in this mini-batch
-    int32_t d, fma_mode;
+    int32_t d;
+    int32_t group_rows;                 // R: rows a warp takes at a time (<= 32)
     const double *coef;                 // d
     double *partials;                   // [gridDim.x][d + 2]
     double *feedback;                   // d + 2: [gradient | totalWeight | totalLoss]
     SgdState *state;
 };
 
-template <int LOSS>
+template <int LOSS, bool FMA>
 __global__ void __launch_bounds__(kSgdMaxWarps * 32) sgd_batch_kernel(const SgdBatchParams p) {
     if (p.state->stop) return; // the loop has ended (TerminateOnMaxIterOrTol): nothing left to do
     extern __shared__ __align__(16) double sgd_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
-    const int d = p.d;
-    double *coef_s = sgd_smem;                             // [d]
-    double *tile = coef_s + d + (size_t)warp * kSgdTile;   // this warp's 32 x 33
-    double *grads = coef_s + d + (size_t)warps * kSgdTile; // [warps][d]
+    const int d = p.d, R = p.group_rows;
+    const size_t stage_elems = sgd_stage_elems(d, R);
+    double *coef_s = sgd_smem;                                              // [d]
+    double *stage = coef_s + d + (size_t)warp * stage_elems;   // this warp's R rows at stride S
+    double *grads = coef_s + d + (size_t)warps * stage_elems;  // [warps][d]
     double *gw = grads + (size_t)warp * d;
-    double *lw = grads + (size_t)warps * d;                // [warps][2]: weight, loss
+    double *lw = grads + (size_t)warps * d;                    // [warps][2]: weight, loss
+    const int S = sgd_stride(d);
     for (int i = threadIdx.x; i < d; i += blockDim.x) coef_s[i] = p.coef[i];
     for (int i = lane; i < d; i += 32) gw[i] = 0.0;
     __syncthreads();
     const int64_t n = p.end - p.begin;
-    const int64_t groups = (n + 31) / 32;
+    const int64_t groups = (n + R - 1) / R;
     double my_loss = 0.0, my_weight = 0.0; // this lane's rows, in row order
     for (int64_t g = (int64_t)blockIdx.x * warps + warp; g < groups; g += (int64_t)gridDim.x * warps) {
-        const int64_t row0 = p.begin + g * 32;
-        const int rows = (int)min((int64_t)32, p.end - row0);
-        const double dot = sgd_rows_dot(p.x, row0, rows, d, tile, coef_s, lane, p.fma_mode);
-        double mult = 0.0;
+        const int64_t row0 = p.begin + g * R;
+        const int rows = (int)min((int64_t)R, p.end - row0);
+        double label = 0.0, weight = 1.0; // (requested before the rows, used after the dot)
         if (lane < rows) {
-            const double label = p.labels[row0 + lane];
-            const double weight = p.weights ? p.weights[row0 + lane] : 1.0;
+            label = __ldg(p.labels + row0 + lane);
+            if (p.weights) weight = __ldg(p.weights + row0 + lane);
+        }
+        sgd_load_group(stage, p.x + row0 * d, rows, d, lane);
+        double mult = 0.0, dot = 0.0;
+        if (lane < rows) {
+            dot = sgd_ddot<FMA>(stage + (size_t)lane * S, coef_s, d);
             if (LOSS == 0) { // BinaryLogisticLoss.java:35-50
                 const double ls = __dadd_rn(__dmul_rn(2.0, label), -1.0);
                 my_loss = __dadd_rn(my_loss, __dmul_rn(weight, log(__dadd_rn(1.0, exp(__dmul_rn(-dot, ls))))));
@@ -122,15 +147,47 @@ __global__ void __launch_bounds__(kSgdMaxWarps * 32) sgd_batch_kernel(const SgdB
             my_weight = __dadd_rn(my_weight, weight);
         }
         // pass 2: cumGradient += multiplier * features (BLAS.axpy; a zero multiplier adds nothing, as daxpy returns early)
-        for (int c0 = 0; c0 < d; c0 += 32) {
-            const int c = c0 + lane;
-            double acc = c < d ? gw[c] : 0.0;
-            for (int r = 0; r < rows; r++) {
-                const double m = __shfl_sync(0xffffffffu, mult, r);
-                if (c < d && m != 0.0) acc = ref_mul_add(m, __ldg(p.x + (row0 + r) * d + c), acc, p.fma_mode);
+        const bool dense = rows == 32 && __all_sync(0xffffffffu, isfinite(dot));
+        if (dense) {
+            // on the FP64 tensor cores: gradient[c0 .. c0+7] += multiplier[4 ks .. 4 ks+3] . x[4 ks .. 4 ks+3][c0 .. c0+7] as
+            // row 0 of D = A B + C (mma.sync.m8n8k4: A's other rows are zero) -- a tenth of the instructions of the
+            // scalar loop below.  Every element of the group is finite here (a non-finite one makes its row's dot
+            // non-finite), so a zero multiplier times x is a zero that changes nothing, like the skipped axpy.
+            double a[8];
+#pragma unroll
+            for (int ks = 0; ks < 8; ks++) {
+                const double m = __shfl_sync(0xffffffffu, mult, 4 * ks + (lane & 3));
+                a[ks] = lane < 4 ? m : 0.0;
             }
-            if (c < d) gw[c] = acc;
+            const double *xb = stage + (size_t)(lane & 3) * S + (lane >> 2); // B fragment: row 4 ks + lane % 4, column c0 + lane / 4
+            for (int c0 = 0; c0 < d; c0 += 8) {
+                const int oc = c0 + 2 * (lane & 3); // row 0 of D: lanes 0..3 hold columns c0 + 2 lane, + 1
+                double acc0 = (lane < 4 && oc < d) ? gw[oc] : 0.0;
+                double acc1 = (lane < 4 && oc + 1 < d) ? gw[oc + 1] : 0.0;
+                const bool col_ok = c0 + (lane >> 2) < d;
+#pragma unroll
+                for (int ks = 0; ks < 8; ks++) {
+                    const double bfrag = col_ok ? xb[(size_t)(4 * ks) * S + c0] : 0.0;
+                    dmma884(acc0, acc1, a[ks], bfrag);
+                }
+                if (lane < 4) {
+                    if (oc < d) gw[oc] = acc0;
+                    if (oc + 1 < d) gw[oc + 1] = acc1;
+                }
+            }
+        } else {
+            // short last group, short groups of long rows, or a non-finite row: one column per lane, rows in order
+            for (int c = lane; c < ((d + 31) & ~31); c += 32) {
+                double acc = c < d ? gw[c] : 0.0;
+#pragma unroll 4
+                for (int r = 0; r < rows; r++) {
+                    const double m = __shfl_sync(0xffffffffu, mult, r);
+                    if (c < d && m != 0.0) acc = sgd_mul_add<FMA>(m, stage[(size_t)r * S + c], acc);
+                }
+                if (c < d) gw[c] = acc;
+            }
         }
+        __syncwarp();
     }
     // lanes in a fixed (butterfly) order, then warps in warp order, then CTAs in CTA order
 #pragma unroll
@@ -158,7 +215,14 @@ __global__ void __launch_bounds__(kSgdMaxWarps * 32) sgd_batch_kernel(const SgdB
     __threadfence();
     for (int i = threadIdx.x; i < d + 2; i += blockDim.x) {
         double acc = 0.0;
-        for (unsigned b = 0; b < gridDim.x; b++) acc = __dadd_rn(acc, __ldcg(p.partials + (size_t)b * (d + 2) + i));
+        for (unsigned b0 = 0; b0 < gridDim.x; b0 += 8) { // eight loads in flight, added in CTA order
+            double v[8];
+#pragma unroll
+            for (unsigned q = 0; q < 8; q++) v[q] = b0 + q < gridDim.x ? __ldcg(p.partials + (size_t)(b0 + q) * (d + 2) + i) : 0.0;
+#pragma unroll
+            for (unsigned q = 0; q < 8; q++)
+                if (b0 + q < gridDim.x) acc = __dadd_rn(acc, v[q]);
+        }
         p.feedback[i] = acc;
     }
     if (threadIdx.x == 0) p.state->ctas_done = 0;
@@ -204,22 +268,26 @@ __global__ void sgd_update_kernel(double *coef, const double *feedback, int d, d
 
 // predictOneDataPoint of the three models: LogisticRegressionModel.java:164-168, LinearSVCModel.java:170-174,
 // LinearRegressionModel.java:158-160.  One row per lane, the dot in the reference's order.
-template <int KIND>
-__global__ void __launch_bounds__(kSgdMaxWarps * 32) linear_predict_kernel(const double *x, int64_t n, int d, const double *coef,
-                                                                           double threshold, int fma_mode, double *prediction,
+template <int KIND, bool FMA>
+__global__ void __launch_bounds__(kSgdMaxWarps * 32) linear_predict_kernel(const double *x, int64_t n, int d, int group_rows, const double *coef,
+                                                                           double threshold, double *prediction,
                                                                            double *raw) {
     extern __shared__ __align__(16) double sgd_smem[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, warps = blockDim.x >> 5;
+    const int R = group_rows;
+    const size_t stage_elems = sgd_stage_elems(d, R);
     double *coef_s = sgd_smem;
-    double *tile = coef_s + d + (size_t)warp * kSgdTile;
+    double *stage = coef_s + d + (size_t)warp * stage_elems;
+    const int S = sgd_stride(d);
     for (int i = threadIdx.x; i < d; i += blockDim.x) coef_s[i] = coef[i];
     __syncthreads();
-    const int64_t groups = (n + 31) / 32;
+    const int64_t groups = (n + R - 1) / R;
     for (int64_t g = (int64_t)blockIdx.x * warps + warp; g < groups; g += (int64_t)gridDim.x * warps) {
-        const int64_t row0 = g * 32;
-        const int rows = (int)min((int64_t)32, n - row0);
-        const double dot = sgd_rows_dot(x, row0, rows, d, tile, coef_s, lane, fma_mode);
+        const int64_t row0 = g * R;
+        const int rows = (int)min((int64_t)R, n - row0);
+        sgd_load_group(stage, x + row0 * d, rows, d, lane);
         if (lane >= rows) continue;
+        const double dot = sgd_ddot<FMA>(stage + (size_t)lane * S, coef_s, d);
         const int64_t r = row0 + lane;
         if (KIND == 0) {
             const double prob = __dadd_rn(1.0, -__ddiv_rn(1.0, __dadd_rn(1.0, exp(dot))));

@@ -224,6 +224,25 @@ def test_gpu_fit_is_bit_identical_from_run_to_run_and_stops_on_tol(ctx):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("loss", [O.LOSS_LOGISTIC, O.LOSS_HINGE, O.LOSS_LEAST_SQUARE])
+def test_gpu_non_finite_rows_follow_the_reference(ctx, loss):
+    # an Inf or NaN feature makes its row's dot non-finite: with the hinge loss such a row adds no gradient (its
+    # `1 - labelScaled * dot > 0` is false) and the other rows' sums stay finite -- the tensor-core gradient pass, where
+    # 0 * Inf would be NaN, must not take that group; the epoch's loss is NaN, which ends the loop (NaN > tol is false)
+    x, y, w = _synthetic(640, 12, 3, loss)
+    x[5, 3] = np.inf
+    x[100, 0] = np.nan
+    ctx.sgd_set_data(x, y, w)
+    coef, epochs, last = ctx.sgd_fit(loss, max_iter=4, global_batch_size=256, tol=0.0)
+    ocoef, oepochs, olosses = O.sgd_fit([(x, y, w)], loss, max_iter=4, global_batch_size=256, tol=0.0)
+    assert epochs == oepochs == 1 and np.isnan(last) and np.isnan(olosses[-1])
+    assert np.array_equal(np.isnan(coef), np.isnan(ocoef))
+    assert np.allclose(coef, ocoef, rtol=COEF_RTOL, atol=COEF_ATOL, equal_nan=True)
+    if loss == O.LOSS_HINGE:
+        assert np.isfinite(coef).all()
+
+
+@pytest.mark.gpu
 @pytest.mark.parametrize("n,d", [(10000, 100), (33, 7), (1, 3), (4097, 260), (500, 1)])
 def test_gpu_predictions_are_bit_exact(ctx, n, d):
     rng = np.random.default_rng(n + d)
