@@ -433,7 +433,7 @@ def run_ours(args):
 
     # ---- the other two entry points north_star names, each device-timed and end to end from pinned host rows:
     # KMeansModel.transform (config 3's shape, a bounded number of rows) and OnlineKMeans mini-batches (config 5)
-    transform_rec = online_rec = knn_rec = None
+    transform_rec = online_rec = knn_rec = sgd_rec = None
     if not args.no_extra and args.workload == "c2":
         modes = [("f64", 0)] + ([] if args.no_fast else [("tf32x3+f64-recheck", native.FLAG_FAST_TF32)])
         tn, td, tk = args.transform_rows, 128, 1000
@@ -588,6 +588,44 @@ def run_ours(args):
         del feats, rows_q, host_q, table_q
         torch.cuda.empty_cache()
 
+        # SGD (allReduceSum's other caller): logisticregression-benchmark.json's conf per GPU (10 M x 100
+        # rows resident in HBM, maxIter 20, a mini-batch of 100 000 rows per GPU and epoch), the whole loop on the device
+        sn, sd, sb, se = args.sgd_rows, 100, 100_000, 20
+        free_b, _ = torch.cuda.mem_get_info(local)
+        if free_b > sn * sd * 8 + (4 << 30):
+            xs = generate(sn, sd)
+            ys = ((xs @ torch.linspace(-1.0, 1.0, sd, dtype=torch.float64, device=dev)) > 0).to(torch.float64)
+            cl = K.Cluster(rank, world, local, flags=0, host_group=host_group)
+            cx = cl.context()
+            cx.set_stream(stream.cuda_stream)
+            cx.sgd_set_data_dev(xs.data_ptr(), ys.data_ptr(), None, sn, sd, keep=(xs, ys))
+            for _ in range(2):
+                coef, ran, last = cx.sgd_fit(native.LOSS_LOGISTIC, max_iter=se, global_batch_size=sb * world, tol=0.0)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            e0.record(stream)
+            for _ in range(3):
+                coef, ran, last = cx.sgd_fit(native.LOSS_LOGISTIC, max_iter=se, global_batch_size=sb * world, tol=0.0)
+            e1.record(stream)
+            barrier()
+            ms = torch.tensor([e0.elapsed_time(e1) / 3], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+            sgd_ms = float(ms.item())
+            sgd_gbs = 8.0 * sd * sb * ran / (sgd_ms * 1e-3) * 1e-9
+            sgd_rec = {"workload": "LogisticRegression.fit (SGD): %d x %d FP64 rows per GPU in HBM, maxIter=%d, globalBatchSize=%d"
+                                   % (sn, sd, se, sb * world),
+                       "unit": "rows/s", "value": sb * world * ran / (sgd_ms * 1e-3), "ms_per_fit": sgd_ms,
+                       "us_per_epoch": sgd_ms * 1e3 / max(ran, 1), "epochs": ran, "last_loss": last,
+                       "gpu_launches_per_epoch": 2 + (1 if world > 1 else 0),
+                       "roofline": {"bound": "hbm", "achieved": sgd_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                                    "frac": sgd_gbs / peaks["hbm_gbs"],
+                                    "note": "8 d bytes per mini-batch row; at this batch size the epoch is bound by launch and "
+                                            "instruction latency, not by the row stream (DESIGN.md)"}}
+            cl.close()
+            del xs, ys
+            torch.cuda.empty_cache()
+
     # ---- the north-star shape (config 4: 1e9 x 64, k = 1000 over 8 GPUs): this GPU's share, a short run
     north = strong = None
     if not args.no_north_star and args.workload == "c2":
@@ -662,7 +700,7 @@ def run_ours(args):
             "clocks": clocks, "e2e": e2e, "gpu_launches": prof["total_launches"],
             "roofline": roofline, "cpu_baseline": base, "parity": parity,
             "wall_ms_per_step": wall / args.steps * 1e3, "rechecked_rows": prof["rechecked_rows"],
-            "fast_mode": fast_rec, "transform": transform_rec, "online": online_rec, "knn": knn_rec, "north_star": north, "strong_scaling": strong,
+            "fast_mode": fast_rec, "transform": transform_rec, "online": online_rec, "knn": knn_rec, "sgd": sgd_rec, "north_star": north, "strong_scaling": strong,
         }
         print(json.dumps(out))
     if world > 1:
@@ -687,6 +725,7 @@ def main():
     ap.add_argument("--no-fast", action="store_true", help="skip the fast-mode sub-record of the default run")
     ap.add_argument("--no-north-star", action="store_true", help="skip the config-4-share sub-record")
     ap.add_argument("--knn-rows", type=int, default=1 << 17, help="rows per GPU of the KnnModel.transform sub-record")
+    ap.add_argument("--sgd-rows", type=int, default=10_000_000, help="rows per GPU of the SGD (LogisticRegression) sub-record")
     ap.add_argument("--no-extra", action="store_true", help="skip the transform (config 3) and online (config 5) sub-records")
     ap.add_argument("--transform-rows", type=int, default=4_000_000, help="rows per GPU of the transform sub-record")
     ap.add_argument("--online-batches", type=int, default=40)

@@ -8,6 +8,8 @@
              (ModelDataGlobalReducer, OnlineKMeans.java:188-211) against the oracle at parallelism = world
   allreduce  DataStreamUtils.allReduceSum on AllReduceImplTest's sizes, identical on every rank, and the
              unequal-length error message (AllReduceImpl.java:71-302)
+  sgd        SGD.optimize (SGD.java:84-160) of a LogisticRegression over p shards of different sizes: per-rank local
+             batches (SGD.java:205-211) that wrap around the shards, one all-reduce per epoch, against the oracle
 
 `run_checks` is what bench.py's N > 1 arm calls before its timed region (the result goes into the
 JSON line as "parity"); standalone:
@@ -22,7 +24,7 @@ import numpy as np  # noqa: E402
 
 
 def run_checks(cluster, host_group, n_total=200003, d=32, k=50, iters=5, verbose=False):
-    """Collective: every rank calls it.  Returns {"world", "fit", "labels", "online", "allreduce", "ok"}
+    """Collective: every rank calls it.  Returns {"world", "fit", "labels", "online", "allreduce", "sgd", "ok"}
     (the same dict on every rank)."""
     import torch.distributed as dist
     import flink_ml_b200 as F
@@ -98,8 +100,34 @@ def run_checks(cluster, host_group, n_total=200003, d=32, k=50, iters=5, verbose
     ar_ok = everywhere(ar_ok)
     if verbose and rank == 0:
         print("allReduceSum on every rank:", ar_ok)
-    return {"world": world, "fit": fit_ok, "labels": labels_ok, "online": online_ok, "allreduce": ar_ok,
-            "ok": bool(fit_ok and labels_ok and online_ok and ar_ok),
+    # SGD over the same all-reduce (SGD.java:130): LogisticRegression on p shards, a global batch that does not divide by p
+    # and wraps around the shards, against the oracle at parallelism = world
+    def sgd_shard(t):
+        rng = np.random.default_rng(40 + t)
+        xs = rng.random((3001 + 17 * t, 24))
+        ys = (xs @ np.linspace(-1.0, 1.0, 24) > 0.0).astype(np.float64)
+        return xs, ys, rng.integers(1, 4, size=xs.shape[0]).astype(np.float64)
+
+    sx, sy, sw = sgd_shard(rank)
+    gb = 1000 * world + 3
+    ctx.sgd_set_data(sx, sy, sw)
+    coef, epochs, last = ctx.sgd_fit(native.LOSS_LOGISTIC, max_iter=12, learning_rate=0.1, global_batch_size=gb, tol=0.0,
+                                     reg=0.01, elastic_net=0.5)
+    coefs = [None] * world
+    dist.all_gather_object(coefs, (coef.tobytes(), epochs), group=host_group)
+    sgd_ok = all(c == coefs[0] for c in coefs)
+    if rank == 0:
+        ocoef, oepochs, _ = O.sgd_fit([sgd_shard(t) for t in range(world)], O.LOSS_LOGISTIC, max_iter=12, learning_rate=0.1,
+                                      global_batch_size=gb, tol=0.0, reg=0.01, elastic_net=0.5)
+        sgd_ok = sgd_ok and epochs == oepochs and bool(np.allclose(coef, ocoef, rtol=1e-9, atol=1e-12))
+    sgd_ok = everywhere(sgd_ok)
+    verdict = [sgd_ok if rank == 0 else None]
+    dist.broadcast_object_list(verdict, src=0, group=host_group)
+    sgd_ok = bool(verdict[0])
+    if verbose and rank == 0:
+        print("SGD (LogisticRegression, %d shards) within 1e-9 of the oracle, identical on all ranks:" % world, sgd_ok)
+    return {"world": world, "fit": fit_ok, "labels": labels_ok, "online": online_ok, "allreduce": ar_ok, "sgd": sgd_ok,
+            "ok": bool(fit_ok and labels_ok and online_ok and ar_ok and sgd_ok),
             "checked_against": "CPU oracle at parallelism = world (rows_total=%d, d=%d, k=%d, maxIter=%d)"
                                % (n_total, d, k, iters)}
 
