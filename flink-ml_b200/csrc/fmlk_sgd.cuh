@@ -50,15 +50,32 @@ __host__ __device__ inline size_t sgd_smem_bytes(int d, int warps, int rows, boo
     return ((size_t)d + (size_t)warps * sgd_stage_elems(d, rows) + (with_grad ? (size_t)warps * d + 2 * (size_t)warps : 0)) * sizeof(double);
 }
 
+__device__ __forceinline__ void cp_async8_s(unsigned smem_addr, const void *gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\n" ::"r"(smem_addr), "l"(gmem_src) : "memory");
+}
+
 // rows x d doubles from src (global, contiguous) into this warp's staging buffer, row r at r * S.  All lanes return with
-// the data visible.
+// the data visible.  32-bit shared addresses and running pointers: with the addresses computed per element this loop was
+// 59 % of the kernel's instructions (profiles/r2_sgd_batch_ncu_summary.txt).
 __device__ __forceinline__ void sgd_load_group(double *stage, const double *src, int rows, int d, int lane) {
-    const int S = sgd_stride(d);
     __syncwarp(); // every lane is done with the previous group
+    unsigned sa = (unsigned)__cvta_generic_to_shared(stage) + (unsigned)lane * 8u;
+    const char *ga = reinterpret_cast<const char *>(src) + lane * 8;
+    const unsigned srow = (unsigned)sgd_stride(d) * 8u;
+    const size_t grow = (size_t)d * 8u;
+    const int full = d >> 5;           // whole 32-column chunks of a row
+    const bool tail = lane < (d & 31); // and this lane's element of the last, partial one
     for (int r = 0; r < rows; r++) {
-        const double *s = src + (size_t)r * d;
-        double *t = stage + (size_t)r * S;
-        for (int c = lane; c < d; c += 32) cp_async8(t + c, s + c);
+        unsigned s = sa;
+        const char *g = ga;
+        for (int q = 0; q < full; q++) {
+            cp_async8_s(s, g);
+            s += 256u;
+            g += 256;
+        }
+        if (tail) cp_async8_s(s, g);
+        sa += srow;
+        ga += grow;
     }
     cp_async_commit();
     cp_async_wait<0>();
@@ -159,17 +176,20 @@ __global__ void __launch_bounds__(kSgdMaxWarps * 32) sgd_batch_kernel(const SgdB
                 const double m = __shfl_sync(0xffffffffu, mult, 4 * ks + (lane & 3));
                 a[ks] = lane < 4 ? m : 0.0;
             }
-            const double *xb = stage + (size_t)(lane & 3) * S + (lane >> 2); // B fragment: row 4 ks + lane % 4, column c0 + lane / 4
+            // B fragment of k-step ks: row 4 ks + lane % 4, column c0 + lane / 4 (32-bit shared addresses, one add per tile).
+            // Columns past d in the last tile read the next row's first elements (finite, inside the CTA's shared memory)
+            // and only reach output columns past d, which are not stored.
+            unsigned xa[8];
+#pragma unroll
+            for (int ks = 0; ks < 8; ks++)
+                xa[ks] = (unsigned)__cvta_generic_to_shared(stage) + (unsigned)(((4 * ks + (lane & 3)) * S + (lane >> 2)) * 8);
             for (int c0 = 0; c0 < d; c0 += 8) {
                 const int oc = c0 + 2 * (lane & 3); // row 0 of D: lanes 0..3 hold columns c0 + 2 lane, + 1
                 double acc0 = (lane < 4 && oc < d) ? gw[oc] : 0.0;
                 double acc1 = (lane < 4 && oc + 1 < d) ? gw[oc + 1] : 0.0;
-                const bool col_ok = c0 + (lane >> 2) < d;
+                const unsigned off = (unsigned)c0 * 8u;
 #pragma unroll
-                for (int ks = 0; ks < 8; ks++) {
-                    const double bfrag = col_ok ? xb[(size_t)(4 * ks) * S + c0] : 0.0;
-                    dmma884(acc0, acc1, a[ks], bfrag);
-                }
+                for (int ks = 0; ks < 8; ks++) dmma884(acc0, acc1, a[ks], lds_f64(xa[ks] + off));
                 if (lane < 4) {
                     if (oc < d) gw[oc] = acc0;
                     if (oc + 1 < d) gw[oc + 1] = acc1;
