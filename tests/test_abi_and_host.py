@@ -302,7 +302,8 @@ def test_java_operator_sources_are_present_and_name_their_reference_bodies():
             "GpuOnlinePredictLabelOperator.java": ("OnlineKMeansModel.java:108-196", "modelDataVersion", "bufferedPoints"),
             "GpuModelDataLocalUpdater.java": ("OnlineKMeans.java:227-326", "TwoInputStreamOperator", "onlineRound"),
             "GpuKnnPredictOperator.java": ("KnnModel.java:141-192", "OneInputStreamOperator", "knnPredict"),
-            "GpuCacheDataAndDoTrain.java": ("SGD.java:164-300", "BoundedOneInput", "sgdFit")}
+            "GpuCacheDataAndDoTrain.java": ("SGD.java:164-300", "BoundedOneInput", "sgdFit"),
+            "GpuLinearPredictOperator.java": ("LogisticRegressionModel.java:130-168", "prepareSnapshotPreBarrier", "linearPredict")}
     for name, needles in want.items():
         text = open(os.path.join(jdir, name)).read()
         assert "package org.apache.flink.ml.cuda;" in text and "KMeansNative" in text
