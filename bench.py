@@ -618,7 +618,7 @@ def run_ours(args):
                                    % (sn, sd, se, sb * world),
                        "unit": "rows/s", "value": sb * world * ran / (sgd_ms * 1e-3), "ms_per_fit": sgd_ms,
                        "us_per_epoch": sgd_ms * 1e3 / max(ran, 1), "epochs": ran, "last_loss": last,
-                       "gpu_launches_per_epoch": 2 + (1 if world > 1 else 0),
+                       "gpu_launches_per_epoch": 1 if world == 1 else 3,
                        "roofline": {"bound": "hbm", "achieved": sgd_gbs, "peak": peaks["hbm_gbs"], "unit": "GB/s",
                                     "frac": sgd_gbs / peaks["hbm_gbs"],
                                     "note": "8 d bytes per mini-batch row; at this batch size the epoch is bound by launch and "

@@ -2365,6 +2365,8 @@ int32_t fmlk_sgd_fit(fmlk_ctx *ctx, int32_t loss, int32_t max_iter, double learn
     p.partials = ctx->sgd_partials;
     p.feedback = ctx->sgd_feedback;
     p.state = ctx->sgd_state;
+    p.fuse_update = (ctx->world == 1 && env_int("FMLK_TUNE_SGD_FUSE", 1)) ? 1 : 0; // (several subtasks: all-reduce, then sgd_update_kernel)
+    p.update = fmlk::SgdUpdateParams{learning_rate, reg, elastic_net, tol, max_iter, fma ? 1 : 0};
     int64_t offset = 0; // nextBatchOffset (SGD.java:181)
     for (int epoch = 0; epoch < max_iter; epoch++) {
         p.begin = offset;
@@ -2375,10 +2377,11 @@ int32_t fmlk_sgd_fit(fmlk_ctx *ctx, int32_t loss, int32_t max_iter, double learn
         CK(ctx, cudaGetLastError());
         if (ctx->world > 1)
             CKN(ctx, nccl().AllReduce(ctx->sgd_feedback, ctx->sgd_feedback, (size_t)d + 2, ncclFloat64, ncclSum, ctx->comm, ctx->stream));
-        fmlk::sgd_update_kernel<<<1, 256, 0, ctx->stream>>>(ctx->sgd_coef, ctx->sgd_feedback, d, learning_rate, reg, elastic_net, max_iter,
-                                                           tol, fma ? 1 : 0, ctx->sgd_state);
-        CK(ctx, cudaGetLastError());
-        ctx->total_launches += 2;
+        if (!p.fuse_update) {
+            fmlk::sgd_update_kernel<<<1, 256, 0, ctx->stream>>>(ctx->sgd_coef, ctx->sgd_feedback, d, p.update, ctx->sgd_state);
+            CK(ctx, cudaGetLastError());
+        }
+        ctx->total_launches += p.fuse_update ? 1 : 2;
     }
     fmlk::SgdState st{};
     CK(ctx, cudaMemcpyAsync(out_coefficient_host, ctx->sgd_coef, (size_t)d * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));

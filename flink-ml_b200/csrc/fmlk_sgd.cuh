@@ -25,7 +25,8 @@
 //   - the CTA adds its warps in warp order, the last CTA to finish adds the CTAs in CTA order: the feedback is
 //     bit-identical from run to run (it differs from the reference's row-by-row order in the last bits only).
 // Measured (scripts/measure_sgd.py, logisticregression-benchmark.json's shape): see DESIGN.md.
-// sgd_update_kernel applies updateModel and the termination test on the device; once the test says stop, the
+// updateModel and the termination test run on the device (the last CTA of the batch kernel with one subtask, sgd_update_kernel
+// after the all-reduce with several); once the test says stop, the
 // remaining epochs' kernels return at their first instruction, so the host never waits inside the loop.
 #pragma once
 #include "fmlk_kernels.cuh"
@@ -105,15 +106,60 @@ __device__ __forceinline__ double sgd_ddot(const double *x, const double *y, int
     return sum;
 }
 
+__device__ __forceinline__ double java_signum(double v) { return (v == 0.0 || v != v) ? v : (v > 0.0 ? 1.0 : -1.0); }
+
+// what an epoch's update needs besides the reduced feedback
+struct SgdUpdateParams {
+    double learning_rate, reg, elastic_net, tol;
+    int32_t max_iter, fma_mode;
+};
+
+// updateModel (SGD.java:223-235) on the reduced feedback, RegularizationUtils.regularize (its loss term is never read:
+// SGD.java:230-232 adds it to an array that line 256 zeroes), then TerminateOnMaxIterOrTol.java:62-67 with
+// loss = totalLoss / totalWeight (SGD.java:135-141).  The threads of ONE CTA; element-wise, so exact in any order.
+__device__ __forceinline__ void sgd_update_model(double *coef, const double *feedback, int d, const SgdUpdateParams &u, SgdState *state) {
+    const double total_weight = feedback[d], total_loss = feedback[d + 1];
+    if (total_weight > 0) {
+        const double a = __ddiv_rn(-u.learning_rate, total_weight);
+        for (int i = threadIdx.x; i < d; i += blockDim.x) {
+            double c = coef[i];
+            if (a != 0.0) c = ref_mul_add(a, feedback[i], c, u.fma_mode); // daxpy
+            if (u.reg != 0.0) {
+                if (u.elastic_net == 0.0) {
+                    c = __dmul_rn(c, __dadd_rn(1.0, -__dmul_rn(u.learning_rate, u.reg))); // BLAS.scal(1 - learningRate * reg, coefficient)
+                } else if (u.elastic_net == 1.0) {
+                    // Double.compare(c, 0) == 0 skips +0.0 only
+                    if (!(c == 0.0 && !signbit(c)))
+                        c = __dadd_rn(c, -__dmul_rn(__dmul_rn(__dmul_rn(u.learning_rate, u.elastic_net), u.reg), java_signum(c)));
+                } else {
+                    const double l1 = __dmul_rn(__dmul_rn(u.elastic_net, u.reg), java_signum(c));
+                    const double l2 = __dmul_rn(__dmul_rn(__dadd_rn(1.0, -u.elastic_net), u.reg), c);
+                    c = __dadd_rn(c, -__dmul_rn(u.learning_rate, __dadd_rn(l1, l2)));
+                }
+            }
+            coef[i] = c;
+        }
+    }
+    if (threadIdx.x == 0) {
+        const double loss = __ddiv_rn(total_loss, total_weight);
+        const int epochs = state->epochs + 1;
+        state->epochs = epochs;
+        state->last_loss = loss;
+        if (!(epochs < u.max_iter && loss > u.tol)) state->stop = 1;
+    }
+}
+
 struct SgdBatchParams {
     const double *x, *labels, *weights; // weights may be null (1.0)
     int64_t begin, end;                 // rows of the cache in this mini-batch
     int32_t d;
     int32_t group_rows;                 // R: rows a warp takes at a time (<= 32)
-    const double *coef;                 // d
+    double *coef;                       // d (updated here when fuse_update)
     double *partials;                   // [gridDim.x][d + 2]
     double *feedback;                   // d + 2: [gradient | totalWeight | totalLoss]
     SgdState *state;
+    int32_t fuse_update;                // 1 (one subtask: nothing to all-reduce): the last CTA also applies updateModel
+    SgdUpdateParams update;
 };
 
 template <int LOSS, bool FMA>
@@ -246,44 +292,18 @@ __global__ void __launch_bounds__(kSgdMaxWarps * 32) sgd_batch_kernel(const SgdB
         p.feedback[i] = acc;
     }
     if (threadIdx.x == 0) p.state->ctas_done = 0;
+    if (p.fuse_update) {
+        // every other CTA has read the coefficient long ago (it has finished): the epoch's second launch is saved
+        __threadfence_block();
+        __syncthreads();
+        sgd_update_model(p.coef, p.feedback, d, p.update, p.state);
+    }
 }
 
-__device__ __forceinline__ double java_signum(double v) { return (v == 0.0 || v != v) ? v : (v > 0.0 ? 1.0 : -1.0); }
-
-// updateModel (SGD.java:223-235) on the reduced feedback, RegularizationUtils.regularize (its loss term is never read:
-// SGD.java:230-232 adds it to an array that line 256 zeroes), then TerminateOnMaxIterOrTol.java:62-67 with
-// loss = totalLoss / totalWeight (SGD.java:135-141).  One CTA.
-__global__ void sgd_update_kernel(double *coef, const double *feedback, int d, double learning_rate, double reg, double elastic_net,
-                                  int max_iter, double tol, int fma_mode, SgdState *state) {
+// the update as a launch of its own (after the all-reduce when there are several subtasks).  One CTA.
+__global__ void sgd_update_kernel(double *coef, const double *feedback, int d, const SgdUpdateParams u, SgdState *state) {
     if (state->stop) return;
-    const double total_weight = feedback[d], total_loss = feedback[d + 1];
-    if (total_weight > 0) {
-        const double a = __ddiv_rn(-learning_rate, total_weight);
-        for (int i = threadIdx.x; i < d; i += blockDim.x) {
-            double c = coef[i];
-            if (a != 0.0) c = ref_mul_add(a, feedback[i], c, fma_mode); // daxpy
-            if (reg != 0.0) {
-                if (elastic_net == 0.0) {
-                    c = __dmul_rn(c, __dadd_rn(1.0, -__dmul_rn(learning_rate, reg))); // BLAS.scal(1 - learningRate * reg, coefficient)
-                } else if (elastic_net == 1.0) {
-                    // Double.compare(c, 0) == 0 skips +0.0 only
-                    if (!(c == 0.0 && !signbit(c))) c = __dadd_rn(c, -__dmul_rn(__dmul_rn(__dmul_rn(learning_rate, elastic_net), reg), java_signum(c)));
-                } else {
-                    const double l1 = __dmul_rn(__dmul_rn(elastic_net, reg), java_signum(c));
-                    const double l2 = __dmul_rn(__dmul_rn(__dadd_rn(1.0, -elastic_net), reg), c);
-                    c = __dadd_rn(c, -__dmul_rn(learning_rate, __dadd_rn(l1, l2)));
-                }
-            }
-            coef[i] = c;
-        }
-    }
-    if (threadIdx.x == 0) {
-        const double loss = __ddiv_rn(total_loss, total_weight);
-        const int epochs = state->epochs + 1;
-        state->epochs = epochs;
-        state->last_loss = loss;
-        if (!(epochs < max_iter && loss > tol)) state->stop = 1;
-    }
+    sgd_update_model(coef, feedback, d, u, state);
 }
 
 // predictOneDataPoint of the three models: LogisticRegressionModel.java:164-168, LinearSVCModel.java:170-174,
