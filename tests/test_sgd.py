@@ -145,6 +145,40 @@ def test_mirror_params_and_model_data_bytes():
         F.LogisticRegression().set_multi_class("multinomial").fit(bad)
 
 
+def test_mirror_models_save_and_load_without_a_device(tmp_path):
+    # save / load are host logic (ReadWriteUtils.saveMetadata + the model data encoder): metadata with the reference's
+    # class name and params, data/part-0 with the encoder's bytes
+    import json
+    import os
+    import flink_ml_b200 as F
+    from flink_ml_b200.linear import LinearModelData
+    coef = np.array([0.25, -1.5, 3.0])
+    for cls, java, with_version in ((F.LogisticRegressionModel, "classification.logisticregression.LogisticRegressionModel", True),
+                                    (F.LinearSVCModel, "classification.linearsvc.LinearSVCModel", False),
+                                    (F.LinearRegressionModel, "regression.linearregression.LinearRegressionModel", False)):
+        model = cls().set_model_data(LinearModelData(coef, 3 if with_version else None).to_table())
+        if cls is F.LinearSVCModel:
+            model.set_threshold(0.5)
+        path = str(tmp_path / cls.__name__)
+        model.save(path)
+        meta = json.load(open(os.path.join(path, "metadata")))
+        assert meta["className"] == "org.apache.flink.ml." + java
+        blob = open(os.path.join(path, "data", "part-0"), "rb").read()
+        assert len(blob) == 4 + 24 + (8 if with_version else 0)
+        back = cls.load(path)
+        md = LinearModelData.from_table(back.get_model_data()[0])
+        assert md.coefficient.tolist() == coef.tolist() and md.model_version == (3 if with_version else None)
+        assert back.get_param_map() == model.get_param_map()
+        with pytest.raises(IOError):
+            model.save(path)  # "File ... already exists." (ReadWriteUtils.java:98-109)
+    est = F.LinearSVC().set_max_iter(7).set_threshold(0.25).set_weight_col("w")
+    est.save(str(tmp_path / "est"))
+    again = F.LinearSVC.load(str(tmp_path / "est"))
+    assert again.get_param_map() == est.get_param_map()
+    with pytest.raises(RuntimeError, match="does not match the expected class name"):
+        F.LinearRegression.load(str(tmp_path / "est"))
+
+
 # ------------------------------------------------------------------------------------------ CUDA path (GPU)
 def _synthetic(n, d, seed, loss):
     rng = np.random.default_rng(seed)
