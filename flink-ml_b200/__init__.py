@@ -2,6 +2,9 @@
 Estimator/Model API (flink-ml-python/pyflink/ml/lib/clustering/kmeans.py and the Java classes
 under flink-ml-lib/.../clustering/kmeans/) over libflinkml_kmeans_cuda.so.
 
+Next to KMeans, on the same boundary: Knn / KnnModel (knn.py) and the SGD-trained linear models --
+LogisticRegression, LinearSVC, LinearRegression and their models (linear.py).
+
 There is no CPU fallback: every compute call goes through the CUDA library and raises if it
 cannot be loaded or no B200 is present.
 """

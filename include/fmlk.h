@@ -1,6 +1,8 @@
 /*
  * fmlk.h -- C ABI of libflinkml_kmeans_cuda.so: the B200 (sm_100a) KMeans hot path
- * of Flink ML behind the reference's three operator bodies.
+ * of Flink ML behind the reference's three operator bodies, and the callers next to it on
+ * the same rows and the same all-reduce (serialized-row ingest, KnnModel, the SGD optimizer
+ * with the three linear models it trains).
  *
  * The reference (weibozhao/flink-ml @ 169aca44) has no FFI for this path; the seams
  * are the per-subtask operator bodies, and each entry point below replaces one of
