@@ -109,6 +109,37 @@ def test_oracle_local_batch_sizes_and_termination():
     assert c.tolist() == [1.0, 2.0]
 
 
+def test_oracle_properties_of_the_update():
+    rng = np.random.default_rng(21)
+    x = rng.normal(size=(200, 9))
+    y = (rng.random(200) > 0.4).astype(np.float64)
+    w = rng.integers(1, 5, size=200).astype(np.float64)
+    for loss in (O.LOSS_LOGISTIC, O.LOSS_HINGE, O.LOSS_LEAST_SQUARE):
+        # every weight times a power of two: gradient and totalWeight scale exactly, -learningRate / totalWeight * gradient
+        # does not change -- the coefficients are the same to the bit
+        a, ea, _ = O.sgd_fit([(x, y, w)], loss, max_iter=6, global_batch_size=64, tol=0.0, reg=0.05, elastic_net=0.5)
+        b, eb, _ = O.sgd_fit([(x, y, 4.0 * w)], loss, max_iter=6, global_batch_size=64, tol=0.0, reg=0.05, elastic_net=0.5)
+        assert ea == eb and np.array_equal(a, b)
+        # no weight column == a column of ones
+        c, _, _ = O.sgd_fit([(x, y, None)], loss, max_iter=4, global_batch_size=50, tol=0.0)
+        d, _, _ = O.sgd_fit([(x, y, np.ones(200))], loss, max_iter=4, global_batch_size=50, tol=0.0)
+        assert np.array_equal(c, d)
+    # the JDK >= 11 variant of netlib (Math.fma in dot and axpy) moves last bits only
+    base, _, _ = O.sgd_fit([(x, y, w)], O.LOSS_LOGISTIC, max_iter=10, global_batch_size=64, tol=0.0)
+    O.set_blas_mode(1)
+    try:
+        fused, _, _ = O.sgd_fit([(x, y, w)], O.LOSS_LOGISTIC, max_iter=10, global_batch_size=64, tol=0.0)
+    finally:
+        O.set_blas_mode(0)
+    assert np.allclose(fused, base, rtol=1e-12, atol=1e-15)
+    # elastic net on a negative zero: signum(-0.0) = -0.0, the coefficient comes back as +0.0 (c - (-0.0)); L1 alone goes
+    # through the same arithmetic (Double.compare(-0.0, 0) != 0: not skipped)
+    fb = np.array([0.0, 0.0, 1.0, 0.0])
+    for en in (0.5, 1.0):
+        out = O.sgd_update(np.array([-0.0, 2.0]), fb, 0.1, 0.5, en)
+        assert out[0] == 0.0 and not np.signbit(out[0])
+
+
 def test_mirror_params_and_model_data_bytes():
     import flink_ml_b200 as F
     from flink_ml_b200.linear import LinearModelData
